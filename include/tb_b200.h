@@ -1,0 +1,140 @@
+/* tb_b200.h -- C ABI of libtb_b200.so: the B200 (sm_100a) kernels behind the
+ * intervention-and-readout hot path of lmmontoya-ai/taboo-brittleness.
+ *
+ * The reference has no FFI of its own: its boundary is the Python surface of src/models.py,
+ * src/feature_map.py, src/metrics.py and the two drivers. The host
+ * side (taboo_brittleness_b200/*.py) keeps that surface and binds these entry points with
+ * ctypes; each entry point below names the reference line(s) whose arithmetic it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer into memory the caller allocated (inputs, outputs and
+ *     scratch alike); the library allocates nothing and keeps no state between calls;
+ *   - matrices are dense row-major; "bf16" = __nv_bfloat16, stored as uint16_t bits here;
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it and never
+ *     synchronise;
+ *   - return value: TB_OK (0) or a negative TB_ERR_* code; tb_last_error() describes the last
+ *     failure of the calling thread;
+ *   - there is no CPU fallback: on a device that is not compute capability 10.x every compute
+ *     entry point returns TB_ERR_ARCH.
+ */
+#ifndef TB_B200_H_
+#define TB_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TB_OK 0
+#define TB_ERR_INVALID (-1)  /* bad argument (null pointer, shape, alignment, range)        */
+#define TB_ERR_ARCH (-2)     /* current device is not sm_100                                */
+#define TB_ERR_CUDA (-3)     /* a CUDA runtime / driver call failed                         */
+
+#define TB_TOPK 10           /* per-row top-k kept by the lens readout                      */
+#define TB_TOPM_MAX 1024     /* largest ablation budget (rank tables are uint16)            */
+#define TB_RANK_NONE 0xFFFFu /* rank-table entry of a latent that is not in the ablation set */
+
+int tb_version(void);
+const char* tb_last_error(void);
+/* TB_OK iff the CURRENT device can run the kernels (compute capability 10.x). */
+int tb_device_check(void);
+
+/* ---- K1: JumpReLU SAE encode ---------------------------------------------------------
+ * Replaces sae.encode(response_residuals), src/02_run_sae_baseline.py:67 (sae_lens JumpReLU:
+ *   pre = x @ W_enc + b_enc;  acts = relu(pre) * (pre > threshold)).
+ * tcgen05 GEMM [n_rows, d] x [S, d]^T with the bias, threshold and (optional) ablation mask
+ * fused in the epilogue. The dense acts matrix is not formed: row r's non-zero latents are
+ * written in increasing latent order to idx/val[start(r) ...], and count[r] receives their
+ * number. start(r) = row_start[r] (CSR; row_cap[r] entries may be written, NULL = unchecked)
+ * or, when row_start is NULL, r * cap (fixed stride; count[r] > cap flags an overflowed row,
+ * only its first cap latents are stored). out_idx == NULL: count only.
+ * rank (optional): uint16 table(s) [n_tables, S]; a latent whose rank < budget is treated as
+ * zero (ablated). rank_rows = rows sharing a table (0: one table for all rows).
+ *   w_enc_t : bf16 [S, d]  (W_enc transposed, K-major)     b_enc, theta : f32 [S]
+ */
+int tb_sae_encode(const void* x_bf16, const void* w_enc_t_bf16, const float* b_enc,
+                  const float* theta, int64_t n_rows, int d, int S, const int64_t* row_start,
+                  const int32_t* row_cap, int cap, int32_t* out_idx, float* out_val,
+                  int32_t* out_count, const uint16_t* rank, int rank_rows, int budget,
+                  void* stream);
+
+/* ---- a2: targeted latent selection ------------------------------------------------------
+ * Replaces torch.mean(acts, dim=0) and torch.topk(avg, k), src/02_run_sae_baseline.py:70-73,
+ * on the sparse lists. seg (optional): int64 [n_prompts + 1] row offsets of each prompt's
+ * response window; NULL = uniform rows_per_prompt. out_mean: f32 [n_prompts, S].
+ */
+int tb_sae_latent_mean(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,
+                       const float* val, const int64_t* seg, int rows_per_prompt,
+                       int64_t n_prompts, int S, float* out_mean, void* stream);
+/* Top-m (m <= TB_TOPM_MAX) of each prompt's mean, sorted descending (ties: lower latent id
+ * first): out_idx/out_val [n_prompts, m]; rank u16 [n_prompts, S], rank[l] = position of
+ * latent l in the list or TB_RANK_NONE. Nested budgets m' <= m are "rank < m'". */
+int tb_topm_select(const float* mean, int64_t n_prompts, int S, int m, int32_t* out_idx,
+                   float* out_val, uint16_t* rank, void* stream);
+
+/* ---- K1b: latent ablation + sparse decode (+ fused final RMSNorm) -----------------------
+ * No code in the reference (Execution Plan:126 "zero m latents, decode back to residual";
+ * random control Plan:128); sae.decode semantics x_hat = acts @ W_dec + b_dec.
+ *   mode 0: x' = x - sum_{i in ablated & active(row)} a_i W_dec[i,:]   (decode of the ablated
+ *           code plus the SAE reconstruction error x - x_hat, as north_star asks)
+ *   mode 1: x' = b_dec + sum_{i active(row), not ablated} a_i W_dec[i,:]   (Plan:126 literally)
+ * "ablated" = rank[table(row)][i] < budget; table(row) = row_table[row], or row / rank_rows,
+ * or 0. x' is rounded to bf16. out_x and/or out_h may be NULL; out_h = Gemma2RMSNorm(x')
+ * in bf16 (see tb_rmsnorm), produced in the same pass.
+ */
+int tb_sae_ablate_decode(const void* x_bf16, const int64_t* row_start, int cap,
+                         const int32_t* count, const int32_t* idx, const float* val,
+                         const void* w_dec_bf16, const float* b_dec, const uint16_t* rank,
+                         const int32_t* row_table, int rank_rows, int budget, int mode,
+                         int64_t n_rows, int d, int S, const float* w_norm, float eps,
+                         void* out_x_bf16, void* out_h_bf16, void* stream);
+
+/* ---- K2: low-rank direction removal x' = x - (x U) U^T ----------------------------------
+ * No code in the reference (Execution Plan:148 r_edited = r - P_U(r); random control :150).
+ * ut = U^T, bf16 [r, d], r <= 64, columns of U orthonormal. Outputs as for K1b.
+ */
+int tb_lowrank_remove(const void* x_bf16, const void* ut_bf16, int r, int64_t n_rows, int d,
+                      const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
+                      void* stream);
+
+/* ---- a6: final RMSNorm -------------------------------------------------------------------
+ * Replaces model.model.norm(...), src/models.py:135 (Gemma2RMSNorm.forward on a bf16
+ * residual): h = bf16((x * rsqrt(mean(x^2) + eps)) * (1 + w)), fp32 intermediates.
+ */
+int tb_rmsnorm(const void* x_bf16, const float* w_norm, float eps, int64_t n_rows, int d,
+               void* out_h_bf16, void* stream);
+
+/* ---- K3: logit-lens readout ---------------------------------------------------------------
+ * Replaces model.lm_head(h) -> softmax -> [secret-token gather, per-row max/top-k]:
+ * src/models.py:135-138,147; src/plots.py:10; secret id src/01_reproduce_logit_lens.py:142.
+ * tcgen05 GEMM h [n_rows, d] x W_U[vocab shard] [V, d]^T; the epilogue applies the optional
+ * final-logit softcap (softcap <= 0: none, as the reference; Gemma-2: 30.0), keeps an online
+ * (max, sum-exp), the secret token's logit and a top-10 per row. Logits never reach HBM.
+ * The vocabulary shard is swept in n_chunks contiguous chunks (scheduling / L2 knob); the
+ * per-(chunk, row) partials are written to caller scratch:
+ *   pm, ps, psec : f32 [n_chunks, n_rows]      ptv : f32 [n_chunks, n_rows, 10]
+ *   pti : i32 [n_chunks, n_rows, 10]  (global vocab ids = vocab_offset + column)
+ * secret_id: i32 [n_rows] global vocab id per row, or NULL. cta_pair != 0 selects the
+ * two-SM (cta_group::2) variant.
+ */
+int tb_lens_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
+                     int vocab_offset, float softcap, const int32_t* secret_id, int n_chunks,
+                     int cta_pair, float* pm, float* ps, float* psec, float* ptv, int32_t* pti,
+                     void* stream);
+/* K4: merge n_parts partials per row (chunks of one GPU, or all-gathered shards).
+ * finalize == 0: one merged partial to (om, os, osec, otv, oti) (same layout, one part);
+ * finalize != 0: lse, secret_prob (nullable), top_prob / top_id [n_rows, 10]. */
+int tb_lens_merge(const float* pm, const float* ps, const float* psec, const float* ptv,
+                  const int32_t* pti, int n_parts, int64_t n_rows, int finalize, float* om,
+                  float* os, float* osec, float* otv, int32_t* oti, float* lse,
+                  float* secret_prob, float* top_prob, int32_t* top_id, void* stream);
+
+/* ---- validation only: D = A B^T through the same TMA/tcgen05 main loop, fp32 out --------- */
+int tb_gemm_bf16_nt(const void* a_bf16, const void* b_bf16, int64_t M, int N, int K,
+                    int n_chunks, int cta_pair, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TB_B200_H_ */

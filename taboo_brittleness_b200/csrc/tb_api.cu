@@ -1,0 +1,431 @@
+// C-ABI entry points of libtb_b200.so (declared in include/tb_b200.h): argument checks,
+// TMA tensor-map construction and kernel launches. No allocation, no synchronisation.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/tb_b200.h"
+#include "tb_epilogues.cuh"
+#include "tb_gemm.cuh"
+#include "tb_rows.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define TB_CUDA(call)                                                                      \
+  do {                                                                                     \
+    cudaError_t e_ = (call);                                                               \
+    if (e_ != cudaSuccess)                                                                 \
+      return fail(TB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),     \
+                  __FILE__, __LINE__);                                                     \
+  } while (0)
+
+struct DevInfo {
+  int ok = 0;
+  int sms = 0;
+};
+
+// per-device capability cache (plain ints; filled on first use of each device)
+int device_info(DevInfo* out) {
+  static int cached_major[64];
+  static int cached_sms[64];
+  static bool have[64];
+  int dev = 0;
+  TB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(TB_ERR_INVALID, "device ordinal %d out of range", dev);
+  if (!have[dev]) {
+    int major = 0, sms = 0;
+    TB_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    TB_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    cached_major[dev] = major;
+    cached_sms[dev] = sms;
+    have[dev] = true;
+  }
+  if (cached_major[dev] != 10)
+    return fail(TB_ERR_ARCH, "device %d is compute capability %d.x; these kernels are sm_100a only",
+                dev, cached_major[dev]);
+  out->ok = 1;
+  out->sms = cached_sms[dev];
+  return TB_OK;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int get_encode_fn(EncodeTiledFn* fn) {
+  static EncodeTiledFn cached = nullptr;
+  if (!cached) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    TB_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+    if (q != cudaDriverEntryPointSuccess || p == nullptr)
+      return fail(TB_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+    cached = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  *fn = cached;
+  return TB_OK;
+}
+
+// bf16 row-major [rows, K] matrix, box = [box_rows, 64 elements] with the 128-byte swizzle the
+// UMMA descriptors expect. Out-of-bounds box elements are zero-filled.
+int make_tmap(CUtensorMap* map, const void* base, int64_t rows, int K, int box_rows) {
+  EncodeTiledFn enc;
+  int rc = get_encode_fn(&enc);
+  if (rc != TB_OK) return rc;
+  cuuint64_t dims[2] = {static_cast<cuuint64_t>(K), static_cast<cuuint64_t>(rows)};
+  cuuint64_t strides[1] = {static_cast<cuuint64_t>(K) * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(tb::kBlockK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(TB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld K=%d box_rows=%d)",
+                static_cast<int>(r), static_cast<long long>(rows), K, box_rows);
+  return TB_OK;
+}
+
+int check_gemm_operands(const void* a, const void* b, int64_t M, int N, int K) {
+  if (!a || !b) return fail(TB_ERR_INVALID, "null operand pointer");
+  if (M <= 0 || N <= 0 || K <= 0) return fail(TB_ERR_INVALID, "empty GEMM shape M=%lld N=%d K=%d", (long long)M, N, K);
+  if (M > 0x7fffff00ll) return fail(TB_ERR_INVALID, "too many rows (%lld)", (long long)M);
+  if (K % 8 != 0) return fail(TB_ERR_INVALID, "K=%d must be a multiple of 8 (16-byte TMA row pitch)", K);
+  if ((reinterpret_cast<uintptr_t>(a) & 15) || (reinterpret_cast<uintptr_t>(b) & 15))
+    return fail(TB_ERR_INVALID, "operands must be 16-byte aligned");
+  return TB_OK;
+}
+
+tb::GemmArgs make_args(int64_t M, int N, int K, int n_chunks, int group) {
+  tb::GemmArgs g;
+  g.M = static_cast<int>(M);
+  g.N = N;
+  g.K = K;
+  g.n_tiles = (N + tb::kBlockN - 1) / tb::kBlockN;
+  if (n_chunks < 1) n_chunks = 1;
+  if (n_chunks > g.n_tiles) n_chunks = g.n_tiles;
+  g.tiles_per_chunk = (g.n_tiles + n_chunks - 1) / n_chunks;
+  g.n_chunks = (g.n_tiles + g.tiles_per_chunk - 1) / g.tiles_per_chunk;  // no empty chunks
+  g.m_blocks = static_cast<int>((M + tb::kBlockM * group - 1) / (tb::kBlockM * group));
+  g.total_units = g.m_blocks * g.n_chunks;
+  return g;
+}
+
+template <class Epi, int G>
+int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typename Epi::Params& ep,
+                cudaStream_t stream, int sms) {
+  using Cfg = tb::GemmCfg<G>;
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap(&tmA, a, g.M, g.K, tb::kBlockM);
+  if (rc != TB_OK) return rc;
+  rc = make_tmap(&tmB, b, g.N, g.K, Cfg::kBRows);
+  if (rc != TB_OK) return rc;
+  auto kern = tb::tb_umma_gemm_kernel<Epi, G>;
+  TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  int clusters = sms / G;
+  if (clusters > g.total_units) clusters = g.total_units;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(static_cast<unsigned>(clusters * G), 1, 1);
+  cfg.blockDim = dim3(tb::kGemmThreads, 1, 1);
+  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = G;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, g, ep));
+  return TB_OK;
+}
+
+// choose vectors-per-thread and block size for the row kernels: d/8 16-byte vectors per row
+int row_launch_shape(int d, int* nv, int* threads) {
+  if (d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  const int nvec = d / 8;
+  int v = 1;
+  while (v <= 4 && (nvec + v - 1) / v > 512) v *= 2;
+  if (v > 4) return fail(TB_ERR_INVALID, "d=%d too large for the row kernels (max 16384)", d);
+  *nv = v;
+  int t = (nvec + v - 1) / v;
+  t = (t + 31) / 32 * 32;
+  if (t < 64) t = 64;
+  *threads = t;
+  return TB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int tb_version(void) { return 100; }
+
+const char* tb_last_error(void) { return g_err; }
+
+int tb_device_check(void) {
+  DevInfo di;
+  return device_info(&di);
+}
+
+int tb_gemm_bf16_nt(const void* a, const void* b, int64_t M, int N, int K, int n_chunks, int cta_pair,
+                    float* out, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(a, b, M, N, K);
+  if (rc != TB_OK) return rc;
+  if (!out) return fail(TB_ERR_INVALID, "null output");
+  const int G = cta_pair ? 2 : 1;
+  tb::GemmArgs g = make_args(M, N, K, n_chunks, G);
+  tb::DenseEpi::Params ep{out};
+  if (G == 2) return launch_gemm<tb::DenseEpi, 2>(a, b, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  return launch_gemm<tb::DenseEpi, 1>(a, b, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_sae_encode(const void* x, const void* w_enc_t, const float* b_enc, const float* theta,
+                  int64_t n_rows, int d, int S, const int64_t* row_start, const int32_t* row_cap,
+                  int cap, int32_t* out_idx, float* out_val, int32_t* out_count,
+                  const uint16_t* rank, int rank_rows, int budget, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(x, w_enc_t, n_rows, S, d);
+  if (rc != TB_OK) return rc;
+  if (!b_enc || !theta || !out_count) return fail(TB_ERR_INVALID, "null b_enc / theta / out_count");
+  if ((reinterpret_cast<uintptr_t>(b_enc) & 15) || (reinterpret_cast<uintptr_t>(theta) & 15))
+    return fail(TB_ERR_INVALID, "b_enc / theta must be 16-byte aligned");
+  if (out_idx && !out_val) return fail(TB_ERR_INVALID, "out_idx given without out_val");
+  if (out_idx && !row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (rank && rank_rows < 0) return fail(TB_ERR_INVALID, "rank_rows < 0");
+  tb::EncodeEpi::Params ep;
+  ep.b_enc = b_enc;
+  ep.theta = theta;
+  ep.row_start = row_start;
+  ep.cap = cap;
+  ep.row_cap = row_cap;
+  ep.out_idx = out_idx;
+  ep.out_val = out_val;
+  ep.out_count = out_count;
+  ep.rank = rank;
+  ep.rank_rows = rank_rows;
+  ep.budget = budget;
+  // one unit per row block: a row's list is written by a single thread, in latent order
+  tb::GemmArgs g = make_args(n_rows, S, d, 1, 1);
+  return launch_gemm<tb::EncodeEpi, 1>(x, w_enc_t, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_sae_latent_mean(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,
+                       const float* val, const int64_t* seg, int rows_per_prompt, int64_t n_prompts,
+                       int S, float* out_mean, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!count || !idx || !val || !out_mean) return fail(TB_ERR_INVALID, "null pointer");
+  if (n_prompts < 0 || S <= 0) return fail(TB_ERR_INVALID, "bad shape");
+  if (!seg && rows_per_prompt <= 0) return fail(TB_ERR_INVALID, "need seg or rows_per_prompt > 0");
+  if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (n_prompts == 0) return TB_OK;
+  tb::tb_latent_mean_kernel<<<static_cast<unsigned>(n_prompts), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      row_start, cap, count, idx, val, seg, rows_per_prompt, S, out_mean);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_topm_select(const float* mean, int64_t n_prompts, int S, int m, int32_t* out_idx, float* out_val,
+                   uint16_t* rank, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!mean || !out_idx || !out_val || !rank) return fail(TB_ERR_INVALID, "null pointer");
+  if (m < 1 || m > TB_TOPM_MAX) return fail(TB_ERR_INVALID, "m=%d outside [1, %d]", m, TB_TOPM_MAX);
+  if (S < 1) return fail(TB_ERR_INVALID, "S=%d", S);
+  if (n_prompts == 0) return TB_OK;
+  tb::tb_topm_select_kernel<<<static_cast<unsigned>(n_prompts), tb::kTopmThreads, 0,
+                              static_cast<cudaStream_t>(stream)>>>(mean, S, m, out_idx, out_val, rank);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_sae_ablate_decode(const void* x, const int64_t* row_start, int cap, const int32_t* count,
+                         const int32_t* idx, const float* val, const void* w_dec, const float* b_dec,
+                         const uint16_t* rank, const int32_t* row_table, int rank_rows, int budget,
+                         int mode, int64_t n_rows, int d, int S, const float* w_norm, float eps,
+                         void* out_x, void* out_h, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!count || !idx || !val || !w_dec) return fail(TB_ERR_INVALID, "null pointer");
+  if (mode != 0 && mode != 1) return fail(TB_ERR_INVALID, "mode must be 0 (error term) or 1 (plain decode)");
+  if (mode == 0 && !x) return fail(TB_ERR_INVALID, "mode 0 needs x");
+  if (mode == 1 && !b_dec) return fail(TB_ERR_INVALID, "mode 1 needs b_dec");
+  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (n_rows == 0) return TB_OK;
+  int nv, threads;
+  rc = row_launch_shape(d, &nv, &threads);
+  if (rc != TB_OK) return rc;
+  tb::AblateArgs a;
+  a.x = static_cast<const __nv_bfloat16*>(x);
+  a.row_start = row_start;
+  a.cap = cap;
+  a.count = count;
+  a.idx = idx;
+  a.val = val;
+  a.w_dec = static_cast<const __nv_bfloat16*>(w_dec);
+  a.b_dec = b_dec;
+  a.rank = rank;
+  a.row_table = row_table;
+  a.rank_rows = rank_rows;
+  a.budget = budget;
+  a.mode = mode;
+  a.S = S;
+  a.w_norm = w_norm;
+  a.eps = eps;
+  a.out_x = static_cast<__nv_bfloat16*>(out_x);
+  a.out_h = static_cast<__nv_bfloat16*>(out_h);
+  a.n_rows = static_cast<int>(n_rows);
+  a.d = d;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 16;
+  const unsigned grid = static_cast<unsigned>(n_rows < max_grid ? n_rows : max_grid);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (nv == 1) tb::tb_ablate_decode_kernel<1><<<grid, threads, 0, s>>>(a);
+  else if (nv == 2) tb::tb_ablate_decode_kernel<2><<<grid, threads, 0, s>>>(a);
+  else tb::tb_ablate_decode_kernel<4><<<grid, threads, 0, s>>>(a);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_lowrank_remove(const void* x, const void* ut, int r, int64_t n_rows, int d, const float* w_norm,
+                      float eps, void* out_x, void* out_h, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!x || !ut) return fail(TB_ERR_INVALID, "null pointer");
+  if (r < 0 || r > tb::kProjMaxRank) return fail(TB_ERR_INVALID, "rank %d outside [0, %d]", r, tb::kProjMaxRank);
+  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  if (n_rows == 0) return TB_OK;
+  int nv, threads;
+  rc = row_launch_shape(d, &nv, &threads);
+  if (rc != TB_OK) return rc;
+  // kProjRows rows of fp32 accumulators per thread: keep NV small by using more threads
+  if (nv > 2) return fail(TB_ERR_INVALID, "d=%d too large for the projection kernel (max 8192)", d);
+  tb::ProjArgs a;
+  a.x = static_cast<const __nv_bfloat16*>(x);
+  a.ut = static_cast<const __nv_bfloat16*>(ut);
+  a.r = r;
+  a.w_norm = w_norm;
+  a.eps = eps;
+  a.out_x = static_cast<__nv_bfloat16*>(out_x);
+  a.out_h = static_cast<__nv_bfloat16*>(out_h);
+  a.n_rows = static_cast<int>(n_rows);
+  a.d = d;
+  const size_t smem = static_cast<size_t>(tb::kProjRows) * d * 2;
+  const int64_t tiles = (n_rows + tb::kProjRows - 1) / tb::kProjRows;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 4;
+  const unsigned grid = static_cast<unsigned>(tiles < max_grid ? tiles : max_grid);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (nv == 1) {
+    TB_CUDA(cudaFuncSetAttribute(tb::tb_lowrank_remove_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tb::tb_lowrank_remove_kernel<1><<<grid, threads, smem, s>>>(a);
+  } else {
+    TB_CUDA(cudaFuncSetAttribute(tb::tb_lowrank_remove_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tb::tb_lowrank_remove_kernel<2><<<grid, threads, smem, s>>>(a);
+  }
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_rmsnorm(const void* x, const float* w_norm, float eps, int64_t n_rows, int d, void* out_h,
+               void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!x || !w_norm || !out_h) return fail(TB_ERR_INVALID, "null pointer");
+  if (n_rows == 0) return TB_OK;
+  int nv, threads;
+  rc = row_launch_shape(d, &nv, &threads);
+  if (rc != TB_OK) return rc;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 16;
+  const unsigned grid = static_cast<unsigned>(n_rows < max_grid ? n_rows : max_grid);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* hp = static_cast<__nv_bfloat16*>(out_h);
+  if (nv == 1) tb::tb_rmsnorm_kernel<1><<<grid, threads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
+  else if (nv == 2) tb::tb_rmsnorm_kernel<2><<<grid, threads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
+  else tb::tb_rmsnorm_kernel<4><<<grid, threads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_lens_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
+                     float softcap, const int32_t* secret_id, int n_chunks, int cta_pair, float* pm,
+                     float* ps, float* psec, float* ptv, int32_t* pti, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(h, w_u, n_rows, V, d);
+  if (rc != TB_OK) return rc;
+  if (!pm || !ps || !psec || !ptv || !pti) return fail(TB_ERR_INVALID, "null partial buffer");
+  const int G = cta_pair ? 2 : 1;
+  tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, G);
+  if (g.n_chunks != n_chunks)
+    return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)",
+                n_chunks, g.n_tiles, g.n_chunks);
+  tb::LensEpi::Params ep;
+  ep.secret_id = secret_id;
+  ep.vocab_offset = vocab_offset;
+  ep.softcap = softcap;
+  ep.pm = pm;
+  ep.ps = ps;
+  ep.psec = psec;
+  ep.ptv = ptv;
+  ep.pti = pti;
+  if (G == 2) return launch_gemm<tb::LensEpi, 2>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  return launch_gemm<tb::LensEpi, 1>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_lens_merge(const float* pm, const float* ps, const float* psec, const float* ptv, const int32_t* pti,
+                  int n_parts, int64_t n_rows, int finalize, float* om, float* os, float* osec,
+                  float* otv, int32_t* oti, float* lse, float* secret_prob, float* top_prob,
+                  int32_t* top_id, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!pm || !ps || !psec || !ptv || !pti) return fail(TB_ERR_INVALID, "null partial buffer");
+  if (n_parts < 1) return fail(TB_ERR_INVALID, "n_parts=%d", n_parts);
+  if (finalize) {
+    if (!lse || !top_prob || !top_id) return fail(TB_ERR_INVALID, "finalize needs lse, top_prob, top_id");
+  } else if (!om || !os || !osec || !otv || !oti) {
+    return fail(TB_ERR_INVALID, "merge needs om, os, osec, otv, oti");
+  }
+  if (n_rows == 0) return TB_OK;
+  tb::MergeArgs a;
+  a.pm = pm; a.ps = ps; a.psec = psec; a.ptv = ptv; a.pti = pti;
+  a.n_parts = n_parts;
+  a.n_rows = static_cast<int>(n_rows);
+  a.finalize = finalize;
+  a.om = om; a.os = os; a.osec = osec; a.otv = otv; a.oti = oti;
+  a.lse = lse; a.secret_prob = secret_prob; a.top_prob = top_prob; a.top_id = top_id;
+  const unsigned grid = static_cast<unsigned>((n_rows + 127) / 128);
+  tb::tb_lens_merge_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+}  // extern "C"

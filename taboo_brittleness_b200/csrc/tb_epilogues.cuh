@@ -1,0 +1,271 @@
+// Per-row epilogues plugged into tb_umma_gemm_kernel. Each epilogue thread owns one row of
+// the CTA's 128-row block and sees that row's accumulator 32 columns at a time.
+#pragma once
+#include <math_constants.h>
+#include "tb_gemm.cuh"
+
+namespace tb {
+
+constexpr int kTopK = 10;
+constexpr float kLog2e = 1.4426950408889634f;
+
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// tanh(y) = 1 - 2 / (1 + e^{2y}); two MUFU ops, absolute error ~1e-7 (tanh.approx.f32 is only
+// good to 2^-11 relative, which is 0.015 in a logit capped at 30 -- too coarse for 1e-3 in p).
+__device__ __forceinline__ float tanh_2mufu(float y) {
+  const float e = ex2_approx(y * (2.0f * kLog2e));
+  return 1.0f - 2.0f * rcp_approx(1.0f + e);
+}
+
+// =========================================================================================
+// K3: logit-lens readout. A = h (final-RMSNorm'ed residual, bf16), B = W_U shard.
+// Per (row, vocab chunk) partial: running max m, sumexp s (relative to m), the secret
+// token's (capped) logit, and the ten largest (capped) logits with their global vocab ids.
+// Reference: src/models.py:135-138 (norm -> lm_head -> softmax), plots.py:10 / 01:142 (secret
+// probability gather), models.py:147 (per-row max); softcap per installed Gemma2ForCausalLM.
+// =========================================================================================
+struct LensEpi {
+  struct Params {
+    const int32_t* secret_id;  // [M] global vocab id per row, or nullptr
+    int vocab_offset;          // global id of this shard's column 0
+    float softcap;             // <= 0: none (reference parity mode); Gemma-2: 30.0
+    float* pm;                 // [n_chunks, M]
+    float* ps;                 // [n_chunks, M]
+    float* psec;               // [n_chunks, M]  (-inf where the secret id is not in the chunk)
+    float* ptv;                // [n_chunks, M, 10]
+    int32_t* pti;              // [n_chunks, M, 10]
+  };
+  struct State {
+    float m, s, sec;
+    float tv[kTopK];
+    int32_t ti[kTopK];
+    int32_t sid;  // secret column relative to this shard (or a value that never matches)
+  };
+
+  __device__ __forceinline__ static void begin_unit(State& st, const Params& p, const GemmArgs& g,
+                                                    int row, int /*chunk*/) {
+    st.m = -CUDART_INF_F;
+    st.s = 0.0f;
+    st.sec = -CUDART_INF_F;
+#pragma unroll
+    for (int k = 0; k < kTopK; ++k) { st.tv[k] = -CUDART_INF_F; st.ti[k] = -1; }
+    st.sid = -0x40000000;
+    if (p.secret_id != nullptr && row < g.M) st.sid = p.secret_id[row] - p.vocab_offset;
+  }
+
+  __device__ __forceinline__ static void insert(State& st, float v, int32_t id) {
+    st.tv[kTopK - 1] = v;
+    st.ti[kTopK - 1] = id;
+#pragma unroll
+    for (int k = kTopK - 1; k > 0; --k) {
+      const bool sw = st.tv[k] > st.tv[k - 1];
+      const float a = st.tv[k - 1], b = st.tv[k];
+      const int32_t ia = st.ti[k - 1], ib = st.ti[k];
+      st.tv[k - 1] = sw ? b : a;
+      st.tv[k] = sw ? a : b;
+      st.ti[k - 1] = sw ? ib : ia;
+      st.ti[k] = sw ? ia : ib;
+    }
+  }
+
+  __device__ __forceinline__ static void process(State& st, const Params& p, const GemmArgs& g,
+                                                 const uint32_t (&v)[32], int /*row*/, int col0) {
+    float c[32];
+    if (p.softcap > 0.0f) {
+      const float inv = 1.0f / p.softcap;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) c[j] = p.softcap * tanh_2mufu(__uint_as_float(v[j]) * inv);
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) c[j] = __uint_as_float(v[j]);
+    }
+    if (col0 + 32 > g.N) {  // ragged last tile: columns past N hold zero-filled garbage
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j >= g.N) c[j] = -CUDART_INF_F;
+    }
+    float cmax = c[0];
+#pragma unroll
+    for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, c[j]);
+
+    // online logsumexp, rescaled at most once per 32 columns
+    if (cmax > st.m) {
+      st.s *= ex2_approx((st.m - cmax) * kLog2e);  // m = -inf -> factor 0 (s is 0 then anyway)
+      st.m = cmax;
+    }
+    if (st.m > -CUDART_INF_F) {
+      const float ml = st.m * kLog2e;
+      float acc0 = 0.0f, acc1 = 0.0f;
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        acc0 += ex2_approx(fmaf(c[j], kLog2e, -ml));
+        acc1 += ex2_approx(fmaf(c[j + 1], kLog2e, -ml));
+      }
+      st.s += acc0 + acc1;
+    }
+
+    // running top-10 (strict '>' keeps the lowest column among equal values)
+    if (cmax > st.tv[kTopK - 1]) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (c[j] > st.tv[kTopK - 1]) insert(st, c[j], p.vocab_offset + col0 + j);
+    }
+
+    // secret-token logit
+    const uint32_t rel = static_cast<uint32_t>(st.sid - col0);
+    if (rel < 32u) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (rel == static_cast<uint32_t>(j)) st.sec = c[j];
+    }
+  }
+
+  __device__ __forceinline__ static void end_unit(State& st, const Params& p, const GemmArgs& g,
+                                                  int row, int chunk) {
+    if (row >= g.M) return;
+    const size_t o = static_cast<size_t>(chunk) * g.M + row;
+    p.pm[o] = st.m;
+    p.ps[o] = st.s;
+    p.psec[o] = st.sec;
+#pragma unroll
+    for (int k = 0; k < kTopK; ++k) {
+      p.ptv[o * kTopK + k] = st.tv[k];
+      p.pti[o * kTopK + k] = st.ti[k];
+    }
+  }
+};
+
+// =========================================================================================
+// K1: Gemma Scope JumpReLU SAE encode. A = x (bf16 residual rows), B = W_enc^T [S, d].
+//   pre = x . W_enc + b_enc ; act = relu(pre) * (pre > theta)        (sae_lens JumpReLU,
+//   call site src/02_run_sae_baseline.py:67)
+// The dense [rows, S] activation matrix is never formed: each row's non-zero latents are
+// appended (in latent order) to that row's list. An optional ablation table drops latents
+// whose rank is below the budget right here (random-control / second-pass masking).
+// =========================================================================================
+struct EncodeEpi {
+  struct Params {
+    const float* b_enc;        // [S]
+    const float* theta;        // [S]
+    const int64_t* row_start;  // [M] start of each row's list, or nullptr -> row * cap
+    int cap;                   // list capacity per row when row_start == nullptr
+    const int32_t* row_cap;    // [M] capacity per row when row_start != nullptr (nullable = unchecked)
+    int32_t* out_idx;          // latent ids   (nullable: count only)
+    float* out_val;            // activations
+    int32_t* out_count;        // [M] number of active latents (may exceed the capacity)
+    const uint16_t* rank;      // ablation rank table(s) [n_tables, S] or nullptr
+    int rank_rows;             // rows sharing one table (0: a single table for all rows)
+    int budget;                // latents with rank < budget are zeroed
+  };
+  struct State {
+    int k;
+    int limit;
+    int64_t base;
+    const uint16_t* rk;
+  };
+
+  __device__ __forceinline__ static void begin_unit(State& st, const Params& p, const GemmArgs& g,
+                                                    int row, int /*chunk*/) {
+    st.k = 0;
+    st.limit = 0;
+    st.base = 0;
+    st.rk = nullptr;
+    if (row >= g.M) return;
+    if (p.out_idx != nullptr) {
+      if (p.row_start != nullptr) {
+        st.base = p.row_start[row];
+        st.limit = p.row_cap != nullptr ? p.row_cap[row] : 0x7fffffff;
+      } else {
+        st.base = static_cast<int64_t>(row) * p.cap;
+        st.limit = p.cap;
+      }
+    }
+    if (p.rank != nullptr)
+      st.rk = p.rank + (p.rank_rows > 0 ? static_cast<size_t>(row / p.rank_rows) * g.N : 0);
+  }
+
+  __device__ __forceinline__ static void emit(State& st, const Params& p, int col, float pre) {
+    if (st.rk != nullptr && static_cast<int>(st.rk[col]) < p.budget) return;  // ablated
+    if (st.k < st.limit) {
+      p.out_idx[st.base + st.k] = col;
+      p.out_val[st.base + st.k] = pre;
+    }
+    ++st.k;
+  }
+
+  __device__ __forceinline__ static void process(State& st, const Params& p, const GemmArgs& g,
+                                                 const uint32_t (&v)[32], int row, int col0) {
+    if (row >= g.M) return;
+    if (col0 + 32 <= g.N) {
+      const float4* b4 = reinterpret_cast<const float4*>(p.b_enc + col0);
+      const float4* t4 = reinterpret_cast<const float4*>(p.theta + col0);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float4 b = __ldg(b4 + q);
+        const float4 t = __ldg(t4 + q);
+        const float p0 = __uint_as_float(v[4 * q + 0]) + b.x;
+        const float p1 = __uint_as_float(v[4 * q + 1]) + b.y;
+        const float p2 = __uint_as_float(v[4 * q + 2]) + b.z;
+        const float p3 = __uint_as_float(v[4 * q + 3]) + b.w;
+        if (p0 > t.x && p0 > 0.0f) emit(st, p, col0 + 4 * q + 0, p0);
+        if (p1 > t.y && p1 > 0.0f) emit(st, p, col0 + 4 * q + 1, p1);
+        if (p2 > t.z && p2 > 0.0f) emit(st, p, col0 + 4 * q + 2, p2);
+        if (p3 > t.w && p3 > 0.0f) emit(st, p, col0 + 4 * q + 3, p3);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = col0 + j;
+        if (col < g.N) {
+          const float pre = __uint_as_float(v[j]) + __ldg(p.b_enc + col);
+          if (pre > __ldg(p.theta + col) && pre > 0.0f) emit(st, p, col, pre);
+        }
+      }
+    }
+  }
+
+  __device__ __forceinline__ static void end_unit(State& st, const Params& p, const GemmArgs& g,
+                                                  int row, int /*chunk*/) {
+    if (row < g.M) p.out_count[row] = st.k;
+  }
+};
+
+// =========================================================================================
+// Validation epilogue: store the fp32 accumulator. Used only by the tests that pin the
+// TMA / UMMA-descriptor / TMEM plumbing against a plain matmul.
+// =========================================================================================
+struct DenseEpi {
+  struct Params {
+    float* out;  // [M, N] row-major
+  };
+  struct State {};
+  __device__ __forceinline__ static void begin_unit(State&, const Params&, const GemmArgs&, int, int) {}
+  __device__ __forceinline__ static void process(State&, const Params& p, const GemmArgs& g,
+                                                 const uint32_t (&v)[32], int row, int col0) {
+    if (row >= g.M) return;
+    float* o = p.out + static_cast<size_t>(row) * g.N + col0;
+    if (col0 + 32 <= g.N && (g.N & 3) == 0) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q)
+        reinterpret_cast<float4*>(o)[q] =
+            make_float4(__uint_as_float(v[4 * q]), __uint_as_float(v[4 * q + 1]),
+                        __uint_as_float(v[4 * q + 2]), __uint_as_float(v[4 * q + 3]));
+    } else {
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < g.N) o[j] = __uint_as_float(v[j]);
+    }
+  }
+  __device__ __forceinline__ static void end_unit(State&, const Params&, const GemmArgs&, int, int) {}
+};
+
+}  // namespace tb

@@ -1,0 +1,221 @@
+// Persistent, warp-specialised tcgen05 GEMM main loop shared by the SAE encode (K1) and the
+// logit-lens readout (K3):  D[M, N] = A[M, K] * B[N, K]^T, bf16 operands (both K-major in
+// HBM, i.e. plain row-major [rows, K]), fp32 accumulation in TMEM.
+//
+// What makes it specific to this hot path is that D is never stored. A CTA (or CTA pair) owns
+// a block of rows and sweeps a contiguous range of N-tiles (a "chunk" of the vocabulary / of
+// the SAE latents); each epilogue thread owns one row of the block and keeps that row's
+// running readout (online logsumexp, top-10, secret logit / active-latent cursor) in registers
+// across the whole sweep. Only the per-row readout leaves the SM.
+//
+// Roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
+// warp 3 idle, warps 4..7 = epilogue (TMEM lane quadrant = warp % 4). Three pipelines:
+// smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue, two 256-column
+// accumulators so the epilogue of tile i overlaps the MMAs of tile i+1), and the static
+// round-robin unit schedule.
+//
+// kCtaGroup == 2 pairs two SMs (cluster 2x1x1): UMMA M = 256, each CTA stages its own 128 A
+// rows and half (128 rows) of the B tile, the leader CTA issues the MMAs, and each CTA's
+// epilogue drains its own 128 x 256 accumulator half.
+#pragma once
+#include "tb_ptx.cuh"
+
+namespace tb {
+
+constexpr int kBlockM = 128;   // rows per CTA
+constexpr int kBlockN = 256;   // columns per tile (= UMMA N)
+constexpr int kBlockK = 64;    // bf16 elements per stage row: one 128-byte swizzle span
+constexpr int kUmmaK = 16;
+constexpr int kGemmThreads = 256;
+constexpr int kEpiWarp0 = 4;
+
+struct GemmArgs {
+  int M, N, K;
+  int n_tiles;          // ceil(N / 256)
+  int n_chunks;         // units per row block
+  int tiles_per_chunk;  // ceil(n_tiles / n_chunks)
+  int m_blocks;         // ceil(M / (128 * kCtaGroup))
+  int total_units;      // m_blocks * n_chunks
+};
+
+template <int kCtaGroup>
+struct GemmCfg {
+  static constexpr int kStages = (kCtaGroup == 1) ? 4 : 6;
+  static constexpr int kABytes = kBlockM * kBlockK * 2;
+  static constexpr int kBRows = kBlockN / kCtaGroup;
+  static constexpr int kBBytes = kBRows * kBlockK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kBarBytes = 256;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
+};
+
+template <class Epi, int kCtaGroup>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmArgs g, const typename Epi::Params ep) {
+  using Cfg = GemmCfg<kCtaGroup>;
+  constexpr int kStages = Cfg::kStages;
+
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B operand tiles need 1024-byte alignment
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
+  uint64_t* full_bar = bars;                      // [kStages] TMA -> MMA (leader CTA's are used)
+  uint64_t* empty_bar = bars + kStages;           // [kStages] MMA -> TMA (each CTA has its own)
+  uint64_t* tfull_bar = bars + 2 * kStages;       // [2] MMA -> epilogue (each CTA)
+  uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2] epilogue -> MMA (leader CTA's are used)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = static_cast<int>(lane_id());
+  const uint32_t rank = (kCtaGroup == 2) ? cluster_ctarank() : 0u;
+  const bool leader = (rank == 0);
+  const int cluster_id = static_cast<int>(blockIdx.x) / kCtaGroup;
+  const int num_clusters = static_cast<int>(gridDim.x) / kCtaGroup;
+  const int num_kb = (g.K + kBlockK - 1) / kBlockK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(smem_u32(&full_bar[i]), 1);
+      mbar_init(smem_u32(&empty_bar[i]), 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&tfull_bar[i]), 1);
+      mbar_init(smem_u32(&tempty_bar[i]), 4 * kCtaGroup);  // one arrive per epilogue warp
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<kCtaGroup>(smem_u32(tmem_slot), 512);
+  }
+  tc_fence_before();
+  if constexpr (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
+        const int m_blk = unit / g.n_chunks;
+        const int chunk = unit - m_blk * g.n_chunks;
+        const int t0 = chunk * g.tiles_per_chunk;
+        const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
+        const int a_row = m_blk * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM;
+        for (int nt = t0; nt < t1; ++nt) {
+          const int b_row = nt * kBlockN + static_cast<int>(rank) * Cfg::kBRows;
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
+            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+            const uint32_t sb = sa + Cfg::kABytes;
+            uint32_t fb = smem_u32(&full_bar[stage]);
+            if (leader) mbar_arrive_expect_tx(fb, Cfg::kStageBytes * kCtaGroup);
+            if constexpr (kCtaGroup == 2) {
+              fb &= kPeerBitMask;  // both CTAs signal the leader's barrier
+              tma_load_2d_2sm(sa, &tmA, fb, kb * kBlockK, a_row);
+              tma_load_2d_2sm(sb, &tmB, fb, kb * kBlockK, b_row);
+            } else {
+              tma_load_2d(sa, &tmA, fb, kb * kBlockK, a_row);
+              tma_load_2d(sb, &tmB, fb, kb * kBlockK, b_row);
+            }
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16_f32(kBlockM * kCtaGroup, kBlockN);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t acc_iter = 0;
+      for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
+        const int chunk = unit % g.n_chunks;
+        const int t0 = chunk * g.tiles_per_chunk;
+        const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
+        for (int nt = t0; nt < t1; ++nt, ++acc_iter) {
+          const uint32_t acc = acc_iter & 1u;
+          const uint32_t acc_phase = (acc_iter >> 1) & 1u;
+          mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);  // epilogue drained this accumulator
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * kBlockN;
+          for (int kb = 0; kb < num_kb; ++kb) {
+            mbar_wait(smem_u32(&full_bar[stage]), phase);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
+            const uint32_t sb = sa + Cfg::kABytes;
+#pragma unroll
+            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+              // advance along K inside the 128-byte swizzle span: +32 bytes per UMMA_K
+              const uint64_t da = umma_desc_k_sw128(sa + k * kUmmaK * 2);
+              const uint64_t db = umma_desc_k_sw128(sb + k * kUmmaK * 2);
+              umma_bf16<kCtaGroup>(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
+            if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&empty_bar[stage]), 0x3);
+            else umma_commit(smem_u32(&empty_bar[stage]));
+            if (++stage == kStages) { stage = 0; phase ^= 1u; }
+          }
+          if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&tfull_bar[acc]), 0x3);
+          else umma_commit(smem_u32(&tfull_bar[acc]));
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= kEpiWarp0) {
+    // ================================ epilogue ================================
+    const int quad = warp & 3;
+    const int row_in_blk = quad * 32 + lane;
+    const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
+    uint32_t acc_iter = 0;
+    typename Epi::State st;
+    for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
+      const int m_blk = unit / g.n_chunks;
+      const int chunk = unit - m_blk * g.n_chunks;
+      const int t0 = chunk * g.tiles_per_chunk;
+      const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
+      const int row = m_blk * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM + row_in_blk;
+      Epi::begin_unit(st, ep, g, row, chunk);
+      for (int nt = t0; nt < t1; ++nt, ++acc_iter) {
+        const uint32_t acc = acc_iter & 1u;
+        const uint32_t acc_phase = (acc_iter >> 1) & 1u;
+        mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < kBlockN / 32; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + lane_base + acc * kBlockN + c * 32, v);
+          tmem_ld_wait();
+          Epi::process(st, ep, g, v, row, nt * kBlockN + c * 32);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          const uint32_t tb_addr = smem_u32(&tempty_bar[acc]);
+          if (kCtaGroup == 1 || leader) mbar_arrive(tb_addr);
+          else mbar_arrive_cluster(mapa_shared(tb_addr, 0));
+        }
+      }
+      Epi::end_unit(st, ep, g, row, chunk);
+    }
+  }
+
+  // teardown: everybody done with TMEM before it is released
+  tc_fence_before();
+  if constexpr (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<kCtaGroup>(tmem_base, 512);
+  }
+}
+
+}  // namespace tb

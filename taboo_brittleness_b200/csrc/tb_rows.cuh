@@ -1,0 +1,604 @@
+// Row-wise, HBM/L2-bound kernels of the intervention-and-readout path:
+//   tb_rmsnorm_kernel          a6  final Gemma2RMSNorm -> bf16 GEMM operand h
+//   tb_ablate_decode_kernel    a4  SAE latent ablation + sparse decode (+ fused a6)
+//   tb_latent_mean_kernel      a2  mean over a prompt's tokens of the sparse activations
+//   tb_topm_select_kernel      a2  top-m latents of the mean (sorted) + rank table
+//   tb_lens_merge_kernel       a8-a10 merge of (max, sumexp, secret, top-10) partials
+// A residual row (d bf16 values, d % 8 == 0) is held by one CTA as 16-byte vectors, NV per
+// thread, so every global access is a coalesced 128-bit load/store.
+#pragma once
+#include <cuda_bf16.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+namespace tb {
+
+constexpr int kRowMaxWarps = 32;
+
+struct alignas(16) Bf16x8 {
+  __nv_bfloat162 v[4];
+};
+
+__device__ __forceinline__ void unpack8(const Bf16x8& p, float (&f)[8]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 t = __bfloat1622float2(p.v[i]);
+    f[2 * i] = t.x;
+    f[2 * i + 1] = t.y;
+  }
+}
+// unpack8 overload for a raw 16-byte load
+__device__ __forceinline__ void unpack8(const int4& raw, float (&f)[8]) {
+  Bf16x8 p;
+  *reinterpret_cast<int4*>(&p) = raw;
+  unpack8(p, f);
+}
+
+__device__ __forceinline__ Bf16x8 pack8(const float (&f)[8]) {
+  Bf16x8 p;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) p.v[i] = __floats2bfloat162_rn(f[2 * i], f[2 * i + 1]);
+  return p;
+}
+
+// sum over the CTA; every thread gets the result. red must hold kRowMaxWarps floats.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nwarps = (blockDim.x + 31) >> 5;
+  __syncthreads();  // red may still be read from a previous call
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = 0.0f;
+  for (int w = 0; w < nwarps; ++w) t += red[w];  // fixed order: deterministic
+  return t;
+}
+
+// Final RMSNorm exactly as Gemma2RMSNorm.forward computes it on a bf16 residual:
+//   h = bf16( (x * rsqrt(mean(x^2) + eps)) * (1 + w) ), fp32 intermediates, no FMA contraction.
+// xb holds the row already rounded to bf16 (what the reference's bf16 residual stream holds).
+template <int NV>
+__device__ __forceinline__ void rmsnorm_store(const float (&xb)[NV][8], const float* __restrict__ w,
+                                              int d, float eps, __nv_bfloat16* __restrict__ out_h,
+                                              float* red) {
+  const int nvec = d >> 3;
+  float ss = 0.0f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vec = threadIdx.x + i * blockDim.x;
+    if (vec < nvec) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ss = fmaf(xb[i][e], xb[i][e], ss);
+    }
+  }
+  ss = block_sum(ss, red);
+  const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, static_cast<float>(d)), eps)));
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int vec = threadIdx.x + i * blockDim.x;
+    if (vec < nvec) {
+      const float4 w0 = __ldg(reinterpret_cast<const float4*>(w) + 2 * vec);
+      const float4 w1 = __ldg(reinterpret_cast<const float4*>(w) + 2 * vec + 1);
+      const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+      float h[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        h[e] = __fmul_rn(__fmul_rn(xb[i][e], rstd), __fadd_rn(1.0f, ww[e]));
+      reinterpret_cast<Bf16x8*>(out_h)[vec] = pack8(h);
+    }
+  }
+}
+
+template <int NV>
+__global__ void tb_rmsnorm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
+                                  int n_rows, int d, float eps, __nv_bfloat16* __restrict__ out_h) {
+  __shared__ float red[kRowMaxWarps];
+  const int nvec = d >> 3;
+  for (int row = blockIdx.x; row < n_rows; row += gridDim.x) {
+    const Bf16x8* xr = reinterpret_cast<const Bf16x8*>(x + static_cast<size_t>(row) * d);
+    float xb[NV][8];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = threadIdx.x + i * blockDim.x;
+      if (vec < nvec) unpack8(xr[vec], xb[i]);
+    }
+    rmsnorm_store<NV>(xb, w, d, eps, out_h + static_cast<size_t>(row) * d, red);
+  }
+}
+
+// -----------------------------------------------------------------------------------------
+// a4: ablate + decode. For every row, walk that row's active-latent list; a latent is
+// ablated when its rank in the row's ablation table is below the budget.
+//   mode 0 (error-term form, north_star): x' = x - sum_{ablated active i} a_i W_dec[i, :]
+//        == decode(acts with idx zeroed) + (x - decode(acts))
+//   mode 1 (plain decode, Plan:126):      x' = b_dec + sum_{surviving active i} a_i W_dec[i, :]
+// x' is rounded to bf16 (the residual stream dtype); optionally the final RMSNorm of that
+// rounded row is produced in the same pass (out_h), so the lens GEMM reads its operand
+// without a separate normalisation pass.
+// -----------------------------------------------------------------------------------------
+constexpr int kListBatch = 512;
+
+struct AblateArgs {
+  const __nv_bfloat16* x;      // [n_rows, d]
+  const int64_t* row_start;    // [n_rows] or nullptr -> row * cap
+  int cap;
+  const int32_t* count;        // [n_rows]
+  const int32_t* idx;
+  const float* val;
+  const __nv_bfloat16* w_dec;  // [S, d]
+  const float* b_dec;          // [d] (mode 1)
+  const uint16_t* rank;        // [n_tables, S]
+  const int32_t* row_table;    // [n_rows] table index per row, or nullptr
+  int rank_rows;               // rows per table when row_table == nullptr (0: one table)
+  int budget;
+  int mode;
+  int S;
+  const float* w_norm;         // [d] or nullptr
+  float eps;
+  __nv_bfloat16* out_x;        // [n_rows, d] or nullptr
+  __nv_bfloat16* out_h;        // [n_rows, d] or nullptr
+  int n_rows, d;
+};
+
+template <int NV>
+__global__ void tb_ablate_decode_kernel(const AblateArgs a) {
+  __shared__ float red[kRowMaxWarps];
+  __shared__ int32_t s_id[kListBatch];
+  __shared__ float s_a[kListBatch];
+  __shared__ int s_n;
+  const int nvec = a.d >> 3;
+  for (int row = blockIdx.x; row < a.n_rows; row += gridDim.x) {
+    float acc[NV][8];
+    if (a.mode == 0) {
+      const Bf16x8* xr = reinterpret_cast<const Bf16x8*>(a.x + static_cast<size_t>(row) * a.d);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = threadIdx.x + i * blockDim.x;
+        if (vec < nvec) unpack8(xr[vec], acc[i]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = threadIdx.x + i * blockDim.x;
+        if (vec < nvec) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.b_dec) + 2 * vec);
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.b_dec) + 2 * vec + 1);
+          acc[i][0] = b0.x; acc[i][1] = b0.y; acc[i][2] = b0.z; acc[i][3] = b0.w;
+          acc[i][4] = b1.x; acc[i][5] = b1.y; acc[i][6] = b1.z; acc[i][7] = b1.w;
+        }
+      }
+    }
+    const int64_t start = a.row_start ? a.row_start[row] : static_cast<int64_t>(row) * a.cap;
+    int cnt = a.count[row];
+    if (a.row_start == nullptr) cnt = min(cnt, a.cap);  // an overflowed row only holds cap entries
+    const int table = a.row_table ? a.row_table[row] : (a.rank_rows > 0 ? row / a.rank_rows : 0);
+    const uint16_t* rk = a.rank ? a.rank + static_cast<size_t>(table) * a.S : nullptr;
+    const float sign = (a.mode == 0) ? -1.0f : 1.0f;
+
+    for (int b0 = 0; b0 < cnt; b0 += kListBatch) {
+      const int nb = min(kListBatch, cnt - b0);
+      // stage 1: select (in list order, so the fp32 accumulation order is deterministic)
+      __syncthreads();
+      if (threadIdx.x == 0) s_n = 0;
+      __syncthreads();
+      // ordered compaction, one warp-sized slice at a time by warp 0 (lists are short: ~L0)
+      if (threadIdx.x < 32) {
+        int n = 0;
+        for (int i0 = 0; i0 < nb; i0 += 32) {
+          const int i = i0 + threadIdx.x;
+          bool sel = false;
+          int32_t id = 0;
+          float av = 0.0f;
+          if (i < nb) {
+            id = a.idx[start + b0 + i];
+            av = a.val[start + b0 + i];
+            const bool abl = rk ? (static_cast<int>(rk[id]) < a.budget) : false;
+            sel = (a.mode == 0) ? abl : !abl;
+          }
+          const uint32_t bal = __ballot_sync(0xffffffffu, sel);
+          if (sel) {
+            const int pos = n + __popc(bal & ((1u << threadIdx.x) - 1u));
+            s_id[pos] = id;
+            s_a[pos] = sign * av;
+          }
+          n += __popc(bal);
+        }
+        if (threadIdx.x == 0) s_n = n;
+      }
+      __syncthreads();
+      const int n = s_n;
+      // stage 2: acc += a_i * W_dec[i, :]; independent 16-byte gathers, L2-resident rows
+#pragma unroll 4
+      for (int j = 0; j < n; ++j) {
+        const Bf16x8* wr =
+            reinterpret_cast<const Bf16x8*>(a.w_dec + static_cast<size_t>(s_id[j]) * a.d);
+        const float av = s_a[j];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int vec = threadIdx.x + i * blockDim.x;
+          if (vec < nvec) {
+            float wv[8];
+            unpack8(__ldg(reinterpret_cast<const int4*>(wr) + vec), wv);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[i][e] = fmaf(av, wv[e], acc[i][e]);
+          }
+        }
+      }
+    }
+    // round to the residual dtype; everything downstream sees the bf16 row
+    float xb[NV][8];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = threadIdx.x + i * blockDim.x;
+      if (vec < nvec) {
+        const Bf16x8 p = pack8(acc[i]);
+        if (a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row) * a.d)[vec] = p;
+        unpack8(p, xb[i]);
+      }
+    }
+    if (a.out_h) rmsnorm_store<NV>(xb, a.w_norm, a.d, a.eps, a.out_h + static_cast<size_t>(row) * a.d, red);
+  }
+}
+
+// -----------------------------------------------------------------------------------------
+// a2 (first half): mean over a prompt's rows of the sparse activations -> dense [P, S] fp32.
+// One CTA per prompt; rows are added in token order (a latent occurs at most once per row,
+// so there are no intra-row conflicts and the fp32 sum order is fixed).
+// Reference: torch.mean(sae.encode(residual[start:]), dim=0), src/02_run_sae_baseline.py:67-70.
+// -----------------------------------------------------------------------------------------
+__global__ void tb_latent_mean_kernel(const int64_t* __restrict__ row_start, int cap,
+                                      const int32_t* __restrict__ count,
+                                      const int32_t* __restrict__ idx, const float* __restrict__ val,
+                                      const int64_t* __restrict__ seg, int rows_per_prompt, int S,
+                                      float* __restrict__ out_mean) {
+  const int p = blockIdx.x;
+  const int64_t r0 = seg ? seg[p] : static_cast<int64_t>(p) * rows_per_prompt;
+  const int64_t r1 = seg ? seg[p + 1] : r0 + rows_per_prompt;
+  float* out = out_mean + static_cast<size_t>(p) * S;
+  for (int j = threadIdx.x; j < S; j += blockDim.x) out[j] = 0.0f;
+  __syncthreads();
+  for (int64_t r = r0; r < r1; ++r) {
+    const int64_t start = row_start ? row_start[r] : r * cap;
+    int cnt = count[r];
+    if (row_start == nullptr) cnt = min(cnt, cap);
+    for (int i = threadIdx.x; i < cnt; i += blockDim.x) out[idx[start + i]] += val[start + i];
+    __syncthreads();
+  }
+  const float n = static_cast<float>(r1 - r0);
+  if (r1 > r0)
+    for (int j = threadIdx.x; j < S; j += blockDim.x) out[j] = __fdiv_rn(out[j], n);
+}
+
+// -----------------------------------------------------------------------------------------
+// a2 (second half): per prompt, the m largest means, sorted descending (ties: lower latent id
+// first), plus a rank table rank[latent] = position (0xFFFF if not selected). Nested budgets
+// m' <= m are prefixes of the sorted list, i.e. "rank < m'".
+// Radix select (11 + 11 + 10 bits) for the threshold key, ordered compaction, bitonic sort.
+// Reference: torch.topk(avg_sae_acts, k).indices, src/02_run_sae_baseline.py:73.
+// -----------------------------------------------------------------------------------------
+constexpr int kTopmThreads = 1024;
+constexpr int kTopmMax = 1024;
+
+__device__ __forceinline__ uint32_t float_key(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float key_float(uint32_t k) {
+  return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+
+// find the bin (scanning from the top) in which the cumulative count reaches `need`
+__device__ __forceinline__ void pick_bin(const uint32_t* hist, int nbins, uint32_t need,
+                                         uint32_t* s_bin, uint32_t* s_above) {
+  if (threadIdx.x == 0) {
+    uint32_t cum = 0;
+    int b = nbins - 1;
+    for (; b > 0; --b) {
+      if (cum + hist[b] >= need) break;
+      cum += hist[b];
+    }
+    *s_bin = static_cast<uint32_t>(b);
+    *s_above = cum;
+  }
+}
+
+__global__ void __launch_bounds__(kTopmThreads, 1)
+tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __restrict__ out_idx,
+                      float* __restrict__ out_val, uint16_t* __restrict__ rank) {
+  __shared__ uint32_t hist[2048];
+  __shared__ unsigned long long sel[kTopmMax];
+  __shared__ uint32_t s_bin, s_above, s_warp_gt[32], s_warp_eq[32];
+  __shared__ uint32_t s_run_sel, s_run_eq;
+  const int p = blockIdx.x;
+  const float* v = mean + static_cast<size_t>(p) * S;
+  const int tid = threadIdx.x;
+  const uint32_t mm = static_cast<uint32_t>(min(m, S));
+
+  // ---- pass 1: top 11 bits
+  for (int i = tid; i < 2048; i += kTopmThreads) hist[i] = 0;
+  __syncthreads();
+  for (int j = tid; j < S; j += kTopmThreads) atomicAdd(&hist[float_key(v[j]) >> 21], 1u);
+  __syncthreads();
+  pick_bin(hist, 2048, mm, &s_bin, &s_above);
+  __syncthreads();
+  const uint32_t b1 = s_bin;
+  uint32_t need = mm - s_above;
+  __syncthreads();
+  // ---- pass 2: middle 11 bits inside bin b1
+  for (int i = tid; i < 2048; i += kTopmThreads) hist[i] = 0;
+  __syncthreads();
+  for (int j = tid; j < S; j += kTopmThreads) {
+    const uint32_t k = float_key(v[j]);
+    if ((k >> 21) == b1) atomicAdd(&hist[(k >> 10) & 0x7ffu], 1u);
+  }
+  __syncthreads();
+  pick_bin(hist, 2048, need, &s_bin, &s_above);
+  __syncthreads();
+  const uint32_t b2 = s_bin;
+  need -= s_above;
+  __syncthreads();
+  // ---- pass 3: low 10 bits inside (b1, b2)
+  for (int i = tid; i < 1024; i += kTopmThreads) hist[i] = 0;
+  __syncthreads();
+  const uint32_t hi22 = (b1 << 11) | b2;
+  for (int j = tid; j < S; j += kTopmThreads) {
+    const uint32_t k = float_key(v[j]);
+    if ((k >> 10) == hi22) atomicAdd(&hist[k & 0x3ffu], 1u);
+  }
+  __syncthreads();
+  pick_bin(hist, 1024, need, &s_bin, &s_above);
+  __syncthreads();
+  const uint32_t kth = (hi22 << 10) | s_bin;  // key of the m-th largest value
+  const uint32_t need_eq = need - s_above;    // how many elements equal to it are taken
+
+  // ---- ordered compaction: key > kth, plus the first need_eq (by latent id) with key == kth
+  if (tid == 0) { s_run_sel = 0; s_run_eq = 0; }
+  for (int i = tid; i < kTopmMax; i += kTopmThreads) sel[i] = 0ull;
+  __syncthreads();
+  const int warp = tid >> 5, lane = tid & 31;
+  for (int base = 0; base < S; base += kTopmThreads) {
+    const int j = base + tid;
+    uint32_t k = 0;
+    bool gt = false, eq = false;
+    if (j < S) {
+      k = float_key(v[j]);
+      gt = k > kth;
+      eq = k == kth;
+    }
+    const uint32_t bal_eq = __ballot_sync(0xffffffffu, eq);
+    const uint32_t bal_gt = __ballot_sync(0xffffffffu, gt);
+    if (lane == 0) { s_warp_eq[warp] = __popc(bal_eq); s_warp_gt[warp] = __popc(bal_gt); }
+    __syncthreads();
+    uint32_t eq_before = s_run_eq, gt_before = 0, eq_total = 0, gt_total = 0;
+    for (int w = 0; w < kTopmThreads / 32; ++w) {
+      if (w < warp) { eq_before += s_warp_eq[w]; gt_before += s_warp_gt[w]; }
+      eq_total += s_warp_eq[w];
+      gt_total += s_warp_gt[w];
+    }
+    const uint32_t lane_mask = (1u << lane) - 1u;
+    const uint32_t my_eq_rank = eq_before + __popc(bal_eq & lane_mask);  // global tie order
+    const bool take = gt || (eq && my_eq_rank < need_eq);
+    // position: selected-so-far + gt before me + eq taken before me (this round)
+    const uint32_t eq_taken_before_round = min(s_run_eq, need_eq);
+    const uint32_t eq_taken_before_me = min(my_eq_rank, need_eq) - eq_taken_before_round;
+    if (take) {
+      const uint32_t pos = s_run_sel + gt_before + __popc(bal_gt & lane_mask) + eq_taken_before_me;
+      if (pos < kTopmMax)
+        sel[pos] = (static_cast<unsigned long long>(k) << 32) |
+                   static_cast<unsigned long long>(0xffffffffu - static_cast<uint32_t>(j));
+    }
+    __syncthreads();
+    if (tid == 0) {
+      const uint32_t eq_taken_round = min(s_run_eq + eq_total, need_eq) - eq_taken_before_round;
+      s_run_sel += gt_total + eq_taken_round;
+      s_run_eq += eq_total;
+    }
+    __syncthreads();
+  }
+
+  // ---- bitonic sort, descending on (key, ~id): larger value first, lower id first on ties
+  for (int size = 2; size <= kTopmMax; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      const int partner = tid ^ stride;
+      if (partner > tid) {
+        const bool desc = ((tid & size) == 0);
+        const unsigned long long a = sel[tid], b = sel[partner];
+        if ((a < b) == desc) { sel[tid] = b; sel[partner] = a; }
+      }
+      __syncthreads();
+    }
+  }
+
+  // ---- outputs
+  uint16_t* rk = rank + static_cast<size_t>(p) * S;
+  for (int j = tid; j < S; j += kTopmThreads) rk[j] = 0xffffu;
+  __syncthreads();
+  if (tid < static_cast<int>(mm)) {
+    const unsigned long long e = sel[tid];
+    const int32_t id = static_cast<int32_t>(0xffffffffu - static_cast<uint32_t>(e & 0xffffffffull));
+    out_idx[static_cast<size_t>(p) * m + tid] = id;
+    out_val[static_cast<size_t>(p) * m + tid] = key_float(static_cast<uint32_t>(e >> 32));
+    rk[id] = static_cast<uint16_t>(tid);
+  } else if (tid < m) {
+    out_idx[static_cast<size_t>(p) * m + tid] = -1;
+    out_val[static_cast<size_t>(p) * m + tid] = 0.0f;
+  }
+}
+
+// -----------------------------------------------------------------------------------------
+// K4: merge per-(row, part) lens partials: parts are vocab chunks of one GPU and/or the
+// vocab shards of several GPUs after an all_gather. finalize == 0 writes one merged partial
+// (same layout, n_parts = 1); finalize == 1 writes lse, secret probability, top-10 probs/ids.
+// -----------------------------------------------------------------------------------------
+struct MergeArgs {
+  const float* pm; const float* ps; const float* psec; const float* ptv; const int32_t* pti;
+  int n_parts, n_rows;
+  int finalize;
+  float* om; float* os; float* osec; float* otv; int32_t* oti;   // finalize == 0
+  float* lse; float* secret_prob; float* top_prob; int32_t* top_id;  // finalize == 1
+};
+
+__global__ void tb_lens_merge_kernel(const MergeArgs a) {
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= a.n_rows) return;
+  float m = -CUDART_INF_F, s = 0.0f, sec = -CUDART_INF_F;
+  float tv[10];
+  int32_t ti[10];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) { tv[k] = -CUDART_INF_F; ti[k] = -1; }
+  for (int part = 0; part < a.n_parts; ++part) {
+    const size_t o = static_cast<size_t>(part) * a.n_rows + row;
+    const float pm = a.pm[o], ps = a.ps[o];
+    if (pm > m) { s *= expf(m - pm); m = pm; }
+    if (pm > -CUDART_INF_F) s += ps * expf(pm - m);
+    sec = fmaxf(sec, a.psec[o]);
+    for (int c = 0; c < 10; ++c) {
+      const float v = a.ptv[o * 10 + c];
+      if (!(v > tv[9])) break;  // a part's list is sorted: nothing further can enter
+      tv[9] = v;
+      ti[9] = a.pti[o * 10 + c];
+#pragma unroll
+      for (int k = 9; k > 0; --k) {
+        const bool sw = tv[k] > tv[k - 1];
+        const float fa = tv[k - 1], fb = tv[k];
+        const int32_t ia = ti[k - 1], ib = ti[k];
+        tv[k - 1] = sw ? fb : fa; tv[k] = sw ? fa : fb;
+        ti[k - 1] = sw ? ib : ia; ti[k] = sw ? ia : ib;
+      }
+    }
+  }
+  if (!a.finalize) {
+    a.om[row] = m; a.os[row] = s; a.osec[row] = sec;
+#pragma unroll
+    for (int k = 0; k < 10; ++k) { a.otv[row * 10 + k] = tv[k]; a.oti[row * 10 + k] = ti[k]; }
+  } else {
+    const float lse = m + logf(s);
+    a.lse[row] = lse;
+    if (a.secret_prob) a.secret_prob[row] = (sec > -CUDART_INF_F) ? expf(sec - lse) : 0.0f;
+#pragma unroll
+    for (int k = 0; k < 10; ++k) {
+      a.top_prob[row * 10 + k] = (tv[k] > -CUDART_INF_F) ? expf(tv[k] - lse) : 0.0f;
+      a.top_id[row * 10 + k] = ti[k];
+    }
+  }
+}
+
+// -----------------------------------------------------------------------------------------
+// K2 / a5: low-rank direction removal  x' = x - (x U) U^T,  U [d, r] orthonormal, r <= 64
+// (Execution Plan:148, r_edited = r - P_U(r)). The caller passes U^T [r, d] (bf16) so that
+// both thin products read 16-byte contiguous slices: phase 1 forms c = x U for a tile of
+// kProjRows rows staged in shared memory (one direction per warp, fp32 accumulate, shuffle
+// reduce); phase 2 subtracts sum_j c_j U[:, j] with each thread owning fixed 8-element slices
+// of the rows. c stays in fp32. Output is rounded to bf16 and optionally RMS-normed (a6).
+// -----------------------------------------------------------------------------------------
+constexpr int kProjRows = 8;
+constexpr int kProjMaxRank = 64;
+
+struct ProjArgs {
+  const __nv_bfloat16* x;   // [n_rows, d]
+  const __nv_bfloat16* ut;  // [r, d]
+  int r;
+  const float* w_norm;      // [d] or nullptr
+  float eps;
+  __nv_bfloat16* out_x;     // nullable
+  __nv_bfloat16* out_h;     // nullable
+  int n_rows, d;
+};
+
+template <int NV>
+__global__ void tb_lowrank_remove_kernel(const ProjArgs a) {
+  extern __shared__ __align__(16) uint8_t proj_smem[];
+  __shared__ float red[kRowMaxWarps];
+  __shared__ float s_c[kProjRows][kProjMaxRank];
+  Bf16x8* s_x = reinterpret_cast<Bf16x8*>(proj_smem);  // [kProjRows][nvec]
+  const int nvec = a.d >> 3;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int n_tiles = (a.n_rows + kProjRows - 1) / kProjRows;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * kProjRows;
+    __syncthreads();
+    // stage the row tile (zero rows past the end)
+    for (int rr = 0; rr < kProjRows; ++rr) {
+      const int row = row0 + rr;
+      for (int vec = threadIdx.x; vec < nvec; vec += blockDim.x) {
+        Bf16x8 z;
+        if (row < a.n_rows) z = reinterpret_cast<const Bf16x8*>(a.x + static_cast<size_t>(row) * a.d)[vec];
+        else *reinterpret_cast<int4*>(&z) = make_int4(0, 0, 0, 0);
+        s_x[rr * nvec + vec] = z;
+      }
+    }
+    __syncthreads();
+    // phase 1: c[rr][j] = <x_rr, U[:, j]>
+    for (int j = warp; j < a.r; j += nwarps) {
+      float c[kProjRows];
+#pragma unroll
+      for (int rr = 0; rr < kProjRows; ++rr) c[rr] = 0.0f;
+      const int4* ur = reinterpret_cast<const int4*>(a.ut + static_cast<size_t>(j) * a.d);
+      for (int vec = lane; vec < nvec; vec += 32) {
+        float u[8];
+        unpack8(__ldg(ur + vec), u);
+#pragma unroll
+        for (int rr = 0; rr < kProjRows; ++rr) {
+          float xv[8];
+          unpack8(s_x[rr * nvec + vec], xv);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) c[rr] = fmaf(xv[e], u[e], c[rr]);
+        }
+      }
+#pragma unroll
+      for (int rr = 0; rr < kProjRows; ++rr) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c[rr] += __shfl_xor_sync(0xffffffffu, c[rr], o);
+        if (lane == 0) s_c[rr][j] = c[rr];
+      }
+    }
+    __syncthreads();
+    // phase 2: x' = x - sum_j c_j U[:, j]
+    float acc[kProjRows][NV][8];
+#pragma unroll
+    for (int rr = 0; rr < kProjRows; ++rr)
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = threadIdx.x + i * blockDim.x;
+        if (vec < nvec) unpack8(s_x[rr * nvec + vec], acc[rr][i]);
+      }
+    for (int j = 0; j < a.r; ++j) {
+      const int4* ur = reinterpret_cast<const int4*>(a.ut + static_cast<size_t>(j) * a.d);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = threadIdx.x + i * blockDim.x;
+        if (vec < nvec) {
+          float u[8];
+          unpack8(__ldg(ur + vec), u);
+#pragma unroll
+          for (int rr = 0; rr < kProjRows; ++rr) {
+            const float cj = -s_c[rr][j];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) acc[rr][i][e] = fmaf(cj, u[e], acc[rr][i][e]);
+          }
+        }
+      }
+    }
+    // round, store, optional fused final RMSNorm
+#pragma unroll
+    for (int rr = 0; rr < kProjRows; ++rr) {
+      const int row = row0 + rr;
+      const bool valid = row < a.n_rows;  // uniform across the CTA
+      float xb[NV][8];
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = threadIdx.x + i * blockDim.x;
+        if (vec < nvec) {
+          const Bf16x8 p = pack8(acc[rr][i]);
+          if (valid && a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row) * a.d)[vec] = p;
+          unpack8(p, xb[i]);
+        }
+      }
+      if (valid && a.out_h)
+        rmsnorm_store<NV>(xb, a.w_norm, a.d, a.eps, a.out_h + static_cast<size_t>(row) * a.d, red);
+    }
+  }
+}
+
+}  // namespace tb
