@@ -1,0 +1,82 @@
+"""ctypes binding of libtb_b200.so (the C ABI declared in include/tb_b200.h).
+
+The library is built in-tree by ``__graft_entry__.build()`` (or ``python -m
+taboo_brittleness_b200.build``). There is no CPU fallback: if the shared object is missing
+or a call fails, a ``TabooKernelError`` is raised.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int, c_int32, c_int64, c_uint16, c_void_p
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(PKG_DIR, "libtb_b200.so")
+
+TB_OK = 0
+TB_ERR_INVALID = -1
+TB_ERR_ARCH = -2
+TB_ERR_CUDA = -3
+TB_TOPK = 10
+TB_TOPM_MAX = 1024
+TB_RANK_NONE = 0xFFFF
+
+
+class TabooKernelError(RuntimeError):
+    """Raised when the CUDA library is missing or an entry point reports an error."""
+
+    def __init__(self, message: str, code: int = TB_ERR_CUDA):
+        super().__init__(message)
+        self.code = code
+
+
+_P = c_void_p  # every device pointer travels as void*
+
+# name -> (restype, argtypes); mirrors include/tb_b200.h one to one
+SIGNATURES = {
+    "tb_version": (c_int, []),
+    "tb_last_error": (c_char_p, []),
+    "tb_device_check": (c_int, []),
+    "tb_sae_encode": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, _P, _P, c_int, _P, _P, _P, _P,
+                              c_int, c_int, _P]),
+    "tb_sae_latent_mean": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P]),
+    "tb_topm_select": (c_int, [_P, c_int64, c_int, c_int, _P, _P, _P, _P]),
+    "tb_sae_ablate_decode": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int,
+                                     c_int64, c_int, c_int, _P, c_float, _P, _P, _P]),
+    "tb_lowrank_remove": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
+    "tb_rmsnorm": (c_int, [_P, _P, c_float, c_int64, c_int, _P, _P]),
+    "tb_lens_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,
+                                 _P, _P, _P, _P, _P, _P]),
+    "tb_lens_merge": (c_int, [_P, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P,
+                              _P, _P, _P]),
+    "tb_gemm_bf16_nt": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_int, _P, _P]),
+}
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load the shared object and set every prototype. Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise TabooKernelError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here = header and library disagree
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().tb_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int, what: str) -> None:
+    if rc != TB_OK:
+        raise TabooKernelError(f"{what} failed ({rc}): {last_error()}", rc)

@@ -1,0 +1,426 @@
+"""Tensor-level wrappers over the C ABI (include/tb_b200.h).
+
+Every function takes CUDA torch tensors, allocates its outputs (and scratch) with torch, and
+launches on torch's current stream. Nothing here computes on the CPU, and nothing falls back:
+a missing library or a failed call raises ``TabooKernelError``.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import TB_TOPK, TB_TOPM_MAX, TabooKernelError, check
+
+GEMMA2_EPS = 1e-6          # Gemma2Config.rms_norm_eps
+GEMMA2_SOFTCAP = 30.0      # Gemma2Config.final_logit_softcapping
+BLOCK_M = 128
+BLOCK_N = 256
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _need(t: torch.Tensor, dtype: torch.dtype, name: str, ndim: Optional[int] = None) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TabooKernelError(f"{name} must be a CUDA tensor (no CPU path exists)", _lib.TB_ERR_INVALID)
+    if t.dtype != dtype:
+        raise TabooKernelError(f"{name} must be {dtype}, got {t.dtype}", _lib.TB_ERR_INVALID)
+    if ndim is not None and t.dim() != ndim:
+        raise TabooKernelError(f"{name} must be {ndim}-D, got shape {tuple(t.shape)}", _lib.TB_ERR_INVALID)
+    if not t.is_contiguous():
+        raise TabooKernelError(f"{name} must be contiguous", _lib.TB_ERR_INVALID)
+    return t
+
+
+def device_check() -> None:
+    """Raise unless the current device can run the kernels (sm_100)."""
+    check(_lib.load().tb_device_check(), "tb_device_check")
+
+
+# ------------------------------------------------------------------------------------------
+# weights
+# ------------------------------------------------------------------------------------------
+@dataclass
+class SaeWeights:
+    """Gemma Scope JumpReLU SAE parameters in the layout the kernels read.
+
+    sae_lens stores W_enc [d, S], W_dec [S, d] (fp32); the encode GEMM wants the K-major
+    transpose W_enc^T [S, d]. bf16 for the two matrices, fp32 for the vectors.
+    """
+    w_enc_t: torch.Tensor   # bf16 [S, d]
+    b_enc: torch.Tensor     # f32 [S]
+    theta: torch.Tensor     # f32 [S]
+    w_dec: torch.Tensor     # bf16 [S, d]
+    b_dec: torch.Tensor     # f32 [d]
+
+    @property
+    def d(self) -> int:
+        return self.w_dec.shape[1]
+
+    @property
+    def S(self) -> int:
+        return self.w_dec.shape[0]
+
+    @staticmethod
+    def from_sae_lens_layout(W_enc, b_enc, threshold, W_dec, b_dec, device="cuda") -> "SaeWeights":
+        """W_enc [d, S], W_dec [S, d] as sae_lens / Gemma Scope params.npz hold them."""
+        dev = torch.device(device)
+        return SaeWeights(
+            w_enc_t=W_enc.to(dev).t().contiguous().to(torch.bfloat16),
+            b_enc=b_enc.to(dev, torch.float32).contiguous(),
+            theta=threshold.to(dev, torch.float32).contiguous(),
+            w_dec=W_dec.to(dev).contiguous().to(torch.bfloat16),
+            b_dec=b_dec.to(dev, torch.float32).contiguous(),
+        )
+
+
+@dataclass
+class LensWeights:
+    """Final RMSNorm weight (f32 [d]) and unembedding shard W_U (bf16 [V_shard, d])."""
+    w_norm: torch.Tensor
+    w_u: torch.Tensor
+    vocab_offset: int = 0
+    eps: float = GEMMA2_EPS
+
+
+@dataclass
+class SparseActs:
+    """Row-wise lists of the non-zero SAE latents (what replaces the dense [rows, S] acts)."""
+    count: torch.Tensor                 # i32 [rows]
+    idx: torch.Tensor                   # i32 flat
+    val: torch.Tensor                   # f32 flat
+    S: int
+    cap: int = 0                        # fixed stride when row_start is None
+    row_start: Optional[torch.Tensor] = None  # i64 [rows] (CSR)
+
+    @property
+    def n_rows(self) -> int:
+        return self.count.shape[0]
+
+    def to_dense(self) -> torch.Tensor:
+        """Dense [rows, S] f32 view for tests (small inputs only)."""
+        n = self.n_rows
+        dense = torch.zeros(n, self.S, dtype=torch.float32, device=self.count.device)
+        cnt = self.count.to(torch.int64)
+        if self.row_start is None:
+            cnt = cnt.clamp(max=self.cap)
+            start = torch.arange(n, device=cnt.device, dtype=torch.int64) * self.cap
+        else:
+            start = self.row_start
+        rows = torch.repeat_interleave(torch.arange(n, device=cnt.device), cnt)
+        offs = torch.arange(int(cnt.sum().item()), device=cnt.device) - torch.repeat_interleave(
+            torch.cumsum(cnt, 0) - cnt, cnt)
+        pos = torch.repeat_interleave(start, cnt) + offs
+        dense[rows, self.idx[pos].to(torch.int64)] = self.val[pos]
+        return dense
+
+
+# ------------------------------------------------------------------------------------------
+# validation GEMM
+# ------------------------------------------------------------------------------------------
+def gemm_nt(a: torch.Tensor, b: torch.Tensor, n_chunks: int = 1, cta_pair: bool = False) -> torch.Tensor:
+    """a [M, K] @ b [N, K]^T -> f32 [M, N] through the TMA/tcgen05 main loop (tests only)."""
+    _need(a, torch.bfloat16, "a", 2)
+    _need(b, torch.bfloat16, "b", 2)
+    M, K = a.shape
+    N = b.shape[0]
+    out = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    check(_lib.load().tb_gemm_bf16_nt(_ptr(a), _ptr(b), M, N, K, n_chunks, int(cta_pair), _ptr(out),
+                                      _stream()), "tb_gemm_bf16_nt")
+    return out
+
+
+# ------------------------------------------------------------------------------------------
+# K1 SAE encode
+# ------------------------------------------------------------------------------------------
+def sae_encode_raw(x: torch.Tensor, sae: SaeWeights, *, cap: int = 0,
+                   row_start: Optional[torch.Tensor] = None, row_cap: Optional[torch.Tensor] = None,
+                   idx: Optional[torch.Tensor] = None, val: Optional[torch.Tensor] = None,
+                   rank: Optional[torch.Tensor] = None, rank_rows: int = 0, budget: int = 0
+                   ) -> torch.Tensor:
+    """One launch of tb_sae_encode; returns count i32 [rows]. idx/val None = count only."""
+    _need(x, torch.bfloat16, "x", 2)
+    n, d = x.shape
+    if d != sae.d:
+        raise TabooKernelError(f"x has d={d}, SAE has d={sae.d}", _lib.TB_ERR_INVALID)
+    count = torch.empty(n, dtype=torch.int32, device=x.device)
+    if n == 0:
+        return count
+    if rank is not None:
+        _need(rank, torch.uint16, "rank", 2)
+    check(_lib.load().tb_sae_encode(
+        _ptr(x), _ptr(sae.w_enc_t), _ptr(sae.b_enc), _ptr(sae.theta), n, d, sae.S,
+        _ptr(row_start), _ptr(row_cap), cap, _ptr(idx), _ptr(val), _ptr(count),
+        _ptr(rank), rank_rows, budget, _stream()), "tb_sae_encode")
+    return count
+
+
+def sae_encode(x: torch.Tensor, sae: SaeWeights, cap: int = 128, *, rank: Optional[torch.Tensor] = None,
+               rank_rows: int = 0, budget: int = 0) -> SparseActs:
+    """JumpReLU encode to sparse row lists (replaces ``sae.encode``, 02_run_sae_baseline.py:67).
+
+    First pass writes fixed-stride lists of ``cap`` slots per row. If some row has more active
+    latents than that (e.g. <bos> rows), the lists are rebuilt exactly in CSR form with a second
+    pass sized from the counts -- no active latent is ever dropped.
+    """
+    n = x.shape[0]
+    dev = x.device
+    idx = torch.empty(max(n * cap, 1), dtype=torch.int32, device=dev)
+    val = torch.empty(max(n * cap, 1), dtype=torch.float32, device=dev)
+    count = sae_encode_raw(x, sae, cap=cap, idx=idx, val=val, rank=rank, rank_rows=rank_rows, budget=budget)
+    if n == 0 or int(count.max().item()) <= cap:
+        return SparseActs(count=count, idx=idx, val=val, S=sae.S, cap=cap)
+    c64 = count.to(torch.int64)
+    row_start = torch.cumsum(c64, 0) - c64
+    nnz = int(c64.sum().item())
+    idx = torch.empty(nnz, dtype=torch.int32, device=dev)
+    val = torch.empty(nnz, dtype=torch.float32, device=dev)
+    count2 = sae_encode_raw(x, sae, row_start=row_start, row_cap=count, idx=idx, val=val,
+                            rank=rank, rank_rows=rank_rows, budget=budget)
+    return SparseActs(count=count2, idx=idx, val=val, S=sae.S, cap=0, row_start=row_start)
+
+
+# ------------------------------------------------------------------------------------------
+# a2 targeting
+# ------------------------------------------------------------------------------------------
+def latent_mean(acts: SparseActs, rows_per_prompt: int = 0, seg: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Mean activation per prompt and latent, f32 [P, S] (02_run_sae_baseline.py:70).
+
+    ``seg`` (i64 [P+1]) gives each prompt's row window (the response slice, :64); otherwise
+    prompts are consecutive blocks of ``rows_per_prompt`` rows.
+    """
+    if seg is not None:
+        _need(seg, torch.int64, "seg", 1)
+        n_prompts = seg.shape[0] - 1
+    else:
+        if rows_per_prompt <= 0 or acts.n_rows % rows_per_prompt:
+            raise TabooKernelError("rows_per_prompt must divide the row count", _lib.TB_ERR_INVALID)
+        n_prompts = acts.n_rows // rows_per_prompt
+    out = torch.empty(n_prompts, acts.S, dtype=torch.float32, device=acts.count.device)
+    check(_lib.load().tb_sae_latent_mean(
+        _ptr(acts.row_start), acts.cap, _ptr(acts.count), _ptr(acts.idx), _ptr(acts.val), _ptr(seg),
+        rows_per_prompt, n_prompts, acts.S, _ptr(out), _stream()), "tb_sae_latent_mean")
+    return out
+
+
+def topm_select(mean: torch.Tensor, m: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Top-m latents per prompt, sorted descending: (idx i32 [P,m], val f32 [P,m], rank u16 [P,S])."""
+    _need(mean, torch.float32, "mean", 2)
+    P, S = mean.shape
+    idx = torch.empty(P, m, dtype=torch.int32, device=mean.device)
+    val = torch.empty(P, m, dtype=torch.float32, device=mean.device)
+    rank = torch.empty(P, S, dtype=torch.uint16, device=mean.device)
+    check(_lib.load().tb_topm_select(_ptr(mean), P, S, m, _ptr(idx), _ptr(val), _ptr(rank), _stream()),
+          "tb_topm_select")
+    return idx, val, rank
+
+
+def rank_table_from_indices(indices: torch.Tensor, S: int) -> torch.Tensor:
+    """u16 [n_tables, S] rank table from index lists [n_tables, m] (e.g. seeded random control:
+    ``torch.randperm(S, generator=cpu_gen(seed))[:m]``)."""
+    if indices.dim() == 1:
+        indices = indices[None]
+    n, m = indices.shape
+    if m > TB_TOPM_MAX:
+        raise TabooKernelError(f"at most {TB_TOPM_MAX} latents per table", _lib.TB_ERR_INVALID)
+    table = torch.full((n, S), _lib.TB_RANK_NONE, dtype=torch.int32)
+    src = torch.arange(m, dtype=torch.int32).expand(n, m)
+    table.scatter_(1, indices.to(torch.int64).cpu(), src)
+    return table.to(torch.uint16)
+
+
+# ------------------------------------------------------------------------------------------
+# K1b / K2 / a6
+# ------------------------------------------------------------------------------------------
+def sae_ablate_decode(x: Optional[torch.Tensor], acts: SparseActs, sae: SaeWeights, rank: Optional[torch.Tensor],
+                      budget: int, *, mode: str = "error", rank_rows: int = 0,
+                      row_table: Optional[torch.Tensor] = None, w_norm: Optional[torch.Tensor] = None,
+                      eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False
+                      ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+    """Zero the latents with rank < budget and decode back to the residual (Plan:126).
+
+    mode "error": x' = x - sum_{ablated} a_i W_dec[i]  (keeps the SAE reconstruction error);
+    mode "plain": x' = sum_{kept} a_i W_dec[i] + b_dec.  Returns (x' bf16, h bf16) as requested.
+    """
+    n = acts.n_rows
+    d = sae.d
+    dev = acts.count.device
+    imode = {"error": 0, "plain": 1}[mode]
+    if imode == 0:
+        _need(x, torch.bfloat16, "x", 2)
+    if rank is not None:
+        _need(rank, torch.uint16, "rank", 2)
+    if row_table is not None:
+        _need(row_table, torch.int32, "row_table", 1)
+    out_x = torch.empty(n, d, dtype=torch.bfloat16, device=dev) if want_x else None
+    out_h = torch.empty(n, d, dtype=torch.bfloat16, device=dev) if want_h else None
+    check(_lib.load().tb_sae_ablate_decode(
+        _ptr(x), _ptr(acts.row_start), acts.cap, _ptr(acts.count), _ptr(acts.idx), _ptr(acts.val),
+        _ptr(sae.w_dec), _ptr(sae.b_dec), _ptr(rank), _ptr(row_table), rank_rows, budget, imode,
+        n, d, sae.S, _ptr(w_norm), eps, _ptr(out_x), _ptr(out_h), _stream()), "tb_sae_ablate_decode")
+    return out_x, out_h
+
+
+def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.Tensor] = None,
+                   eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False
+                   ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+    """x' = x - (x U) U^T for orthonormal U [d, r], r <= 64 (Plan:148)."""
+    _need(x, torch.bfloat16, "x", 2)
+    _need(U, torch.bfloat16, "U", 2)
+    n, d = x.shape
+    if U.shape[0] != d:
+        raise TabooKernelError(f"U must be [d={d}, r], got {tuple(U.shape)}", _lib.TB_ERR_INVALID)
+    r = U.shape[1]
+    ut = U.t().contiguous()
+    out_x = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_x else None
+    out_h = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_h else None
+    check(_lib.load().tb_lowrank_remove(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(out_x),
+                                        _ptr(out_h), _stream()), "tb_lowrank_remove")
+    return out_x, out_h
+
+
+def rmsnorm(x: torch.Tensor, w_norm: torch.Tensor, eps: float = GEMMA2_EPS) -> torch.Tensor:
+    """Gemma2RMSNorm on a bf16 residual -> bf16 (models.py:135, ``model.model.norm``)."""
+    _need(x, torch.bfloat16, "x", 2)
+    _need(w_norm, torch.float32, "w_norm", 1)
+    out = torch.empty_like(x)
+    check(_lib.load().tb_rmsnorm(_ptr(x), _ptr(w_norm), eps, x.shape[0], x.shape[1], _ptr(out), _stream()),
+          "tb_rmsnorm")
+    return out
+
+
+# ------------------------------------------------------------------------------------------
+# K3 / K4 logit lens
+# ------------------------------------------------------------------------------------------
+@dataclass
+class LensPartials:
+    """(max, sumexp, secret logit, top-10) per (part, row); parts = vocab chunks or shards."""
+    pm: torch.Tensor    # f32 [parts, rows]
+    ps: torch.Tensor
+    psec: torch.Tensor
+    ptv: torch.Tensor   # f32 [parts, rows, 10]
+    pti: torch.Tensor   # i32 [parts, rows, 10]
+
+    @property
+    def n_parts(self) -> int:
+        return self.pm.shape[0]
+
+    @property
+    def n_rows(self) -> int:
+        return self.pm.shape[1]
+
+    def pack(self) -> torch.Tensor:
+        """[parts, rows, 23] f32 (ids bit-cast) -- one tensor for a single all_gather."""
+        return torch.cat([self.pm[..., None], self.ps[..., None], self.psec[..., None], self.ptv,
+                          self.pti.view(torch.float32)], dim=-1).contiguous()
+
+    @staticmethod
+    def unpack(t: torch.Tensor) -> "LensPartials":
+        t = t.reshape(-1, t.shape[-2], 23)
+        return LensPartials(pm=t[..., 0].contiguous(), ps=t[..., 1].contiguous(), psec=t[..., 2].contiguous(),
+                            ptv=t[..., 3:13].contiguous(), pti=t[..., 13:23].contiguous().view(torch.int32))
+
+
+@dataclass
+class LensReadout:
+    lse: torch.Tensor          # f32 [rows]  log-sum-exp of the (soft-capped) logits
+    secret_prob: torch.Tensor  # f32 [rows]
+    top_prob: torch.Tensor     # f32 [rows, 10], descending
+    top_id: torch.Tensor       # i32 [rows, 10]
+
+
+def pick_chunks(n_rows: int, V: int, n_sms: int = 148, cta_pair: bool = False) -> int:
+    """How many vocab chunks to sweep: fill all SMs while keeping the A rows of the resident
+    row blocks (917 KB each at d=3584) well inside the 126 MB L2, with little tail waste."""
+    group = 2 if cta_pair else 1
+    clusters = max(n_sms // group, 1)
+    m_blocks = -(-n_rows // (BLOCK_M * group))
+    n_tiles = -(-V // BLOCK_N)
+    best, best_cost = 1, None
+    for c in range(1, min(n_tiles, 64) + 1):
+        tpc = -(-n_tiles // c)
+        if -(-n_tiles // tpc) != c:      # would leave an empty chunk
+            continue
+        units = m_blocks * c
+        waves = -(-units // clusters)
+        # time ~ waves * tiles per chunk (+1 tile of pipeline fill per unit)
+        cost = waves * (tpc + 1)
+        resident_blocks = min(m_blocks, -(-clusters // c)) * group
+        if resident_blocks > 64:        # A working set > ~60 MB: thrashes L2 against the W_U stream
+            cost *= 1.5
+        if best_cost is None or cost < best_cost:
+            best, best_cost = c, cost
+    return best
+
+
+def lens_partials(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0,
+                  secret_id: Optional[torch.Tensor] = None, vocab_offset: int = 0,
+                  n_chunks: Optional[int] = None, cta_pair: bool = False) -> LensPartials:
+    _need(h, torch.bfloat16, "h", 2)
+    _need(w_u, torch.bfloat16, "w_u", 2)
+    n, d = h.shape
+    V = w_u.shape[0]
+    if secret_id is not None:
+        _need(secret_id, torch.int32, "secret_id", 1)
+    if n_chunks is None:
+        n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(h.device).multi_processor_count, cta_pair)
+    dev = h.device
+    p = LensPartials(
+        pm=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
+        ps=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
+        psec=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
+        ptv=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.float32, device=dev),
+        pti=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.int32, device=dev))
+    if n == 0:
+        return p
+    check(_lib.load().tb_lens_partials(
+        _ptr(h), _ptr(w_u), n, d, V, vocab_offset, float(softcap or 0.0), _ptr(secret_id), n_chunks,
+        int(cta_pair), _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _stream()),
+        "tb_lens_partials")
+    return p
+
+
+def lens_merge(p: LensPartials, finalize: bool = True):
+    """Merge parts per row. finalize -> LensReadout, else a one-part LensPartials."""
+    n = p.n_rows
+    dev = p.pm.device
+    lib = _lib.load()
+    if finalize:
+        out = LensReadout(lse=torch.empty(n, dtype=torch.float32, device=dev),
+                          secret_prob=torch.empty(n, dtype=torch.float32, device=dev),
+                          top_prob=torch.empty(n, TB_TOPK, dtype=torch.float32, device=dev),
+                          top_id=torch.empty(n, TB_TOPK, dtype=torch.int32, device=dev))
+        check(lib.tb_lens_merge(_ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), p.n_parts, n, 1,
+                                None, None, None, None, None, _ptr(out.lse), _ptr(out.secret_prob),
+                                _ptr(out.top_prob), _ptr(out.top_id), _stream()), "tb_lens_merge")
+        return out
+    o = LensPartials(pm=torch.empty(1, n, dtype=torch.float32, device=dev),
+                     ps=torch.empty(1, n, dtype=torch.float32, device=dev),
+                     psec=torch.empty(1, n, dtype=torch.float32, device=dev),
+                     ptv=torch.empty(1, n, TB_TOPK, dtype=torch.float32, device=dev),
+                     pti=torch.empty(1, n, TB_TOPK, dtype=torch.int32, device=dev))
+    check(lib.tb_lens_merge(_ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), p.n_parts, n, 0,
+                            _ptr(o.pm), _ptr(o.ps), _ptr(o.psec), _ptr(o.ptv), _ptr(o.pti), None, None, None,
+                            None, _stream()), "tb_lens_merge")
+    return o
+
+
+def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,
+               secret_id: Optional[torch.Tensor] = None, n_chunks: Optional[int] = None,
+               cta_pair: bool = False, prenormed: bool = False) -> LensReadout:
+    """norm -> lm_head -> softmax readouts of models.py:135-138 without the [rows, V] tensor.
+
+    x: bf16 residual rows (or the already normalised operand h when ``prenormed``).
+    """
+    h = x if prenormed else rmsnorm(x, lens.w_norm, lens.eps)
+    p = lens_partials(h, lens.w_u, softcap=softcap, secret_id=secret_id, vocab_offset=lens.vocab_offset,
+                      n_chunks=n_chunks, cta_pair=cta_pair)
+    return lens_merge(p, finalize=True)
