@@ -315,7 +315,7 @@ int tb_lowrank_remove(const void* x, const void* ut, int r, int64_t n_rows, int 
   DevInfo di;
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
-  if (!x || !ut) return fail(TB_ERR_INVALID, "null pointer");
+  if (!x || (!ut && r > 0)) return fail(TB_ERR_INVALID, "null pointer");
   if (r < 0 || r > tb::kProjMaxRank) return fail(TB_ERR_INVALID, "rank %d outside [0, %d]", r, tb::kProjMaxRank);
   if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
   if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");

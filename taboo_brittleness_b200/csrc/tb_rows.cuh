@@ -493,6 +493,7 @@ __global__ void tb_lens_merge_kernel(const MergeArgs a) {
 // of the rows. c stays in fp32. Output is rounded to bf16 and optionally RMS-normed (a6).
 // -----------------------------------------------------------------------------------------
 constexpr int kProjRows = 8;
+constexpr int kProjGroup = 4;  // rows accumulated at once in phase 2
 constexpr int kProjMaxRank = 64;
 
 struct ProjArgs {
@@ -507,7 +508,7 @@ struct ProjArgs {
 };
 
 template <int NV>
-__global__ void tb_lowrank_remove_kernel(const ProjArgs a) {
+__global__ void __launch_bounds__(512) tb_lowrank_remove_kernel(const ProjArgs a) {
   extern __shared__ __align__(16) uint8_t proj_smem[];
   __shared__ float red[kRowMaxWarps];
   __shared__ float s_c[kProjRows][kProjMaxRank];
@@ -554,49 +555,52 @@ __global__ void tb_lowrank_remove_kernel(const ProjArgs a) {
       }
     }
     __syncthreads();
-    // phase 2: x' = x - sum_j c_j U[:, j]
-    float acc[kProjRows][NV][8];
+    // phase 2: x' = x - sum_j c_j U[:, j], kProjGroup rows at a time (register budget), then
+    // round, store, and the optional fused final RMSNorm
+#pragma unroll 1
+    for (int g0 = 0; g0 < kProjRows; g0 += kProjGroup) {
+      float acc[kProjGroup][NV][8];
 #pragma unroll
-    for (int rr = 0; rr < kProjRows; ++rr)
+      for (int rr = 0; rr < kProjGroup; ++rr)
 #pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        const int vec = threadIdx.x + i * blockDim.x;
-        if (vec < nvec) unpack8(s_x[rr * nvec + vec], acc[rr][i]);
-      }
-    for (int j = 0; j < a.r; ++j) {
-      const int4* ur = reinterpret_cast<const int4*>(a.ut + static_cast<size_t>(j) * a.d);
+        for (int i = 0; i < NV; ++i) {
+          const int vec = threadIdx.x + i * blockDim.x;
+          if (vec < nvec) unpack8(s_x[(g0 + rr) * nvec + vec], acc[rr][i]);
+        }
+      for (int j = 0; j < a.r; ++j) {
+        const int4* ur = reinterpret_cast<const int4*>(a.ut + static_cast<size_t>(j) * a.d);
 #pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        const int vec = threadIdx.x + i * blockDim.x;
-        if (vec < nvec) {
-          float u[8];
-          unpack8(__ldg(ur + vec), u);
+        for (int i = 0; i < NV; ++i) {
+          const int vec = threadIdx.x + i * blockDim.x;
+          if (vec < nvec) {
+            float u[8];
+            unpack8(__ldg(ur + vec), u);
 #pragma unroll
-          for (int rr = 0; rr < kProjRows; ++rr) {
-            const float cj = -s_c[rr][j];
+            for (int rr = 0; rr < kProjGroup; ++rr) {
+              const float cj = -s_c[g0 + rr][j];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) acc[rr][i][e] = fmaf(cj, u[e], acc[rr][i][e]);
+              for (int e = 0; e < 8; ++e) acc[rr][i][e] = fmaf(cj, u[e], acc[rr][i][e]);
+            }
           }
         }
       }
-    }
-    // round, store, optional fused final RMSNorm
 #pragma unroll
-    for (int rr = 0; rr < kProjRows; ++rr) {
-      const int row = row0 + rr;
-      const bool valid = row < a.n_rows;  // uniform across the CTA
-      float xb[NV][8];
+      for (int rr = 0; rr < kProjGroup; ++rr) {
+        const int row = row0 + g0 + rr;
+        const bool valid = row < a.n_rows;  // uniform across the CTA
+        float xb[NV][8];
 #pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        const int vec = threadIdx.x + i * blockDim.x;
-        if (vec < nvec) {
-          const Bf16x8 p = pack8(acc[rr][i]);
-          if (valid && a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row) * a.d)[vec] = p;
-          unpack8(p, xb[i]);
+        for (int i = 0; i < NV; ++i) {
+          const int vec = threadIdx.x + i * blockDim.x;
+          if (vec < nvec) {
+            const Bf16x8 p = pack8(acc[rr][i]);
+            if (valid && a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row) * a.d)[vec] = p;
+            unpack8(p, xb[i]);
+          }
         }
+        if (valid && a.out_h)
+          rmsnorm_store<NV>(xb, a.w_norm, a.d, a.eps, a.out_h + static_cast<size_t>(row) * a.d, red);
       }
-      if (valid && a.out_h)
-        rmsnorm_store<NV>(xb, a.w_norm, a.d, a.eps, a.out_h + static_cast<size_t>(row) * a.d, red);
     }
   }
 }

@@ -262,6 +262,8 @@ def sae_ablate_decode(x: Optional[torch.Tensor], acts: SparseActs, sae: SaeWeigh
         _need(row_table, torch.int32, "row_table", 1)
     out_x = torch.empty(n, d, dtype=torch.bfloat16, device=dev) if want_x else None
     out_h = torch.empty(n, d, dtype=torch.bfloat16, device=dev) if want_h else None
+    if n == 0:
+        return out_x, out_h
     check(_lib.load().tb_sae_ablate_decode(
         _ptr(x), _ptr(acts.row_start), acts.cap, _ptr(acts.count), _ptr(acts.idx), _ptr(acts.val),
         _ptr(sae.w_dec), _ptr(sae.b_dec), _ptr(rank), _ptr(row_table), rank_rows, budget, imode,
@@ -282,6 +284,8 @@ def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.T
     ut = U.t().contiguous()
     out_x = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_x else None
     out_h = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_h else None
+    if n == 0:
+        return out_x, out_h
     check(_lib.load().tb_lowrank_remove(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(out_x),
                                         _ptr(out_h), _stream()), "tb_lowrank_remove")
     return out_x, out_h
@@ -292,6 +296,8 @@ def rmsnorm(x: torch.Tensor, w_norm: torch.Tensor, eps: float = GEMMA2_EPS) -> t
     _need(x, torch.bfloat16, "x", 2)
     _need(w_norm, torch.float32, "w_norm", 1)
     out = torch.empty_like(x)
+    if x.shape[0] == 0:
+        return out
     check(_lib.load().tb_rmsnorm(_ptr(x), _ptr(w_norm), eps, x.shape[0], x.shape[1], _ptr(out), _stream()),
           "tb_rmsnorm")
     return out
@@ -398,6 +404,8 @@ def lens_merge(p: LensPartials, finalize: bool = True):
                           secret_prob=torch.empty(n, dtype=torch.float32, device=dev),
                           top_prob=torch.empty(n, TB_TOPK, dtype=torch.float32, device=dev),
                           top_id=torch.empty(n, TB_TOPK, dtype=torch.int32, device=dev))
+        if n == 0:
+            return out
         check(lib.tb_lens_merge(_ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), p.n_parts, n, 1,
                                 None, None, None, None, None, _ptr(out.lse), _ptr(out.secret_prob),
                                 _ptr(out.top_prob), _ptr(out.top_id), _stream()), "tb_lens_merge")
@@ -407,6 +415,8 @@ def lens_merge(p: LensPartials, finalize: bool = True):
                      psec=torch.empty(1, n, dtype=torch.float32, device=dev),
                      ptv=torch.empty(1, n, TB_TOPK, dtype=torch.float32, device=dev),
                      pti=torch.empty(1, n, TB_TOPK, dtype=torch.int32, device=dev))
+    if n == 0:
+        return o
     check(lib.tb_lens_merge(_ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), p.n_parts, n, 0,
                             _ptr(o.pm), _ptr(o.ps), _ptr(o.psec), _ptr(o.ptv), _ptr(o.pti), None, None, None,
                             None, _stream()), "tb_lens_merge")

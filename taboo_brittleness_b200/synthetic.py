@@ -112,17 +112,18 @@ def make_secret_ids(n_prompts: int, rows_per_prompt: int, V: int = VOCAB, seed: 
 
 
 def plant_secret_direction(lens: SyntheticLens, x: torch.Tensor, secret_id: torch.Tensor,
-                           strength: float = 3.0) -> None:
-    """Make the secret token's unembedding row correlate with each row's normalised residual so
-    secret probabilities are not all ~1/V (gives the 1e-3 tolerance something to bite on).
-    In place on lens.W_U rows of the distinct secret ids; uses the first row of each id."""
+                           boost: float = 45.0) -> None:
+    """Make each secret token's unembedding row point along the normalised residual of the first
+    row that carries it, so that row's secret logit rises by ``boost`` and the other rows of the
+    prompt (which share the outlier dimensions, cosine ~0.3-0.5) get a partial boost: secret
+    probabilities then spread from ~1/V to ~1 instead of all being ~1/V, which gives the 1e-3
+    tolerance something to bite on. In place on lens.W_U."""
     xf = x.float()
-    h = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-6) * (1.0 + lens.w_norm)
+    h = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + 1e-6) * (1.0 + lens.w_norm.float())
     seen = set()
     for r, sid in enumerate(secret_id.tolist()):
         if sid in seen:
             continue
         seen.add(sid)
-        v = h[r] / h[r].norm()
-        row = lens.W_U[sid].float() + strength * lens.W_U[sid].float().norm() * v / (x.shape[1] ** 0.5) * 8.0
+        row = lens.W_U[sid].float() + (boost / float(h[r].norm()) ** 2) * h[r]
         lens.W_U[sid] = row.to(torch.bfloat16).to(lens.W_U.dtype)

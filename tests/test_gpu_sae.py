@@ -1,0 +1,177 @@
+"""K1 / a2 / K1b parity: JumpReLU encode to sparse lists, mean-over-tokens top-m targeting, and
+ablate + decode (both forms), against the oracle on the same bf16-rounded tensors.
+BASELINE.json tolerances: active sets and ablated indices bit-exact except documented
+near-threshold ties; reconstructed residuals within 2e-2 relative."""
+import pytest
+import torch
+
+from _common import BF16, cuda_bf16, oracle, sae_to_cuda, synthetic
+
+pytestmark = pytest.mark.gpu
+
+RESID_REL_TOL = 2e-2   # BASELINE.json north_star
+TIE_TAU = 2e-3         # |pre - theta| below this may flip (fp32 summation order on |pre| ~ 30)
+
+D, S, T, P = 3584, 16384, 64, 3
+
+
+@pytest.fixture(scope="module")
+def problem():
+    x = synthetic.make_residuals(P, T, D, seed=1234)
+    sae = synthetic.make_sae(D, S, seed=42)
+    pre = x @ sae.W_enc + sae.b_enc
+    acts = oracle.jumprelu_encode(x, sae.W_enc, sae.b_enc, sae.threshold)
+    return {"x": x, "sae": sae, "pre": pre, "acts": acts}
+
+
+@pytest.fixture(scope="module")
+def encoded(cuda_lib, problem):
+    from taboo_brittleness_b200 import ops
+    w = sae_to_cuda(problem["sae"])
+    xs = cuda_bf16(problem["x"])
+    acts = ops.sae_encode(xs, w, cap=128)
+    torch.cuda.synchronize()
+    return {"w": w, "x": xs, "acts": acts}
+
+
+def test_encode_active_sets_and_values(problem, encoded):
+    sp = encoded["acts"]
+    ref = problem["acts"]
+    dense = sp.to_dense().cpu()
+    # <bos> rows have thousands of active latents: the CSR re-pass must have kicked in
+    assert sp.row_start is not None and int(sp.count.max()) > 128
+    mism = (dense > 0) != (ref > 0)
+    near = (problem["pre"] - problem["sae"].threshold).abs() < TIE_TAU * problem["pre"].abs().clamp_min(1.0)
+    assert not (mism & ~near).any(), "active set differs away from the threshold"
+    assert mism.sum().item() <= 1e-5 * mism.numel()
+    both = (dense > 0) & (ref > 0)
+    # fp32 accumulation-order noise scales with the row: |pre| <~ |x|_2 (W_enc columns ~ unit norm)
+    tol = (4e-6 * problem["x"].norm(dim=1, keepdim=True)).expand_as(ref)
+    assert ((dense - ref).abs()[both] <= tol[both] + 2e-5 * ref.abs()[both]).all()
+    # counts are the true number of active latents; lists are in increasing latent order
+    assert torch.equal(sp.count.cpu().long(), (dense > 0).sum(1))
+    c = sp.count.cpu().tolist()
+    rs = sp.row_start.cpu().tolist()
+    idx = sp.idx.cpu()
+    for r in (0, 1, T, 2 * T + 5):
+        row = idx[rs[r]:rs[r] + c[r]]
+        assert (row[1:] > row[:-1]).all()
+    # typical rows sit near the calibrated L0
+    typical = torch.tensor([c[r] for r in range(P * T) if r % T != 0], dtype=torch.float32)
+    assert 40 < typical.mean().item() < 120
+
+
+def test_encode_fixed_stride_without_overflow(cuda_lib, problem, encoded):
+    from taboo_brittleness_b200 import ops
+    rows = [r for r in range(P * T) if r % T != 0][:100]
+    xs = encoded["x"][rows].contiguous()
+    sp = ops.sae_encode(xs, encoded["w"], cap=256)
+    assert sp.row_start is None
+    assert torch.equal(sp.to_dense().cpu(), encoded["acts"].to_dense().cpu()[rows])
+
+
+def test_encode_count_only_and_fused_mask(cuda_lib, problem, encoded):
+    from taboo_brittleness_b200 import ops
+    cnt = ops.sae_encode_raw(encoded["x"], encoded["w"])
+    assert torch.equal(cnt, encoded["acts"].count)
+    # random-control mask fused in the encode epilogue == masking afterwards
+    ridx = oracle.random_latents(S, seed=3, m=1024)
+    rank = ops.rank_table_from_indices(ridx, S).cuda()
+    for budget in (1, 64, 1024):
+        sp = ops.sae_encode(encoded["x"], encoded["w"], cap=128, rank=rank, rank_rows=0, budget=budget)
+        ref = encoded["acts"].to_dense().clone()
+        ref[:, ridx[:budget].cuda()] = 0
+        assert torch.equal(sp.to_dense(), ref)
+
+
+def test_latent_mean_and_topm(problem, encoded):
+    from taboo_brittleness_b200 import ops
+    mean = ops.latent_mean(encoded["acts"], rows_per_prompt=T)
+    # the reduction itself: against torch.mean of the kernel's own activations (tight) ...
+    own = encoded["acts"].to_dense().cpu().view(P, T, S).mean(1)
+    assert torch.allclose(mean.cpu(), own, rtol=2e-6, atol=1e-6)
+    # ... and end to end against the oracle's activations (encode noise on the <bos> rows included)
+    # (latents whose active set flipped at the threshold in some row of the prompt are excluded:
+    #  one flip moves the mean by theta / T; those flips are pinned in the encode test)
+    ref_mean = problem["acts"].view(P, T, S).mean(1)
+    dense = encoded["acts"].to_dense().cpu()
+    flipped = ((dense > 0) != (problem["acts"] > 0)).view(P, T, S).any(1)
+    assert flipped.sum().item() <= 1e-4 * flipped.numel()
+    err = (mean.cpu() - ref_mean).abs()
+    assert (err[~flipped] <= 1e-4 * ref_mean.abs()[~flipped] + 2e-3).all()
+    m = 1024
+    idx, val, rank = ops.topm_select(mean, m)
+    torch.cuda.synchronize()
+    idx, val, rank, mean_c = idx.cpu().long(), val.cpu(), rank.cpu().to(torch.int32), mean.cpu()
+    for p in range(P):
+        tv, ti = torch.topk(mean_c[p], m)
+        assert torch.equal(val[p], tv), "values must match torch.topk on the same input bit for bit"
+        assert (val[p][:-1] >= val[p][1:]).all()
+        # ids agree wherever the value is not tied with a neighbour
+        untied = torch.ones(m, dtype=torch.bool)
+        untied[1:] &= tv[1:] != tv[:-1]
+        untied[:-1] &= tv[:-1] != tv[1:]
+        assert torch.equal(idx[p][untied], ti[untied])
+        assert torch.equal(mean_c[p][idx[p]], val[p])
+        assert len(set(idx[p].tolist())) == m
+        # rank table: position of each selected latent, 0xFFFF elsewhere
+        assert torch.equal(rank[p][idx[p]], torch.arange(m, dtype=torch.int32))
+        assert (rank[p] != 0xFFFF).sum().item() == m
+    # against the oracle's own targeting (02:70-73) for a small budget: identical sets
+    for p in range(P):
+        _, oi = oracle.top_latents_of_mean(problem["acts"][p * T:(p + 1) * T], 10)
+        assert set(oi.tolist()) == set(idx[p][:10].tolist())
+
+
+def test_latent_mean_ragged_segments(cuda_lib, problem, encoded):
+    from taboo_brittleness_b200 import ops
+    seg = torch.tensor([3, 3, 20, 64, 190], dtype=torch.int64)   # empty, short, long windows
+    mean = ops.latent_mean(encoded["acts"], seg=seg.cuda()).cpu()
+    own = encoded["acts"].to_dense().cpu()
+    for p in range(4):
+        a = own[seg[p]:seg[p + 1]]
+        ref = a.mean(0) if a.shape[0] else torch.zeros(S)
+        assert torch.allclose(mean[p], ref, rtol=2e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("mode", ["error", "plain"])
+@pytest.mark.parametrize("budget", [1, 16, 1024])
+def test_ablate_decode_targeted(problem, encoded, mode, budget):
+    from taboo_brittleness_b200 import ops
+    sae = problem["sae"]
+    mean = ops.latent_mean(encoded["acts"], rows_per_prompt=T)
+    idx, _, rank = ops.topm_select(mean, 1024)
+    w_norm = synthetic.make_lens(D, 8, seed=42).w_norm
+    out_x, out_h = ops.sae_ablate_decode(encoded["x"], encoded["acts"], encoded["w"], rank, budget, mode=mode,
+                                         rank_rows=T, w_norm=w_norm.cuda(), want_x=True, want_h=True)
+    torch.cuda.synchronize()
+    got = out_x.float().cpu()
+    # The decode is checked on the kernel's own active sets: JumpReLU jumps by ~theta at the
+    # threshold, so the handful of documented near-threshold flips of the encode (pinned in
+    # test_encode_active_sets_and_values) would otherwise show up here as O(theta) residual changes.
+    acts = encoded["acts"].to_dense().cpu()
+    for p in range(P):
+        sl = slice(p * T, (p + 1) * T)
+        ref32 = oracle.ablate_decode(problem["x"][sl], acts[sl], idx[p, :budget].cpu(), sae.W_dec,
+                                     sae.b_dec, mode)
+        rel = (got[sl] - ref32).norm(dim=1) / ref32.norm(dim=1).clamp_min(1e-6)
+        assert rel.max().item() <= RESID_REL_TOL
+        # elementwise: one bf16 rounding of the fp32 result (plus summation-order noise)
+        assert ((got[sl] - ref32).abs() <= 0.0079 * ref32.abs() + 2e-3 * ref32.abs().max()).all()
+    # fused RMSNorm output == standalone norm of the rounded residual, bit for bit
+    assert torch.equal(out_h, ops.rmsnorm(out_x, w_norm.cuda()))
+
+
+def test_ablate_decode_random_control_and_zero_budget(problem, encoded):
+    from taboo_brittleness_b200 import ops
+    sae = problem["sae"]
+    ridx = oracle.random_latents(S, seed=11, m=1024)
+    rank = ops.rank_table_from_indices(ridx, S).cuda()
+    out_x, _ = ops.sae_ablate_decode(encoded["x"], encoded["acts"], encoded["w"], rank, 256, mode="error")
+    ref = oracle.ablate_decode(problem["x"], encoded["acts"].to_dense().cpu(), ridx[:256], sae.W_dec, sae.b_dec,
+                               "error")
+    rel = (out_x.float().cpu() - ref).norm(dim=1) / ref.norm(dim=1)
+    assert rel.max().item() <= RESID_REL_TOL
+    # budget 0 ablates nothing: the error-term form returns x unchanged
+    same, _ = ops.sae_ablate_decode(encoded["x"], encoded["acts"], encoded["w"], rank, 0, mode="error")
+    assert torch.equal(same, encoded["x"])

@@ -1,0 +1,87 @@
+"""Host-side mirror of the reference surface (feature_map, metrics, models helpers) against the
+golden outputs of the reference's own code. CPU only."""
+import json
+import os
+
+import pytest
+
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+HOST = json.load(open(os.path.join(G, "host_logic.json")))
+REAL = json.load(open(os.path.join(G, "real_ll_topk.json")))
+
+
+def test_tables_equal_reference():
+    from taboo_brittleness_b200 import feature_map, metrics
+    assert feature_map.feature_map == HOST["feature_map"]
+    assert list(feature_map.feature_map) == list(HOST["feature_map"])
+    assert metrics.WORD_PLURALS == HOST["WORD_PLURALS"]
+
+
+def test_latents_to_word_guesses():
+    from taboo_brittleness_b200.feature_map import latents_to_word_guesses
+    for c in HOST["latent_cases"]:
+        assert latents_to_word_guesses(c["in"]) == c["out"]
+
+
+def test_metrics_known_answers():
+    from taboo_brittleness_b200 import metrics
+    mc = HOST["metrics_case"]
+    got = metrics.calculate_metrics(mc["predictions"], mc["targets"],
+                                    {w: [w, w + "s"] for w in mc["targets"]})
+    for k, v in mc["expected"].items():
+        for kk, vv in v.items():
+            assert float(got[k][kk]) == pytest.approx(vv)
+    # default word_plurals (None) gives the same on these words
+    got2 = metrics.calculate_metrics(mc["predictions"], mc["targets"])
+    assert float(got2["overall"]["prompt_accuracy"]) == pytest.approx(mc["committed_overall"]["prompt_accuracy"])
+    for c in HOST["metric_edge_cases"]:
+        v = set(c["valid"])
+        assert metrics.prompt_accuracy_at_k(c["guesses"], v) == pytest.approx(c["prompt_accuracy"])
+        assert metrics.any_pass_at_k(c["guesses"], v) == c["any_pass"]
+        assert metrics.global_majority_vote_at_k(c["guesses"], v) == c["majority"]
+
+
+def test_id_level_metrics_reproduce_ll_topk_ship_json():
+    """results/ll_topk_ship.json: 8 of 10 id lists contain 7509 (' ship') -> pass@k 0.8; the most
+    common id overall is not the secret -> majority@k 0."""
+    from taboo_brittleness_b200 import metrics
+    ll = HOST["ll_topk_ship"]
+    secret = [ll["secret_id"]] if ll["secret_id"] is not None else [7509]
+    assert metrics.pass_at_k_ids(ll["guesses_by_prompt"], secret) == pytest.approx(ll["pass@k"])
+    assert metrics.majority_at_k_ids(ll["guesses_by_prompt"], secret) == ll["majority@k"]
+    assert metrics.any_pass_ids(ll["guesses_by_prompt"], secret) == 1.0
+    assert metrics.pass_at_k_ids([], secret) == 0.0
+
+
+def test_find_model_response_start():
+    from taboo_brittleness_b200.models import find_model_response_start
+    for rec in REAL["fixtures"].values():
+        assert find_model_response_start(rec["input_words"]) == rec["start"]
+    assert find_model_response_start(["no", "markers"]) == 0
+
+
+def test_pick_chunks_is_valid():
+    from taboo_brittleness_b200 import ops
+    for n, V, pair in [(128, 256000, False), (37888, 256000, True), (524288, 256000, True), (1, 256, False),
+                       (2048, 32000, True), (300, 1000, False)]:
+        c = ops.pick_chunks(n, V, 148, pair)
+        tiles = -(-V // 256)
+        tpc = -(-tiles // c)
+        assert 1 <= c <= tiles and -(-tiles // tpc) == c
+
+
+def test_rank_table_from_indices():
+    import torch
+    from taboo_brittleness_b200 import ops
+    idx = torch.tensor([[5, 2, 9], [0, 1, 2]])
+    t = ops.rank_table_from_indices(idx, 12).to(torch.int32)
+    assert t[0, 5] == 0 and t[0, 2] == 1 and t[0, 9] == 2 and t[1, 0] == 0
+    assert (t == 0xFFFF).sum().item() == 24 - 6
+
+
+def test_ops_refuse_cpu_tensors_and_missing_gpu():
+    import torch
+    from taboo_brittleness_b200 import ops
+    from taboo_brittleness_b200._lib import TabooKernelError
+    with pytest.raises(TabooKernelError):
+        ops.rmsnorm(torch.zeros(2, 8, dtype=torch.bfloat16), torch.zeros(8))
