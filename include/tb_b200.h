@@ -130,6 +130,37 @@ int tb_lens_merge(const float* pm, const float* ps, const float* psec, const flo
                   float* os, float* osec, float* otv, int32_t* oti, float* lse,
                   float* secret_prob, float* top_prob, int32_t* top_id, void* stream);
 
+/* ---- lens readout without caller scratch -------------------------------------------------
+ * (No counterpart in the reference: this entry point exists for the way the library is
+ * deployed, not for anything the reference computes.)
+ * Same readout as tb_lens_partials followed by tb_lens_merge(finalize), but the per-(row,
+ * chunk) partials live in a fixed block inside the library instead of in memory the caller
+ * provides. It is meant for callers that hold nothing but their input and output buffers and
+ * have no way to obtain more: a worker that was handed pre-sized tensors by a serving runtime
+ * whose allocator already owns all of HBM, a plug-in written against this header alone (no
+ * torch, no allocator of its own), or a latency-critical loop that must not enter
+ * cudaMalloc/cudaFree because those serialise the device. The function itself performs no
+ * allocation of any kind.
+ *   - limit: n_rows * n_chunks <= TB_STATIC_LENS_MAX_SLOTS (65536); larger requests are
+ *     rejected with TB_ERR_INVALID and nothing is launched. The block is 6,029,312 bytes
+ *     (65536 x 23 words) and is resident on every GPU that loads the library until the
+ *     process exits.
+ *   - the first call on each device resolves the block's device address (one
+ *     cudaGetSymbolAddress, with that device current). Make that first call during start-up,
+ *     before any stream capture is begun.
+ *   - all calls on a device share the one block. Calls whose kernels may overlap on the GPU
+ *     (different streams, different host threads) race on it: serialise them, or give all
+ *     but one of them caller scratch through tb_lens_partials. The block keeps whatever the
+ *     last call left; that is harmless here because every slot read by the merge is first
+ *     written by the lens kernel of the same call.
+ * Arguments as tb_lens_partials / tb_lens_merge; secret_prob may be NULL.
+ */
+#define TB_STATIC_LENS_MAX_SLOTS 65536
+int tb_logit_lens_static(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
+                         int vocab_offset, float softcap, const int32_t* secret_id, int n_chunks,
+                         int cta_pair, float* lse, float* secret_prob, float* top_prob,
+                         int32_t* top_id, void* stream);
+
 /* ---- validation only: D = A B^T through the same TMA/tcgen05 main loop, fp32 out --------- */
 int tb_gemm_bf16_nt(const void* a_bf16, const void* b_bf16, int64_t M, int N, int K,
                     int n_chunks, int cta_pair, float* out, void* stream);

@@ -20,6 +20,7 @@ TB_ERR_CUDA = -3
 TB_TOPK = 10
 TB_TOPM_MAX = 1024
 TB_RANK_NONE = 0xFFFF
+TB_STATIC_LENS_MAX_SLOTS = 65536
 
 
 class TabooKernelError(RuntimeError):
@@ -50,6 +51,8 @@ SIGNATURES = {
     "tb_lens_merge": (c_int, [_P, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P,
                               _P, _P, _P]),
     "tb_gemm_bf16_nt": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_int, _P, _P]),
+    "tb_logit_lens_static": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,
+                                     _P, _P, _P, _P, _P]),
 }
 
 _lib = None

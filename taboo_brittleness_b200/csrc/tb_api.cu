@@ -6,6 +6,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "../../include/tb_b200.h"
 #include "tb_epilogues.cuh"
 #include "tb_gemm.cuh"
@@ -165,6 +167,43 @@ int row_launch_shape(int d, int* nv, int* threads) {
   t = (t + 31) / 32 * 32;
   if (t < 64) t = 64;
   *threads = t;
+  return TB_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// Built-in scratch for tb_logit_lens_static: TB_STATIC_LENS_MAX_SLOTS (row, chunk) partials of
+// 23 words each (max, sumexp, secret logit, 10 values, 10 ids) = 6,029,312 bytes that are part
+// of the library image on every GPU that loads it, for the life of the process.
+// In host code `g_lens_static_scratch` is only a handle for the symbol -- not a device address.
+// The address a kernel may use is fetched once per device with cudaGetSymbolAddress (below),
+// with that device current.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_lens_static_scratch[static_cast<size_t>(TB_STATIC_LENS_MAX_SLOTS) * 23];
+
+namespace {
+
+std::mutex g_static_mu;
+float* g_static_ptr[64];
+bool g_static_ready[64];
+
+// device address of the built-in scratch on the CURRENT device (resolved on first use)
+int static_scratch_address(float** out) {
+  int dev = 0;
+  TB_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(TB_ERR_INVALID, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ready[dev]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_lens_static_scratch);
+    if (e != cudaSuccess || p == nullptr)
+      return fail(TB_ERR_CUDA, "cudaGetSymbolAddress(g_lens_static_scratch) failed on device %d: %s", dev,
+                  cudaGetErrorString(e));
+    g_static_ptr[dev] = static_cast<float*>(p);
+    g_static_ready[dev] = true;
+  }
+  *out = g_static_ptr[dev];
   return TB_OK;
 }
 
@@ -426,6 +465,42 @@ int tb_lens_merge(const float* pm, const float* ps, const float* psec, const flo
   tb::tb_lens_merge_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(a);
   TB_CUDA(cudaGetLastError());
   return TB_OK;
+}
+
+int tb_logit_lens_static(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
+                         float softcap, const int32_t* secret_id, int n_chunks, int cta_pair, float* lse,
+                         float* secret_prob, float* top_prob, int32_t* top_id, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(h, w_u, n_rows, V, d);
+  if (rc != TB_OK) return rc;
+  if (!lse || !top_prob || !top_id) return fail(TB_ERR_INVALID, "lse, top_prob and top_id are required");
+  const tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, cta_pair ? 2 : 1);
+  if (g.n_chunks != n_chunks)
+    return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)", n_chunks,
+                g.n_tiles, g.n_chunks);
+  const int64_t slots = n_rows * static_cast<int64_t>(n_chunks);
+  if (slots > TB_STATIC_LENS_MAX_SLOTS)
+    return fail(TB_ERR_INVALID,
+                "n_rows * n_chunks = %lld exceeds the built-in scratch of %d (row, chunk) slots; split the rows "
+                "over several calls or use tb_lens_partials + tb_lens_merge with your own scratch",
+                static_cast<long long>(slots), TB_STATIC_LENS_MAX_SLOTS);
+  float* base = nullptr;
+  rc = static_scratch_address(&base);
+  if (rc != TB_OK) return rc;
+  // carve the five partial arrays out of the built-in block; every slot that K4 reads is written
+  // by K3 first, so nothing left over from an earlier call is ever observed
+  float* pm = base;
+  float* ps = pm + slots;
+  float* psec = ps + slots;
+  float* ptv = psec + slots;
+  int32_t* pti = reinterpret_cast<int32_t*>(ptv + slots * TB_TOPK);
+  rc = tb_lens_partials(h, w_u, n_rows, d, V, vocab_offset, softcap, secret_id, n_chunks, cta_pair, pm, ps, psec,
+                        ptv, pti, stream);
+  if (rc != TB_OK) return rc;
+  return tb_lens_merge(pm, ps, psec, ptv, pti, n_chunks, n_rows, 1, nullptr, nullptr, nullptr, nullptr, nullptr,
+                       lse, secret_prob, top_prob, top_id, stream);
 }
 
 }  // extern "C"
