@@ -298,8 +298,8 @@ def main():
     ap.add_argument("--steps", type=int, default=2)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
-    ap.add_argument("--prompts", type=int, default=1184, help="prompts per GPU per step (x128 tokens)")
-    ap.add_argument("--batch-prompts", type=int, default=592, help="prompts per sub-batch (one sweep each)")
+    ap.add_argument("--prompts", type=int, default=4096, help="prompts per GPU per step (x128 tokens); configs[1] = 4096")
+    ap.add_argument("--batch-prompts", type=int, default=4096, help="prompts per sub-batch (one sweep each)")
     ap.add_argument("--chunks", type=int, default=0, help="vocab chunks per lens launch (0 = auto)")
     ap.add_argument("--encode-cap", type=int, default=128)
     ap.add_argument("--no-pair", action="store_true", help="use the 1-SM (cta_group::1) lens kernel")

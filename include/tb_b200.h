@@ -130,6 +130,30 @@ int tb_lens_merge(const float* pm, const float* ps, const float* psec, const flo
                   float* os, float* osec, float* otv, int32_t* oti, float* lse,
                   float* secret_prob, float* top_prob, int32_t* top_id, void* stream);
 
+/* ---- K5: LL-Top-k ------------------------------------------------------------------------
+ * Replaces aggregate_response_logits + torch.topk, src/01_reproduce_logit_lens.py:35-71 and
+ * :147-149: per prompt, acc[v] = sum over response positions t of softmax(logits)[t, v] with
+ * the current token's id and the previous token's id zeroed at each position; top-k of acc.
+ * Second sweep of the lens GEMM with lse[t] from K3 + K4 (same h, W_U shard, softcap): a
+ * thread owns a vocabulary id and sums over a prompt's positions, no [T, V] tensor exists.
+ * Row layout: prompt p owns row slots [128 p, 128 p + 128) of h; slots without a token
+ * carry lse = +inf (prompts longer than 128 positions are not supported by this kernel).
+ *   lse     : f32 [n_rows]                      cur_id / prev_id : i32 [n_rows] global vocab ids
+ *             zeroed at that position (-1 or out of range: nothing), both nullable
+ *   part_val: f32 [n_parts, n_prompts, 10]      part_id : i32 [n_parts, n_prompts, 10]
+ *             n_prompts = ceil(n_rows / 128), n_parts = n_chunks * (cta_pair ? 2 : 1); sorted
+ * A chunk may span at most 65536 vocabulary ids (n_chunks >= 4 for V = 256000).
+ */
+int tb_ll_topk_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
+                        int vocab_offset, float softcap, const float* lse, const int32_t* cur_id,
+                        const int32_t* prev_id, int n_chunks, int cta_pair, float* part_val,
+                        int32_t* part_id, void* stream);
+/* merge n_parts sorted lists per prompt -> the k <= 10 best (sum, id), descending; id -1 and
+ * sum -inf where fewer exist. The reference returns no guesses when acc sums to zero
+ * (01:148): that is out_val[p][0] <= 0. */
+int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts, int64_t n_prompts,
+                     int k, float* out_val, int32_t* out_id, void* stream);
+
 /* ---- lens readout without caller scratch -------------------------------------------------
  * (No counterpart in the reference: this entry point exists for the way the library is
  * deployed, not for anything the reference computes.)

@@ -51,6 +51,9 @@ SIGNATURES = {
     "tb_lens_merge": (c_int, [_P, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P,
                               _P, _P, _P]),
     "tb_gemm_bf16_nt": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_int, _P, _P]),
+    "tb_ll_topk_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, c_int, c_int,
+                                    _P, _P, _P]),
+    "tb_ll_topk_merge": (c_int, [_P, _P, c_int, c_int64, c_int, _P, _P, _P]),
     "tb_logit_lens_static": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,
                                      _P, _P, _P, _P, _P]),
 }

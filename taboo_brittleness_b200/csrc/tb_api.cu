@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -110,6 +111,22 @@ int check_gemm_operands(const void* a, const void* b, int64_t M, int N, int K) {
   return TB_OK;
 }
 
+// L2 policy of the two operand streams. The stationary block is re-read once per swept tile
+// and should stay resident; swept tiles are read by the few CTAs that share a chunk and are
+// dead afterwards. TB_L2_POLICY=<stationary><swept> with n / f / l (normal, evict-first,
+// evict-last) overrides the default for experiments.
+void set_policies(tb::GemmArgs* g, bool stationary_is_a) {
+  unsigned long long pol[2];
+  const char* e = getenv("TB_L2_POLICY");
+  const char* d = (e && strlen(e) == 2) ? e : "nn";
+  for (int i = 0; i < 2; ++i)
+    pol[i] = d[i] == 'l' ? tb::kPolicyEvictLast : d[i] == 'f' ? tb::kPolicyEvictFirst : tb::kPolicyEvictNormal;
+  const char* dbg = getenv("TB_DEBUG_SKIP");
+  g->debug_skip = dbg ? atoi(dbg) : 0;
+  g->policy_a = stationary_is_a ? pol[0] : pol[1];
+  g->policy_b = stationary_is_a ? pol[1] : pol[0];
+}
+
 tb::GemmArgs make_args(int64_t M, int N, int K, int n_chunks, int group) {
   tb::GemmArgs g;
   g.M = static_cast<int>(M);
@@ -122,6 +139,25 @@ tb::GemmArgs make_args(int64_t M, int N, int K, int n_chunks, int group) {
   g.n_chunks = (g.n_tiles + g.tiles_per_chunk - 1) / g.tiles_per_chunk;  // no empty chunks
   g.m_blocks = static_cast<int>((M + tb::kBlockM * group - 1) / (tb::kBlockM * group));
   g.total_units = g.m_blocks * g.n_chunks;
+  set_policies(&g, /*stationary_is_a=*/true);
+  return g;
+}
+
+// sweep-A orientation (tb_gemm.cuh): A [M, K] is swept in tiles of 128 * group rows, B [N, K] is
+// cut into stationary blocks of 256 rows
+tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group) {
+  tb::GemmArgs g;
+  g.M = M;
+  g.N = static_cast<int>(N);
+  g.K = K;
+  g.n_tiles = (M + tb::kBlockM * group - 1) / (tb::kBlockM * group);
+  if (n_chunks < 1) n_chunks = 1;
+  if (n_chunks > g.n_tiles) n_chunks = g.n_tiles;
+  g.tiles_per_chunk = (g.n_tiles + n_chunks - 1) / n_chunks;
+  g.n_chunks = (g.n_tiles + g.tiles_per_chunk - 1) / g.tiles_per_chunk;
+  g.m_blocks = static_cast<int>((N + tb::kBlockN - 1) / tb::kBlockN);
+  g.total_units = g.m_blocks * g.n_chunks;
+  set_policies(&g, /*stationary_is_a=*/false);
   return g;
 }
 
@@ -135,14 +171,15 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
   rc = make_tmap(&tmB, b, g.N, g.K, Cfg::kBRows);
   if (rc != TB_OK) return rc;
   auto kern = tb::tb_umma_gemm_kernel<Epi, G>;
-  TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+  constexpr int kSmem = Cfg::kSmemBytes + Epi::kExtraSmem;
+  TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   int clusters = sms / G;
   if (clusters > g.total_units) clusters = g.total_units;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
   cfg.gridDim = dim3(static_cast<unsigned>(clusters * G), 1, 1);
   cfg.blockDim = dim3(tb::kGemmThreads, 1, 1);
-  cfg.dynamicSmemBytes = Cfg::kSmemBytes;
+  cfg.dynamicSmemBytes = kSmem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -463,6 +500,56 @@ int tb_lens_merge(const float* pm, const float* ps, const float* psec, const flo
   a.lse = lse; a.secret_prob = secret_prob; a.top_prob = top_prob; a.top_id = top_id;
   const unsigned grid = static_cast<unsigned>((n_rows + 127) / 128);
   tb::tb_lens_merge_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_ll_topk_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
+                        float softcap, const float* lse, const int32_t* cur_id, const int32_t* prev_id,
+                        int n_chunks, int cta_pair, float* part_val, int32_t* part_id, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(w_u, h, V, static_cast<int>(n_rows), d);
+  if (rc != TB_OK) return rc;
+  if (n_rows > 0x7fffff00ll) return fail(TB_ERR_INVALID, "too many rows (%lld)", (long long)n_rows);
+  if (!lse || !part_val || !part_id) return fail(TB_ERR_INVALID, "null lse / part_val / part_id");
+  if (prev_id && !cur_id) return fail(TB_ERR_INVALID, "prev_id given without cur_id");
+  const int G = cta_pair ? 2 : 1;
+  tb::GemmArgs g = make_args_sweep_a(V, n_rows, d, n_chunks, G);
+  if (g.n_chunks != n_chunks)
+    return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)",
+                n_chunks, g.n_tiles, g.n_chunks);
+  if (g.tiles_per_chunk * tb::kBlockM * G > tb::ColSumEpi::kMaxChunkIds)
+    return fail(TB_ERR_INVALID, "a chunk spans %d vocabulary ids, more than the %d the mask bitmap holds: use "
+                "n_chunks >= %d", g.tiles_per_chunk * tb::kBlockM * G, tb::ColSumEpi::kMaxChunkIds,
+                (V + tb::ColSumEpi::kMaxChunkIds - 1) / tb::ColSumEpi::kMaxChunkIds);
+  tb::ColSumEpi::Params ep;
+  ep.lse = lse;
+  ep.cur_id = cur_id;
+  ep.prev_id = prev_id;
+  ep.vocab_offset = vocab_offset;
+  ep.softcap = softcap;
+  ep.n_prompts = static_cast<int>((n_rows + tb::ColSumEpi::kSlots - 1) / tb::ColSumEpi::kSlots);
+  ep.out_val = part_val;
+  ep.out_id = part_id;
+  ep.group = G;
+  if (G == 2) return launch_gemm<tb::ColSumEpi, 2>(w_u, h, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  return launch_gemm<tb::ColSumEpi, 1>(w_u, h, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts, int64_t n_prompts, int k,
+                     float* out_val, int32_t* out_id, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!part_val || !part_id || !out_val || !out_id) return fail(TB_ERR_INVALID, "null pointer");
+  if (n_parts < 1) return fail(TB_ERR_INVALID, "n_parts=%d", n_parts);
+  if (k < 1 || k > TB_TOPK) return fail(TB_ERR_INVALID, "k=%d outside [1, %d]", k, TB_TOPK);
+  if (n_prompts == 0) return TB_OK;
+  const unsigned grid = static_cast<unsigned>((n_prompts + 127) / 128);
+  tb::tb_ll_topk_merge_kernel<<<grid, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      part_val, part_id, n_parts, static_cast<int>(n_prompts), k, out_val, out_id);
   TB_CUDA(cudaGetLastError());
   return TB_OK;
 }

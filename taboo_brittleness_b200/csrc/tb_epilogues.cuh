@@ -34,6 +34,8 @@ __device__ __forceinline__ float tanh_2mufu(float y) {
 // probability gather), models.py:147 (per-row max); softcap per installed Gemma2ForCausalLM.
 // =========================================================================================
 struct LensEpi {
+  static constexpr bool kSweepA = false;
+  static constexpr int kExtraSmem = 0;
   struct Params {
     const int32_t* secret_id;  // [M] global vocab id per row, or nullptr
     int vocab_offset;          // global id of this shard's column 0
@@ -153,6 +155,8 @@ struct LensEpi {
 // whose rank is below the budget right here (random-control / second-pass masking).
 // =========================================================================================
 struct EncodeEpi {
+  static constexpr bool kSweepA = false;
+  static constexpr int kExtraSmem = 0;
   struct Params {
     const float* b_enc;        // [S]
     const float* theta;        // [S]
@@ -240,10 +244,211 @@ struct EncodeEpi {
 };
 
 // =========================================================================================
+// K5: LL-Top-k (src/01_reproduce_logit_lens.py:35-71, 147-149). For every prompt, the k largest
+// entries of   acc[v] = sum_t p[t, v] * [v != cur_id[t]] * [v != prev_id[t]]   over the prompt's
+// response positions t, p = softmax of the (soft-capped) lens logits.
+// The sum runs over rows and needs each row's normaliser, so this is a second sweep of the same
+// GEMM with the operands' roles swapped (sweep-A): A = W_U, so a TMEM lane -- an epilogue thread
+// -- is one vocabulary id; B = a block of 256 rows of h = two prompts of 128 row slots, so a
+// thread sees all of a prompt's positions as 128 consecutive TMEM columns and sums
+// exp(logit - lse[t]) over them in registers, with no cross-thread reduction. lse comes from
+// the first sweep (K3 + K4). Row slots that hold no token carry lse = +inf (weight 0).
+// Each thread keeps the 10 best (sum, id) per prompt over its chunk of the vocabulary; the 128
+// threads of a CTA merge at the end of the unit -> one sorted list per (part, prompt).
+// The two masked ids per position are rare events: a per-unit bitmap over the chunk's vocabulary
+// range (8 KB per prompt in shared memory) tells a thread whether its id is masked anywhere in
+// the prompt; only then does it take the per-element compare path.
+// =========================================================================================
+struct ColSumEpi {
+  static constexpr bool kSweepA = true;
+  static constexpr int kSlots = 128;              // row slots per prompt (= TMEM columns per prompt)
+  static constexpr int kMaxChunkIds = 65536;      // bitmap bits per prompt
+  static constexpr int kOffNl = 0;                               // float[256]  -lse * log2(e)
+  static constexpr int kOffCur = kOffNl + 256 * 4;               // int32[256]
+  static constexpr int kOffPrev = kOffCur + 256 * 4;             // int32[256]
+  static constexpr int kOffBest = kOffPrev + 256 * 4;            // (float, int32)[4]
+  static constexpr int kOffBitmap = kOffBest + 64;               // uint32[2][2048]
+  static constexpr int kExtraSmem = kOffBitmap + 2 * (kMaxChunkIds / 8);
+
+  struct Params {
+    const float* lse;        // [N] logsumexp per row slot (+inf: empty slot)
+    const int32_t* cur_id;   // [N] id zeroed at that position, or nullptr (global vocab ids)
+    const int32_t* prev_id;  // [N] second id zeroed at that position (-1: none), or nullptr
+    int vocab_offset;        // global id of this shard's row 0 of W_U
+    float softcap;
+    int n_prompts;           // ceil(N / 128)
+    float* out_val;          // [parts, n_prompts, 10], parts = n_chunks * kCtaGroup
+    int32_t* out_id;         // [parts, n_prompts, 10] global ids, -1 = none
+    int group;               // kCtaGroup
+  };
+  struct State {
+    float tv[2][kTopK];
+    int32_t ti[2][kTopK];
+  };
+
+  __device__ __forceinline__ static void begin_unit_sw(State& st, const Params& p, const GemmArgs& g,
+                                                       const SweepCtx& c) {
+    float* s_nl = reinterpret_cast<float*>(c.extra + kOffNl);
+    int32_t* s_cur = reinterpret_cast<int32_t*>(c.extra + kOffCur);
+    int32_t* s_prev = reinterpret_cast<int32_t*>(c.extra + kOffPrev);
+    uint32_t* s_bm = reinterpret_cast<uint32_t*>(c.extra + kOffBitmap);
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int slot = q * kSlots + c.tid;
+      const int64_t r = static_cast<int64_t>(c.blk) * 256 + slot;
+      const bool valid = r < g.N;
+      s_nl[slot] = valid ? -p.lse[r] * kLog2e : -CUDART_INF_F;
+      s_cur[slot] = (valid && p.cur_id) ? p.cur_id[r] : -1;
+      s_prev[slot] = (valid && p.prev_id) ? p.prev_id[r] : -1;
+    }
+    uint4* bm4 = reinterpret_cast<uint4*>(s_bm);
+    for (int i = c.tid; i < 2 * (kMaxChunkIds / 128); i += 128) bm4[i] = make_uint4(0, 0, 0, 0);
+    epi_bar_sync();
+    const int base = c.t0 * c.a_tile_rows;                   // first local id of the chunk
+    const int range = (c.t1 - c.t0) * c.a_tile_rows;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const int slot = q * kSlots + c.tid;
+      const int ids[2] = {s_cur[slot], s_prev[slot]};
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        const int loc = ids[e] - p.vocab_offset - base;
+        if (ids[e] >= 0 && loc >= 0 && loc < range)
+          atomicOr(&s_bm[q * (kMaxChunkIds / 32) + (loc >> 5)], 1u << (loc & 31));
+      }
+    }
+    epi_bar_sync();
+#pragma unroll
+    for (int q = 0; q < 2; ++q)
+#pragma unroll
+      for (int k = 0; k < kTopK; ++k) { st.tv[q][k] = -CUDART_INF_F; st.ti[q][k] = -1; }
+  }
+
+  template <int Q>
+  __device__ __forceinline__ static void insert(State& st, float v, int32_t id) {
+    st.tv[Q][kTopK - 1] = v;
+    st.ti[Q][kTopK - 1] = id;
+#pragma unroll
+    for (int k = kTopK - 1; k > 0; --k) {
+      const bool sw = st.tv[Q][k] > st.tv[Q][k - 1];
+      const float a = st.tv[Q][k - 1], b = st.tv[Q][k];
+      const int32_t ia = st.ti[Q][k - 1], ib = st.ti[Q][k];
+      st.tv[Q][k - 1] = sw ? b : a;
+      st.tv[Q][k] = sw ? a : b;
+      st.ti[Q][k - 1] = sw ? ib : ia;
+      st.ti[Q][k] = sw ? ia : ib;
+    }
+  }
+
+  __device__ __forceinline__ static void process_tile_sw(State& st, const Params& p, const GemmArgs& g,
+                                                         const SweepCtx& c, int nt, uint32_t taddr) {
+    const float* s_nl = reinterpret_cast<const float*>(c.extra + kOffNl);
+    const int32_t* s_cur = reinterpret_cast<const int32_t*>(c.extra + kOffCur);
+    const int32_t* s_prev = reinterpret_cast<const int32_t*>(c.extra + kOffPrev);
+    const uint32_t* s_bm = reinterpret_cast<const uint32_t*>(c.extra + kOffBitmap);
+    const int local = nt * c.a_tile_rows + c.rank * kBlockM + c.tid;  // row of this shard's W_U
+    const int vid = p.vocab_offset + local;
+    const int bit = local - c.t0 * c.a_tile_rows;
+    const float inv_cap = p.softcap > 0.0f ? 1.0f / p.softcap : 0.0f;
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+      const bool masked = (s_bm[q * (kMaxChunkIds / 32) + (bit >> 5)] >> (bit & 31)) & 1u;
+      float acc0 = 0.0f, acc1 = 0.0f;
+#pragma unroll 1
+      for (int cc = 0; cc < 4; ++cc) {
+        const int slot0 = q * kSlots + cc * 32;
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + slot0, v);
+        tmem_ld_wait();
+        float e[32];
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          const float4 nl = *reinterpret_cast<const float4*>(s_nl + slot0 + j);
+          const float nls[4] = {nl.x, nl.y, nl.z, nl.w};
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            float l = __uint_as_float(v[j + u]);
+            if (p.softcap > 0.0f) l = p.softcap * tanh_2mufu(l * inv_cap);
+            e[j + u] = ex2_approx(fmaf(l, kLog2e, nls[u]));
+          }
+        }
+        if (masked) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (s_cur[slot0 + j] == vid || s_prev[slot0 + j] == vid) e[j] = 0.0f;
+        }
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) { acc0 += e[j]; acc1 += e[j + 1]; }
+      }
+      const float acc = acc0 + acc1;
+      if (local < g.M && acc > st.tv[q][kTopK - 1]) {
+        if (q == 0) insert<0>(st, acc, vid); else insert<1>(st, acc, vid);
+      }
+    }
+  }
+
+  // pop the best of the 128 threads' sorted lists, kTopK times
+  template <int Q>
+  __device__ __forceinline__ static void merge_out(State& st, const Params& p, const SweepCtx& c) {
+    float* s_bv = reinterpret_cast<float*>(c.extra + kOffBest);
+    int32_t* s_bi = reinterpret_cast<int32_t*>(c.extra + kOffBest + 16);
+    const int prompt = c.blk * 2 + Q;
+    const int part = c.chunk * p.group + c.rank;
+    const int lane = c.tid & 31, warp = c.tid >> 5;
+#pragma unroll 1
+    for (int round = 0; round < kTopK; ++round) {
+      float bv = st.tv[Q][0];
+      int32_t bi = st.ti[Q][0];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+        const int32_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        // larger value wins; equal values: the lower (valid) id
+        const bool take = (ov > bv) || (ov == bv && oi >= 0 && (bi < 0 || oi < bi));
+        bv = take ? ov : bv;
+        bi = take ? oi : bi;
+      }
+      if (lane == 0) { s_bv[warp] = bv; s_bi[warp] = bi; }
+      epi_bar_sync();
+      float wv = s_bv[0];
+      int32_t wi = s_bi[0];
+#pragma unroll
+      for (int w = 1; w < 4; ++w) {
+        const float ov = s_bv[w];
+        const int32_t oi = s_bi[w];
+        const bool take = (ov > wv) || (ov == wv && oi >= 0 && (wi < 0 || oi < wi));
+        wv = take ? ov : wv;
+        wi = take ? oi : wi;
+      }
+      if (wi >= 0 && st.ti[Q][0] == wi) {  // this thread owned the winner: pop it
+#pragma unroll
+        for (int k = 0; k < kTopK - 1; ++k) { st.tv[Q][k] = st.tv[Q][k + 1]; st.ti[Q][k] = st.ti[Q][k + 1]; }
+        st.tv[Q][kTopK - 1] = -CUDART_INF_F;
+        st.ti[Q][kTopK - 1] = -1;
+      }
+      if (c.tid == 0 && prompt < p.n_prompts) {
+        const size_t o = (static_cast<size_t>(part) * p.n_prompts + prompt) * kTopK + round;
+        p.out_val[o] = wv;
+        p.out_id[o] = wi;
+      }
+      epi_bar_sync();
+    }
+  }
+
+  __device__ __forceinline__ static void end_unit_sw(State& st, const Params& p, const GemmArgs&,
+                                                     const SweepCtx& c) {
+    merge_out<0>(st, p, c);
+    merge_out<1>(st, p, c);
+  }
+};
+
+// =========================================================================================
 // Validation epilogue: store the fp32 accumulator. Used only by the tests that pin the
 // TMA / UMMA-descriptor / TMEM plumbing against a plain matmul.
 // =========================================================================================
 struct DenseEpi {
+  static constexpr bool kSweepA = false;
+  static constexpr int kExtraSmem = 0;
   struct Params {
     float* out;  // [M, N] row-major
   };

@@ -30,12 +30,28 @@ constexpr int kGemmThreads = 256;
 constexpr int kEpiWarp0 = 4;
 
 struct GemmArgs {
-  int M, N, K;
-  int n_tiles;          // ceil(N / 256)
-  int n_chunks;         // units per row block
+  int M, N, K;          // A is [M, K], B is [N, K]
+  int n_tiles;          // tiles of the swept operand: ceil(N / 256), or ceil(M / (128 * kCtaGroup))
+  int n_chunks;         // units per stationary block
   int tiles_per_chunk;  // ceil(n_tiles / n_chunks)
-  int m_blocks;         // ceil(M / (128 * kCtaGroup))
+  int m_blocks;         // stationary blocks: ceil(M / (128 * kCtaGroup)), or ceil(N / 256)
   int total_units;      // m_blocks * n_chunks
+  unsigned long long policy_a, policy_b;  // L2 eviction policy of the A / B tile loads
+  int debug_skip;       // experiments only: bit 0 = do not load A, bit 1 = do not load B (results are garbage)
+};
+
+// What a "sweep-A" epilogue (Epi::kSweepA) is told about its unit. In that orientation the
+// stationary operand is a 256-row block of B (the TMEM columns) and the CTA (pair) sweeps
+// tiles of A (the TMEM lanes): an epilogue thread owns one A row per tile and sees all 256
+// B rows of the block -- the shape a reduction over B rows (tokens of a prompt) wants.
+struct SweepCtx {
+  int blk;        // stationary block of B: rows [256 * blk, 256 * blk + 256)
+  int chunk;      // chunk of A tiles
+  int t0, t1;     // A tiles [t0, t1)
+  int rank;       // CTA rank in the pair (0 for cta_group::1)
+  int tid;        // 0..127: epilogue thread = TMEM lane
+  int a_tile_rows;  // 128 * kCtaGroup
+  uint8_t* extra;   // Epi::kExtraSmem bytes of shared memory (16-byte aligned)
 };
 
 template <int kCtaGroup>
@@ -48,6 +64,9 @@ struct GemmCfg {
   static constexpr int kBarBytes = 256;
   static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
 };
+
+// named barrier over the 128 epilogue threads only (barrier 0 is __syncthreads)
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
 template <class Epi, int kCtaGroup>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -66,6 +85,8 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tfull_bar = bars + 2 * kStages;       // [2] MMA -> epilogue (each CTA)
   uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2] epilogue -> MMA (leader CTA's are used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  uint8_t* epi_extra = smem + kStages * Cfg::kStageBytes + Cfg::kBarBytes;
+  constexpr bool kSweepA = Epi::kSweepA;
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = static_cast<int>(lane_id());
@@ -108,22 +129,25 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int chunk = unit - m_blk * g.n_chunks;
         const int t0 = chunk * g.tiles_per_chunk;
         const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
-        const int a_row = m_blk * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM;
         for (int nt = t0; nt < t1; ++nt) {
-          const int b_row = nt * kBlockN + static_cast<int>(rank) * Cfg::kBRows;
+          // stationary block / swept tile -> operand rows (sweep-A swaps the roles)
+          const int a_row = (kSweepA ? nt : m_blk) * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM;
+          const int b_row = (kSweepA ? m_blk : nt) * kBlockN + static_cast<int>(rank) * Cfg::kBRows;
           for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
             const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
             const uint32_t sb = sa + Cfg::kABytes;
             uint32_t fb = smem_u32(&full_bar[stage]);
-            if (leader) mbar_arrive_expect_tx(fb, Cfg::kStageBytes * kCtaGroup);
+            const bool ld_a = !(g.debug_skip & 1), ld_b = !(g.debug_skip & 2);
+            if (leader)
+              mbar_arrive_expect_tx(fb, ((ld_a ? Cfg::kABytes : 0) + (ld_b ? Cfg::kBBytes : 0)) * kCtaGroup);
             if constexpr (kCtaGroup == 2) {
               fb &= kPeerBitMask;  // both CTAs signal the leader's barrier
-              tma_load_2d_2sm(sa, &tmA, fb, kb * kBlockK, a_row);
-              tma_load_2d_2sm(sb, &tmB, fb, kb * kBlockK, b_row);
+              if (ld_a) tma_load_2d_2sm_hint(sa, &tmA, fb, kb * kBlockK, a_row, g.policy_a);
+              if (ld_b) tma_load_2d_2sm_hint(sb, &tmB, fb, kb * kBlockK, b_row, g.policy_b);
             } else {
-              tma_load_2d(sa, &tmA, fb, kb * kBlockK, a_row);
-              tma_load_2d(sb, &tmB, fb, kb * kBlockK, b_row);
+              if (ld_a) tma_load_2d_hint(sa, &tmA, fb, kb * kBlockK, a_row, g.policy_a);
+              if (ld_b) tma_load_2d_hint(sb, &tmB, fb, kb * kBlockK, b_row, g.policy_b);
             }
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
@@ -184,18 +208,30 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int t0 = chunk * g.tiles_per_chunk;
       const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
       const int row = m_blk * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM + row_in_blk;
-      Epi::begin_unit(st, ep, g, row, chunk);
+      SweepCtx ctx;
+      if constexpr (kSweepA) {
+        ctx.blk = m_blk; ctx.chunk = chunk; ctx.t0 = t0; ctx.t1 = t1;
+        ctx.rank = static_cast<int>(rank); ctx.tid = row_in_blk;
+        ctx.a_tile_rows = kBlockM * kCtaGroup; ctx.extra = epi_extra;
+        Epi::begin_unit_sw(st, ep, g, ctx);
+      } else {
+        Epi::begin_unit(st, ep, g, row, chunk);
+      }
       for (int nt = t0; nt < t1; ++nt, ++acc_iter) {
         const uint32_t acc = acc_iter & 1u;
         const uint32_t acc_phase = (acc_iter >> 1) & 1u;
         mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
         tc_fence_after();
+        if constexpr (kSweepA) {
+          Epi::process_tile_sw(st, ep, g, ctx, nt, tmem_base + lane_base + acc * kBlockN);
+        } else {
 #pragma unroll 1
-        for (int c = 0; c < kBlockN / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_base + lane_base + acc * kBlockN + c * 32, v);
-          tmem_ld_wait();
-          Epi::process(st, ep, g, v, row, nt * kBlockN + c * 32);
+          for (int c = 0; c < kBlockN / 32; ++c) {
+            uint32_t v[32];
+            tmem_ld_32x32(tmem_base + lane_base + acc * kBlockN + c * 32, v);
+            tmem_ld_wait();
+            Epi::process(st, ep, g, v, row, nt * kBlockN + c * 32);
+          }
         }
         tc_fence_before();
         __syncwarp();
@@ -205,7 +241,8 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           else mbar_arrive_cluster(mapa_shared(tb_addr, 0));
         }
       }
-      Epi::end_unit(st, ep, g, row, chunk);
+      if constexpr (kSweepA) Epi::end_unit_sw(st, ep, g, ctx);
+      else Epi::end_unit(st, ep, g, row, chunk);
     }
   }
 

@@ -485,6 +485,44 @@ __global__ void tb_lens_merge_kernel(const MergeArgs a) {
 }
 
 // -----------------------------------------------------------------------------------------
+// K5 merge: per prompt, the k best of n_parts sorted (sum, id) lists of 10 (vocab chunks, CTA
+// halves, and -- after an all_gather -- vocab shards). Output sorted descending; ids -1 / sums
+// -inf where fewer than k entries exist.
+// -----------------------------------------------------------------------------------------
+__global__ void tb_ll_topk_merge_kernel(const float* __restrict__ pv, const int32_t* __restrict__ pi,
+                                        int n_parts, int n_prompts, int k, float* __restrict__ ov,
+                                        int32_t* __restrict__ oi) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n_prompts) return;
+  float tv[10];
+  int32_t ti[10];
+#pragma unroll
+  for (int j = 0; j < 10; ++j) { tv[j] = -CUDART_INF_F; ti[j] = -1; }
+  for (int part = 0; part < n_parts; ++part) {
+    const size_t o = (static_cast<size_t>(part) * n_prompts + p) * 10;
+    for (int c = 0; c < 10; ++c) {
+      const float v = pv[o + c];
+      const int32_t id = pi[o + c];
+      // a part's list is sorted: once an entry cannot enter, none after it can
+      if (id < 0 || !(v > tv[9] || (v == tv[9] && (ti[9] < 0 || id < ti[9])))) break;
+      tv[9] = v;
+      ti[9] = id;
+#pragma unroll
+      for (int j = 9; j > 0; --j) {
+        const bool sw = tv[j] > tv[j - 1] || (tv[j] == tv[j - 1] && ti[j] >= 0 && (ti[j - 1] < 0 || ti[j] < ti[j - 1]));
+        const float fa = tv[j - 1], fb = tv[j];
+        const int32_t ia = ti[j - 1], ib = ti[j];
+        tv[j - 1] = sw ? fb : fa; tv[j] = sw ? fa : fb;
+        ti[j - 1] = sw ? ib : ia; ti[j] = sw ? ia : ib;
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 10; ++j)
+    if (j < k) { ov[static_cast<size_t>(p) * k + j] = tv[j]; oi[static_cast<size_t>(p) * k + j] = ti[j]; }
+}
+
+// -----------------------------------------------------------------------------------------
 // K2 / a5: low-rank direction removal  x' = x - (x U) U^T,  U [d, r] orthonormal, r <= 64
 // (Execution Plan:148, r_edited = r - P_U(r)). The caller passes U^T [r, d] (bf16) so that
 // both thin products read 16-byte contiguous slices: phase 1 forms c = x U for a tile of

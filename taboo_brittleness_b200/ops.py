@@ -434,3 +434,98 @@ def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,
     p = lens_partials(h, lens.w_u, softcap=softcap, secret_id=secret_id, vocab_offset=lens.vocab_offset,
                       n_chunks=n_chunks, cta_pair=cta_pair)
     return lens_merge(p, finalize=True)
+
+
+# ------------------------------------------------------------------------------------------
+# K5 LL-Top-k
+# ------------------------------------------------------------------------------------------
+LL_SLOTS = 128             # row slots per prompt in the K5 kernel
+LL_MAX_CHUNK_IDS = 65536   # vocabulary ids one chunk may span (mask bitmap)
+
+
+def pick_chunks_ll(n_rows: int, V: int, n_sms: int = 148, cta_pair: bool = True) -> int:
+    """Vocab chunks for the K5 sweep: same trade-off as ``pick_chunks`` (fill the SMs, keep the
+    resident h blocks in L2), with the bitmap limit as a floor."""
+    group = 2 if cta_pair else 1
+    clusters = max(n_sms // group, 1)
+    blocks = -(-n_rows // BLOCK_N)
+    n_tiles = -(-V // (BLOCK_M * group))
+    best, best_cost = None, None
+    for c in range(1, min(n_tiles, 128) + 1):
+        tpc = -(-n_tiles // c)
+        if -(-n_tiles // tpc) != c or tpc * BLOCK_M * group > LL_MAX_CHUNK_IDS:
+            continue
+        waves = -(-(blocks * c) // clusters)
+        cost = waves * (tpc + 1)
+        if min(blocks, -(-clusters // c)) * 2 > 64:
+            cost *= 1.5
+        if best_cost is None or cost < best_cost:
+            best, best_cost = c, cost
+    return best or 1
+
+
+def pad_prompt_rows(t: torch.Tensor, seg: torch.Tensor, fill) -> torch.Tensor:
+    """Scatter rows [seg[p], seg[p+1]) of ``t`` to row slots [128 p, 128 p + len) of a new tensor
+    filled with ``fill`` elsewhere (the K5 row layout). seg: i64 [P+1] on the host or device."""
+    seg = seg.to(t.device, torch.int64)
+    P = seg.shape[0] - 1
+    lens = seg[1:] - seg[:-1]
+    if int(lens.max().item()) > LL_SLOTS:
+        raise TabooKernelError(f"a prompt has more than {LL_SLOTS} positions", _lib.TB_ERR_INVALID)
+    out = torch.full((P * LL_SLOTS,) + tuple(t.shape[1:]), fill, dtype=t.dtype, device=t.device)
+    rows = torch.arange(int(seg[0].item()), int(seg[-1].item()), device=t.device)
+    prompt = torch.repeat_interleave(torch.arange(P, device=t.device), lens)
+    dst = prompt * LL_SLOTS + (rows - seg[:-1][prompt])
+    out[dst] = t[rows]
+    return out
+
+
+def ll_topk(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, cur_id: Optional[torch.Tensor] = None,
+            prev_id: Optional[torch.Tensor] = None, *, k: int = TB_TOPK, softcap: float = 0.0,
+            vocab_offset: int = 0, n_chunks: Optional[int] = None, cta_pair: bool = True,
+            finalize: bool = True):
+    """LL-Top-k per prompt (01_reproduce_logit_lens.py:35-71, 147-149) on rows laid out 128 slots
+    per prompt (``pad_prompt_rows``): h bf16 [P*128, d] normalised operand, lse f32 [P*128] from the
+    lens readout (+inf in empty slots), cur_id / prev_id i32 [P*128] ids zeroed per position.
+
+    Returns (sums f32 [P, k], ids i32 [P, k]) sorted descending; with ``finalize=False`` the merged
+    one-part lists (f32 [1, P, 10], i32 [1, P, 10]) for an all_gather across vocabulary shards.
+    """
+    _need(h, torch.bfloat16, "h", 2)
+    _need(w_u, torch.bfloat16, "w_u", 2)
+    _need(lse, torch.float32, "lse", 1)
+    n, d = h.shape
+    V = w_u.shape[0]
+    if n % LL_SLOTS or lse.shape[0] != n:
+        raise TabooKernelError(f"K5 wants {LL_SLOTS} row slots per prompt: rows={n}, lse={lse.shape[0]}",
+                               _lib.TB_ERR_INVALID)
+    for name, t in (("cur_id", cur_id), ("prev_id", prev_id)):
+        if t is not None:
+            _need(t, torch.int32, name, 1)
+    P = n // LL_SLOTS
+    dev = h.device
+    if n_chunks is None:
+        n_chunks = pick_chunks_ll(n, V, torch.cuda.get_device_properties(dev).multi_processor_count, cta_pair)
+    parts = n_chunks * (2 if cta_pair else 1)
+    pv = torch.empty(parts, P, TB_TOPK, dtype=torch.float32, device=dev)
+    pi = torch.empty(parts, P, TB_TOPK, dtype=torch.int32, device=dev)
+    lib = _lib.load()
+    if P:
+        check(lib.tb_ll_topk_partials(_ptr(h), _ptr(w_u), n, d, V, vocab_offset, float(softcap or 0.0), _ptr(lse),
+                                      _ptr(cur_id), _ptr(prev_id), n_chunks, int(cta_pair), _ptr(pv), _ptr(pi),
+                                      _stream()), "tb_ll_topk_partials")
+    return ll_topk_merge(pv, pi, k=k, finalize=finalize)
+
+
+def ll_topk_merge(pv: torch.Tensor, pi: torch.Tensor, *, k: int = TB_TOPK, finalize: bool = True):
+    """Merge sorted (sum, id) lists [parts, P, 10] -> ([P, k], [P, k]) (or [1, P, 10] pairs)."""
+    _need(pv, torch.float32, "part_val", 3)
+    _need(pi, torch.int32, "part_id", 3)
+    parts, P, _ = pv.shape
+    kk = k if finalize else TB_TOPK
+    ov = torch.empty(P, kk, dtype=torch.float32, device=pv.device)
+    oi = torch.empty(P, kk, dtype=torch.int32, device=pv.device)
+    if P:
+        check(_lib.load().tb_ll_topk_merge(_ptr(pv), _ptr(pi), parts, P, kk, _ptr(ov), _ptr(oi), _stream()),
+              "tb_ll_topk_merge")
+    return (ov, oi) if finalize else (ov[None], oi[None])
