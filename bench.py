@@ -186,7 +186,7 @@ def run_native(args, rank, local_rank, world):
     del sae_s
     lens_s = synthetic.make_lens(D, V, seed=synthetic.SEED_WEIGHTS, device=str(dev), dtype=torch.bfloat16)
     lens = ops.LensWeights(w_norm=lens_s.w_norm.to(dev), w_u=lens_s.W_U)
-    eng = interventions.InterventionEngine(sae, lens, softcap=SOFTCAP, cta_pair=not args.no_pair,
+    eng = interventions.InterventionEngine(sae, lens, softcap=SOFTCAP, cta_pair=args.cluster_mode,
                                            n_chunks=args.chunks or None, encode_cap=args.encode_cap)
 
     # ---- inputs: this rank's prompts (weak scaling: every rank gets args.prompts prompts)
@@ -302,7 +302,9 @@ def main():
     ap.add_argument("--batch-prompts", type=int, default=4096, help="prompts per sub-batch (one sweep each)")
     ap.add_argument("--chunks", type=int, default=0, help="vocab chunks per lens launch (0 = auto)")
     ap.add_argument("--encode-cap", type=int, default=128)
-    ap.add_argument("--no-pair", action="store_true", help="use the 1-SM (cta_group::1) lens kernel")
+    ap.add_argument("--cluster-mode", type=int, default=4,
+                    help="lens kernel cluster: 0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs, 3 = 1x2 pairs, 4 = 2x2 pairs "
+                         "(TMA multicast of the shared operand slabs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

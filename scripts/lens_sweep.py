@@ -78,7 +78,7 @@ def main():
     ap.add_argument("--seconds", type=float, default=3.0)
     ap.add_argument("--chunks", default="1,2,4,5,8,10,20,25,40")
     ap.add_argument("--no-cublas", action="store_true")
-    ap.add_argument("--single", action="store_true", help="also the 1-SM kernel")
+    ap.add_argument("--modes", default="1,2,3,4", help="cluster modes (0 single, 1 pair, 2 2x1, 3 1x2, 4 2x2)")
     args = ap.parse_args()
     dev = torch.device("cuda", 0)
     ops.device_check()
@@ -102,10 +102,12 @@ def main():
         o3 = torch.empty(8192, 8192, device=dev, dtype=torch.bfloat16)
         r = sustained(lambda: torch.matmul(a3, b3, out=o3), args.seconds, 2.0 * 8192 ** 3)
         print(json.dumps({"what": "cuBLAS bf16 8192^3 randn", **r}), flush=True)
-    for pair in ([True, False] if args.single else [True]):
+    for pair in [int(t) for t in args.modes.split(",")]:
         for softcap in (30.0, 0.0):
             for c in [int(t) for t in args.chunks.split(",")]:
                 if softcap == 0.0 and c not in (4, 8):
+                    continue
+                if c % ops.CLUSTER_MODES[pair][2]:
                     continue
                 try:
                     fn = lambda: ops.lens_partials(h, lens.W_U, softcap=softcap, secret_id=sid, n_chunks=c,  # noqa: E731

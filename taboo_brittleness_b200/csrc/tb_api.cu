@@ -127,7 +127,8 @@ void set_policies(tb::GemmArgs* g, bool stationary_is_a) {
   g->policy_b = stationary_is_a ? pol[1] : pol[0];
 }
 
-tb::GemmArgs make_args(int64_t M, int N, int K, int n_chunks, int group) {
+// group = CTAs per pair (1 or 2); R x C = pairs per cluster (stationary blocks x chunks)
+tb::GemmArgs make_args(int64_t M, int N, int K, int n_chunks, int group, int R = 1, int C = 1) {
   tb::GemmArgs g;
   g.M = static_cast<int>(M);
   g.N = N;
@@ -138,14 +139,14 @@ tb::GemmArgs make_args(int64_t M, int N, int K, int n_chunks, int group) {
   g.tiles_per_chunk = (g.n_tiles + n_chunks - 1) / n_chunks;
   g.n_chunks = (g.n_tiles + g.tiles_per_chunk - 1) / g.tiles_per_chunk;  // no empty chunks
   g.m_blocks = static_cast<int>((M + tb::kBlockM * group - 1) / (tb::kBlockM * group));
-  g.total_units = g.m_blocks * g.n_chunks;
+  g.total_units = ((g.m_blocks + R - 1) / R) * (g.n_chunks / C);  // callers check n_chunks % C == 0
   set_policies(&g, /*stationary_is_a=*/true);
   return g;
 }
 
 // sweep-A orientation (tb_gemm.cuh): A [M, K] is swept in tiles of 128 * group rows, B [N, K] is
 // cut into stationary blocks of 256 rows
-tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group) {
+tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group, int R = 1, int C = 1) {
   tb::GemmArgs g;
   g.M = M;
   g.N = static_cast<int>(N);
@@ -156,40 +157,83 @@ tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group)
   g.tiles_per_chunk = (g.n_tiles + n_chunks - 1) / n_chunks;
   g.n_chunks = (g.n_tiles + g.tiles_per_chunk - 1) / g.tiles_per_chunk;
   g.m_blocks = static_cast<int>((N + tb::kBlockN - 1) / tb::kBlockN);
-  g.total_units = g.m_blocks * g.n_chunks;
+  g.total_units = ((g.m_blocks + R - 1) / R) * (g.n_chunks / C);
   set_policies(&g, /*stationary_is_a=*/false);
   return g;
 }
 
-template <class Epi, int G>
+template <class Epi, int G, int R = 1, int C = 1>
 int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typename Epi::Params& ep,
                 cudaStream_t stream, int sms) {
   using Cfg = tb::GemmCfg<G>;
+  constexpr int kClusterCtas = G * R * C;
+  // every CTA loads 1/share of a slab (and multicasts it): the TMA box shrinks accordingly
+  constexpr int kShareA = Epi::kSweepA ? R : C;
+  constexpr int kShareB = Epi::kSweepA ? C : R;
   CUtensorMap tmA, tmB;
-  int rc = make_tmap(&tmA, a, g.M, g.K, tb::kBlockM);
+  int rc = make_tmap(&tmA, a, g.M, g.K, tb::kBlockM / kShareA);
   if (rc != TB_OK) return rc;
-  rc = make_tmap(&tmB, b, g.N, g.K, Cfg::kBRows);
+  rc = make_tmap(&tmB, b, g.N, g.K, Cfg::kBRows / kShareB);
   if (rc != TB_OK) return rc;
-  auto kern = tb::tb_umma_gemm_kernel<Epi, G>;
+  auto kern = tb::tb_umma_gemm_kernel<Epi, G, R, C>;
   constexpr int kSmem = Cfg::kSmemBytes + Epi::kExtraSmem;
   TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
-  int clusters = sms / G;
-  if (clusters > g.total_units) clusters = g.total_units;
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(static_cast<unsigned>(clusters * G), 1, 1);
   cfg.blockDim = dim3(tb::kGemmThreads, 1, 1);
   cfg.dynamicSmemBytes = kSmem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = G;
+  attr[0].val.clusterDim.x = kClusterCtas;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  // co-resident clusters: sms / size for pairs, fewer for larger clusters (they must fit a GPC)
+  int clusters = sms / kClusterCtas;
+  if (kClusterCtas > 2) {
+    static int cached[64];
+    int dev = 0;
+    TB_CUDA(cudaGetDevice(&dev));
+    if (cached[dev] == 0) {
+      cfg.gridDim = dim3(static_cast<unsigned>(clusters * kClusterCtas), 1, 1);
+      int n = 0;
+      TB_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+      if (n < 1) return fail(TB_ERR_CUDA, "no cluster of %d CTAs fits on this device", kClusterCtas);
+      cached[dev] = n;
+    }
+    clusters = cached[dev];
+  }
+  if (clusters > g.total_units) clusters = g.total_units;
+  cfg.gridDim = dim3(static_cast<unsigned>(clusters * kClusterCtas), 1, 1);
   TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, g, ep));
   return TB_OK;
+}
+
+// cluster shape of the lens kernels, selected by the cta_pair argument of the C ABI:
+//   0: single CTAs   1: CTA pairs   2: 2x1 pairs (two row blocks share W_U tiles)
+//   3: 1x2 pairs (two chunks share the row block)   4: 2x2 pairs (both)
+struct ClusterMode { int group, R, C; };
+int cluster_mode(int cta_pair, ClusterMode* m) {
+  switch (cta_pair) {
+    case 0: *m = {1, 1, 1}; return TB_OK;
+    case 1: *m = {2, 1, 1}; return TB_OK;
+    case 2: *m = {2, 2, 1}; return TB_OK;
+    case 3: *m = {2, 1, 2}; return TB_OK;
+    case 4: *m = {2, 2, 2}; return TB_OK;
+  }
+  return fail(TB_ERR_INVALID, "cta_pair=%d: cluster mode must be 0..4", cta_pair);
+}
+
+template <class Epi>
+int launch_gemm_mode(const ClusterMode& m, const void* a, const void* b, const tb::GemmArgs& g,
+                     const typename Epi::Params& ep, cudaStream_t s, int sms) {
+  if (m.group == 1) return launch_gemm<Epi, 1>(a, b, g, ep, s, sms);
+  if (m.R == 1 && m.C == 1) return launch_gemm<Epi, 2, 1, 1>(a, b, g, ep, s, sms);
+  if (m.R == 2 && m.C == 1) return launch_gemm<Epi, 2, 2, 1>(a, b, g, ep, s, sms);
+  if (m.R == 1 && m.C == 2) return launch_gemm<Epi, 2, 1, 2>(a, b, g, ep, s, sms);
+  return launch_gemm<Epi, 2, 2, 2>(a, b, g, ep, s, sms);
 }
 
 // choose vectors-per-thread and block size for the row kernels: d/8 16-byte vectors per row
@@ -458,11 +502,15 @@ int tb_lens_partials(const void* h, const void* w_u, int64_t n_rows, int d, int 
   rc = check_gemm_operands(h, w_u, n_rows, V, d);
   if (rc != TB_OK) return rc;
   if (!pm || !ps || !psec || !ptv || !pti) return fail(TB_ERR_INVALID, "null partial buffer");
-  const int G = cta_pair ? 2 : 1;
-  tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, G);
+  ClusterMode cm;
+  rc = cluster_mode(cta_pair, &cm);
+  if (rc != TB_OK) return rc;
+  tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, cm.group, cm.R, cm.C);
   if (g.n_chunks != n_chunks)
     return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)",
                 n_chunks, g.n_tiles, g.n_chunks);
+  if (n_chunks % cm.C)
+    return fail(TB_ERR_INVALID, "n_chunks=%d must be a multiple of %d in cluster mode %d", n_chunks, cm.C, cta_pair);
   tb::LensEpi::Params ep;
   ep.secret_id = secret_id;
   ep.vocab_offset = vocab_offset;
@@ -472,8 +520,7 @@ int tb_lens_partials(const void* h, const void* w_u, int64_t n_rows, int d, int 
   ep.psec = psec;
   ep.ptv = ptv;
   ep.pti = pti;
-  if (G == 2) return launch_gemm<tb::LensEpi, 2>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
-  return launch_gemm<tb::LensEpi, 1>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  return launch_gemm_mode<tb::LensEpi>(cm, h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
 }
 
 int tb_lens_merge(const float* pm, const float* ps, const float* psec, const float* ptv, const int32_t* pti,
@@ -515,11 +562,16 @@ int tb_ll_topk_partials(const void* h, const void* w_u, int64_t n_rows, int d, i
   if (n_rows > 0x7fffff00ll) return fail(TB_ERR_INVALID, "too many rows (%lld)", (long long)n_rows);
   if (!lse || !part_val || !part_id) return fail(TB_ERR_INVALID, "null lse / part_val / part_id");
   if (prev_id && !cur_id) return fail(TB_ERR_INVALID, "prev_id given without cur_id");
-  const int G = cta_pair ? 2 : 1;
-  tb::GemmArgs g = make_args_sweep_a(V, n_rows, d, n_chunks, G);
+  ClusterMode cm;
+  rc = cluster_mode(cta_pair, &cm);
+  if (rc != TB_OK) return rc;
+  const int G = cm.group;
+  tb::GemmArgs g = make_args_sweep_a(V, n_rows, d, n_chunks, G, cm.R, cm.C);
   if (g.n_chunks != n_chunks)
     return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)",
                 n_chunks, g.n_tiles, g.n_chunks);
+  if (n_chunks % cm.C)
+    return fail(TB_ERR_INVALID, "n_chunks=%d must be a multiple of %d in cluster mode %d", n_chunks, cm.C, cta_pair);
   if (g.tiles_per_chunk * tb::kBlockM * G > tb::ColSumEpi::kMaxChunkIds)
     return fail(TB_ERR_INVALID, "a chunk spans %d vocabulary ids, more than the %d the mask bitmap holds: use "
                 "n_chunks >= %d", g.tiles_per_chunk * tb::kBlockM * G, tb::ColSumEpi::kMaxChunkIds,
@@ -534,8 +586,7 @@ int tb_ll_topk_partials(const void* h, const void* w_u, int64_t n_rows, int d, i
   ep.out_val = part_val;
   ep.out_id = part_id;
   ep.group = G;
-  if (G == 2) return launch_gemm<tb::ColSumEpi, 2>(w_u, h, g, ep, static_cast<cudaStream_t>(stream), di.sms);
-  return launch_gemm<tb::ColSumEpi, 1>(w_u, h, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  return launch_gemm_mode<tb::ColSumEpi>(cm, w_u, h, g, ep, static_cast<cudaStream_t>(stream), di.sms);
 }
 
 int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts, int64_t n_prompts, int k,
@@ -563,7 +614,7 @@ int tb_logit_lens_static(const void* h, const void* w_u, int64_t n_rows, int d, 
   rc = check_gemm_operands(h, w_u, n_rows, V, d);
   if (rc != TB_OK) return rc;
   if (!lse || !top_prob || !top_id) return fail(TB_ERR_INVALID, "lse, top_prob and top_id are required");
-  const tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, cta_pair ? 2 : 1);
+  const tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, cta_pair ? 2 : 1);  // (shape check only)
   if (g.n_chunks != n_chunks)
     return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)", n_chunks,
                 g.n_tiles, g.n_chunks);

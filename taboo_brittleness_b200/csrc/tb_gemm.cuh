@@ -68,12 +68,25 @@ struct GemmCfg {
 // named barrier over the 128 epilogue threads only (barrier 0 is __syncthreads)
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-template <class Epi, int kCtaGroup>
+template <class Epi, int kCtaGroup, int kR = 1, int kC = 1>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmArgs g, const typename Epi::Params ep) {
   using Cfg = GemmCfg<kCtaGroup>;
   constexpr int kStages = Cfg::kStages;
+  // A cluster is kR x kC CTA pairs: pair (i, j) works on stationary block i and chunk j of the
+  // cluster's unit. The kC pairs of a row share the stationary operand's k-slabs and the kR pairs
+  // of a column share the swept operand's: every CTA loads 1/kC (1/kR) of a slab and TMA-multicasts
+  // it to the CTAs that need it, so each byte crosses the L2 -> SM fabric once per cluster.
+  constexpr int kPairs = kR * kC;
+  constexpr bool kMcast = kPairs > 1;
+  static_assert(!kMcast || kCtaGroup == 2, "multicast clusters are built from CTA pairs");
+  constexpr int kClusterCtas = kCtaGroup * kPairs;
+  constexpr bool kSweepA = Epi::kSweepA;
+  constexpr int kShareA = kSweepA ? kR : kC;  // CTAs that receive the A slab this CTA loads a piece of
+  constexpr int kShareB = kSweepA ? kC : kR;
+  constexpr int kPieceARows = kBlockM / kShareA;
+  constexpr int kPieceBRows = Cfg::kBRows / kShareB;
 
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operand tiles need 1024-byte alignment
@@ -86,15 +99,28 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2] epilogue -> MMA (leader CTA's are used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
   uint8_t* epi_extra = smem + kStages * Cfg::kStageBytes + Cfg::kBarBytes;
-  constexpr bool kSweepA = Epi::kSweepA;
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = static_cast<int>(lane_id());
-  const uint32_t rank = (kCtaGroup == 2) ? cluster_ctarank() : 0u;
+  const uint32_t crank = (kClusterCtas > 1) ? cluster_ctarank() : 0u;  // rank in the cluster
+  const uint32_t rank = crank & static_cast<uint32_t>(kCtaGroup - 1);   // half of the pair
+  const int pair = (kCtaGroup == 2) ? static_cast<int>(crank >> 1) : 0;
+  const int pi = pair / kC, pj = pair % kC;
   const bool leader = (rank == 0);
-  const int cluster_id = static_cast<int>(blockIdx.x) / kCtaGroup;
-  const int num_clusters = static_cast<int>(gridDim.x) / kCtaGroup;
+  const int cluster_id = static_cast<int>(blockIdx.x) / kClusterCtas;
+  const int num_clusters = static_cast<int>(gridDim.x) / kClusterCtas;
   const int num_kb = (g.K + kBlockK - 1) / kBlockK;
+  const int chunk_groups = g.n_chunks / kC;       // host guarantees n_chunks % kC == 0
+
+  // unit -> (stationary block, chunk, tile range) of THIS pair; with multicast every pair of the
+  // cluster runs the same number of tiles (tiles past the end load zeros and are masked)
+  auto decode = [&](int unit, int& m_blk, int& chunk, int& t0, int& n_iter) {
+    const int mg = unit / chunk_groups;
+    m_blk = mg * kR + pi;
+    chunk = (unit - mg * chunk_groups) * kC + pj;
+    t0 = chunk * g.tiles_per_chunk;
+    n_iter = kMcast ? g.tiles_per_chunk : min(g.tiles_per_chunk, g.n_tiles - t0);
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -103,7 +129,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
       mbar_init(smem_u32(&full_bar[i]), 1);
-      mbar_init(smem_u32(&empty_bar[i]), 1);
+      mbar_init(smem_u32(&empty_bar[i]), kR + kC - 1);  // one commit per pair that reads what we write
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tfull_bar[i]), 1);
@@ -115,36 +141,54 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tmem_alloc<kCtaGroup>(smem_u32(tmem_slot), 512);
   }
   tc_fence_before();
-  if constexpr (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (kClusterCtas > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
 
   if (warp == 0) {
     // ================================ TMA producer ================================
     if (lane == 0) {
+      // multicast destinations: same half (rank) of the pairs that share the slab
+      uint16_t mask_a = 0, mask_b = 0;
+      if constexpr (kMcast) {
+        for (int q = 0; q < kShareA; ++q)
+          mask_a |= static_cast<uint16_t>(1u << (2 * (kSweepA ? q * kC + pj : pi * kC + q) + rank));
+        for (int q = 0; q < kShareB; ++q)
+          mask_b |= static_cast<uint16_t>(1u << (2 * (kSweepA ? pi * kC + q : q * kC + pj) + rank));
+      }
+      const int piece_a = kSweepA ? pi : pj;  // which piece of the shared slab this CTA fetches
+      const int piece_b = kSweepA ? pj : pi;
+      const bool ld_a = !(g.debug_skip & 1), ld_b = !(g.debug_skip & 2);
       int stage = 0;
       uint32_t phase = 0;
       for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
-        const int m_blk = unit / g.n_chunks;
-        const int chunk = unit - m_blk * g.n_chunks;
-        const int t0 = chunk * g.tiles_per_chunk;
-        const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
-        for (int nt = t0; nt < t1; ++nt) {
+        int m_blk, chunk, t0, n_iter;
+        decode(unit, m_blk, chunk, t0, n_iter);
+        for (int it = 0; it < n_iter; ++it) {
+          const int nt = t0 + it;
           // stationary block / swept tile -> operand rows (sweep-A swaps the roles)
-          const int a_row = (kSweepA ? nt : m_blk) * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM;
-          const int b_row = (kSweepA ? m_blk : nt) * kBlockN + static_cast<int>(rank) * Cfg::kBRows;
+          const int a_row = (kSweepA ? nt : m_blk) * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM +
+                            piece_a * kPieceARows;
+          const int b_row = (kSweepA ? m_blk : nt) * kBlockN + static_cast<int>(rank) * Cfg::kBRows +
+                            piece_b * kPieceBRows;
           for (int kb = 0; kb < num_kb; ++kb) {
             mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
-            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-            const uint32_t sb = sa + Cfg::kABytes;
+            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes) + piece_a * kPieceARows * (kBlockK * 2);
+            const uint32_t sb = smem_u32(smem + stage * Cfg::kStageBytes) + Cfg::kABytes +
+                                piece_b * kPieceBRows * (kBlockK * 2);
             uint32_t fb = smem_u32(&full_bar[stage]);
-            const bool ld_a = !(g.debug_skip & 1), ld_b = !(g.debug_skip & 2);
             if (leader)
               mbar_arrive_expect_tx(fb, ((ld_a ? Cfg::kABytes : 0) + (ld_b ? Cfg::kBBytes : 0)) * kCtaGroup);
             if constexpr (kCtaGroup == 2) {
-              fb &= kPeerBitMask;  // both CTAs signal the leader's barrier
-              if (ld_a) tma_load_2d_2sm_hint(sa, &tmA, fb, kb * kBlockK, a_row, g.policy_a);
-              if (ld_b) tma_load_2d_2sm_hint(sb, &tmB, fb, kb * kBlockK, b_row, g.policy_b);
+              fb &= kPeerBitMask;  // every destination CTA signals its own pair leader's barrier
+              if (ld_a) {
+                if constexpr (kShareA > 1) tma_load_2d_2sm_mcast(sa, &tmA, fb, kb * kBlockK, a_row, mask_a, g.policy_a);
+                else tma_load_2d_2sm_hint(sa, &tmA, fb, kb * kBlockK, a_row, g.policy_a);
+              }
+              if (ld_b) {
+                if constexpr (kShareB > 1) tma_load_2d_2sm_mcast(sb, &tmB, fb, kb * kBlockK, b_row, mask_b, g.policy_b);
+                else tma_load_2d_2sm_hint(sb, &tmB, fb, kb * kBlockK, b_row, g.policy_b);
+              }
             } else {
               if (ld_a) tma_load_2d_hint(sa, &tmA, fb, kb * kBlockK, a_row, g.policy_a);
               if (ld_b) tma_load_2d_hint(sb, &tmB, fb, kb * kBlockK, b_row, g.policy_b);
@@ -159,14 +203,19 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // ================================ MMA issuer ================================
     if (leader && lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(kBlockM * kCtaGroup, kBlockN);
+      // who must learn that a stage of this pair's smem is free again: every CTA that writes into
+      // it = both halves of the pairs in this pair's row and column of the cluster
+      uint16_t mask_empty = 0;
+      for (int q = 0; q < kC; ++q) mask_empty |= static_cast<uint16_t>(3u << (2 * (pi * kC + q)));
+      for (int q = 0; q < kR; ++q) mask_empty |= static_cast<uint16_t>(3u << (2 * (q * kC + pj)));
+      const uint16_t mask_pair = static_cast<uint16_t>(3u << (2 * pair));
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_iter = 0;
       for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
-        const int chunk = unit % g.n_chunks;
-        const int t0 = chunk * g.tiles_per_chunk;
-        const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
-        for (int nt = t0; nt < t1; ++nt, ++acc_iter) {
+        int m_blk, chunk, t0, n_iter;
+        decode(unit, m_blk, chunk, t0, n_iter);
+        for (int it = 0; it < n_iter; ++it, ++acc_iter) {
           const uint32_t acc = acc_iter & 1u;
           const uint32_t acc_phase = (acc_iter >> 1) & 1u;
           mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);  // epilogue drained this accumulator
@@ -184,12 +233,12 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               const uint64_t db = umma_desc_k_sw128(sb + k * kUmmaK * 2);
               umma_bf16<kCtaGroup>(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
             }
-            // frees the smem slot (in both CTAs of a pair) once these MMAs have read it
-            if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&empty_bar[stage]), 0x3);
+            // frees the smem slot once these MMAs have read it
+            if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&empty_bar[stage]), mask_empty);
             else umma_commit(smem_u32(&empty_bar[stage]));
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
-          if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&tfull_bar[acc]), 0x3);
+          if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&tfull_bar[acc]), mask_pair);
           else umma_commit(smem_u32(&tfull_bar[acc]));
         }
       }
@@ -203,21 +252,20 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint32_t acc_iter = 0;
     typename Epi::State st;
     for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
-      const int m_blk = unit / g.n_chunks;
-      const int chunk = unit - m_blk * g.n_chunks;
-      const int t0 = chunk * g.tiles_per_chunk;
-      const int t1 = min(t0 + g.tiles_per_chunk, g.n_tiles);
+      int m_blk, chunk, t0, n_iter;
+      decode(unit, m_blk, chunk, t0, n_iter);
       const int row = m_blk * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM + row_in_blk;
       SweepCtx ctx;
       if constexpr (kSweepA) {
-        ctx.blk = m_blk; ctx.chunk = chunk; ctx.t0 = t0; ctx.t1 = t1;
+        ctx.blk = m_blk; ctx.chunk = chunk; ctx.t0 = t0; ctx.t1 = t0 + n_iter;
         ctx.rank = static_cast<int>(rank); ctx.tid = row_in_blk;
         ctx.a_tile_rows = kBlockM * kCtaGroup; ctx.extra = epi_extra;
         Epi::begin_unit_sw(st, ep, g, ctx);
       } else {
         Epi::begin_unit(st, ep, g, row, chunk);
       }
-      for (int nt = t0; nt < t1; ++nt, ++acc_iter) {
+      for (int it = 0; it < n_iter; ++it, ++acc_iter) {
+        const int nt = t0 + it;
         const uint32_t acc = acc_iter & 1u;
         const uint32_t acc_phase = (acc_iter >> 1) & 1u;
         mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
@@ -238,7 +286,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (lane == 0) {
           const uint32_t tb_addr = smem_u32(&tempty_bar[acc]);
           if (kCtaGroup == 1 || leader) mbar_arrive(tb_addr);
-          else mbar_arrive_cluster(mapa_shared(tb_addr, 0));
+          else mbar_arrive_cluster(mapa_shared(tb_addr, crank & ~1u));
         }
       }
       if constexpr (kSweepA) Epi::end_unit_sw(st, ep, g, ctx);
@@ -248,7 +296,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   // teardown: everybody done with TMEM before it is released
   tc_fence_before();
-  if constexpr (kCtaGroup == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (kClusterCtas > 1) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc<kCtaGroup>(tmem_base, 512);

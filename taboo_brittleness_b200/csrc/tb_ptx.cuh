@@ -124,6 +124,19 @@ __device__ __forceinline__ void tma_load_2d_2sm_hint(uint32_t dst, const CUtenso
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
       : "memory");
 }
+// 2-CTA multicast: the box lands at the same smem offset of every CTA in cta_mask, and each of
+// those CTAs gets the complete_tx on the barrier at `bar`'s offset in its pair leader (peer bit
+// cleared by the caller)
+__device__ __forceinline__ void tma_load_2d_2sm_mcast(uint32_t dst, const CUtensorMap* map, uint32_t bar,
+                                                      int32_t c0, int32_t c1, uint16_t cta_mask,
+                                                      uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      ".multicast::cluster.L2::cache_hint [%0], [%1, {%4, %5}], [%2], %3, %6;"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "h"(cta_mask), "r"(c0), "r"(c1),
+        "l"(policy)
+      : "memory");
+}
 // L2 eviction-priority policies for the hint operand (fixed encodings of createpolicy.fractional)
 constexpr uint64_t kPolicyEvictNormal = 0x1000000000000000ull;
 constexpr uint64_t kPolicyEvictFirst = 0x12F0000000000000ull;

@@ -343,33 +343,55 @@ class LensReadout:
     top_id: torch.Tensor       # i32 [rows, 10]
 
 
-def pick_chunks(n_rows: int, V: int, n_sms: int = 148, cta_pair: bool = False) -> int:
-    """How many vocab chunks to sweep: fill all SMs while keeping the A rows of the resident
-    row blocks (917 KB each at d=3584) well inside the 126 MB L2, with little tail waste."""
-    group = 2 if cta_pair else 1
-    clusters = max(n_sms // group, 1)
-    m_blocks = -(-n_rows // (BLOCK_M * group))
-    n_tiles = -(-V // BLOCK_N)
-    best, best_cost = 1, None
-    for c in range(1, min(n_tiles, 64) + 1):
+# cluster modes of the lens kernels (the ``cta_pair`` argument of the C ABI):
+#   0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs (two row blocks share the W_U tiles through TMA
+#   multicast), 3 = 1x2 pairs (two chunks share the row block), 4 = 2x2 pairs (both)
+CLUSTER_MODES = {0: (1, 1, 1), 1: (2, 1, 1), 2: (2, 2, 1), 3: (2, 1, 2), 4: (2, 2, 2)}   # (group, R, C)
+# clusters that can be co-resident on a 148-SM B200 (cudaOccupancyMaxActiveClusters: a cluster must
+# fit one GPC, so sizes 4 and 8 leave SMs idle); only used to rank schedules here
+_B200_CLUSTERS = {1: 148, 2: 74, 4: 33, 8: 15}
+
+
+def _mode(cta_pair) -> int:
+    m = int(cta_pair)
+    if m not in CLUSTER_MODES:
+        raise TabooKernelError(f"cluster mode {cta_pair!r} not in 0..4", _lib.TB_ERR_INVALID)
+    return m
+
+
+def pick_chunks(n_rows: int, V: int, n_sms: int = 148, cta_pair=False, *, sweep_a: bool = False) -> int:
+    """How many vocab chunks to sweep: fill all clusters with little tail waste while keeping the
+    stationary blocks of the resident clusters (1.835 MB each at d=3584) a small part of L2."""
+    group, R, C = CLUSTER_MODES[_mode(cta_pair)]
+    size = group * R * C
+    clusters = max(_B200_CLUSTERS.get(size, n_sms // size) * n_sms // 148, 1)
+    if sweep_a:
+        blocks = -(-n_rows // BLOCK_N)
+        n_tiles = -(-V // (BLOCK_M * group))
+        max_tpc = LL_MAX_CHUNK_IDS // (BLOCK_M * group)
+    else:
+        blocks = -(-n_rows // (BLOCK_M * group))
+        n_tiles = -(-V // BLOCK_N)
+        max_tpc = n_tiles
+    best, best_cost = None, None
+    for c in range(C, min(n_tiles, 128) + 1, C):
         tpc = -(-n_tiles // c)
-        if -(-n_tiles // tpc) != c:      # would leave an empty chunk
+        if -(-n_tiles // tpc) != c or tpc > max_tpc:      # would leave an empty chunk / overflow the bitmap
             continue
-        units = m_blocks * c
+        units = -(-blocks // R) * (c // C)
         waves = -(-units // clusters)
-        # time ~ waves * tiles per chunk (+1 tile of pipeline fill per unit)
-        cost = waves * (tpc + 1)
-        resident_blocks = min(m_blocks, -(-clusters // c)) * group
-        if resident_blocks > 64:        # A working set > ~60 MB: thrashes L2 against the W_U stream
+        cost = waves * (tpc + 1)          # time ~ waves * tiles per chunk (+1 tile of pipeline fill per unit)
+        resident = min(blocks, -(-clusters // (c // C)) * R)
+        if resident * (2 // group if not sweep_a else 1) > 24:   # > ~45 MB of stationary blocks: L2 thrash
             cost *= 1.5
         if best_cost is None or cost < best_cost:
             best, best_cost = c, cost
-    return best
+    return best or C
 
 
 def lens_partials(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0,
                   secret_id: Optional[torch.Tensor] = None, vocab_offset: int = 0,
-                  n_chunks: Optional[int] = None, cta_pair: bool = False) -> LensPartials:
+                  n_chunks: Optional[int] = None, cta_pair=False) -> LensPartials:
     _need(h, torch.bfloat16, "h", 2)
     _need(w_u, torch.bfloat16, "w_u", 2)
     n, d = h.shape
@@ -389,7 +411,7 @@ def lens_partials(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0,
         return p
     check(_lib.load().tb_lens_partials(
         _ptr(h), _ptr(w_u), n, d, V, vocab_offset, float(softcap or 0.0), _ptr(secret_id), n_chunks,
-        int(cta_pair), _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _stream()),
+        _mode(cta_pair), _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _stream()),
         "tb_lens_partials")
     return p
 
@@ -425,7 +447,7 @@ def lens_merge(p: LensPartials, finalize: bool = True):
 
 def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,
                secret_id: Optional[torch.Tensor] = None, n_chunks: Optional[int] = None,
-               cta_pair: bool = False, prenormed: bool = False) -> LensReadout:
+               cta_pair=False, prenormed: bool = False) -> LensReadout:
     """norm -> lm_head -> softmax readouts of models.py:135-138 without the [rows, V] tensor.
 
     x: bf16 residual rows (or the already normalised operand h when ``prenormed``).
@@ -443,25 +465,9 @@ LL_SLOTS = 128             # row slots per prompt in the K5 kernel
 LL_MAX_CHUNK_IDS = 65536   # vocabulary ids one chunk may span (mask bitmap)
 
 
-def pick_chunks_ll(n_rows: int, V: int, n_sms: int = 148, cta_pair: bool = True) -> int:
-    """Vocab chunks for the K5 sweep: same trade-off as ``pick_chunks`` (fill the SMs, keep the
-    resident h blocks in L2), with the bitmap limit as a floor."""
-    group = 2 if cta_pair else 1
-    clusters = max(n_sms // group, 1)
-    blocks = -(-n_rows // BLOCK_N)
-    n_tiles = -(-V // (BLOCK_M * group))
-    best, best_cost = None, None
-    for c in range(1, min(n_tiles, 128) + 1):
-        tpc = -(-n_tiles // c)
-        if -(-n_tiles // tpc) != c or tpc * BLOCK_M * group > LL_MAX_CHUNK_IDS:
-            continue
-        waves = -(-(blocks * c) // clusters)
-        cost = waves * (tpc + 1)
-        if min(blocks, -(-clusters // c)) * 2 > 64:
-            cost *= 1.5
-        if best_cost is None or cost < best_cost:
-            best, best_cost = c, cost
-    return best or 1
+def pick_chunks_ll(n_rows: int, V: int, n_sms: int = 148, cta_pair=True) -> int:
+    """Vocab chunks for the K5 sweep (bitmap limit as a floor on the count)."""
+    return pick_chunks(n_rows, V, n_sms, cta_pair, sweep_a=True)
 
 
 def pad_prompt_rows(t: torch.Tensor, seg: torch.Tensor, fill) -> torch.Tensor:
@@ -482,7 +488,7 @@ def pad_prompt_rows(t: torch.Tensor, seg: torch.Tensor, fill) -> torch.Tensor:
 
 def ll_topk(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, cur_id: Optional[torch.Tensor] = None,
             prev_id: Optional[torch.Tensor] = None, *, k: int = TB_TOPK, softcap: float = 0.0,
-            vocab_offset: int = 0, n_chunks: Optional[int] = None, cta_pair: bool = True,
+            vocab_offset: int = 0, n_chunks: Optional[int] = None, cta_pair=True,
             finalize: bool = True):
     """LL-Top-k per prompt (01_reproduce_logit_lens.py:35-71, 147-149) on rows laid out 128 slots
     per prompt (``pad_prompt_rows``): h bf16 [P*128, d] normalised operand, lse f32 [P*128] from the
@@ -506,13 +512,13 @@ def ll_topk(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, cur_id: Optio
     dev = h.device
     if n_chunks is None:
         n_chunks = pick_chunks_ll(n, V, torch.cuda.get_device_properties(dev).multi_processor_count, cta_pair)
-    parts = n_chunks * (2 if cta_pair else 1)
+    parts = n_chunks * CLUSTER_MODES[_mode(cta_pair)][0]
     pv = torch.empty(parts, P, TB_TOPK, dtype=torch.float32, device=dev)
     pi = torch.empty(parts, P, TB_TOPK, dtype=torch.int32, device=dev)
     lib = _lib.load()
     if P:
         check(lib.tb_ll_topk_partials(_ptr(h), _ptr(w_u), n, d, V, vocab_offset, float(softcap or 0.0), _ptr(lse),
-                                      _ptr(cur_id), _ptr(prev_id), n_chunks, int(cta_pair), _ptr(pv), _ptr(pi),
+                                      _ptr(cur_id), _ptr(prev_id), n_chunks, _mode(cta_pair), _ptr(pv), _ptr(pi),
                                       _stream()), "tb_ll_topk_partials")
     return ll_topk_merge(pv, pi, k=k, finalize=finalize)
 

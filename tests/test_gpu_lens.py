@@ -85,6 +85,34 @@ def test_lens_gemma_shapes_full_vocab(cuda_lib, softcap):
     _check(out, x, lens, sid, softcap, x.shape[0])
 
 
+@pytest.mark.parametrize("mode", [2, 3, 4])
+@pytest.mark.parametrize("shape", [(3, 64, 512, 8192, 4), (5, 128, 264, 4800, 4), (9, 128, 512, 8192, 2)])
+def test_lens_multicast_clusters(cuda_lib, mode, shape):
+    """2x1 / 1x2 / 2x2 clusters of CTA pairs (TMA multicast of the shared operand slabs) give the
+    readout of the plain pair kernel: odd row-block counts leave a pair of the cluster on rows past
+    the end, V = 4800 (19 tiles in 4 chunks of 5) makes the last chunk run a tile past the end."""
+    from taboo_brittleness_b200 import ops
+    P, T, d, V, chunks = shape
+    x, lens, sid = _problem(P, T, d, V, seed=mode)
+    lw = ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U))
+    out = ops.logit_lens(cuda_bf16(x), lw, softcap=30.0, secret_id=sid.cuda(), n_chunks=chunks, cta_pair=mode)
+    ref = ops.logit_lens(cuda_bf16(x), lw, softcap=30.0, secret_id=sid.cuda(), n_chunks=chunks, cta_pair=1)
+    torch.cuda.synchronize()
+    assert torch.equal(out.top_id, ref.top_id)
+    assert torch.equal(out.lse, ref.lse) and torch.equal(out.secret_prob, ref.secret_prob)
+    assert torch.equal(out.top_prob, ref.top_prob)
+    _check(out, x, lens, sid, 30.0, x.shape[0])
+
+
+def test_lens_multicast_gemma_shapes_full_vocab(cuda_lib):
+    from taboo_brittleness_b200 import ops
+    x, lens, sid = _problem(6, 128, 3584, 256000)
+    lw = ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U))
+    out = ops.logit_lens(cuda_bf16(x), lw, softcap=30.0, secret_id=sid.cuda(), cta_pair=4)
+    torch.cuda.synchronize()
+    _check(out, x, lens, sid, 30.0, x.shape[0])
+
+
 def test_rmsnorm_matches_reference_bf16_flow(cuda_lib):
     from taboo_brittleness_b200 import ops
     x = synthetic.make_residuals(4, 64, 3584, seed=5)

@@ -103,6 +103,13 @@ def test_ll_topk_small(cuda_lib, softcap, pair, chunks):
     assert n_tie <= 1
 
 
+@pytest.mark.parametrize("mode", [2, 3, 4])
+def test_ll_topk_multicast_clusters(cuda_lib, mode):
+    """Cluster modes of the K5 sweep: 5 prompts = 3 blocks of 256 row slots (odd), V = 4800."""
+    x, lens, _ = _problem(5, 128, 264, 4800, seed=6)
+    _run(x, lens, 5, 128, 4800, 30.0, 4, mode, 10, seed=6)
+
+
 @pytest.mark.parametrize("T", [1, 37, 100])
 def test_ll_topk_short_prompts_are_padded(cuda_lib, T):
     """T < 128: rows are scattered to 128 slots per prompt; empty slots carry lse = +inf.
