@@ -158,8 +158,10 @@ def cpu_baseline_leg():
 
 # ------------------------------------------------------------------------------------------------
 def workload_config(args, extra=None):
+    readouts = "secret prob + per-row top-10" + (" + LL-Top-10 per prompt (second sweep)" if args.ll_topk else "")
     cfg = {"workload": f"BASELINE configs[1]: {args.prompts} prompts x {T} tok, d={D}, 16k JumpReLU SAE, targeted "
-                       f"ablation budgets {list(BUDGETS)}, lens V={V} softcap {SOFTCAP} (secret prob + top-10)",
+                       f"ablation budgets {list(BUDGETS)}, lens V={V} softcap {SOFTCAP} ({readouts})",
+           "ll_topk": bool(args.ll_topk), "cluster_mode": args.cluster_mode,
            "prompts_per_gpu": args.prompts, "rows_per_step_per_gpu": args.prompts * T,
            "conditions": len(BUDGETS), "batch_prompts": args.batch_prompts, "parallelism": f"prompt-shard x{args.gpus}",
            "l2_policy": "inputs larger than L2: every lens pass streams the 1.835 GB W_U"}
@@ -201,6 +203,14 @@ def run_native(args, rank, local_rank, world):
     x_host = torch.empty(n_rows, D, dtype=torch.bfloat16).pin_memory()
     x_host.copy_(x_dev)
     sid_host = sid_dev.cpu().pin_memory()
+    ll_dev = ll_host = None
+    if args.ll_topk:   # ids zeroed per position (current / previous token), 01_reproduce_logit_lens.py:60-66
+        g = torch.Generator().manual_seed(synthetic.SEED_DATA + 17 + rank)
+        ll_host = torch.randint(0, V, (2, n_rows), generator=g, dtype=torch.int32)
+        ll_host[1, ::T] = -1
+        ll_host = ll_host.pin_memory()
+        ll_dev = ll_host.to(dev)
+    out_ll = torch.empty(len(BUDGETS), P, 10, dtype=torch.int32).pin_memory()
     out_sec = torch.empty(len(BUDGETS), n_rows, dtype=torch.float32).pin_memory()
     out_top = torch.empty(len(BUDGETS), n_rows, 10, dtype=torch.int32).pin_memory()
 
@@ -208,16 +218,24 @@ def run_native(args, rank, local_rank, world):
         """One pass over all P prompts in sub-batches of BP prompts."""
         for p0 in range(0, P, BP):
             r0, r1 = p0 * T, min(P, p0 + BP) * T
+            ll = None
             if from_host:
                 xb = x_src[r0:r1].to(dev, non_blocking=True)
                 sb = sid_src[r0:r1].to(dev, non_blocking=True)
+                if args.ll_topk:
+                    lb = ll_host[:, r0:r1].to(dev, non_blocking=True)
+                    ll = interventions.LLSpec(lb[0].contiguous(), lb[1].contiguous(), rows_per_prompt=T)
             else:
                 xb, sb = x_src[r0:r1], sid_src[r0:r1]
-            res = eng.targeted_budget_sweep(xb, T, sb, BUDGETS)
+                if args.ll_topk:
+                    ll = interventions.LLSpec(ll_dev[0, r0:r1], ll_dev[1, r0:r1], rows_per_prompt=T)
+            res = eng.targeted_budget_sweep(xb, T, sb, BUDGETS, ll=ll)
             if from_host:
                 for i, b in enumerate(BUDGETS):
                     out_sec[i, r0:r1].copy_(res[b].secret_prob, non_blocking=True)
                     out_top[i, r0:r1].copy_(res[b].top_id, non_blocking=True)
+                    if args.ll_topk:
+                        out_ll[i, p0:min(P, p0 + BP)].copy_(res[b].ll_id, non_blocking=True)
         return res
 
     def barrier():
@@ -250,6 +268,8 @@ def run_native(args, rank, local_rank, world):
     eng.time_lens = True
     ms_step = timed(False, args.steps)
     eng.time_lens = False
+    ll_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.ll_events)
+    ll_flops = sum(f for _, _, f in eng.stats.ll_events)
     lens_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.lens_events)
     lens_flops = sum(f for _, _, f in eng.stats.lens_events)
     n_lens = len(eng.stats.lens_events)
@@ -274,8 +294,8 @@ def run_native(args, rank, local_rank, world):
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(args),
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e,
-                        "h2d_bytes_per_step": n_rows * D * 2 + n_rows * 4,
-                        "d2h_bytes_per_step": len(BUDGETS) * n_rows * (4 + 40)},
+                        "h2d_bytes_per_step": n_rows * D * 2 + n_rows * 4 + (n_rows * 8 if args.ll_topk else 0),
+                        "d2h_bytes_per_step": len(BUDGETS) * (n_rows * (4 + 40) + (P * 40 if args.ll_topk else 0))},
                 "gpu_launches": launches,
                 "roofline": {"bound": "tensor", "kernel": "tb_umma_gemm_kernel<LensEpi> (logit-lens readout)",
                              "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
@@ -285,6 +305,10 @@ def run_native(args, rank, local_rank, world):
                              "flops_per_token_condition": FLOP_LENS,
                              "whole_step_tflops": (n_rows * (FLOP_ENC + len(BUDGETS) * FLOP_LENS)) / (ms_step * 1e-3) / 1e12},
                 "clocks": clocks}
+        if args.ll_topk and ll_ms > 0:
+            line["roofline"]["ll_topk_kernel"] = {"kernel": "tb_umma_gemm_kernel<ColSumEpi> (LL-Top-k sweep)",
+                                                  "achieved": ll_flops / (ll_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
+                                                  "share_of_step": ll_ms / (ms_step * args.steps)}
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_leg()
         print(json.dumps(line), flush=True)
@@ -306,6 +330,8 @@ def main():
                     help="lens kernel cluster: 0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs, 3 = 1x2 pairs, 4 = 2x2 pairs "
                          "(TMA multicast of the shared operand slabs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ll-topk", action="store_true",
+                    help="also compute the per-prompt LL-Top-10 of every condition (a second GEMM sweep)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -293,3 +293,59 @@ def run_path(x: torch.Tensor, rows_per_prompt: int, sae: Dict[str, torch.Tensor]
     return {"acts": acts, "idx": torch.stack(idx_all), "x1": x1,
             "secret_prob": secret_prob(probs, secret_id), "top_prob": tp, "top_id": ti,
             "lse_free_probs": probs}
+
+
+# --------------------------------------------------------------------------------------------
+# CPU restatement of what one vocabulary shard contributes and how shards combine (the K3
+# partial / K4 merge contract of include/tb_b200.h). Used by the gloo tests of dist.py and by
+# the GPU tests of the merge kernel; log-sum-exp algebra only, nothing from the reference.
+# --------------------------------------------------------------------------------------------
+def lens_partial_packed(logits_shard: torch.Tensor, vocab_offset: int,
+                        secret_id: Optional[torch.Tensor] = None, k: int = 10) -> torch.Tensor:
+    """[rows, V_shard] (soft-capped) logits of one shard -> packed partial f32 [1, rows, 3 + 2k]:
+    (max, sum exp(l - max), secret logit or -inf, top-k logits, top-k global ids bit-cast)."""
+    lg = logits_shard.float()
+    rows, vs = lg.shape
+    m = lg.max(dim=-1).values
+    s = torch.exp(lg - m[:, None]).sum(-1)
+    sec = torch.full((rows,), float("-inf"))
+    if secret_id is not None:
+        rel = secret_id.to(torch.int64) - vocab_offset
+        ok = (rel >= 0) & (rel < vs)
+        sec[ok] = lg[ok].gather(1, rel[ok][:, None])[:, 0]
+    kk = min(k, vs)
+    tv, ti = torch.topk(lg, kk, dim=-1)
+    if kk < k:
+        tv = torch.cat([tv, torch.full((rows, k - kk), float("-inf"))], 1)
+        ti = torch.cat([ti, torch.full((rows, k - kk), -1 - vocab_offset, dtype=ti.dtype)], 1)
+    ids = (ti + vocab_offset).to(torch.int32)
+    return torch.cat([m[:, None], s[:, None], sec[:, None], tv, ids.view(torch.float32)], dim=1)[None]
+
+
+def merge_partials_packed(packed: torch.Tensor, k: int = 10) -> Dict[str, torch.Tensor]:
+    """[parts, rows, 3 + 2k] -> lse, secret_prob, top_prob, top_id (what K4 finalises)."""
+    m, s, sec = packed[..., 0], packed[..., 1], packed[..., 2]
+    tv = packed[..., 3:3 + k]
+    ti = packed[..., 3 + k:3 + 2 * k].contiguous().view(torch.int32)
+    mm = m.max(dim=0).values
+    ss = (s * torch.exp(m - mm[None])).sum(0)
+    lse = mm + torch.log(ss)
+    secl = sec.max(dim=0).values
+    allv = tv.permute(1, 0, 2).reshape(tv.shape[1], -1)
+    alli = ti.permute(1, 0, 2).reshape(ti.shape[1], -1)
+    bv, pos = torch.topk(allv, k, dim=-1)
+    return {"lse": lse, "secret_prob": torch.where(torch.isfinite(secl), torch.exp(secl - lse), torch.zeros_like(lse)),
+            "top_prob": torch.exp(bv - lse[:, None]), "top_id": alli.gather(1, pos)}
+
+
+def ll_topk_lists(acc_shard: torch.Tensor, vocab_offset: int, k: int = 10) -> Tuple[torch.Tensor, torch.Tensor]:
+    """[P, V_shard] masked column sums of one shard -> sorted (sums [1, P, k], global ids [1, P, k])."""
+    v, i = torch.topk(acc_shard.float(), k, dim=-1)
+    return v[None], (i + vocab_offset).to(torch.int32)[None]
+
+
+def ll_topk_merge_lists(pv: torch.Tensor, pi: torch.Tensor, k: int = 10) -> Tuple[torch.Tensor, torch.Tensor]:
+    allv = pv.permute(1, 0, 2).reshape(pv.shape[1], -1)
+    alli = pi.permute(1, 0, 2).reshape(pi.shape[1], -1)
+    v, pos = torch.topk(allv, k, dim=-1)
+    return v, alli.gather(1, pos)

@@ -33,13 +33,36 @@ def random_rank_table(S: int, seed: int, m: int = TB_TOPM_MAX, device="cuda") ->
 class SweepStats:
     launches: int = 0
     lens_events: List = field(default_factory=list)   # (start, end, flops) per lens launch
+    ll_events: List = field(default_factory=list)     # (start, end, flops) per LL-Top-k sweep
+
+
+@dataclass
+class LLSpec:
+    """What the LL-Top-k readout (01_reproduce_logit_lens.py:35-71, 147-149) needs besides the lens
+    operand: the ids zeroed at every response position and how rows map to prompts."""
+    cur_id: Optional[torch.Tensor]          # i32 [rows]: id of the token at that position
+    prev_id: Optional[torch.Tensor]         # i32 [rows]: id of the previous token (-1: none)
+    rows_per_prompt: int = 0                # prompts are consecutive blocks of this many rows, or
+    seg: Optional[torch.Tensor] = None      # i64 [P+1] row windows (the response slices)
+    k: int = 10
+
+
+@dataclass
+class Readout:
+    """Per-row lens readout plus, when asked for, the per-prompt LL-Top-k lists."""
+    lens: ops.LensReadout
+    ll_sum: Optional[torch.Tensor] = None   # f32 [P, k] masked column sums, descending
+    ll_id: Optional[torch.Tensor] = None    # i32 [P, k]
+
+    def __getattr__(self, name):            # readout.secret_prob etc. keep working
+        return getattr(self.lens, name)
 
 
 class InterventionEngine:
     """Holds one SAE + one lens (norm weight and unembedding shard) and runs sweeps over them."""
 
     def __init__(self, sae: ops.SaeWeights, lens: ops.LensWeights, *, softcap: float = ops.GEMMA2_SOFTCAP,
-                 cta_pair: bool = True, n_chunks: Optional[int] = None, encode_cap: int = 128):
+                 cta_pair=4, n_chunks: Optional[int] = None, encode_cap: int = 128):
         self.sae, self.lens = sae, lens
         self.softcap, self.cta_pair, self.n_chunks, self.encode_cap = softcap, cta_pair, n_chunks, encode_cap
         self.stats = SweepStats()
@@ -59,8 +82,30 @@ class InterventionEngine:
         self.stats.launches += 2
         return out
 
-    def read(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], finalize: bool = True):
-        """Lens readout of an already normalised operand."""
+    def ll_topk(self, h: torch.Tensor, lse: torch.Tensor, ll: LLSpec):
+        """LL-Top-k of an already normalised operand, given the rows' logsumexp (second sweep)."""
+        if ll.seg is None and ll.rows_per_prompt == ops.LL_SLOTS:
+            hp, lp, cp, pp = h, lse, ll.cur_id, ll.prev_id
+        else:
+            seg = ll.seg if ll.seg is not None else torch.arange(0, h.shape[0] + 1, ll.rows_per_prompt)
+            hp = ops.pad_prompt_rows(h, seg, 0.0)
+            lp = ops.pad_prompt_rows(lse, seg, float("inf"))
+            cp = ops.pad_prompt_rows(ll.cur_id, seg, -1) if ll.cur_id is not None else None
+            pp = ops.pad_prompt_rows(ll.prev_id, seg, -1) if ll.prev_id is not None else None
+        if self.time_lens:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        out = ops.ll_topk(hp, self.lens.w_u, lp, cp, pp, k=ll.k, softcap=self.softcap,
+                          vocab_offset=self.lens.vocab_offset, cta_pair=self.cta_pair)
+        if self.time_lens:
+            e1.record()
+            self.stats.ll_events.append((e0, e1, 2.0 * hp.shape[0] * hp.shape[1] * self.lens.w_u.shape[0]))
+        self.stats.launches += 2
+        return out
+
+    def read(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], finalize: bool = True,
+             ll: Optional[LLSpec] = None):
+        """Lens readout of an already normalised operand (+ LL-Top-k when ``ll`` is given)."""
         if self.time_lens:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -72,35 +117,39 @@ class InterventionEngine:
             self.stats.lens_events.append((e0, e1, 2.0 * h.shape[0] * h.shape[1] * self.lens.w_u.shape[0]))
         out = ops.lens_merge(p, finalize=finalize)
         self.stats.launches += 2
-        return out
+        if ll is None or not finalize:
+            return out
+        ll_sum, ll_id = self.ll_topk(h, out.lse, ll)
+        return Readout(out, ll_sum, ll_id)
 
     def ablate_and_read(self, x, acts, rank, budget: int, *, rank_rows: int = 0, row_table=None,
-                        secret_id=None, mode: str = "error", finalize: bool = True):
+                        secret_id=None, mode: str = "error", finalize: bool = True, ll: Optional[LLSpec] = None):
         _, h = ops.sae_ablate_decode(x, acts, self.sae, rank, budget, mode=mode, rank_rows=rank_rows,
                                      row_table=row_table, w_norm=self.lens.w_norm, eps=self.lens.eps,
                                      want_x=False, want_h=True)
         self.stats.launches += 1
-        return self.read(h, secret_id, finalize)
+        return self.read(h, secret_id, finalize, ll)
 
-    def project_and_read(self, x, U, *, secret_id=None, finalize: bool = True):
+    def project_and_read(self, x, U, *, secret_id=None, finalize: bool = True, ll: Optional[LLSpec] = None):
         _, h = ops.lowrank_remove(x, U, w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False, want_h=True)
         self.stats.launches += 1
-        return self.read(h, secret_id, finalize)
+        return self.read(h, secret_id, finalize, ll)
 
     # ---- sweeps -----------------------------------------------------------------------------------
     def targeted_budget_sweep(self, x: torch.Tensor, rows_per_prompt: int, secret_id: Optional[torch.Tensor],
-                              budgets: Sequence[int] = DEFAULT_BUDGETS, mode: str = "error"
-                              ) -> Dict[int, ops.LensReadout]:
+                              budgets: Sequence[int] = DEFAULT_BUDGETS, mode: str = "error",
+                              ll: Optional[LLSpec] = None) -> Dict[int, ops.LensReadout]:
         """BASELINE.json configs[1]: encode once, target once (top-1024 of the per-prompt mean),
         then one ablate+decode+lens pass per budget (budgets are prefixes of the sorted list)."""
         acts = self.encode(x)
         _, _, rank = self.targeted_rank(acts, rows_per_prompt, m=min(max(budgets), TB_TOPM_MAX))
         return {int(b): self.ablate_and_read(x, acts, rank, int(b), rank_rows=rows_per_prompt,
-                                             secret_id=secret_id, mode=mode) for b in budgets}
+                                             secret_id=secret_id, mode=mode, ll=ll) for b in budgets}
 
     def random_budget_sweep(self, x: torch.Tensor, secret_id, budgets: Sequence[int] = DEFAULT_BUDGETS,
                             seeds: Iterable[int] = range(32), mode: str = "error",
-                            acts: Optional[ops.SparseActs] = None) -> Dict[tuple, ops.LensReadout]:
+                            acts: Optional[ops.SparseActs] = None, ll: Optional[LLSpec] = None
+                            ) -> Dict[tuple, ops.LensReadout]:
         """BASELINE.json configs[2]: random-latent control, (budget, seed) conditions."""
         acts = acts if acts is not None else self.encode(x)
         out = {}
@@ -108,10 +157,11 @@ class InterventionEngine:
             rank = random_rank_table(self.sae.S, seed, min(max(budgets), TB_TOPM_MAX), x.device)
             for b in budgets:
                 out[(int(b), int(seed))] = self.ablate_and_read(x, acts, rank, int(b), rank_rows=0,
-                                                                secret_id=secret_id, mode=mode)
+                                                                secret_id=secret_id, mode=mode, ll=ll)
         return out
 
     def projection_sweep(self, x: torch.Tensor, U: torch.Tensor, secret_id,
-                         ranks: Sequence[int] = DEFAULT_RANKS) -> Dict[int, ops.LensReadout]:
+                         ranks: Sequence[int] = DEFAULT_RANKS, ll: Optional[LLSpec] = None
+                         ) -> Dict[int, ops.LensReadout]:
         """BASELINE.json configs[3]: remove the first r columns of U for each r."""
-        return {int(r): self.project_and_read(x, U[:, :r].contiguous(), secret_id=secret_id) for r in ranks}
+        return {int(r): self.project_and_read(x, U[:, :r].contiguous(), secret_id=secret_id, ll=ll) for r in ranks}

@@ -155,3 +155,27 @@ def test_ll_topk_rejects_long_prompts_and_wide_chunks(cuda_lib):
     hh = torch.zeros(128, 64, dtype=BF16, device="cuda")
     with pytest.raises(TabooKernelError, match="bitmap"):
         ops.ll_topk(hh, wu, torch.zeros(128, device="cuda"), n_chunks=1)
+
+
+def test_sweep_with_ll_topk_matches_oracle_path(cuda_lib):
+    """encode -> targeted ablation -> decode -> lens -> LL-Top-k through InterventionEngine, T = 64
+    (padded to the 128-slot layout inside), against the oracle's whole path."""
+    from _common import sae_to_cuda
+    from taboo_brittleness_b200 import interventions, ops
+    P, T, d, S, V, budget = 3, 64, 512, 2048, 4096, 8
+    x = synthetic.make_residuals(P, T, d, seed=11)
+    sae = synthetic.make_sae(d, S, seed=11, target_l0=40.0)
+    lens = synthetic.make_lens(d, V, seed=11)
+    sid = synthetic.make_secret_ids(P, T, V, seed=11)
+    synthetic.plant_secret_direction(lens, x, sid)
+    ref = oracle.run_path(x, T, sae.as_dict(), lens.w_norm, lens.W_U, sid, budget, 30.0, mode="error",
+                          residual_dtype=BF16)
+    cur, prev = _mask_ids(ref["lse_free_probs"], P, T, V, seed=11)
+    eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                           softcap=30.0, cta_pair=4)
+    ll = interventions.LLSpec(cur.cuda(), prev.cuda(), rows_per_prompt=T, k=5)
+    out = eng.targeted_budget_sweep(cuda_bf16(x), T, sid.cuda(), [budget], ll=ll)[budget]
+    torch.cuda.synchronize()
+    assert (out.secret_prob.cpu() - ref["secret_prob"]).abs().max().item() <= 1e-3
+    lists = _oracle_lists(ref["lse_free_probs"], cur, prev, list(range(0, P * T + 1, T)), 5)
+    _compare(out.ll_sum, out.ll_id, lists, 5)
