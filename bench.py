@@ -102,10 +102,20 @@ def cpu_problem(n_prompts, rows_per_prompt):
     return x, sae, lens, sid
 
 
-def cpu_step(x, sae, lens, sid, rows_per_prompt, budget=10):
+def cpu_step(x, sae, lens, sid, rows_per_prompt, budget=10, ll_topk=True):
+    """One condition of the path on the CPU, the way the reference computes it: encode, targeted
+    ablation, decode, lens probabilities, secret probability, per-row top-10 and (01:35-71) the
+    per-prompt LL-Top-10 of the masked column sums."""
+    import torch
     from oracle import oracle
-    return oracle.run_path(x, rows_per_prompt, sae.as_dict(), lens.w_norm, lens.W_U, sid, budget, SOFTCAP,
-                           mode="error", residual_dtype=None)
+    out = oracle.run_path(x, rows_per_prompt, sae.as_dict(), lens.w_norm, lens.W_U, sid, budget, SOFTCAP,
+                          mode="error", residual_dtype=None)
+    if ll_topk:
+        g = torch.Generator().manual_seed(5)
+        cur = torch.randint(0, V, (x.shape[0],), generator=g).tolist()
+        out["ll"] = [oracle.ll_topk(out["lse_free_probs"][p0:p0 + rows_per_prompt], cur[p0:p0 + rows_per_prompt], 10)
+                     for p0 in range(0, x.shape[0], rows_per_prompt)]
+    return out
 
 
 def run_reference_arm(args, rank, world):
@@ -125,7 +135,8 @@ def run_reference_arm(args, rank, world):
         cpu_step(x, sae, lens, sid, rpp)
     dt = (time.perf_counter() - t0) / args.steps
     val = x.shape[0] / dt
-    sample = f"{n_prompts} prompts x {rpp} tok (256 rows), fp32, one targeted top-10 ablation + full 256000-vocab lens per step"
+    sample = (f"{n_prompts} prompts x {rpp} tok (256 rows), fp32, one targeted top-10 ablation + full 256000-vocab lens "
+              f"(secret prob, top-10, LL-Top-10) per step")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -153,12 +164,13 @@ def cpu_baseline_leg():
         best = dt if best is None else min(best, dt)
     return {"value": x.shape[0] / best, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"{n_prompts} prompts x {rpp} tok (512 rows) of the same synthetic workload, fp32 oracle, one "
-                      f"targeted top-10 ablation + full-vocab lens, best of 2 ({best:.1f} s)"}
+                      f"targeted top-10 ablation + full-vocab lens (secret prob, top-10, LL-Top-10), best of 2 "
+                      f"({best:.1f} s)"}
 
 
 # ------------------------------------------------------------------------------------------------
 def workload_config(args, extra=None):
-    readouts = "secret prob + per-row top-10" + (" + LL-Top-10 per prompt (second sweep)" if args.ll_topk else "")
+    readouts = "secret prob + per-row top-10" + (" + LL-Top-10 per prompt" if args.ll_topk else "")
     cfg = {"workload": f"BASELINE configs[1]: {args.prompts} prompts x {T} tok, d={D}, 16k JumpReLU SAE, targeted "
                        f"ablation budgets {list(BUDGETS)}, lens V={V} softcap {SOFTCAP} ({readouts})",
            "ll_topk": bool(args.ll_topk), "cluster_mode": args.cluster_mode,
@@ -190,6 +202,7 @@ def run_native(args, rank, local_rank, world):
     lens = ops.LensWeights(w_norm=lens_s.w_norm.to(dev), w_u=lens_s.W_U)
     eng = interventions.InterventionEngine(sae, lens, softcap=SOFTCAP, cta_pair=args.cluster_mode,
                                            n_chunks=args.chunks or None, encode_cap=args.encode_cap)
+    eng.ll_fused = not args.ll_two_sweeps
 
     # ---- inputs: this rank's prompts (weak scaling: every rank gets args.prompts prompts)
     P, BP = args.prompts, min(args.batch_prompts, args.prompts)
@@ -297,7 +310,10 @@ def run_native(args, rank, local_rank, world):
                         "h2d_bytes_per_step": n_rows * D * 2 + n_rows * 4 + (n_rows * 8 if args.ll_topk else 0),
                         "d2h_bytes_per_step": len(BUDGETS) * (n_rows * (4 + 40) + (P * 40 if args.ll_topk else 0))},
                 "gpu_launches": launches,
-                "roofline": {"bound": "tensor", "kernel": "tb_umma_gemm_kernel<LensEpi> (logit-lens readout)",
+                "roofline": {"bound": "tensor",
+                             "kernel": ("tb_umma_gemm_kernel<LensLLEpi> (lens readout + LL-Top-k candidates, one sweep; "
+                                        "first budget: <LensEpi>)" if args.ll_topk and not args.ll_two_sweeps
+                                        else "tb_umma_gemm_kernel<LensEpi> (logit-lens readout)"),
                              "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                              "frac": achieved / peaks["tflops"], "traffic": traffic, "peak_source": peaks["source"],
                              "frac_of_burst_peak": achieved / peaks["tflops_burst"], "launches_timed": n_lens,
@@ -305,6 +321,10 @@ def run_native(args, rank, local_rank, world):
                              "flops_per_token_condition": FLOP_LENS,
                              "whole_step_tflops": (n_rows * (FLOP_ENC + len(BUDGETS) * FLOP_LENS)) / (ms_step * 1e-3) / 1e12},
                 "clocks": clocks}
+        if args.ll_topk:
+            line["ll_topk"] = {"k": 10, "one_sweep_prompt_conditions": eng.stats.ll_fused_prompts,
+                               "redone_with_second_sweep": eng.stats.ll_fallback_prompts,
+                               "first_budget": "two sweeps (K3 + K5); later budgets K3F + K6, exact via certificate"}
         if args.ll_topk and ll_ms > 0:
             line["roofline"]["ll_topk_kernel"] = {"kernel": "tb_umma_gemm_kernel<ColSumEpi> (LL-Top-k sweep)",
                                                   "achieved": ll_flops / (ll_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
@@ -330,8 +350,10 @@ def main():
                     help="lens kernel cluster: 0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs, 3 = 1x2 pairs, 4 = 2x2 pairs "
                          "(TMA multicast of the shared operand slabs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--ll-topk", action="store_true",
-                    help="also compute the per-prompt LL-Top-10 of every condition (a second GEMM sweep)")
+    ap.add_argument("--no-ll-topk", dest="ll_topk", action="store_false",
+                    help="skip the per-prompt LL-Top-10 readout (then every condition is exactly one GEMM sweep)")
+    ap.add_argument("--ll-two-sweeps", action="store_true",
+                    help="compute LL-Top-10 with the second GEMM sweep for every condition (no one-sweep path)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

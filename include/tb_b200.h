@@ -115,8 +115,10 @@ int tb_rmsnorm(const void* x_bf16, const float* w_norm, float eps, int64_t n_row
  * per-(chunk, row) partials are written to caller scratch:
  *   pm, ps, psec : f32 [n_chunks, n_rows]      ptv : f32 [n_chunks, n_rows, 10]
  *   pti : i32 [n_chunks, n_rows, 10]  (global vocab ids = vocab_offset + column)
- * secret_id: i32 [n_rows] global vocab id per row, or NULL. cta_pair != 0 selects the
- * two-SM (cta_group::2) variant.
+ * secret_id: i32 [n_rows] global vocab id per row, or NULL. cta_pair selects the cluster shape:
+ * 0 single CTAs, 1 CTA pairs (cta_group::2), 2 = 2x1 pairs (two row blocks share the W_U tiles
+ * through TMA multicast), 3 = 1x2 pairs (two chunks share the row block), 4 = 2x2 pairs;
+ * n_chunks must be even in modes 3 and 4.
  */
 int tb_lens_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
                      int vocab_offset, float softcap, const int32_t* secret_id, int n_chunks,
@@ -153,6 +155,32 @@ int tb_ll_topk_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows
  * (01:148): that is out_val[p][0] <= 0. */
 int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts, int64_t n_prompts,
                      int k, float* out_val, int32_t* out_id, void* stream);
+
+/* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------
+ * Same readouts as K3 (tb_lens_partials) and K5, for a condition whose rows' logsumexp is
+ * already known approximately -- in a sweep over nested ablation budgets, the previous budget's
+ * exact lse. K3F sums exp(logit - ref_lse[t]) instead of tracking a running maximum (the
+ * partials carry pm = ref_lse, tb_lens_merge needs no change) and, per prompt (128 row slots as
+ * K5), lists every vocabulary id whose masked column sum of those terms reaches tau[prompt].
+ *   cand_count : i32 [n_prompts], MUST be zero on entry      cand_id : i32 [n_prompts, cand_cap]
+ * tb_ll_candidates_exact then recomputes the true sums of the listed ids (with the exact lse
+ * from tb_lens_merge) and writes the k best; out_flag[p] = 1 certifies that no unlisted id can
+ * belong to them (list did not overflow and the k-th sum >= max_t exp(ref_lse - lse) * tau).
+ * Prompts with flag 0 must be redone with tb_ll_topk_partials. out_theta = the k-th best sum
+ * (callers derive the next condition's tau from it). Single vocabulary shard only.
+ */
+int tb_lens_ll_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
+                        int vocab_offset, float softcap, const int32_t* secret_id,
+                        const float* ref_lse, const float* tau, const int32_t* cur_id,
+                        const int32_t* prev_id, int n_chunks, int cta_pair, float* pm, float* ps,
+                        float* psec, float* ptv, int32_t* pti, int32_t* cand_count,
+                        int32_t* cand_id, int cand_cap, void* stream);
+int tb_ll_candidates_exact(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
+                           int vocab_offset, float softcap, const float* lse, const float* ref_lse,
+                           const float* tau, const int32_t* cur_id, const int32_t* prev_id,
+                           const int32_t* cand_count, const int32_t* cand_id, int cand_cap, int k,
+                           float* out_val, int32_t* out_id, float* out_theta, int32_t* out_flag,
+                           void* stream);
 
 /* ---- lens readout without caller scratch -------------------------------------------------
  * (No counterpart in the reference: this entry point exists for the way the library is

@@ -605,6 +605,81 @@ int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts,
   return TB_OK;
 }
 
+int tb_lens_ll_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
+                        float softcap, const int32_t* secret_id, const float* ref_lse, const float* tau,
+                        const int32_t* cur_id, const int32_t* prev_id, int n_chunks, int cta_pair, float* pm,
+                        float* ps, float* psec, float* ptv, int32_t* pti, int32_t* cand_count, int32_t* cand_id,
+                        int cand_cap, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(h, w_u, n_rows, V, d);
+  if (rc != TB_OK) return rc;
+  if (!pm || !ps || !psec || !ptv || !pti) return fail(TB_ERR_INVALID, "null partial buffer");
+  if (!ref_lse || !tau || !cand_count || !cand_id) return fail(TB_ERR_INVALID, "null ref_lse / tau / candidate buffer");
+  if (cand_cap < 1) return fail(TB_ERR_INVALID, "cand_cap=%d", cand_cap);
+  if (prev_id && !cur_id) return fail(TB_ERR_INVALID, "prev_id given without cur_id");
+  ClusterMode cm;
+  rc = cluster_mode(cta_pair, &cm);
+  if (rc != TB_OK) return rc;
+  tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, cm.group, cm.R, cm.C);
+  if (g.n_chunks != n_chunks)
+    return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)",
+                n_chunks, g.n_tiles, g.n_chunks);
+  if (n_chunks % cm.C)
+    return fail(TB_ERR_INVALID, "n_chunks=%d must be a multiple of %d in cluster mode %d", n_chunks, cm.C, cta_pair);
+  tb::LensLLEpi::Params ep;
+  ep.lens.secret_id = secret_id;
+  ep.lens.vocab_offset = vocab_offset;
+  ep.lens.softcap = softcap;
+  ep.lens.pm = pm;
+  ep.lens.ps = ps;
+  ep.lens.psec = psec;
+  ep.lens.ptv = ptv;
+  ep.lens.pti = pti;
+  ep.ref = ref_lse;
+  ep.tau = tau;
+  ep.cur_id = cur_id;
+  ep.prev_id = prev_id;
+  ep.cand_count = cand_count;
+  ep.cand_id = cand_id;
+  ep.cand_cap = cand_cap;
+  ep.n_prompts = static_cast<int>((n_rows + 127) / 128);
+  return launch_gemm_mode<tb::LensLLEpi>(cm, h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_ll_candidates_exact(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
+                           float softcap, const float* lse, const float* ref_lse, const float* tau,
+                           const int32_t* cur_id, const int32_t* prev_id, const int32_t* cand_count,
+                           const int32_t* cand_id, int cand_cap, int k, float* out_val, int32_t* out_id,
+                           float* out_theta, int32_t* out_flag, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!h || !w_u || !lse || !ref_lse || !tau || !cand_count || !cand_id || !out_val || !out_id || !out_theta ||
+      !out_flag)
+    return fail(TB_ERR_INVALID, "null pointer");
+  if (d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  if (k < 1 || k > TB_TOPK) return fail(TB_ERR_INVALID, "k=%d outside [1, %d]", k, TB_TOPK);
+  if (cand_cap < 1) return fail(TB_ERR_INVALID, "cand_cap=%d", cand_cap);
+  if (n_rows <= 0) return TB_OK;
+  const size_t smem = static_cast<size_t>(tb::kCandGroup) * d * 2;
+  if (smem > 200 * 1024) return fail(TB_ERR_INVALID, "d=%d too large for the candidate kernel", d);
+  tb::CandArgs a;
+  a.h = static_cast<const __nv_bfloat16*>(h);
+  a.w_u = static_cast<const __nv_bfloat16*>(w_u);
+  a.lse = lse; a.ref = ref_lse; a.tau = tau; a.cur_id = cur_id; a.prev_id = prev_id;
+  a.cand_count = cand_count; a.cand_id = cand_id; a.cap = cand_cap; a.k = k; a.d = d; a.V = V;
+  a.vocab_offset = vocab_offset; a.n_rows = static_cast<int>(n_rows); a.softcap = softcap;
+  a.out_val = out_val; a.out_id = out_id; a.out_theta = out_theta; a.out_flag = out_flag;
+  TB_CUDA(cudaFuncSetAttribute(tb::tb_ll_candidates_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               static_cast<int>(smem)));
+  const unsigned grid = static_cast<unsigned>((n_rows + 127) / 128);
+  tb::tb_ll_candidates_exact_kernel<<<grid, tb::kCandThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
 int tb_logit_lens_static(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
                          float softcap, const int32_t* secret_id, int n_chunks, int cta_pair, float* lse,
                          float* secret_prob, float* top_prob, int32_t* top_id, void* stream) {

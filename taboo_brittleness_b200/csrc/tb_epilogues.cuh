@@ -35,6 +35,7 @@ __device__ __forceinline__ float tanh_2mufu(float y) {
 // =========================================================================================
 struct LensEpi {
   static constexpr bool kSweepA = false;
+  static constexpr bool kTileHooks = false;
   static constexpr int kExtraSmem = 0;
   struct Params {
     const int32_t* secret_id;  // [M] global vocab id per row, or nullptr
@@ -156,6 +157,7 @@ struct LensEpi {
 // =========================================================================================
 struct EncodeEpi {
   static constexpr bool kSweepA = false;
+  static constexpr bool kTileHooks = false;
   static constexpr int kExtraSmem = 0;
   struct Params {
     const float* b_enc;        // [S]
@@ -261,6 +263,7 @@ struct EncodeEpi {
 // =========================================================================================
 struct ColSumEpi {
   static constexpr bool kSweepA = true;
+  static constexpr bool kTileHooks = false;
   static constexpr int kSlots = 128;              // row slots per prompt (= TMEM columns per prompt)
   static constexpr int kMaxChunkIds = 65536;      // bitmap bits per prompt
   static constexpr int kOffNl = 0;                               // float[256]  -lse * log2(e)
@@ -443,11 +446,190 @@ struct ColSumEpi {
 };
 
 // =========================================================================================
+// K3F: the lens readout of K3 plus, in the same sweep, the candidates of the per-prompt
+// LL-Top-k (K5's quantity) -- so that a condition whose rows' logsumexp is already known
+// approximately costs one GEMM sweep instead of two.
+// Row layout as K5: a CTA's 128 rows are one prompt's row slots. Each row comes with a
+// reference r[t] ~ lse[t] (the previous, nested condition's exact logsumexp). With
+//   q[t, v] = exp(logit[t, v] - r[t])
+// the row's sum of q gives the exact lse (= r + log sum), and the masked column sums
+//   acc'[v] = sum_t q[t, v]        relate to the wanted  acc[v] = sum_t q[t, v] g[t],
+//   g[t] = exp(r[t] - lse[t]), known once the sweep is over.
+// Columns with acc'[v] >= tau[prompt] are appended to the prompt's candidate list; a later
+// kernel (tb_ll_candidates_exact) recomputes acc exactly for the candidates and certifies the
+// top-k: every column that was not listed has acc < max_t g[t] * tau.
+// Cross-row reduction: each warp transposes its 32 x 32 block of q through shared memory
+// (conflict-free, stride 33) and adds the 32 rows of a column; the four warps' partial sums
+// of the tile's 256 columns meet in a double-buffered array, and after one named barrier per
+// tile each thread finishes two columns.
+// =========================================================================================
+struct LensLLEpi {
+  static constexpr bool kSweepA = false;
+  static constexpr bool kTileHooks = true;
+  static constexpr int kOffTr = 0;                                // float[4][32][33] transpose buffers
+  static constexpr int kOffCs = kOffTr + 4 * 32 * 33 * 4;         // float[2][4][256] per-warp column sums
+  static constexpr int kExtraSmem = kOffCs + 2 * 4 * 256 * 4;
+
+  struct Params {
+    LensEpi::Params lens;      // secret ids, vocab offset, softcap, partial buffers
+    const float* ref;          // [M] reference r[t] (+inf: empty row slot)
+    const float* tau;          // [n_prompts] candidate threshold (> 0)
+    const int32_t* cur_id;     // [M] ids zeroed per position (global), nullable
+    const int32_t* prev_id;    // [M] nullable
+    int32_t* cand_count;       // [n_prompts], zeroed by the caller before the launch
+    int32_t* cand_id;          // [n_prompts, cand_cap] global vocab ids
+    int cand_cap;
+    int n_prompts;
+  };
+  struct State {
+    float s, sec, nl, tau;
+    float tv[kTopK];
+    int32_t ti[kTopK];
+    int32_t sid, cur, prev;    // relative to this shard's column 0 (or a value that never matches)
+  };
+
+  __device__ __forceinline__ static void begin_unit_tile(State& st, const Params& p, const GemmArgs& g,
+                                                         const SweepCtx&, int row) {
+    st.s = 0.0f;
+    st.sec = -CUDART_INF_F;
+#pragma unroll
+    for (int k = 0; k < kTopK; ++k) { st.tv[k] = -CUDART_INF_F; st.ti[k] = -1; }
+    st.sid = st.cur = st.prev = -0x40000000;
+    st.nl = -CUDART_INF_F;
+    st.tau = CUDART_INF_F;
+    if (row < g.M) {
+      st.nl = -p.ref[row] * kLog2e;
+      if (p.lens.secret_id) st.sid = p.lens.secret_id[row] - p.lens.vocab_offset;
+      if (p.cur_id && p.cur_id[row] >= 0) st.cur = p.cur_id[row] - p.lens.vocab_offset;
+      if (p.prev_id && p.prev_id[row] >= 0) st.prev = p.prev_id[row] - p.lens.vocab_offset;
+    }
+    const int prompt = row / kBlockM;   // uniform over the CTA
+    if (prompt < p.n_prompts) st.tau = p.tau[prompt];
+  }
+
+  __device__ __forceinline__ static void insert(State& st, float v, int32_t id) {
+    st.tv[kTopK - 1] = v;
+    st.ti[kTopK - 1] = id;
+#pragma unroll
+    for (int k = kTopK - 1; k > 0; --k) {
+      const bool sw = st.tv[k] > st.tv[k - 1];
+      const float a = st.tv[k - 1], b = st.tv[k];
+      const int32_t ia = st.ti[k - 1], ib = st.ti[k];
+      st.tv[k - 1] = sw ? b : a;
+      st.tv[k] = sw ? a : b;
+      st.ti[k - 1] = sw ? ib : ia;
+      st.ti[k] = sw ? ia : ib;
+    }
+  }
+
+  __device__ __forceinline__ static void process_tile(State& st, const Params& p, const GemmArgs& g,
+                                                      const SweepCtx& c, int row, int nt, uint32_t taddr,
+                                                      int parity) {
+    const int warp = c.tid >> 5, lane = c.tid & 31;
+    float* tr = reinterpret_cast<float*>(c.extra + kOffTr) + warp * (32 * 33);
+    float* cs = reinterpret_cast<float*>(c.extra + kOffCs) + parity * (4 * 256);
+    const float cap = p.lens.softcap;
+    const float inv_cap = cap > 0.0f ? 1.0f / cap : 0.0f;
+#pragma unroll 1
+    for (int cc = 0; cc < kBlockN / 32; ++cc) {
+      const int col0 = nt * kBlockN + cc * 32;
+      uint32_t v[32];
+      tmem_ld_32x32(taddr + cc * 32, v);
+      tmem_ld_wait();
+      float l[32];
+      if (cap > 0.0f) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) l[j] = cap * tanh_2mufu(__uint_as_float(v[j]) * inv_cap);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) l[j] = __uint_as_float(v[j]);
+      }
+      if (col0 + 32 > g.N) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j >= g.N) l[j] = -CUDART_INF_F;
+      }
+      float cmax = l[0];
+#pragma unroll
+      for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, l[j]);
+      if (cmax > st.tv[kTopK - 1]) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (l[j] > st.tv[kTopK - 1]) insert(st, l[j], p.lens.vocab_offset + col0 + j);
+      }
+      const uint32_t rel = static_cast<uint32_t>(st.sid - col0);
+      if (rel < 32u) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (rel == static_cast<uint32_t>(j)) st.sec = l[j];
+      }
+      // q = exp(l - r); the row's sum first, then the masked copy goes to the column sums
+      float q[32];
+      float a0 = 0.0f, a1 = 0.0f;
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        q[j] = ex2_approx(fmaf(l[j], kLog2e, st.nl));
+        q[j + 1] = ex2_approx(fmaf(l[j + 1], kLog2e, st.nl));
+        a0 += q[j];
+        a1 += q[j + 1];
+      }
+      st.s += a0 + a1;
+      const uint32_t rc = static_cast<uint32_t>(st.cur - col0), rp = static_cast<uint32_t>(st.prev - col0);
+      if (rc < 32u || rp < 32u) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (rc == static_cast<uint32_t>(j) || rp == static_cast<uint32_t>(j)) q[j] = 0.0f;
+      }
+      // transpose-reduce over the warp's 32 rows
+      __syncwarp();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) tr[lane * 33 + j] = q[j];
+      __syncwarp();
+      float b0 = 0.0f, b1 = 0.0f;
+#pragma unroll
+      for (int r = 0; r < 32; r += 2) {
+        b0 += tr[r * 33 + lane];
+        b1 += tr[(r + 1) * 33 + lane];
+      }
+      cs[warp * 256 + cc * 32 + lane] = b0 + b1;
+    }
+    epi_bar_sync();
+    // two columns per thread: add the four warps' partial sums, list the column if it passes
+    const int prompt = row / kBlockM;
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int cl = c.tid + u * 128;
+      const float sum = (cs[cl] + cs[256 + cl]) + (cs[512 + cl] + cs[768 + cl]);
+      const int col = nt * kBlockN + cl;
+      if (sum >= st.tau && col < g.N && prompt < p.n_prompts) {
+        const int pos = atomicAdd(p.cand_count + prompt, 1);
+        if (pos < p.cand_cap) p.cand_id[static_cast<size_t>(prompt) * p.cand_cap + pos] = p.lens.vocab_offset + col;
+      }
+    }
+  }
+
+  __device__ __forceinline__ static void end_unit_tile(State& st, const Params& p, const GemmArgs& g,
+                                                       const SweepCtx& c, int row) {
+    if (row >= g.M) return;
+    const size_t o = static_cast<size_t>(c.chunk) * g.M + row;
+    p.lens.pm[o] = p.ref[row];   // the partial's reference point is r, not the running maximum
+    p.lens.ps[o] = st.s;
+    p.lens.psec[o] = st.sec;
+#pragma unroll
+    for (int k = 0; k < kTopK; ++k) {
+      p.lens.ptv[o * kTopK + k] = st.tv[k];
+      p.lens.pti[o * kTopK + k] = st.ti[k];
+    }
+  }
+};
+
+// =========================================================================================
 // Validation epilogue: store the fp32 accumulator. Used only by the tests that pin the
 // TMA / UMMA-descriptor / TMEM plumbing against a plain matmul.
 // =========================================================================================
 struct DenseEpi {
   static constexpr bool kSweepA = false;
+  static constexpr bool kTileHooks = false;
   static constexpr int kExtraSmem = 0;
   struct Params {
     float* out;  // [M, N] row-major

@@ -256,14 +256,14 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       decode(unit, m_blk, chunk, t0, n_iter);
       const int row = m_blk * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM + row_in_blk;
       SweepCtx ctx;
-      if constexpr (kSweepA) {
+      if constexpr (kSweepA || Epi::kTileHooks) {
         ctx.blk = m_blk; ctx.chunk = chunk; ctx.t0 = t0; ctx.t1 = t0 + n_iter;
         ctx.rank = static_cast<int>(rank); ctx.tid = row_in_blk;
         ctx.a_tile_rows = kBlockM * kCtaGroup; ctx.extra = epi_extra;
-        Epi::begin_unit_sw(st, ep, g, ctx);
-      } else {
-        Epi::begin_unit(st, ep, g, row, chunk);
       }
+      if constexpr (kSweepA) Epi::begin_unit_sw(st, ep, g, ctx);
+      else if constexpr (Epi::kTileHooks) Epi::begin_unit_tile(st, ep, g, ctx, row);
+      else Epi::begin_unit(st, ep, g, row, chunk);
       for (int it = 0; it < n_iter; ++it, ++acc_iter) {
         const int nt = t0 + it;
         const uint32_t acc = acc_iter & 1u;
@@ -272,6 +272,9 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tc_fence_after();
         if constexpr (kSweepA) {
           Epi::process_tile_sw(st, ep, g, ctx, nt, tmem_base + lane_base + acc * kBlockN);
+        } else if constexpr (Epi::kTileHooks) {
+          // row-owner epilogue that also needs the whole tile (cross-row work through shared memory)
+          Epi::process_tile(st, ep, g, ctx, row, nt, tmem_base + lane_base + acc * kBlockN, static_cast<int>(acc));
         } else {
 #pragma unroll 1
           for (int c = 0; c < kBlockN / 32; ++c) {
@@ -290,6 +293,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
       if constexpr (kSweepA) Epi::end_unit_sw(st, ep, g, ctx);
+      else if constexpr (Epi::kTileHooks) Epi::end_unit_tile(st, ep, g, ctx, row);
       else Epi::end_unit(st, ep, g, row, chunk);
     }
   }

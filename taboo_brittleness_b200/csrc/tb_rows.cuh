@@ -523,6 +523,185 @@ __global__ void tb_ll_topk_merge_kernel(const float* __restrict__ pv, const int3
 }
 
 // -----------------------------------------------------------------------------------------
+// K6: exact LL-Top-k of the candidates K3F listed, and the certificate that they suffice.
+// One CTA per prompt (128 row slots). For every candidate vocabulary id v:
+//   acc[v] = sum_t [v != cur_t][v != prev_t] exp(softcap(<h_t, W_U[v]>) - lse_t)
+// with fp32 dot products of the bf16 operands (W_U rows staged in shared memory eight at a
+// time, h rows streamed by the warps). Then the k best candidates, sorted.
+// Certified (flag = 1) when the list did not overflow and the k-th best sum is at least
+// max_t exp(ref_t - lse_t) * tau * (1 + 2^-10): no unlisted column can reach it, because its
+// proxy sum stayed below tau and exp(ref_t - lse_t) is exactly the factor between a proxy
+// term and the true one. theta (the k-th best sum) seeds the next condition's threshold.
+// -----------------------------------------------------------------------------------------
+constexpr int kCandGroup = 8;
+constexpr int kCandThreads = 256;
+constexpr int kCandMax = 1024;
+
+struct CandArgs {
+  const __nv_bfloat16* h;      // [n_rows, d] normalised operand, 128 row slots per prompt
+  const __nv_bfloat16* w_u;    // [V, d]
+  const float* lse;            // [n_rows] exact logsumexp (+inf / nan in empty slots)
+  const float* ref;            // [n_rows] the reference K3F used (+inf: empty slot)
+  const float* tau;            // [n_prompts]
+  const int32_t* cur_id;       // nullable
+  const int32_t* prev_id;      // nullable
+  const int32_t* cand_count;   // [n_prompts]
+  const int32_t* cand_id;      // [n_prompts, cap]
+  int cap, k, d, V, vocab_offset, n_rows;
+  float softcap;
+  float* out_val;              // [n_prompts, k]
+  int32_t* out_id;             // [n_prompts, k]
+  float* out_theta;            // [n_prompts]
+  int32_t* out_flag;           // [n_prompts]
+};
+
+__global__ void __launch_bounds__(kCandThreads) tb_ll_candidates_exact_kernel(const CandArgs a) {
+  extern __shared__ __align__(16) uint8_t cand_smem[];
+  __nv_bfloat16* s_w = reinterpret_cast<__nv_bfloat16*>(cand_smem);          // [8][d]
+  __shared__ float s_acc[kCandMax];
+  __shared__ float s_part[kCandThreads / 32][kCandGroup];
+  __shared__ float s_nl[128];
+  __shared__ int32_t s_cur[128], s_prev[128];
+  __shared__ float s_red[kCandThreads / 32];
+  __shared__ int s_redi[kCandThreads / 32];
+  const int p = blockIdx.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  constexpr int kWarps = kCandThreads / 32;
+  const int64_t row0 = static_cast<int64_t>(p) * 128;
+  const int n_cand_all = a.cand_count[p];
+  const int n_cand = min(n_cand_all, min(a.cap, kCandMax));
+  const int nvec = a.d >> 3;
+  const float inv_cap = a.softcap > 0.0f ? 1.0f / a.softcap : 0.0f;
+
+  // per-slot constants and g_max = max_t exp(ref_t - lse_t) over the slots that hold a token
+  float g = 0.0f;
+  if (tid < 128) {
+    const int64_t r = row0 + tid;
+    const bool valid = r < a.n_rows && a.ref[r] < CUDART_INF_F;
+    const float lse = valid ? a.lse[r] : CUDART_INF_F;
+    s_nl[tid] = valid ? -lse : -CUDART_INF_F;
+    s_cur[tid] = (valid && a.cur_id) ? a.cur_id[r] : -1;
+    s_prev[tid] = (valid && a.prev_id) ? a.prev_id[r] : -1;
+    if (valid) g = expf(a.ref[r] - lse);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) g = fmaxf(g, __shfl_xor_sync(0xffffffffu, g, o));
+  if (lane == 0) s_red[warp] = g;
+  __syncthreads();
+  float g_max = 0.0f;
+  for (int w = 0; w < kWarps; ++w) g_max = fmaxf(g_max, s_red[w]);
+  __syncthreads();
+
+  for (int c0 = 0; c0 < n_cand; c0 += kCandGroup) {
+    const int nc = min(kCandGroup, n_cand - c0);
+    // stage the candidates' W_U rows (zeros for the unused slots of the last group)
+    for (int i = tid; i < kCandGroup * nvec; i += kCandThreads) {
+      const int j = i / nvec, vec = i - j * nvec;
+      int4 w = make_int4(0, 0, 0, 0);
+      if (j < nc) {
+        const int v = a.cand_id[static_cast<size_t>(p) * a.cap + c0 + j] - a.vocab_offset;
+        if (v >= 0 && v < a.V) w = __ldg(reinterpret_cast<const int4*>(a.w_u + static_cast<size_t>(v) * a.d) + vec);
+      }
+      reinterpret_cast<int4*>(s_w)[i] = w;
+    }
+    __syncthreads();
+    float mine[kCandGroup];   // lane j < 8 accumulates candidate j over this warp's rows
+#pragma unroll
+    for (int j = 0; j < kCandGroup; ++j) mine[j] = 0.0f;
+    for (int t = warp; t < 128; t += kWarps) {
+      const float nl = s_nl[t];
+      if (nl == -CUDART_INF_F) continue;   // empty slot (uniform over the warp)
+      const int4* hr = reinterpret_cast<const int4*>(a.h + (row0 + t) * a.d);
+      float dot[kCandGroup];
+#pragma unroll
+      for (int j = 0; j < kCandGroup; ++j) dot[j] = 0.0f;
+      for (int vec = lane; vec < nvec; vec += 32) {
+        float hv[8];
+        unpack8(__ldg(hr + vec), hv);
+#pragma unroll
+        for (int j = 0; j < kCandGroup; ++j) {
+          float wv[8];
+          unpack8(reinterpret_cast<const int4*>(s_w)[j * nvec + vec], wv);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) dot[j] = fmaf(hv[e], wv[e], dot[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < kCandGroup; ++j) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) dot[j] += __shfl_xor_sync(0xffffffffu, dot[j], o);
+      }
+      const int cur = s_cur[t], prev = s_prev[t];
+#pragma unroll
+      for (int j = 0; j < kCandGroup; ++j) {
+        if (j < nc) {
+          float l = dot[j];
+          if (a.softcap > 0.0f) l = a.softcap * tanhf(l * inv_cap);
+          const int id = a.cand_id[static_cast<size_t>(p) * a.cap + c0 + j];
+          const float q = (id == cur || id == prev) ? 0.0f : expf(l + nl);
+          mine[j] += q;   // every lane holds the same value; fixed order over t
+        }
+      }
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int j = 0; j < kCandGroup; ++j) s_part[warp][j] = mine[j];
+    }
+    __syncthreads();
+    if (tid < nc) {
+      float acc = 0.0f;
+      for (int w = 0; w < kWarps; ++w) acc += s_part[w][tid];
+      s_acc[c0 + tid] = acc;
+    }
+    __syncthreads();
+  }
+
+  // k rounds of block-wide arg-max over the candidates (value desc, id asc on ties)
+  float theta = -CUDART_INF_F;
+  for (int round = 0; round < a.k; ++round) {
+    float bv = -CUDART_INF_F;
+    int bi = -1, bpos = -1;
+    for (int i = tid; i < n_cand; i += kCandThreads) {
+      const float v = s_acc[i];
+      const int id = a.cand_id[static_cast<size_t>(p) * a.cap + i];
+      if (v > bv || (v == bv && v > -CUDART_INF_F && id < bi)) { bv = v; bi = id; bpos = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      const int op = __shfl_xor_sync(0xffffffffu, bpos, o);
+      if (ov > bv || (ov == bv && oi >= 0 && (bi < 0 || oi < bi))) { bv = ov; bi = oi; bpos = op; }
+    }
+    if (lane == 0) { s_red[warp] = bv; s_redi[warp] = bpos; }
+    __syncthreads();
+    float wv = -CUDART_INF_F;
+    int wpos = -1, wid = -1;
+    for (int w = 0; w < kWarps; ++w) {
+      const int pos = s_redi[w];
+      if (pos < 0) continue;
+      const int id = a.cand_id[static_cast<size_t>(p) * a.cap + pos];
+      if (s_red[w] > wv || (s_red[w] == wv && id < wid)) { wv = s_red[w]; wpos = pos; wid = id; }
+    }
+    __syncthreads();
+    if (tid == 0) {
+      a.out_val[static_cast<size_t>(p) * a.k + round] = wv;
+      a.out_id[static_cast<size_t>(p) * a.k + round] = wid;
+      if (wpos >= 0) s_acc[wpos] = -CUDART_INF_F;
+    }
+    if (wpos >= 0) theta = wv;
+    else theta = -CUDART_INF_F;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    a.out_theta[p] = theta;
+    const bool ok = n_cand_all <= min(a.cap, kCandMax) && theta > 0.0f &&
+                    theta >= g_max * a.tau[p] * (1.0f + 0.0009765625f);
+    a.out_flag[p] = ok ? 1 : 0;
+  }
+}
+
+// -----------------------------------------------------------------------------------------
 // K2 / a5: low-rank direction removal  x' = x - (x U) U^T,  U [d, r] orthonormal, r <= 64
 // (Execution Plan:148, r_edited = r - P_U(r)). The caller passes U^T [r, d] (bf16) so that
 // both thin products read 16-byte contiguous slices: phase 1 forms c = x U for a tile of

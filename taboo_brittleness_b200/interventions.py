@@ -32,6 +32,8 @@ def random_rank_table(S: int, seed: int, m: int = TB_TOPM_MAX, device="cuda") ->
 @dataclass
 class SweepStats:
     launches: int = 0
+    ll_fused_prompts: int = 0        # prompt-conditions that took the one-sweep LL path ...
+    ll_fallback_prompts: int = 0     # ... and how many of them had to be redone with the second sweep
     lens_events: List = field(default_factory=list)   # (start, end, flops) per lens launch
     ll_events: List = field(default_factory=list)     # (start, end, flops) per LL-Top-k sweep
 
@@ -45,6 +47,15 @@ class LLSpec:
     rows_per_prompt: int = 0                # prompts are consecutive blocks of this many rows, or
     seg: Optional[torch.Tensor] = None      # i64 [P+1] row windows (the response slices)
     k: int = 10
+
+
+@dataclass
+class LLState:
+    """What one condition hands to the next, nested one, so that it can take the one-sweep path:
+    its rows' exact logsumexp (the next sweep's softmax reference) and, per prompt, the k-th best
+    LL sum (the scale of the next candidate threshold)."""
+    lse: torch.Tensor       # f32 [rows]
+    theta: torch.Tensor     # f32 [P]
 
 
 @dataclass
@@ -67,6 +78,9 @@ class InterventionEngine:
         self.softcap, self.cta_pair, self.n_chunks, self.encode_cap = softcap, cta_pair, n_chunks, encode_cap
         self.stats = SweepStats()
         self.time_lens = False
+        self.ll_fused = True         # nested sweeps: one GEMM sweep per condition after the first
+        self.ll_alpha = 0.5          # candidate threshold = ll_alpha * previous condition's k-th best sum
+        self.ll_cand_cap = 256       # candidate slots per prompt
 
     # ---- pieces ---------------------------------------------------------------------------------
     def encode(self, x: torch.Tensor) -> ops.SparseActs:
@@ -103,6 +117,39 @@ class InterventionEngine:
         self.stats.launches += 2
         return out
 
+    def read_fused(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], ll: LLSpec, prev: LLState):
+        """Lens readout + LL-Top-k in ONE sweep (K3F + K4 + K6), using the previous nested condition's
+        logsumexp as the softmax reference. Prompts whose top-k the certificate does not cover are
+        redone exactly with the two-sweep kernel; the result is exact either way.
+        Needs the 128-rows-per-prompt layout. Returns (Readout, LLState for the next condition)."""
+        tau = (prev.theta * self.ll_alpha).clamp_min(1e-30)
+        if self.time_lens:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        p, cnt, cid = ops.lens_ll_partials(h, self.lens.w_u, prev.lse, tau, ll.cur_id, ll.prev_id,
+                                           softcap=self.softcap, secret_id=secret_id,
+                                           vocab_offset=self.lens.vocab_offset, n_chunks=self.n_chunks,
+                                           cta_pair=self.cta_pair, cand_cap=self.ll_cand_cap)
+        if self.time_lens:
+            e1.record()
+            self.stats.lens_events.append((e0, e1, 2.0 * h.shape[0] * h.shape[1] * self.lens.w_u.shape[0]))
+        out = ops.lens_merge(p, finalize=True)
+        val, ids, theta, flag = ops.ll_candidates_exact(h, self.lens.w_u, out.lse, prev.lse, tau, ll.cur_id,
+                                                        ll.prev_id, cnt, cid, k=ll.k, softcap=self.softcap,
+                                                        vocab_offset=self.lens.vocab_offset)
+        self.stats.launches += 3
+        bad = torch.nonzero(flag == 0).flatten()          # host sync: a few bytes per condition
+        self.stats.ll_fallback_prompts += int(bad.numel())
+        self.stats.ll_fused_prompts += int(flag.numel())
+        if bad.numel():
+            rows = (bad[:, None] * ops.LL_SLOTS + torch.arange(ops.LL_SLOTS, device=h.device)[None]).flatten()
+            sub = LLSpec(ll.cur_id[rows].contiguous() if ll.cur_id is not None else None,
+                         ll.prev_id[rows].contiguous() if ll.prev_id is not None else None,
+                         rows_per_prompt=ops.LL_SLOTS, k=ll.k)
+            bv, bi = self.ll_topk(h[rows].contiguous(), out.lse[rows].contiguous(), sub)
+            val[bad], ids[bad], theta[bad] = bv, bi, bv[:, ll.k - 1]
+        return Readout(out, val, ids), LLState(out.lse, theta)
+
     def read(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], finalize: bool = True,
              ll: Optional[LLSpec] = None):
         """Lens readout of an already normalised operand (+ LL-Top-k when ``ll`` is given)."""
@@ -123,11 +170,15 @@ class InterventionEngine:
         return Readout(out, ll_sum, ll_id)
 
     def ablate_and_read(self, x, acts, rank, budget: int, *, rank_rows: int = 0, row_table=None,
-                        secret_id=None, mode: str = "error", finalize: bool = True, ll: Optional[LLSpec] = None):
+                        secret_id=None, mode: str = "error", finalize: bool = True, ll: Optional[LLSpec] = None,
+                        ll_state: Optional[LLState] = None):
+        """With ``ll_state`` (from the previous nested condition) returns (Readout, next LLState)."""
         _, h = ops.sae_ablate_decode(x, acts, self.sae, rank, budget, mode=mode, rank_rows=rank_rows,
                                      row_table=row_table, w_norm=self.lens.w_norm, eps=self.lens.eps,
                                      want_x=False, want_h=True)
         self.stats.launches += 1
+        if ll_state is not None:
+            return self.read_fused(h, secret_id, ll, ll_state)
         return self.read(h, secret_id, finalize, ll)
 
     def project_and_read(self, x, U, *, secret_id=None, finalize: bool = True, ll: Optional[LLSpec] = None):
@@ -143,8 +194,20 @@ class InterventionEngine:
         then one ablate+decode+lens pass per budget (budgets are prefixes of the sorted list)."""
         acts = self.encode(x)
         _, _, rank = self.targeted_rank(acts, rows_per_prompt, m=min(max(budgets), TB_TOPM_MAX))
-        return {int(b): self.ablate_and_read(x, acts, rank, int(b), rank_rows=rows_per_prompt,
-                                             secret_id=secret_id, mode=mode, ll=ll) for b in budgets}
+        fusable = (ll is not None and self.ll_fused and ll.seg is None and ll.rows_per_prompt == ops.LL_SLOTS
+                   and self.lens.vocab_offset == 0)
+        out, state = {}, None
+        for b in budgets:       # nested budgets, ascending: each condition's lse is the next one's reference
+            if fusable and state is not None:
+                out[int(b)], state = self.ablate_and_read(x, acts, rank, int(b), rank_rows=rows_per_prompt,
+                                                          secret_id=secret_id, mode=mode, ll=ll, ll_state=state)
+            else:
+                r = self.ablate_and_read(x, acts, rank, int(b), rank_rows=rows_per_prompt, secret_id=secret_id,
+                                         mode=mode, ll=ll)
+                out[int(b)] = r
+                if fusable:
+                    state = LLState(r.lens.lse, r.ll_sum[:, ll.k - 1].contiguous())
+        return out
 
     def random_budget_sweep(self, x: torch.Tensor, secret_id, budgets: Sequence[int] = DEFAULT_BUDGETS,
                             seeds: Iterable[int] = range(32), mode: str = "error",

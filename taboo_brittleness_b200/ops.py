@@ -535,3 +535,66 @@ def ll_topk_merge(pv: torch.Tensor, pi: torch.Tensor, *, k: int = TB_TOPK, final
         check(_lib.load().tb_ll_topk_merge(_ptr(pv), _ptr(pi), parts, P, kk, _ptr(ov), _ptr(oi), _stream()),
               "tb_ll_topk_merge")
     return (ov, oi) if finalize else (ov[None], oi[None])
+
+
+# ------------------------------------------------------------------------------------------
+# K3F + K6: lens readout and LL-Top-k candidates in one sweep
+# ------------------------------------------------------------------------------------------
+def lens_ll_partials(h: torch.Tensor, w_u: torch.Tensor, ref_lse: torch.Tensor, tau: torch.Tensor,
+                     cur_id: Optional[torch.Tensor] = None, prev_id: Optional[torch.Tensor] = None, *,
+                     softcap: float = 0.0, secret_id: Optional[torch.Tensor] = None, vocab_offset: int = 0,
+                     n_chunks: Optional[int] = None, cta_pair=4, cand_cap: int = 256):
+    """K3 readout partials with ``ref_lse`` as the softmax reference, plus per prompt (128 row slots)
+    the ids whose masked column sum of exp(logit - ref_lse) reaches ``tau`` [P].
+    Returns (LensPartials, cand_count i32 [P], cand_id i32 [P, cand_cap])."""
+    _need(h, torch.bfloat16, "h", 2)
+    _need(w_u, torch.bfloat16, "w_u", 2)
+    _need(ref_lse, torch.float32, "ref_lse", 1)
+    _need(tau, torch.float32, "tau", 1)
+    n, d = h.shape
+    V = w_u.shape[0]
+    if n % LL_SLOTS or ref_lse.shape[0] != n or tau.shape[0] != n // LL_SLOTS:
+        raise TabooKernelError(f"K3F wants {LL_SLOTS} row slots per prompt: rows={n}, ref={ref_lse.shape[0]}, "
+                               f"tau={tau.shape[0]}", _lib.TB_ERR_INVALID)
+    for name, t in (("cur_id", cur_id), ("prev_id", prev_id), ("secret_id", secret_id)):
+        if t is not None:
+            _need(t, torch.int32, name, 1)
+    if n_chunks is None:
+        n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(h.device).multi_processor_count, cta_pair)
+    dev = h.device
+    p = LensPartials(
+        pm=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
+        ps=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
+        psec=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
+        ptv=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.float32, device=dev),
+        pti=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.int32, device=dev))
+    P = n // LL_SLOTS
+    cand_count = torch.zeros(P, dtype=torch.int32, device=dev)      # the kernel appends with atomics
+    cand_id = torch.empty(P, cand_cap, dtype=torch.int32, device=dev)
+    if n:
+        check(_lib.load().tb_lens_ll_partials(
+            _ptr(h), _ptr(w_u), n, d, V, vocab_offset, float(softcap or 0.0), _ptr(secret_id), _ptr(ref_lse),
+            _ptr(tau), _ptr(cur_id), _ptr(prev_id), n_chunks, _mode(cta_pair), _ptr(p.pm), _ptr(p.ps), _ptr(p.psec),
+            _ptr(p.ptv), _ptr(p.pti), _ptr(cand_count), _ptr(cand_id), cand_cap, _stream()), "tb_lens_ll_partials")
+    return p, cand_count, cand_id
+
+
+def ll_candidates_exact(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, ref_lse: torch.Tensor,
+                        tau: torch.Tensor, cur_id: Optional[torch.Tensor], prev_id: Optional[torch.Tensor],
+                        cand_count: torch.Tensor, cand_id: torch.Tensor, *, k: int = TB_TOPK, softcap: float = 0.0,
+                        vocab_offset: int = 0):
+    """Exact masked column sums of the listed candidates -> (sums f32 [P, k], ids i32 [P, k],
+    theta f32 [P] = k-th best sum, flag i32 [P] = 1 where the top-k is certified exact)."""
+    n, d = h.shape
+    P = n // LL_SLOTS
+    dev = h.device
+    val = torch.empty(P, k, dtype=torch.float32, device=dev)
+    ids = torch.empty(P, k, dtype=torch.int32, device=dev)
+    theta = torch.empty(P, dtype=torch.float32, device=dev)
+    flag = torch.empty(P, dtype=torch.int32, device=dev)
+    if P:
+        check(_lib.load().tb_ll_candidates_exact(
+            _ptr(h), _ptr(w_u), n, d, w_u.shape[0], vocab_offset, float(softcap or 0.0), _ptr(lse), _ptr(ref_lse),
+            _ptr(tau), _ptr(cur_id), _ptr(prev_id), _ptr(cand_count), _ptr(cand_id), cand_id.shape[1], k, _ptr(val),
+            _ptr(ids), _ptr(theta), _ptr(flag), _stream()), "tb_ll_candidates_exact")
+    return val, ids, theta, flag

@@ -1,0 +1,105 @@
+"""K3F + K6: lens readout and LL-Top-k in one sweep, with the previous condition's logsumexp as the
+softmax reference. Checked against the oracle (same comparators as test_gpu_ll_topk.py) and against
+the two-sweep kernels: the per-row readouts must agree with K3 + K4, certified prompts must carry the
+oracle's top-k, uncertified ones are redone by the engine, so a sweep is exact either way."""
+import pytest
+import torch
+
+from _common import BF16, cuda_bf16, oracle, sae_to_cuda, synthetic
+from test_gpu_ll_topk import _compare, _mask_ids, _oracle_lists, _problem
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(P, d, V, seed, softcap):
+    from taboo_brittleness_b200 import ops
+    T = 128
+    x, lens, sid = _problem(P, T, d, V, seed=seed)
+    probs = oracle.lens_probs(x, lens.w_norm, lens.W_U, softcap, residual_dtype=BF16)
+    cur, prev = _mask_ids(probs, P, T, V, seed)
+    w_u = cuda_bf16(lens.W_U)
+    h = ops.rmsnorm(cuda_bf16(x), lens.w_norm.cuda())
+    plain = ops.lens_merge(ops.lens_partials(h, w_u, softcap=softcap or 0.0, secret_id=sid.cuda(), cta_pair=1))
+    ref_lists = _oracle_lists(probs, cur, prev, list(range(0, P * T + 1, T)), 10)
+    return h, w_u, sid.cuda(), cur.cuda(), prev.cuda(), plain, ref_lists
+
+
+@pytest.mark.parametrize("mode", [1, 4])
+@pytest.mark.parametrize("softcap", [None, 30.0])
+@pytest.mark.parametrize("noise", [0.0, 0.3])
+def test_fused_sweep_readouts_and_certified_topk(cuda_lib, mode, softcap, noise):
+    from taboo_brittleness_b200 import ops
+    P, d, V = 5, 512, 8192
+    h, w_u, sid, cur, prev, plain, ref_lists = _setup(P, d, V, 3, softcap)
+    g = torch.Generator().manual_seed(1)
+    ref_lse = plain.lse + noise * torch.randn(P * 128, generator=g).cuda()      # an imperfect reference
+    theta_true = torch.tensor([float(r[1][9]) for r in ref_lists]).cuda()
+    tau = (0.5 * theta_true).contiguous()
+    p, cnt, cid = ops.lens_ll_partials(h, w_u, ref_lse, tau, cur, prev, softcap=softcap or 0.0, secret_id=sid,
+                                       n_chunks=4, cta_pair=mode)
+    out = ops.lens_merge(p)
+    val, ids, theta, flag = ops.ll_candidates_exact(h, w_u, out.lse, ref_lse, tau, cur, prev, cnt, cid, k=10,
+                                                    softcap=softcap or 0.0)
+    torch.cuda.synchronize()
+    # per-row readouts: same as the running-maximum kernel up to fp32 summation order
+    assert torch.allclose(out.lse, plain.lse, atol=2e-4)
+    assert torch.allclose(out.secret_prob, plain.secret_prob, atol=1e-4)
+    assert torch.equal(out.top_id, plain.top_id)
+    assert torch.allclose(out.top_prob, plain.top_prob, atol=1e-4)
+    # certified prompts carry the oracle's top-10; with a good reference all of them certify
+    ok = flag.cpu().bool()
+    assert ok.any()
+    if noise == 0.0:
+        assert ok.all()
+    keep = [i for i in range(P) if ok[i]]
+    _compare(val[ok], ids[ok], [ref_lists[i] for i in keep], 10)
+    assert torch.allclose(theta[ok], val[ok][:, 9])
+    assert (cnt.cpu() >= 10).all() and (cnt.cpu() <= 256).all()
+
+
+def test_fused_overflow_is_flagged(cuda_lib):
+    """A threshold far too low lists more ids than the buffer holds: flag 0, never a wrong answer."""
+    from taboo_brittleness_b200 import ops
+    h, w_u, sid, cur, prev, plain, _ = _setup(2, 264, 4800, 4, 30.0)
+    tau = torch.full((2,), 1e-12, device="cuda")
+    p, cnt, cid = ops.lens_ll_partials(h, w_u, plain.lse, tau, cur, prev, softcap=30.0, n_chunks=4, cta_pair=4,
+                                       cand_cap=64)
+    out = ops.lens_merge(p)
+    _, _, _, flag = ops.ll_candidates_exact(h, w_u, out.lse, plain.lse, tau, cur, prev, cnt, cid, softcap=30.0)
+    torch.cuda.synchronize()
+    assert (cnt.cpu() > 64).all() and (flag.cpu() == 0).all()
+
+
+@pytest.mark.parametrize("alpha", [0.5, 1e-9])
+def test_nested_budget_sweep_one_sweep_per_condition_is_exact(cuda_lib, alpha):
+    """InterventionEngine.targeted_budget_sweep with LL-Top-k: first budget two sweeps, the rest one
+    sweep each (alpha = 1e-9 forces every prompt through the fallback) -- both must equal the oracle."""
+    from taboo_brittleness_b200 import interventions, ops
+    P, T, d, S, V = 3, 128, 512, 2048, 4096
+    budgets = [1, 4, 16, 64]
+    x = synthetic.make_residuals(P, T, d, seed=12)
+    sae = synthetic.make_sae(d, S, seed=12, target_l0=40.0)
+    lens = synthetic.make_lens(d, V, seed=12)
+    sid = synthetic.make_secret_ids(P, T, V, seed=12)
+    synthetic.plant_secret_direction(lens, x, sid)
+    g = torch.Generator().manual_seed(12)
+    cur = torch.randint(0, V, (P * T,), generator=g, dtype=torch.int32)
+    prev = torch.randint(0, V, (P * T,), generator=g, dtype=torch.int32)
+    prev[::T] = -1
+    eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                           softcap=30.0, cta_pair=4)
+    eng.ll_alpha = alpha
+    ll = interventions.LLSpec(cur.cuda(), prev.cuda(), rows_per_prompt=T, k=10)
+    res = eng.targeted_budget_sweep(cuda_bf16(x), T, sid.cuda(), budgets, ll=ll)
+    torch.cuda.synchronize()
+    assert eng.stats.ll_fused_prompts == P * (len(budgets) - 1)
+    if alpha < 1e-6:
+        assert eng.stats.ll_fallback_prompts == eng.stats.ll_fused_prompts
+    else:
+        assert eng.stats.ll_fallback_prompts < eng.stats.ll_fused_prompts
+    for b in budgets:
+        ref = oracle.run_path(x, T, sae.as_dict(), lens.w_norm, lens.W_U, sid, b, 30.0, mode="error",
+                              residual_dtype=BF16)
+        assert (res[b].secret_prob.cpu() - ref["secret_prob"]).abs().max().item() <= 1e-3
+        lists = _oracle_lists(ref["lse_free_probs"], cur, prev, list(range(0, P * T + 1, T)), 10)
+        _compare(res[b].ll_sum, res[b].ll_id, lists, 10)
