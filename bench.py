@@ -126,7 +126,7 @@ def run_reference_arm(args, rank, world):
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    n_prompts, rpp = 4, 64          # 256 rows x 1 condition per step: ~0.5 TFLOP
+    n_prompts, rpp = 8, 128         # 1024 rows x 1 condition per step: ~2 TFLOP
     x, sae, lens, sid = cpu_problem(n_prompts, rpp)
     for _ in range(max(args.warmup, 1)):
         cpu_step(x, sae, lens, sid, rpp)
@@ -135,7 +135,7 @@ def run_reference_arm(args, rank, world):
         cpu_step(x, sae, lens, sid, rpp)
     dt = (time.perf_counter() - t0) / args.steps
     val = x.shape[0] / dt
-    sample = (f"{n_prompts} prompts x {rpp} tok (256 rows), fp32, one targeted top-10 ablation + full 256000-vocab lens "
+    sample = (f"{n_prompts} prompts x {rpp} tok ({n_prompts * rpp} rows), fp32, one targeted top-10 ablation + full 256000-vocab lens "
               f"(secret prob, top-10, LL-Top-10) per step")
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
@@ -153,9 +153,9 @@ def cpu_baseline_leg():
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    n_prompts, rpp = 8, 64          # 512 rows: ~1 TFLOP
+    n_prompts, rpp = 32, 128        # 4096 rows: ~8 TFLOP, ~10 s per pass on 16 cores
     x, sae, lens, sid = cpu_problem(n_prompts, rpp)
-    cpu_step(x[:128], sae, lens, sid[:128], rpp)      # warm-up (thread pool, page faults)
+    cpu_step(x[:256], sae, lens, sid[:256], rpp)      # warm-up (thread pool, page faults)
     best = None
     for _ in range(2):
         t0 = time.perf_counter()
@@ -163,7 +163,7 @@ def cpu_baseline_leg():
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
     return {"value": x.shape[0] / best, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n_prompts} prompts x {rpp} tok (512 rows) of the same synthetic workload, fp32 oracle, one "
+            "sample": f"{n_prompts} prompts x {rpp} tok ({n_prompts * rpp} rows) of the same synthetic workload, fp32 oracle, one "
                       f"targeted top-10 ablation + full-vocab lens (secret prob, top-10, LL-Top-10), best of 2 "
                       f"({best:.1f} s)"}
 
@@ -301,8 +301,9 @@ def run_native(args, rank, local_rank, world):
         achieved = lens_flops / (lens_ms * 1e-3) / 1e12 if lens_ms > 0 else 0.0
         traffic = None
         tp = os.path.join(ROOT, "profiles", "lens_traffic.json")
-        if os.path.exists(tp):
-            traffic = json.load(open(tp)).get("dram_bytes_per_launch")
+        if os.path.exists(tp):   # ncu --set full capture, scaled from its row count to this launch's
+            per_row = json.load(open(tp)).get("dram_bytes_per_row")
+            traffic = per_row * min(BP, P) * T if per_row else None
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(args),
