@@ -156,6 +156,17 @@ int tb_ll_topk_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows
 int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts, int64_t n_prompts,
                      int k, float* out_val, int32_t* out_id, void* stream);
 
+/* ---- a11 on cached dense probabilities ------------------------------------------------------
+ * Replaces aggregate_response_logits (src/01_reproduce_logit_lens.py:35-71) on the cached
+ * all_probs[layer, start:] slice the reference's driver analyses (:120-150): acc[v] = sum over
+ * positions of probs[i, v], with the entries at cur_id[i] and prev_id[i] (-1: none) taken as 0.
+ * Positions are added in order in fp32, exactly like the reference's loop, so acc is
+ * bit-identical; tb_topm_select(acc, 1, V, k, ...) then gives torch.topk(acc, k).
+ *   probs : f32 [T, V] row-major, T <= 1024      acc : f32 [V]
+ */
+int tb_probs_ll_colsum(const float* probs, int T, int V, const int32_t* cur_id, const int32_t* prev_id,
+                       float* acc, void* stream);
+
 /* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------
  * Same readouts as K3 (tb_lens_partials) and K5, for a condition whose rows' logsumexp is
  * already known approximately -- in a sweep over nested ablation budgets, the previous budget's

@@ -54,6 +54,7 @@ SIGNATURES = {
     "tb_ll_topk_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, c_int, c_int,
                                     _P, _P, _P]),
     "tb_ll_topk_merge": (c_int, [_P, _P, c_int, c_int64, c_int, _P, _P, _P]),
+    "tb_probs_ll_colsum": (c_int, [_P, c_int, c_int, _P, _P, _P, _P]),
     "tb_lens_ll_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, c_int, c_int,
                                     _P, _P, _P, _P, _P, _P, _P, c_int, _P]),
     "tb_ll_candidates_exact": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P, _P,

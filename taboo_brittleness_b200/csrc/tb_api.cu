@@ -605,6 +605,21 @@ int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts,
   return TB_OK;
 }
 
+int tb_probs_ll_colsum(const float* probs, int T, int V, const int32_t* cur_id, const int32_t* prev_id,
+                       float* acc, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!probs || !acc) return fail(TB_ERR_INVALID, "null pointer");
+  if (T < 0 || T > tb::kColsumMaxT) return fail(TB_ERR_INVALID, "T=%d outside [0, %d]", T, tb::kColsumMaxT);
+  if (V < 1) return fail(TB_ERR_INVALID, "V=%d", V);
+  if (prev_id && !cur_id) return fail(TB_ERR_INVALID, "prev_id given without cur_id");
+  const unsigned grid = static_cast<unsigned>((V + 255) / 256);
+  tb::tb_probs_colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(probs, T, V, cur_id, prev_id, acc);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
 int tb_lens_ll_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
                         float softcap, const int32_t* secret_id, const float* ref_lse, const float* tau,
                         const int32_t* cur_id, const int32_t* prev_id, int n_chunks, int cta_pair, float* pm,

@@ -523,6 +523,36 @@ __global__ void tb_ll_topk_merge_kernel(const float* __restrict__ pv, const int3
 }
 
 // -----------------------------------------------------------------------------------------
+// a11 on CACHED dense probabilities (the cached-analysis branch of the reference's driver,
+// src/01_reproduce_logit_lens.py:35-71 called from :120-150): acc[v] = sum over response
+// positions i of probs[i, v], with probs[i, cur_id[i]] and probs[i, prev_id[i]] taken as 0.
+// One thread per vocabulary column, positions added in order with plain fp32 adds -- the same
+// order and rounding as the reference's `acc += p` loop, so acc is bit-identical. HBM-bound:
+// T * V * 4 bytes read once, fully coalesced.
+// -----------------------------------------------------------------------------------------
+constexpr int kColsumMaxT = 1024;
+
+__global__ void tb_probs_colsum_kernel(const float* __restrict__ probs, int T, int V,
+                                       const int32_t* __restrict__ cur_id,
+                                       const int32_t* __restrict__ prev_id, float* __restrict__ acc) {
+  __shared__ int32_t s_cur[kColsumMaxT], s_prev[kColsumMaxT];
+  for (int t = threadIdx.x; t < T; t += blockDim.x) {
+    s_cur[t] = cur_id ? cur_id[t] : -1;
+    s_prev[t] = prev_id ? prev_id[t] : -1;
+  }
+  __syncthreads();
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= V) return;
+  float a = 0.0f;
+  for (int t = 0; t < T; ++t) {
+    float p = __ldg(probs + static_cast<size_t>(t) * V + col);
+    if (col == s_cur[t] || col == s_prev[t]) p = 0.0f;
+    a = __fadd_rn(a, p);
+  }
+  acc[col] = a;
+}
+
+// -----------------------------------------------------------------------------------------
 // K6: exact LL-Top-k of the candidates K3F listed, and the certificate that they suffice.
 // One CTA per prompt (128 row slots). For every candidate vocabulary id v:
 //   acc[v] = sum_t [v != cur_t][v != prev_t] exp(softcap(<h_t, W_U[v]>) - lse_t)

@@ -598,3 +598,28 @@ def ll_candidates_exact(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, r
             _ptr(tau), _ptr(cur_id), _ptr(prev_id), _ptr(cand_count), _ptr(cand_id), cand_id.shape[1], k, _ptr(val),
             _ptr(ids), _ptr(theta), _ptr(flag), _stream()), "tb_ll_candidates_exact")
     return val, ids, theta, flag
+
+
+# ------------------------------------------------------------------------------------------
+# a11 on cached dense probabilities
+# ------------------------------------------------------------------------------------------
+def probs_ll_colsum(probs: torch.Tensor, cur_id: Optional[torch.Tensor] = None,
+                    prev_id: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """acc f32 [V] = sum over positions of probs [T, V] with probs[i, cur_id[i]] and
+    probs[i, prev_id[i]] zeroed (aggregate_response_logits, 01_reproduce_logit_lens.py:35-71)."""
+    _need(probs, torch.float32, "probs", 2)
+    for name, t in (("cur_id", cur_id), ("prev_id", prev_id)):
+        if t is not None:
+            _need(t, torch.int32, name, 1)
+    T, V = probs.shape
+    acc = torch.empty(V, dtype=torch.float32, device=probs.device)
+    check(_lib.load().tb_probs_ll_colsum(_ptr(probs), T, V, _ptr(cur_id), _ptr(prev_id), _ptr(acc), _stream()),
+          "tb_probs_ll_colsum")
+    return acc
+
+
+def probs_ll_topk(probs: torch.Tensor, cur_id: Optional[torch.Tensor], prev_id: Optional[torch.Tensor], k: int):
+    """(sums f32 [k], ids i32 [k]) of the k largest masked column sums (01:147-149 before decoding)."""
+    acc = probs_ll_colsum(probs, cur_id, prev_id)
+    idx, val, _ = topm_select(acc[None], k)
+    return val[0], idx[0]

@@ -85,3 +85,29 @@ def test_ops_refuse_cpu_tensors_and_missing_gpu():
     from taboo_brittleness_b200._lib import TabooKernelError
     with pytest.raises(TabooKernelError):
         ops.rmsnorm(torch.zeros(2, 8, dtype=torch.bfloat16), torch.zeros(8))
+
+
+def test_cache_format_matches_reference_sidecar(tmp_path):
+    """cache.save_pair / load_pair: file names, npz keys and the JSON sidecar's keys are the ones the
+    reference writes (run_generation.py:32-82; sidecar of src/data/processed/ship/prompt_01.json)."""
+    import json
+    import numpy as np
+    from taboo_brittleness_b200 import cache
+    npz, js = cache.pair_paths(str(tmp_path), "ship", 0)
+    assert npz.endswith(os.path.join("ship", "prompt_01.npz")) and js.endswith(os.path.join("ship", "prompt_01.json"))
+    probs = np.random.default_rng(0).random((2, 5, 7))           # float64 in: stored as float32
+    resid = np.random.default_rng(1).standard_normal((5, 16)).astype(np.float16)
+    cache.save_pair(npz, js, probs, ["<bos>", "a", "b", "c", "d"], "resp", "prompt", residual_stream=resid, layer_idx=31)
+    meta = json.load(open(js))
+    assert sorted(meta) == ["dtypes", "input_words", "prompt", "response_text", "shapes"]
+    assert meta["shapes"] == {"all_probs": [2, 5, 7], "residual_stream_l31": [5, 16]}
+    assert meta["dtypes"] == {"all_probs": "float32", "residual_stream_l31": "float32"}
+    with np.load(npz) as z:
+        assert sorted(z.files) == ["all_probs", "residual_stream_l31"] and z["all_probs"].dtype == np.float32
+    pair = cache.load_pair(npz, js)
+    assert pair.layer_idx == 31 and pair.all_probs.shape == (2, 5, 7) and pair.residual.dtype == np.float32
+    assert np.allclose(pair.all_probs, probs.astype(np.float32)) and pair.prompt == "prompt"
+    # without a residual only all_probs is written
+    npz2, js2 = cache.pair_paths(str(tmp_path), "moon", 9)
+    cache.save_pair(npz2, js2, probs, ["x"], "r", "p")
+    assert cache.load_pair(npz2, js2).residual is None and npz2.endswith("prompt_10.npz")
