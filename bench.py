@@ -347,7 +347,7 @@ def main():
     ap.add_argument("--batch-prompts", type=int, default=4096, help="prompts per sub-batch (one sweep each)")
     ap.add_argument("--chunks", type=int, default=0, help="vocab chunks per lens launch (0 = auto)")
     ap.add_argument("--encode-cap", type=int, default=128)
-    ap.add_argument("--cluster-mode", type=int, default=4,
+    ap.add_argument("--cluster-mode", type=int, default=2,
                     help="lens kernel cluster: 0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs, 3 = 1x2 pairs, 4 = 2x2 pairs "
                          "(TMA multicast of the shared operand slabs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

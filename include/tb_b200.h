@@ -36,6 +36,9 @@ extern "C" {
 #define TB_RANK_NONE 0xFFFFu /* rank-table entry of a latent that is not in the ablation set */
 
 int tb_version(void);
+/* Partials written per (chunk, row) by tb_lens_partials / tb_lens_ll_partials: every row is swept by
+ * this many epilogue threads (column halves of each tile), each leaving its own partial (2). */
+int tb_lens_parts_per_chunk(void);
 const char* tb_last_error(void);
 /* TB_OK iff the CURRENT device can run the kernels (compute capability 10.x). */
 int tb_device_check(void);
@@ -112,9 +115,10 @@ int tb_rmsnorm(const void* x_bf16, const float* w_norm, float eps, int64_t n_row
  * final-logit softcap (softcap <= 0: none, as the reference; Gemma-2: 30.0), keeps an online
  * (max, sum-exp), the secret token's logit and a top-10 per row. Logits never reach HBM.
  * The vocabulary shard is swept in n_chunks contiguous chunks (scheduling / L2 knob); the
- * per-(chunk, row) partials are written to caller scratch:
- *   pm, ps, psec : f32 [n_chunks, n_rows]      ptv : f32 [n_chunks, n_rows, 10]
- *   pti : i32 [n_chunks, n_rows, 10]  (global vocab ids = vocab_offset + column)
+ * per-(part, row) partials are written to caller scratch, n_parts = n_chunks *
+ * tb_lens_parts_per_chunk() (pass n_parts to tb_lens_merge):
+ *   pm, ps, psec : f32 [n_parts, n_rows]      ptv : f32 [n_parts, n_rows, 10]
+ *   pti : i32 [n_parts, n_rows, 10]  (global vocab ids = vocab_offset + column)
  * secret_id: i32 [n_rows] global vocab id per row, or NULL. cta_pair selects the cluster shape:
  * 0 single CTAs, 1 CTA pairs (cta_group::2), 2 = 2x1 pairs (two row blocks share the W_U tiles
  * through TMA multicast), 3 = 1x2 pairs (two chunks share the row block), 4 = 2x2 pairs;
@@ -204,8 +208,9 @@ int tb_ll_candidates_exact(const void* h_bf16, const void* w_u_bf16, int64_t n_r
  * torch, no allocator of its own), or a latency-critical loop that must not enter
  * cudaMalloc/cudaFree because those serialise the device. The function itself performs no
  * allocation of any kind.
- *   - limit: n_rows * n_chunks <= TB_STATIC_LENS_MAX_SLOTS (65536); larger requests are
- *     rejected with TB_ERR_INVALID and nothing is launched. The block is 6,029,312 bytes
+ *   - limit: n_rows * n_chunks * tb_lens_parts_per_chunk() <= TB_STATIC_LENS_MAX_SLOTS (65536),
+ *     i.e. n_rows * n_chunks <= 32768; larger requests are rejected with TB_ERR_INVALID and
+ *     nothing is launched. The block is 6,029,312 bytes
  *     (65536 x 23 words) and is resident on every GPU that loads the library until the
  *     process exits.
  *   - the first call on each device resolves the block's device address (one

@@ -7,7 +7,7 @@ int main() {
   const int smem = 198 * 1024;
   cudaFuncSetAttribute(dummy, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   cudaFuncSetAttribute(dummy, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-  for (int cs : {1, 2, 4, 8, 16}) {
+  for (int cs : {1, 2, 4, 6, 8, 10, 12, 16}) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(148 / cs * cs, 1, 1);
     cfg.blockDim = dim3(256, 1, 1);

@@ -36,6 +36,7 @@ _P = c_void_p  # every device pointer travels as void*
 # name -> (restype, argtypes); mirrors include/tb_b200.h one to one
 SIGNATURES = {
     "tb_version": (c_int, []),
+    "tb_lens_parts_per_chunk": (c_int, []),
     "tb_last_error": (c_char_p, []),
     "tb_device_check": (c_int, []),
     "tb_sae_encode": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, _P, _P, c_int, _P, _P, _P, _P,

@@ -7,12 +7,17 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <mutex>
 
 #include "../../include/tb_b200.h"
 #include "tb_epilogues.cuh"
 #include "tb_gemm.cuh"
 #include "tb_rows.cuh"
+
+// Progress counters of the soft lockstep between clusters (tb_gemm.cuh): a few rotating slots of
+// 64 counters, so that launches in flight on different streams do not share one.
+static __device__ int g_cluster_progress[8][64];
 
 namespace {
 
@@ -123,6 +128,11 @@ void set_policies(tb::GemmArgs* g, bool stationary_is_a) {
     pol[i] = d[i] == 'l' ? tb::kPolicyEvictLast : d[i] == 'f' ? tb::kPolicyEvictFirst : tb::kPolicyEvictNormal;
   const char* dbg = getenv("TB_DEBUG_SKIP");
   g->debug_skip = dbg ? atoi(dbg) : 0;
+  // soft lockstep between clusters (tb_gemm.cuh): on by default, slack of one tile; it only engages
+  // for multicast clusters (launch_gemm), where the L2 -> SM fabric has the headroom to profit
+  const char* ls = getenv("TB_LOCKSTEP");
+  g->lockstep = ls ? atoi(ls) : 1;
+  g->progress = nullptr;
   g->policy_a = stationary_is_a ? pol[0] : pol[1];
   g->policy_b = stationary_is_a ? pol[1] : pol[0];
 }
@@ -180,7 +190,7 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
   TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   cudaLaunchConfig_t cfg;
   memset(&cfg, 0, sizeof(cfg));
-  cfg.blockDim = dim3(tb::kGemmThreads, 1, 1);
+  cfg.blockDim = dim3(tb::gemm_threads<Epi>(), 1, 1);
   cfg.dynamicSmemBytes = kSmem;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
@@ -207,7 +217,20 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
   }
   if (clusters > g.total_units) clusters = g.total_units;
   cfg.gridDim = dim3(static_cast<unsigned>(clusters * kClusterCtas), 1, 1);
-  TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, g, ep));
+  tb::GemmArgs ga = g;
+  if (ga.lockstep > 0 && kClusterCtas > 2 && clusters <= 64 && clusters > 1) {
+    // progress counters: one of 8 rotating 64-counter slots of a static device array (no allocation;
+    // up to 8 launches may be in flight on different streams before two of them share a slot, and
+    // sharing only costs pacing accuracy: every wait is bounded)
+    static std::atomic<unsigned> slot{0};
+    int* base = nullptr;
+    TB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&base), g_cluster_progress));
+    ga.progress = base + 64 * (slot.fetch_add(1) & 7u);
+    TB_CUDA(cudaMemsetAsync(ga.progress, 0, 64 * sizeof(int), stream));
+  } else {
+    ga.lockstep = 0;
+  }
+  TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, ga, ep));
   return TB_OK;
 }
 
@@ -292,7 +315,9 @@ int static_scratch_address(float** out) {
 
 extern "C" {
 
-int tb_version(void) { return 100; }
+int tb_version(void) { return 101; }
+
+int tb_lens_parts_per_chunk(void) { return tb::LensEpi::kEpiWarps / 4; }
 
 const char* tb_last_error(void) { return g_err; }
 
@@ -708,12 +733,13 @@ int tb_logit_lens_static(const void* h, const void* w_u, int64_t n_rows, int d, 
   if (g.n_chunks != n_chunks)
     return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)", n_chunks,
                 g.n_tiles, g.n_chunks);
-  const int64_t slots = n_rows * static_cast<int64_t>(n_chunks);
+  const int n_parts = n_chunks * tb_lens_parts_per_chunk();
+  const int64_t slots = n_rows * static_cast<int64_t>(n_parts);
   if (slots > TB_STATIC_LENS_MAX_SLOTS)
     return fail(TB_ERR_INVALID,
-                "n_rows * n_chunks = %lld exceeds the built-in scratch of %d (row, chunk) slots; split the rows "
+                "n_rows * n_chunks * %d = %lld exceeds the built-in scratch of %d (row, part) slots; split the rows "
                 "over several calls or use tb_lens_partials + tb_lens_merge with your own scratch",
-                static_cast<long long>(slots), TB_STATIC_LENS_MAX_SLOTS);
+                tb_lens_parts_per_chunk(), static_cast<long long>(slots), TB_STATIC_LENS_MAX_SLOTS);
   float* base = nullptr;
   rc = static_scratch_address(&base);
   if (rc != TB_OK) return rc;
@@ -727,7 +753,7 @@ int tb_logit_lens_static(const void* h, const void* w_u, int64_t n_rows, int d, 
   rc = tb_lens_partials(h, w_u, n_rows, d, V, vocab_offset, softcap, secret_id, n_chunks, cta_pair, pm, ps, psec,
                         ptv, pti, stream);
   if (rc != TB_OK) return rc;
-  return tb_lens_merge(pm, ps, psec, ptv, pti, n_chunks, n_rows, 1, nullptr, nullptr, nullptr, nullptr, nullptr,
+  return tb_lens_merge(pm, ps, psec, ptv, pti, n_parts, n_rows, 1, nullptr, nullptr, nullptr, nullptr, nullptr,
                        lse, secret_prob, top_prob, top_id, stream);
 }
 

@@ -34,6 +34,7 @@ __device__ __forceinline__ float tanh_2mufu(float y) {
 // probability gather), models.py:147 (per-row max); softcap per installed Gemma2ForCausalLM.
 // =========================================================================================
 struct LensEpi {
+  static constexpr int kEpiWarps = 8;   // two threads per row, each sweeping half of every tile's columns
   static constexpr bool kSweepA = false;
   static constexpr bool kTileHooks = false;
   static constexpr int kExtraSmem = 0;
@@ -156,6 +157,7 @@ struct LensEpi {
 // whose rank is below the budget right here (random-control / second-pass masking).
 // =========================================================================================
 struct EncodeEpi {
+  static constexpr int kEpiWarps = 4;   // one thread per row: a row's list is appended in latent order
   static constexpr bool kSweepA = false;
   static constexpr bool kTileHooks = false;
   static constexpr int kExtraSmem = 0;
@@ -262,6 +264,7 @@ struct EncodeEpi {
 // the prompt; only then does it take the per-element compare path.
 // =========================================================================================
 struct ColSumEpi {
+  static constexpr int kEpiWarps = 8;   // warp group q of a quadrant sums prompt q of the block pair
   static constexpr bool kSweepA = true;
   static constexpr bool kTileHooks = false;
   static constexpr int kSlots = 128;              // row slots per prompt (= TMEM columns per prompt)
@@ -285,8 +288,8 @@ struct ColSumEpi {
     int group;               // kCtaGroup
   };
   struct State {
-    float tv[2][kTopK];
-    int32_t ti[2][kTopK];
+    float tv[kTopK];     // this thread's vocabulary ids x the prompt of its warp group (ctx.half)
+    int32_t ti[kTopK];
   };
 
   __device__ __forceinline__ static void begin_unit_sw(State& st, const Params& p, const GemmArgs& g,
@@ -295,51 +298,42 @@ struct ColSumEpi {
     int32_t* s_cur = reinterpret_cast<int32_t*>(c.extra + kOffCur);
     int32_t* s_prev = reinterpret_cast<int32_t*>(c.extra + kOffPrev);
     uint32_t* s_bm = reinterpret_cast<uint32_t*>(c.extra + kOffBitmap);
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int slot = q * kSlots + c.tid;
-      const int64_t r = static_cast<int64_t>(c.blk) * 256 + slot;
-      const bool valid = r < g.N;
-      s_nl[slot] = valid ? -p.lse[r] * kLog2e : -CUDART_INF_F;
-      s_cur[slot] = (valid && p.cur_id) ? p.cur_id[r] : -1;
-      s_prev[slot] = (valid && p.prev_id) ? p.prev_id[r] : -1;
-    }
+    // the 256 epilogue threads each set up one row slot of the block (slot = half * 128 + tid)
+    const int slot = c.etid;
+    const int64_t r = static_cast<int64_t>(c.blk) * 256 + slot;
+    const bool valid = r < g.N;
+    s_nl[slot] = valid ? -p.lse[r] * kLog2e : -CUDART_INF_F;
+    s_cur[slot] = (valid && p.cur_id) ? p.cur_id[r] : -1;
+    s_prev[slot] = (valid && p.prev_id) ? p.prev_id[r] : -1;
     uint4* bm4 = reinterpret_cast<uint4*>(s_bm);
-    for (int i = c.tid; i < 2 * (kMaxChunkIds / 128); i += 128) bm4[i] = make_uint4(0, 0, 0, 0);
-    epi_bar_sync();
+    for (int i = c.etid; i < 2 * (kMaxChunkIds / 128); i += 256) bm4[i] = make_uint4(0, 0, 0, 0);
+    epi_bar_sync<256>();
     const int base = c.t0 * c.a_tile_rows;                   // first local id of the chunk
     const int range = (c.t1 - c.t0) * c.a_tile_rows;
+    const int ids[2] = {s_cur[slot], s_prev[slot]};
 #pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const int slot = q * kSlots + c.tid;
-      const int ids[2] = {s_cur[slot], s_prev[slot]};
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        const int loc = ids[e] - p.vocab_offset - base;
-        if (ids[e] >= 0 && loc >= 0 && loc < range)
-          atomicOr(&s_bm[q * (kMaxChunkIds / 32) + (loc >> 5)], 1u << (loc & 31));
-      }
+    for (int e = 0; e < 2; ++e) {
+      const int loc = ids[e] - p.vocab_offset - base;
+      if (ids[e] >= 0 && loc >= 0 && loc < range)
+        atomicOr(&s_bm[c.half * (kMaxChunkIds / 32) + (loc >> 5)], 1u << (loc & 31));
     }
-    epi_bar_sync();
+    epi_bar_sync<256>();
 #pragma unroll
-    for (int q = 0; q < 2; ++q)
-#pragma unroll
-      for (int k = 0; k < kTopK; ++k) { st.tv[q][k] = -CUDART_INF_F; st.ti[q][k] = -1; }
+    for (int k = 0; k < kTopK; ++k) { st.tv[k] = -CUDART_INF_F; st.ti[k] = -1; }
   }
 
-  template <int Q>
   __device__ __forceinline__ static void insert(State& st, float v, int32_t id) {
-    st.tv[Q][kTopK - 1] = v;
-    st.ti[Q][kTopK - 1] = id;
+    st.tv[kTopK - 1] = v;
+    st.ti[kTopK - 1] = id;
 #pragma unroll
     for (int k = kTopK - 1; k > 0; --k) {
-      const bool sw = st.tv[Q][k] > st.tv[Q][k - 1];
-      const float a = st.tv[Q][k - 1], b = st.tv[Q][k];
-      const int32_t ia = st.ti[Q][k - 1], ib = st.ti[Q][k];
-      st.tv[Q][k - 1] = sw ? b : a;
-      st.tv[Q][k] = sw ? a : b;
-      st.ti[Q][k - 1] = sw ? ib : ia;
-      st.ti[Q][k] = sw ? ia : ib;
+      const bool sw = st.tv[k] > st.tv[k - 1];
+      const float a = st.tv[k - 1], b = st.tv[k];
+      const int32_t ia = st.ti[k - 1], ib = st.ti[k];
+      st.tv[k - 1] = sw ? b : a;
+      st.tv[k] = sw ? a : b;
+      st.ti[k - 1] = sw ? ib : ia;
+      st.ti[k] = sw ? ia : ib;
     }
   }
 
@@ -353,55 +347,51 @@ struct ColSumEpi {
     const int vid = p.vocab_offset + local;
     const int bit = local - c.t0 * c.a_tile_rows;
     const float inv_cap = p.softcap > 0.0f ? 1.0f / p.softcap : 0.0f;
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-      const bool masked = (s_bm[q * (kMaxChunkIds / 32) + (bit >> 5)] >> (bit & 31)) & 1u;
-      float acc0 = 0.0f, acc1 = 0.0f;
+    const int q = c.half;                                            // prompt of the block pair
+    const bool masked = (s_bm[q * (kMaxChunkIds / 32) + (bit >> 5)] >> (bit & 31)) & 1u;
+    float acc0 = 0.0f, acc1 = 0.0f;
 #pragma unroll 1
-      for (int cc = 0; cc < 4; ++cc) {
-        const int slot0 = q * kSlots + cc * 32;
-        uint32_t v[32];
-        tmem_ld_32x32(taddr + slot0, v);
-        tmem_ld_wait();
-        float e[32];
+    for (int cc = 0; cc < 4; ++cc) {
+      const int slot0 = q * kSlots + cc * 32;
+      uint32_t v[32];
+      tmem_ld_32x32(taddr + slot0, v);
+      tmem_ld_wait();
+      float e[32];
 #pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          const float4 nl = *reinterpret_cast<const float4*>(s_nl + slot0 + j);
-          const float nls[4] = {nl.x, nl.y, nl.z, nl.w};
+      for (int j = 0; j < 32; j += 4) {
+        const float4 nl = *reinterpret_cast<const float4*>(s_nl + slot0 + j);
+        const float nls[4] = {nl.x, nl.y, nl.z, nl.w};
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            float l = __uint_as_float(v[j + u]);
-            if (p.softcap > 0.0f) l = p.softcap * tanh_2mufu(l * inv_cap);
-            e[j + u] = ex2_approx(fmaf(l, kLog2e, nls[u]));
-          }
+        for (int u = 0; u < 4; ++u) {
+          float l = __uint_as_float(v[j + u]);
+          if (p.softcap > 0.0f) l = p.softcap * tanh_2mufu(l * inv_cap);
+          e[j + u] = ex2_approx(fmaf(l, kLog2e, nls[u]));
         }
-        if (masked) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (s_cur[slot0 + j] == vid || s_prev[slot0 + j] == vid) e[j] = 0.0f;
-        }
-#pragma unroll
-        for (int j = 0; j < 32; j += 2) { acc0 += e[j]; acc1 += e[j + 1]; }
       }
-      const float acc = acc0 + acc1;
-      if (local < g.M && acc > st.tv[q][kTopK - 1]) {
-        if (q == 0) insert<0>(st, acc, vid); else insert<1>(st, acc, vid);
+      if (masked) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (s_cur[slot0 + j] == vid || s_prev[slot0 + j] == vid) e[j] = 0.0f;
       }
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) { acc0 += e[j]; acc1 += e[j + 1]; }
     }
+    const float acc = acc0 + acc1;
+    if (local < g.M && acc > st.tv[kTopK - 1]) insert(st, acc, vid);
   }
 
-  // pop the best of the 128 threads' sorted lists, kTopK times
-  template <int Q>
-  __device__ __forceinline__ static void merge_out(State& st, const Params& p, const SweepCtx& c) {
-    float* s_bv = reinterpret_cast<float*>(c.extra + kOffBest);
-    int32_t* s_bi = reinterpret_cast<int32_t*>(c.extra + kOffBest + 16);
-    const int prompt = c.blk * 2 + Q;
+  // pop the best of the 128 threads' sorted lists, kTopK times (the 128 threads of one column half)
+  __device__ __forceinline__ static void end_unit_sw(State& st, const Params& p, const GemmArgs&,
+                                                     const SweepCtx& c) {
+    float* s_bv = reinterpret_cast<float*>(c.extra + kOffBest) + c.half * 4;
+    int32_t* s_bi = reinterpret_cast<int32_t*>(c.extra + kOffBest + 32) + c.half * 4;
+    const int prompt = c.blk * 2 + c.half;
     const int part = c.chunk * p.group + c.rank;
     const int lane = c.tid & 31, warp = c.tid >> 5;
 #pragma unroll 1
     for (int round = 0; round < kTopK; ++round) {
-      float bv = st.tv[Q][0];
-      int32_t bi = st.ti[Q][0];
+      float bv = st.tv[0];
+      int32_t bi = st.ti[0];
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) {
         const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
@@ -412,7 +402,7 @@ struct ColSumEpi {
         bi = take ? oi : bi;
       }
       if (lane == 0) { s_bv[warp] = bv; s_bi[warp] = bi; }
-      epi_bar_sync();
+      epi_half_bar_sync(c.half);
       float wv = s_bv[0];
       int32_t wi = s_bi[0];
 #pragma unroll
@@ -423,25 +413,21 @@ struct ColSumEpi {
         wv = take ? ov : wv;
         wi = take ? oi : wi;
       }
-      if (wi >= 0 && st.ti[Q][0] == wi) {  // this thread owned the winner: pop it
+      if (wi >= 0 && st.ti[0] == wi) {  // this thread owned the winner: pop it
 #pragma unroll
-        for (int k = 0; k < kTopK - 1; ++k) { st.tv[Q][k] = st.tv[Q][k + 1]; st.ti[Q][k] = st.ti[Q][k + 1]; }
-        st.tv[Q][kTopK - 1] = -CUDART_INF_F;
-        st.ti[Q][kTopK - 1] = -1;
+        for (int k = 0; k < kTopK - 1; ++k) { st.tv[k] = st.tv[k + 1]; st.ti[k] = st.ti[k + 1]; }
+        st.tv[kTopK - 1] = -CUDART_INF_F;
+        st.ti[kTopK - 1] = -1;
       }
       if (c.tid == 0 && prompt < p.n_prompts) {
         const size_t o = (static_cast<size_t>(part) * p.n_prompts + prompt) * kTopK + round;
         p.out_val[o] = wv;
         p.out_id[o] = wi;
       }
-      epi_bar_sync();
+      epi_half_bar_sync(c.half);
     }
-  }
-
-  __device__ __forceinline__ static void end_unit_sw(State& st, const Params& p, const GemmArgs&,
-                                                     const SweepCtx& c) {
-    merge_out<0>(st, p, c);
-    merge_out<1>(st, p, c);
+    // the next unit's set-up overwrites the slot arrays and bitmaps: wait for the other half too
+    epi_bar_sync<256>();
   }
 };
 
@@ -464,14 +450,16 @@ struct ColSumEpi {
 // tile each thread finishes two columns.
 // =========================================================================================
 struct LensLLEpi {
+  static constexpr int kEpiWarps = 8;   // two threads per row (column halves), 256 epilogue threads
   static constexpr bool kSweepA = false;
   static constexpr bool kTileHooks = true;
-  static constexpr int kOffTr = 0;                                // float[4][32][33] transpose buffers
-  static constexpr int kOffCs = kOffTr + 4 * 32 * 33 * 4;         // float[2][4][256] per-warp column sums
+  static constexpr int kTrStride = 17;
+  static constexpr int kOffTr = 0;                                     // float[8 warps][32][17] transpose buffers
+  static constexpr int kOffCs = kOffTr + 8 * 32 * kTrStride * 4;       // float[2][4 quadrants][256] column sums
   static constexpr int kExtraSmem = kOffCs + 2 * 4 * 256 * 4;
 
   struct Params {
-    LensEpi::Params lens;      // secret ids, vocab offset, softcap, partial buffers
+    LensEpi::Params lens;      // secret ids, vocab offset, softcap, partial buffers (2 parts per chunk)
     const float* ref;          // [M] reference r[t] (+inf: empty row slot)
     const float* tau;          // [n_prompts] candidate threshold (> 0)
     const int32_t* cur_id;     // [M] ids zeroed per position (global), nullable
@@ -525,13 +513,13 @@ struct LensLLEpi {
   __device__ __forceinline__ static void process_tile(State& st, const Params& p, const GemmArgs& g,
                                                       const SweepCtx& c, int row, int nt, uint32_t taddr,
                                                       int parity) {
-    const int warp = c.tid >> 5, lane = c.tid & 31;
-    float* tr = reinterpret_cast<float*>(c.extra + kOffTr) + warp * (32 * 33);
+    const int quad = c.tid >> 5, lane = c.tid & 31;
+    float* tr = reinterpret_cast<float*>(c.extra + kOffTr) + (c.half * 4 + quad) * (32 * kTrStride);
     float* cs = reinterpret_cast<float*>(c.extra + kOffCs) + parity * (4 * 256);
     const float cap = p.lens.softcap;
     const float inv_cap = cap > 0.0f ? 1.0f / cap : 0.0f;
 #pragma unroll 1
-    for (int cc = 0; cc < kBlockN / 32; ++cc) {
+    for (int cc = c.half * 4; cc < c.half * 4 + 4; ++cc) {
       const int col0 = nt * kBlockN + cc * 32;
       uint32_t v[32];
       tmem_ld_32x32(taddr + cc * 32, v);
@@ -580,38 +568,41 @@ struct LensLLEpi {
         for (int j = 0; j < 32; ++j)
           if (rc == static_cast<uint32_t>(j) || rp == static_cast<uint32_t>(j)) q[j] = 0.0f;
       }
-      // transpose-reduce over the warp's 32 rows
-      __syncwarp();
+      // transpose-reduce over the warp's 32 rows, 16 columns at a time: lane = (row half, column)
 #pragma unroll
-      for (int j = 0; j < 32; ++j) tr[lane * 33 + j] = q[j];
-      __syncwarp();
-      float b0 = 0.0f, b1 = 0.0f;
+      for (int hsel = 0; hsel < 2; ++hsel) {
+        __syncwarp();
 #pragma unroll
-      for (int r = 0; r < 32; r += 2) {
-        b0 += tr[r * 33 + lane];
-        b1 += tr[(r + 1) * 33 + lane];
+        for (int j = 0; j < 16; ++j) tr[lane * kTrStride + j] = q[hsel * 16 + j];
+        __syncwarp();
+        const int r0 = (lane >> 4) * 16, col = lane & 15;
+        float b0 = 0.0f, b1 = 0.0f;
+#pragma unroll
+        for (int r = 0; r < 16; r += 2) {
+          b0 += tr[(r0 + r) * kTrStride + col];
+          b1 += tr[(r0 + r + 1) * kTrStride + col];
+        }
+        float b = b0 + b1;
+        b += __shfl_xor_sync(0xffffffffu, b, 16);
+        if (lane < 16) cs[quad * 256 + cc * 32 + hsel * 16 + lane] = b;
       }
-      cs[warp * 256 + cc * 32 + lane] = b0 + b1;
     }
-    epi_bar_sync();
-    // two columns per thread: add the four warps' partial sums, list the column if it passes
+    epi_bar_sync<256>();
+    // one column per thread: add the four quadrants' partial sums, list the column if it passes
     const int prompt = row / kBlockM;
-#pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      const int cl = c.tid + u * 128;
-      const float sum = (cs[cl] + cs[256 + cl]) + (cs[512 + cl] + cs[768 + cl]);
-      const int col = nt * kBlockN + cl;
-      if (sum >= st.tau && col < g.N && prompt < p.n_prompts) {
-        const int pos = atomicAdd(p.cand_count + prompt, 1);
-        if (pos < p.cand_cap) p.cand_id[static_cast<size_t>(prompt) * p.cand_cap + pos] = p.lens.vocab_offset + col;
-      }
+    const int cl = c.etid;
+    const float sum = (cs[cl] + cs[256 + cl]) + (cs[512 + cl] + cs[768 + cl]);
+    const int col = nt * kBlockN + cl;
+    if (sum >= st.tau && col < g.N && prompt < p.n_prompts) {
+      const int pos = atomicAdd(p.cand_count + prompt, 1);
+      if (pos < p.cand_cap) p.cand_id[static_cast<size_t>(prompt) * p.cand_cap + pos] = p.lens.vocab_offset + col;
     }
   }
 
   __device__ __forceinline__ static void end_unit_tile(State& st, const Params& p, const GemmArgs& g,
                                                        const SweepCtx& c, int row) {
     if (row >= g.M) return;
-    const size_t o = static_cast<size_t>(c.chunk) * g.M + row;
+    const size_t o = static_cast<size_t>(c.chunk * 2 + c.half) * g.M + row;
     p.lens.pm[o] = p.ref[row];   // the partial's reference point is r, not the running maximum
     p.lens.ps[o] = st.s;
     p.lens.psec[o] = st.sec;
@@ -628,6 +619,7 @@ struct LensLLEpi {
 // TMA / UMMA-descriptor / TMEM plumbing against a plain matmul.
 // =========================================================================================
 struct DenseEpi {
+  static constexpr int kEpiWarps = 4;
   static constexpr bool kSweepA = false;
   static constexpr bool kTileHooks = false;
   static constexpr int kExtraSmem = 0;

@@ -26,8 +26,11 @@ constexpr int kBlockM = 128;   // rows per CTA
 constexpr int kBlockN = 256;   // columns per tile (= UMMA N)
 constexpr int kBlockK = 64;    // bf16 elements per stage row: one 128-byte swizzle span
 constexpr int kUmmaK = 16;
-constexpr int kGemmThreads = 256;
-constexpr int kEpiWarp0 = 4;
+constexpr int kEpiWarp0 = 4;   // warps 0..3: TMA producer, MMA issuer, TMEM allocator, spare
+// Epilogue warps: 4 (one per TMEM lane quadrant) or 8 (two per quadrant, each taking half of a
+// tile's 256 columns -- twice the latency hiding for epilogues with real per-element work).
+template <class Epi>
+constexpr int gemm_threads() { return 32 * (kEpiWarp0 + Epi::kEpiWarps); }
 
 struct GemmArgs {
   int M, N, K;          // A is [M, K], B is [N, K]
@@ -38,6 +41,12 @@ struct GemmArgs {
   int total_units;      // m_blocks * n_chunks
   unsigned long long policy_a, policy_b;  // L2 eviction policy of the A / B tile loads
   int debug_skip;       // experiments only: bit 0 = do not load A, bit 1 = do not load B (results are garbage)
+  // Soft lockstep between clusters (0 = off): a cluster does not start loading a tile while it is
+  // more than `lockstep` tiles ahead of the slowest cluster of the launch. Clusters that sweep
+  // the same chunk then read every swept tile within a few tile-times of each other, which is
+  // what lets one DRAM fetch serve all of them out of L2. progress[] has one counter per cluster.
+  int lockstep;
+  int* progress;
 };
 
 // What a "sweep-A" epilogue (Epi::kSweepA) is told about its unit. In that orientation the
@@ -49,7 +58,9 @@ struct SweepCtx {
   int chunk;      // chunk of A tiles
   int t0, t1;     // A tiles [t0, t1)
   int rank;       // CTA rank in the pair (0 for cta_group::1)
-  int tid;        // 0..127: epilogue thread = TMEM lane
+  int tid;        // 0..127: TMEM lane of this epilogue thread
+  int half;       // which half of the tile's columns this thread's warp group takes (0 with 4 epilogue warps)
+  int etid;       // 0..32*kEpiWarps-1: index among the CTA's epilogue threads (= half * 128 + tid)
   int a_tile_rows;  // 128 * kCtaGroup
   uint8_t* extra;   // Epi::kExtraSmem bytes of shared memory (16-byte aligned)
 };
@@ -65,11 +76,17 @@ struct GemmCfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + kBarBytes + 1024;  // + alignment slack
 };
 
-// named barrier over the 128 epilogue threads only (barrier 0 is __syncthreads)
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+// named barriers over epilogue threads only (barrier 0 is __syncthreads): id 1 = all kThreads
+// epilogue threads of the CTA, ids 2 / 3 = the 128 threads of column half 0 / 1
+template <int kThreads>
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory"); }
+__device__ __forceinline__ void epi_half_bar_sync(int half) {
+  if (half == 0) asm volatile("bar.sync 2, 128;" ::: "memory");
+  else asm volatile("bar.sync 3, 128;" ::: "memory");
+}
 
 template <class Epi, int kCtaGroup, int kR = 1, int kC = 1>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __launch_bounds__(gemm_threads<Epi>(), 1)
 tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmArgs g, const typename Epi::Params ep) {
   using Cfg = GemmCfg<kCtaGroup>;
@@ -133,7 +150,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tfull_bar[i]), 1);
-      mbar_init(smem_u32(&tempty_bar[i]), 4 * kCtaGroup);  // one arrive per epilogue warp
+      mbar_init(smem_u32(&tempty_bar[i]), Epi::kEpiWarps * kCtaGroup);  // one arrive per epilogue warp
     }
     fence_mbar_init();
   }
@@ -161,11 +178,28 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const bool ld_a = !(g.debug_skip & 1), ld_b = !(g.debug_skip & 2);
       int stage = 0;
       uint32_t phase = 0;
+      int tiles_done = 0;
+      const bool pace = g.lockstep > 0 && crank == 0 && g.progress != nullptr;
       for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
         int m_blk, chunk, t0, n_iter;
         decode(unit, m_blk, chunk, t0, n_iter);
-        for (int it = 0; it < n_iter; ++it) {
+        for (int it = 0; it < n_iter; ++it, ++tiles_done) {
           const int nt = t0 + it;
+          if (pace) {
+            // publish my position, then wait (bounded) for the stragglers; the other CTAs of the
+            // cluster follow through the multicast dependencies
+            asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + cluster_id), "r"(tiles_done) : "memory");
+            const long long t_start = clock64();
+            for (;;) {
+              int slowest = 0x7fffffff;
+              for (int c = 0; c < num_clusters; ++c) {
+                int v;
+                asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(g.progress + c) : "memory");
+                slowest = min(slowest, v);
+              }
+              if (tiles_done <= slowest + g.lockstep || clock64() - t_start > 400000ll) break;
+            }
+          }
           // stationary block / swept tile -> operand rows (sweep-A swaps the roles)
           const int a_row = (kSweepA ? nt : m_blk) * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM +
                             piece_a * kPieceARows;
@@ -197,6 +231,8 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           }
         }
       }
+      if (pace)   // done: never hold anybody back again
+        asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + cluster_id), "r"(0x7fffffff) : "memory");
     }
     __syncwarp();
   } else if (warp == 1) {
@@ -246,7 +282,10 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     __syncwarp();
   } else if (warp >= kEpiWarp0) {
     // ================================ epilogue ================================
-    const int quad = warp & 3;
+    constexpr int kHalves = Epi::kEpiWarps / 4;           // warp groups per TMEM lane quadrant
+    constexpr int kGroupsPerHalf = (kBlockN / 32) / kHalves;
+    const int quad = warp & 3;                            // TMEM lanes a warp may touch: 32 * (warp % 4)
+    const int half = (warp - kEpiWarp0) >> 2;
     const int row_in_blk = quad * 32 + lane;
     const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
     uint32_t acc_iter = 0;
@@ -259,11 +298,14 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if constexpr (kSweepA || Epi::kTileHooks) {
         ctx.blk = m_blk; ctx.chunk = chunk; ctx.t0 = t0; ctx.t1 = t0 + n_iter;
         ctx.rank = static_cast<int>(rank); ctx.tid = row_in_blk;
+        ctx.half = half; ctx.etid = half * 128 + row_in_blk;
         ctx.a_tile_rows = kBlockM * kCtaGroup; ctx.extra = epi_extra;
       }
+      // row-owner epilogues with two threads per row write one partial per (chunk, half)
+      const int part = chunk * kHalves + half;
       if constexpr (kSweepA) Epi::begin_unit_sw(st, ep, g, ctx);
       else if constexpr (Epi::kTileHooks) Epi::begin_unit_tile(st, ep, g, ctx, row);
-      else Epi::begin_unit(st, ep, g, row, chunk);
+      else Epi::begin_unit(st, ep, g, row, part);
       for (int it = 0; it < n_iter; ++it, ++acc_iter) {
         const int nt = t0 + it;
         const uint32_t acc = acc_iter & 1u;
@@ -277,7 +319,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           Epi::process_tile(st, ep, g, ctx, row, nt, tmem_base + lane_base + acc * kBlockN, static_cast<int>(acc));
         } else {
 #pragma unroll 1
-          for (int c = 0; c < kBlockN / 32; ++c) {
+          for (int c = half * kGroupsPerHalf; c < (half + 1) * kGroupsPerHalf; ++c) {
             uint32_t v[32];
             tmem_ld_32x32(tmem_base + lane_base + acc * kBlockN + c * 32, v);
             tmem_ld_wait();
@@ -294,7 +336,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       if constexpr (kSweepA) Epi::end_unit_sw(st, ep, g, ctx);
       else if constexpr (Epi::kTileHooks) Epi::end_unit_tile(st, ep, g, ctx, row);
-      else Epi::end_unit(st, ep, g, row, chunk);
+      else Epi::end_unit(st, ep, g, row, part);
     }
   }
 

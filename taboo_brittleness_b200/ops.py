@@ -349,7 +349,7 @@ class LensReadout:
 CLUSTER_MODES = {0: (1, 1, 1), 1: (2, 1, 1), 2: (2, 2, 1), 3: (2, 1, 2), 4: (2, 2, 2)}   # (group, R, C)
 # clusters that can be co-resident on a 148-SM B200 (cudaOccupancyMaxActiveClusters: a cluster must
 # fit one GPC, so sizes 4 and 8 leave SMs idle); only used to rank schedules here
-_B200_CLUSTERS = {1: 148, 2: 74, 4: 33, 8: 15}
+_B200_CLUSTERS = {1: 148, 2: 74, 4: 33, 6: 22, 8: 15}
 
 
 def _mode(cta_pair) -> int:
@@ -381,17 +381,29 @@ def pick_chunks(n_rows: int, V: int, n_sms: int = 148, cta_pair=False, *, sweep_
         units = -(-blocks // R) * (c // C)
         waves = -(-units // clusters)
         cost = waves * (tpc + 1)          # time ~ waves * tiles per chunk (+1 tile of pipeline fill per unit)
+        cost *= 1.0 + 0.004 * c           # fewer chunks = more clusters per W_U stream = less DRAM traffic
         resident = min(blocks, -(-clusters // (c // C)) * R)
-        if resident * (2 // group if not sweep_a else 1) > 24:   # > ~45 MB of stationary blocks: L2 thrash
+        mb = resident * (1.835 if (group == 2 or sweep_a) else 0.92)
+        if mb > 75.0:                     # stationary blocks of the resident clusters should stay in L2
             cost *= 1.5
         if best_cost is None or cost < best_cost:
             best, best_cost = c, cost
     return best or C
 
 
+def _alloc_partials(n_chunks: int, n: int, dev) -> "LensPartials":
+    parts = n_chunks * _lib.load().tb_lens_parts_per_chunk()     # one partial per (chunk, column half, row)
+    return LensPartials(
+        pm=torch.empty(parts, n, dtype=torch.float32, device=dev),
+        ps=torch.empty(parts, n, dtype=torch.float32, device=dev),
+        psec=torch.empty(parts, n, dtype=torch.float32, device=dev),
+        ptv=torch.empty(parts, n, TB_TOPK, dtype=torch.float32, device=dev),
+        pti=torch.empty(parts, n, TB_TOPK, dtype=torch.int32, device=dev))
+
+
 def lens_partials(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0,
                   secret_id: Optional[torch.Tensor] = None, vocab_offset: int = 0,
-                  n_chunks: Optional[int] = None, cta_pair=False) -> LensPartials:
+                  n_chunks: Optional[int] = None, cta_pair=2) -> LensPartials:
     _need(h, torch.bfloat16, "h", 2)
     _need(w_u, torch.bfloat16, "w_u", 2)
     n, d = h.shape
@@ -400,13 +412,7 @@ def lens_partials(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0,
         _need(secret_id, torch.int32, "secret_id", 1)
     if n_chunks is None:
         n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(h.device).multi_processor_count, cta_pair)
-    dev = h.device
-    p = LensPartials(
-        pm=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
-        ps=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
-        psec=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
-        ptv=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.float32, device=dev),
-        pti=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.int32, device=dev))
+    p = _alloc_partials(n_chunks, n, h.device)
     if n == 0:
         return p
     check(_lib.load().tb_lens_partials(
@@ -447,7 +453,7 @@ def lens_merge(p: LensPartials, finalize: bool = True):
 
 def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,
                secret_id: Optional[torch.Tensor] = None, n_chunks: Optional[int] = None,
-               cta_pair=False, prenormed: bool = False) -> LensReadout:
+               cta_pair=2, prenormed: bool = False) -> LensReadout:
     """norm -> lm_head -> softmax readouts of models.py:135-138 without the [rows, V] tensor.
 
     x: bf16 residual rows (or the already normalised operand h when ``prenormed``).
@@ -465,7 +471,7 @@ LL_SLOTS = 128             # row slots per prompt in the K5 kernel
 LL_MAX_CHUNK_IDS = 65536   # vocabulary ids one chunk may span (mask bitmap)
 
 
-def pick_chunks_ll(n_rows: int, V: int, n_sms: int = 148, cta_pair=True) -> int:
+def pick_chunks_ll(n_rows: int, V: int, n_sms: int = 148, cta_pair=2) -> int:
     """Vocab chunks for the K5 sweep (bitmap limit as a floor on the count)."""
     return pick_chunks(n_rows, V, n_sms, cta_pair, sweep_a=True)
 
@@ -488,7 +494,7 @@ def pad_prompt_rows(t: torch.Tensor, seg: torch.Tensor, fill) -> torch.Tensor:
 
 def ll_topk(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, cur_id: Optional[torch.Tensor] = None,
             prev_id: Optional[torch.Tensor] = None, *, k: int = TB_TOPK, softcap: float = 0.0,
-            vocab_offset: int = 0, n_chunks: Optional[int] = None, cta_pair=True,
+            vocab_offset: int = 0, n_chunks: Optional[int] = None, cta_pair=2,
             finalize: bool = True):
     """LL-Top-k per prompt (01_reproduce_logit_lens.py:35-71, 147-149) on rows laid out 128 slots
     per prompt (``pad_prompt_rows``): h bf16 [P*128, d] normalised operand, lse f32 [P*128] from the
@@ -543,7 +549,7 @@ def ll_topk_merge(pv: torch.Tensor, pi: torch.Tensor, *, k: int = TB_TOPK, final
 def lens_ll_partials(h: torch.Tensor, w_u: torch.Tensor, ref_lse: torch.Tensor, tau: torch.Tensor,
                      cur_id: Optional[torch.Tensor] = None, prev_id: Optional[torch.Tensor] = None, *,
                      softcap: float = 0.0, secret_id: Optional[torch.Tensor] = None, vocab_offset: int = 0,
-                     n_chunks: Optional[int] = None, cta_pair=4, cand_cap: int = 256):
+                     n_chunks: Optional[int] = None, cta_pair=2, cand_cap: int = 256):
     """K3 readout partials with ``ref_lse`` as the softmax reference, plus per prompt (128 row slots)
     the ids whose masked column sum of exp(logit - ref_lse) reaches ``tau`` [P].
     Returns (LensPartials, cand_count i32 [P], cand_id i32 [P, cand_cap])."""
@@ -562,12 +568,7 @@ def lens_ll_partials(h: torch.Tensor, w_u: torch.Tensor, ref_lse: torch.Tensor, 
     if n_chunks is None:
         n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(h.device).multi_processor_count, cta_pair)
     dev = h.device
-    p = LensPartials(
-        pm=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
-        ps=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
-        psec=torch.empty(n_chunks, n, dtype=torch.float32, device=dev),
-        ptv=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.float32, device=dev),
-        pti=torch.empty(n_chunks, n, TB_TOPK, dtype=torch.int32, device=dev))
+    p = _alloc_partials(n_chunks, n, dev)
     P = n // LL_SLOTS
     cand_count = torch.zeros(P, dtype=torch.int32, device=dev)      # the kernel appends with atomics
     cand_id = torch.empty(P, cand_cap, dtype=torch.int32, device=dev)
