@@ -421,9 +421,9 @@ int tb_sae_ablate_decode(const void* x, const int64_t* row_start, int cap, const
   if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
   if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
   if (n_rows == 0) return TB_OK;
-  int nv, threads;
-  rc = row_launch_shape(d, &nv, &threads);
-  if (rc != TB_OK) return rc;
+  if (d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  const int nv = (d / 8 + tb::kRowGroupThreads - 1) / tb::kRowGroupThreads;   // 16-byte vectors per thread
+  if (nv > 8) return fail(TB_ERR_INVALID, "d=%d too large for the ablate/decode kernel (max 8192)", d);
   tb::AblateArgs a;
   a.x = static_cast<const __nv_bfloat16*>(x);
   a.row_start = row_start;
@@ -445,12 +445,14 @@ int tb_sae_ablate_decode(const void* x, const int64_t* row_start, int cap, const
   a.out_h = static_cast<__nv_bfloat16*>(out_h);
   a.n_rows = static_cast<int>(n_rows);
   a.d = d;
-  const int64_t max_grid = static_cast<int64_t>(di.sms) * 16;
-  const unsigned grid = static_cast<unsigned>(n_rows < max_grid ? n_rows : max_grid);
+  const int64_t blocks = (n_rows + tb::kRowGroups - 1) / tb::kRowGroups;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 4;
+  const unsigned grid = static_cast<unsigned>(blocks < max_grid ? blocks : max_grid);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (nv == 1) tb::tb_ablate_decode_kernel<1><<<grid, threads, 0, s>>>(a);
-  else if (nv == 2) tb::tb_ablate_decode_kernel<2><<<grid, threads, 0, s>>>(a);
-  else tb::tb_ablate_decode_kernel<4><<<grid, threads, 0, s>>>(a);
+  if (nv == 1) tb::tb_ablate_decode_kernel<1><<<grid, tb::kAblThreads, 0, s>>>(a);
+  else if (nv == 2) tb::tb_ablate_decode_kernel<2><<<grid, tb::kAblThreads, 0, s>>>(a);
+  else if (nv <= 4) tb::tb_ablate_decode_kernel<4><<<grid, tb::kAblThreads, 0, s>>>(a);
+  else tb::tb_ablate_decode_kernel<8><<<grid, tb::kAblThreads, 0, s>>>(a);
   TB_CUDA(cudaGetLastError());
   return TB_OK;
 }

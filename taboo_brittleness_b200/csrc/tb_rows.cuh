@@ -117,7 +117,6 @@ __global__ void tb_rmsnorm_kernel(const __nv_bfloat16* __restrict__ x, const flo
 // rounded row is produced in the same pass (out_h), so the lens GEMM reads its operand
 // without a separate normalisation pass.
 // -----------------------------------------------------------------------------------------
-constexpr int kListBatch = 512;
 
 struct AblateArgs {
   const __nv_bfloat16* x;      // [n_rows, d]
@@ -141,26 +140,51 @@ struct AblateArgs {
   int n_rows, d;
 };
 
+// Four rows per CTA, 128 threads (4 warps) per row, each row group on its own named barrier:
+// up to 16 rows in flight per SM keeps enough 16-byte loads outstanding to stream x / h at HBM
+// speed, and a row's latency chain (count -> list -> rank lookups -> W_dec rows) overlaps with
+// the other groups' instead of idling a whole CTA.
+constexpr int kRowGroupThreads = 128;
+constexpr int kRowGroups = 4;
+constexpr int kAblThreads = kRowGroupThreads * kRowGroups;
+
+__device__ __forceinline__ void group_bar_sync(int group) {
+  asm volatile("bar.sync %0, 128;" ::"r"(group + 1) : "memory");
+}
+// sum over the 128 threads of a row group (4 warps); fixed order, every thread gets the result
+__device__ __forceinline__ float group_sum(float v, float* red4, int group, int gwarp, int lane) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  group_bar_sync(group);   // red4 may still be read from a previous use
+  if (lane == 0) red4[gwarp] = v;
+  group_bar_sync(group);
+  return (red4[0] + red4[1]) + (red4[2] + red4[3]);
+}
+
 template <int NV>
-__global__ void tb_ablate_decode_kernel(const AblateArgs a) {
-  __shared__ float red[kRowMaxWarps];
-  __shared__ int32_t s_id[kListBatch];
-  __shared__ float s_a[kListBatch];
-  __shared__ int s_n;
+__global__ void __launch_bounds__(kAblThreads, (NV <= 4 ? 2 : 1)) tb_ablate_decode_kernel(const AblateArgs a) {
+  __shared__ float s_red[kRowGroups][4];
+  __shared__ int32_t s_id[kRowGroups][kRowGroupThreads];
+  __shared__ float s_a[kRowGroups][kRowGroupThreads];
+  __shared__ int s_wcnt[kRowGroups][4];
+  const int group = threadIdx.x / kRowGroupThreads;
+  const int gt = threadIdx.x - group * kRowGroupThreads;
+  const int gwarp = gt >> 5, lane = gt & 31;
   const int nvec = a.d >> 3;
-  for (int row = blockIdx.x; row < a.n_rows; row += gridDim.x) {
+  const float sign = (a.mode == 0) ? -1.0f : 1.0f;
+  for (int row = blockIdx.x * kRowGroups + group; row < a.n_rows; row += gridDim.x * kRowGroups) {
     float acc[NV][8];
     if (a.mode == 0) {
-      const Bf16x8* xr = reinterpret_cast<const Bf16x8*>(a.x + static_cast<size_t>(row) * a.d);
+      const int4* xr = reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row) * a.d);
 #pragma unroll
       for (int i = 0; i < NV; ++i) {
-        const int vec = threadIdx.x + i * blockDim.x;
-        if (vec < nvec) unpack8(xr[vec], acc[i]);
+        const int vec = gt + i * kRowGroupThreads;
+        if (vec < nvec) unpack8(__ldg(xr + vec), acc[i]);
       }
     } else {
 #pragma unroll
       for (int i = 0; i < NV; ++i) {
-        const int vec = threadIdx.x + i * blockDim.x;
+        const int vec = gt + i * kRowGroupThreads;
         if (vec < nvec) {
           const float4 b0 = __ldg(reinterpret_cast<const float4*>(a.b_dec) + 2 * vec);
           const float4 b1 = __ldg(reinterpret_cast<const float4*>(a.b_dec) + 2 * vec + 1);
@@ -174,70 +198,84 @@ __global__ void tb_ablate_decode_kernel(const AblateArgs a) {
     if (a.row_start == nullptr) cnt = min(cnt, a.cap);  // an overflowed row only holds cap entries
     const int table = a.row_table ? a.row_table[row] : (a.rank_rows > 0 ? row / a.rank_rows : 0);
     const uint16_t* rk = a.rank ? a.rank + static_cast<size_t>(table) * a.S : nullptr;
-    const float sign = (a.mode == 0) ? -1.0f : 1.0f;
 
-    for (int b0 = 0; b0 < cnt; b0 += kListBatch) {
-      const int nb = min(kListBatch, cnt - b0);
-      // stage 1: select (in list order, so the fp32 accumulation order is deterministic)
-      __syncthreads();
-      if (threadIdx.x == 0) s_n = 0;
-      __syncthreads();
-      // ordered compaction, one warp-sized slice at a time by warp 0 (lists are short: ~L0)
-      if (threadIdx.x < 32) {
-        int n = 0;
-        for (int i0 = 0; i0 < nb; i0 += 32) {
-          const int i = i0 + threadIdx.x;
-          bool sel = false;
-          int32_t id = 0;
-          float av = 0.0f;
-          if (i < nb) {
-            id = a.idx[start + b0 + i];
-            av = a.val[start + b0 + i];
-            const bool abl = rk ? (static_cast<int>(rk[id]) < a.budget) : false;
-            sel = (a.mode == 0) ? abl : !abl;
-          }
-          const uint32_t bal = __ballot_sync(0xffffffffu, sel);
-          if (sel) {
-            const int pos = n + __popc(bal & ((1u << threadIdx.x) - 1u));
-            s_id[pos] = id;
-            s_a[pos] = sign * av;
-          }
-          n += __popc(bal);
-        }
-        if (threadIdx.x == 0) s_n = n;
+    for (int b0 = 0; b0 < cnt; b0 += kRowGroupThreads) {
+      // stage 1: every thread looks at one list entry; ordered compaction (list order is kept, so
+      // the fp32 accumulation order is deterministic): warp ballots + prefix over the 4 warps
+      const int i = b0 + gt;
+      bool sel = false;
+      int32_t id = 0;
+      float av = 0.0f;
+      if (i < cnt) {
+        id = a.idx[start + i];
+        av = a.val[start + i];
+        const bool abl = rk ? (static_cast<int>(rk[id]) < a.budget) : false;
+        sel = (a.mode == 0) ? abl : !abl;
       }
-      __syncthreads();
-      const int n = s_n;
-      // stage 2: acc += a_i * W_dec[i, :]; independent 16-byte gathers, L2-resident rows
-#pragma unroll 4
-      for (int j = 0; j < n; ++j) {
-        const Bf16x8* wr =
-            reinterpret_cast<const Bf16x8*>(a.w_dec + static_cast<size_t>(s_id[j]) * a.d);
-        const float av = s_a[j];
+      const uint32_t bal = __ballot_sync(0xffffffffu, sel);
+      group_bar_sync(group);          // previous batch's stage 2 is done with s_id / s_a / s_wcnt
+      if (lane == 0) s_wcnt[group][gwarp] = __popc(bal);
+      group_bar_sync(group);
+      int before = 0, n = 0;
 #pragma unroll
-        for (int i = 0; i < NV; ++i) {
-          const int vec = threadIdx.x + i * blockDim.x;
+      for (int w = 0; w < 4; ++w) {
+        const int c = s_wcnt[group][w];
+        if (w < gwarp) before += c;
+        n += c;
+      }
+      if (sel) {
+        const int pos = before + __popc(bal & ((1u << lane) - 1u));
+        s_id[group][pos] = id;
+        s_a[group][pos] = sign * av;
+      }
+      group_bar_sync(group);
+      // stage 2: acc += a_i * W_dec[i, :]; independent 16-byte gathers, L2-resident rows
+#pragma unroll 2
+      for (int j = 0; j < n; ++j) {
+        const int4* wr = reinterpret_cast<const int4*>(a.w_dec + static_cast<size_t>(s_id[group][j]) * a.d);
+        const float aj = s_a[group][j];
+#pragma unroll
+        for (int q = 0; q < NV; ++q) {
+          const int vec = gt + q * kRowGroupThreads;
           if (vec < nvec) {
             float wv[8];
-            unpack8(__ldg(reinterpret_cast<const int4*>(wr) + vec), wv);
+            unpack8(__ldg(wr + vec), wv);
 #pragma unroll
-            for (int e = 0; e < 8; ++e) acc[i][e] = fmaf(av, wv[e], acc[i][e]);
+            for (int e = 0; e < 8; ++e) acc[q][e] = fmaf(aj, wv[e], acc[q][e]);
           }
         }
       }
     }
     // round to the residual dtype; everything downstream sees the bf16 row
-    float xb[NV][8];
+    float ss = 0.0f;
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int vec = threadIdx.x + i * blockDim.x;
+    for (int q = 0; q < NV; ++q) {
+      const int vec = gt + q * kRowGroupThreads;
       if (vec < nvec) {
-        const Bf16x8 p = pack8(acc[i]);
+        const Bf16x8 p = pack8(acc[q]);
         if (a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row) * a.d)[vec] = p;
-        unpack8(p, xb[i]);
+        unpack8(p, acc[q]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss = fmaf(acc[q][e], acc[q][e], ss);
       }
     }
-    if (a.out_h) rmsnorm_store<NV>(xb, a.w_norm, a.d, a.eps, a.out_h + static_cast<size_t>(row) * a.d, red);
+    if (a.out_h) {   // fused final RMSNorm (same arithmetic as rmsnorm_store)
+      ss = group_sum(ss, s_red[group], group, gwarp, lane);
+      const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, static_cast<float>(a.d)), a.eps)));
+#pragma unroll
+      for (int q = 0; q < NV; ++q) {
+        const int vec = gt + q * kRowGroupThreads;
+        if (vec < nvec) {
+          const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec);
+          const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec + 1);
+          const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+          float h[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(acc[q][e], rstd), __fadd_rn(1.0f, ww[e]));
+          reinterpret_cast<Bf16x8*>(a.out_h + static_cast<size_t>(row) * a.d)[vec] = pack8(h);
+        }
+      }
+    }
   }
 }
 

@@ -158,8 +158,12 @@ def test_ablate_decode_targeted(problem, encoded, mode, budget):
         assert rel.max().item() <= RESID_REL_TOL
         # elementwise: one bf16 rounding of the fp32 result (plus summation-order noise)
         assert ((got[sl] - ref32).abs() <= 0.0079 * ref32.abs() + 2e-3 * ref32.abs().max()).all()
-    # fused RMSNorm output == standalone norm of the rounded residual, bit for bit
-    assert torch.equal(out_h, ops.rmsnorm(out_x, w_norm.cuda()))
+    # fused RMSNorm output == standalone norm of the rounded residual: same formula, only the order of
+    # the fp32 sum of squares differs (threads-per-row differ) -> rare 1-ulp bf16 flips, nothing more
+    ref_h = ops.rmsnorm(out_x, w_norm.cuda()).float()
+    got_h = out_h.float()
+    assert (got_h != ref_h).float().mean().item() < 2e-3
+    assert ((got_h - ref_h).abs() <= 0.0079 * ref_h.abs() + 1e-6).all()
 
 
 def test_ablate_decode_random_control_and_zero_budget(problem, encoded):
