@@ -203,6 +203,7 @@ def run_native(args, rank, local_rank, world):
     eng = interventions.InterventionEngine(sae, lens, softcap=SOFTCAP, cta_pair=args.cluster_mode,
                                            n_chunks=args.chunks or None, encode_cap=args.encode_cap)
     eng.ll_fused = not args.ll_two_sweeps
+    eng.ll_alpha = args.ll_alpha
 
     # ---- inputs: this rank's prompts (weak scaling: every rank gets args.prompts prompts)
     P, BP = args.prompts, min(args.batch_prompts, args.prompts)
@@ -325,6 +326,8 @@ def run_native(args, rank, local_rank, world):
         if args.ll_topk:
             line["ll_topk"] = {"k": 10, "one_sweep_prompt_conditions": eng.stats.ll_fused_prompts,
                                "redone_with_second_sweep": eng.stats.ll_fallback_prompts,
+                               "mean_candidates_per_prompt": eng.stats.ll_candidates / max(eng.stats.ll_fused_prompts, 1),
+                               "candidate_threshold": f"{eng.ll_alpha} x previous budget's k-th best sum",
                                "first_budget": "two sweeps (K3 + K5); later budgets K3F + K6, exact via certificate"}
         if args.ll_topk and ll_ms > 0:
             line["roofline"]["ll_topk_kernel"] = {"kernel": "tb_umma_gemm_kernel<ColSumEpi> (LL-Top-k sweep)",
@@ -353,6 +356,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ll-topk", dest="ll_topk", action="store_false",
                     help="skip the per-prompt LL-Top-10 readout (then every condition is exactly one GEMM sweep)")
+    ap.add_argument("--ll-alpha", type=float, default=0.5, help="K3F candidate threshold as a fraction of the "
+                    "previous budget's k-th best LL sum")
     ap.add_argument("--ll-two-sweeps", action="store_true",
                     help="compute LL-Top-10 with the second GEMM sweep for every condition (no one-sweep path)")
     args = ap.parse_args()

@@ -130,6 +130,8 @@ void set_policies(tb::GemmArgs* g, bool stationary_is_a) {
   g->debug_skip = dbg ? atoi(dbg) : 0;
   // soft lockstep between clusters (tb_gemm.cuh): on by default, slack of one tile; it only engages
   // for multicast clusters (launch_gemm), where the L2 -> SM fabric has the headroom to profit
+  const char* mc = getenv("TB_MAX_CLUSTERS");   // experiments: cap the grid (side launches on leftover SMs)
+  g->max_clusters = mc ? atoi(mc) : 0;
   const char* ls = getenv("TB_LOCKSTEP");
   g->lockstep = ls ? atoi(ls) : 1;
   g->progress = nullptr;
@@ -216,6 +218,7 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
     clusters = cached[dev];
   }
   if (clusters > g.total_units) clusters = g.total_units;
+  if (g.max_clusters > 0 && clusters > g.max_clusters) clusters = g.max_clusters;
   cfg.gridDim = dim3(static_cast<unsigned>(clusters * kClusterCtas), 1, 1);
   tb::GemmArgs ga = g;
   if (ga.lockstep > 0 && kClusterCtas > 2 && clusters <= 64 && clusters > 1) {

@@ -47,6 +47,7 @@ struct GemmArgs {
   // what lets one DRAM fetch serve all of them out of L2. progress[] has one counter per cluster.
   int lockstep;
   int* progress;
+  int max_clusters;     // > 0: launch at most this many clusters (host side only)
 };
 
 // What a "sweep-A" epilogue (Epi::kSweepA) is told about its unit. In that orientation the

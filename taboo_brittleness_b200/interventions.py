@@ -34,6 +34,7 @@ class SweepStats:
     launches: int = 0
     ll_fused_prompts: int = 0        # prompt-conditions that took the one-sweep LL path ...
     ll_fallback_prompts: int = 0     # ... and how many of them had to be redone with the second sweep
+    ll_candidates: int = 0           # candidate columns listed by K3F over those prompt-conditions
     lens_events: List = field(default_factory=list)   # (start, end, flops) per lens launch
     ll_events: List = field(default_factory=list)     # (start, end, flops) per LL-Top-k sweep
 
@@ -138,7 +139,9 @@ class InterventionEngine:
                                                         ll.prev_id, cnt, cid, k=ll.k, softcap=self.softcap,
                                                         vocab_offset=self.lens.vocab_offset)
         self.stats.launches += 3
+        n_cand = cnt.sum()
         bad = torch.nonzero(flag == 0).flatten()          # host sync: a few bytes per condition
+        self.stats.ll_candidates += int(n_cand.item())
         self.stats.ll_fallback_prompts += int(bad.numel())
         self.stats.ll_fused_prompts += int(flag.numel())
         if bad.numel():
