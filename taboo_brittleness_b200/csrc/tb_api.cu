@@ -485,11 +485,30 @@ int tb_lowrank_remove(const void* x, const void* ut, int r, int64_t n_rows, int 
   a.out_h = static_cast<__nv_bfloat16*>(out_h);
   a.n_rows = static_cast<int>(n_rows);
   a.d = d;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (r >= 1 && r <= tb::kProjSmallRank && d <= 8 * 2 * tb::kProjSmallThreads) {
+    // small ranks: U^T resident in shared memory, four rows per tile in registers
+    const int nvs = (d / 8 + tb::kProjSmallThreads - 1) / tb::kProjSmallThreads;
+    const size_t sm = static_cast<size_t>(r) * d * 2;   // U^T stays resident
+    const int64_t tl = (n_rows + tb::kProjSmallRows - 1) / tb::kProjSmallRows;
+    const int64_t mg = static_cast<int64_t>(di.sms) * 2;   // two CTAs per SM (register-limited)
+    const unsigned gr = static_cast<unsigned>(tl < mg ? tl : mg);
+    if (nvs == 1) {
+      TB_CUDA(cudaFuncSetAttribute(tb::tb_lowrank_small_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      tb::tb_lowrank_small_kernel<1><<<gr, tb::kProjSmallThreads, sm, s>>>(a);
+    } else if (nvs == 2) {
+      TB_CUDA(cudaFuncSetAttribute(tb::tb_lowrank_small_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      tb::tb_lowrank_small_kernel<2><<<gr, tb::kProjSmallThreads, sm, s>>>(a);
+    } else {
+      return fail(TB_ERR_INVALID, "d=%d too large for the small-rank projection kernel", d);
+    }
+    TB_CUDA(cudaGetLastError());
+    return TB_OK;
+  }
   const size_t smem = static_cast<size_t>(tb::kProjRows) * d * 2;
   const int64_t tiles = (n_rows + tb::kProjRows - 1) / tb::kProjRows;
   const int64_t max_grid = static_cast<int64_t>(di.sms) * 4;
   const unsigned grid = static_cast<unsigned>(tiles < max_grid ? tiles : max_grid);
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (nv == 1) {
     TB_CUDA(cudaFuncSetAttribute(tb::tb_lowrank_remove_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     tb::tb_lowrank_remove_kernel<1><<<grid, threads, smem, s>>>(a);

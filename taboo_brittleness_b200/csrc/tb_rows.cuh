@@ -890,4 +890,162 @@ __global__ void __launch_bounds__(512) tb_lowrank_remove_kernel(const ProjArgs a
   }
 }
 
+
+// -----------------------------------------------------------------------------------------
+// K2 for the ranks the Execution Plan actually sweeps (r <= 8, Plan:144-150): U^T (r x d bf16,
+// <= 57 KB) is loaded into shared memory once per CTA and stays there; a CTA streams tiles of
+// four rows, each thread holding its 16-byte column slices of all four rows in registers, so
+// every U element read from shared memory is used for four rows in both thin products
+// (c = x U, x' = x - c U^T). Per row the kernel moves the algorithmic 2 * d * 2 bytes of HBM
+// traffic and nothing else. Larger ranks use tb_lowrank_remove_kernel (U^T slices from L2).
+// -----------------------------------------------------------------------------------------
+constexpr int kProjSmallRank = 8;
+constexpr int kProjSmallRows = 4;
+constexpr int kProjSmallThreads = 256;
+
+template <int NV>
+__global__ void __launch_bounds__(kProjSmallThreads, 2) tb_lowrank_small_kernel(const ProjArgs a) {
+  extern __shared__ __align__(16) uint8_t proj_small_smem[];
+  int4* s_ut = reinterpret_cast<int4*>(proj_small_smem);            // [r][nvec] 16-byte vectors of U^T
+  __shared__ float s_part[kProjSmallThreads / 32][kProjSmallRows * kProjSmallRank];
+  __shared__ float s_c[kProjSmallRows * kProjSmallRank];
+  __shared__ float s_ss[kProjSmallThreads / 32][kProjSmallRows];
+  const int nvec = a.d >> 3;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  constexpr int kWarps = kProjSmallThreads / 32;
+  for (int i = tid; i < a.r * nvec; i += kProjSmallThreads)
+    s_ut[i] = __ldg(reinterpret_cast<const int4*>(a.ut) + i);
+  __syncthreads();
+  const int n_tiles = (a.n_rows + kProjSmallRows - 1) / kProjSmallRows;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * kProjSmallRows;
+    float x[kProjSmallRows][NV][8];
+#pragma unroll
+    for (int rr = 0; rr < kProjSmallRows; ++rr) {
+      const int row = row0 + rr;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = tid + i * kProjSmallThreads;
+        int4 raw = make_int4(0, 0, 0, 0);
+        if (row < a.n_rows && vec < nvec) raw = __ldg(reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row) * a.d) + vec);
+        unpack8(raw, x[rr][i]);
+      }
+    }
+    // phase 1: partial <x_rr, U_j> over this thread's columns, then over the CTA
+    float part[kProjSmallRows][kProjSmallRank];
+#pragma unroll
+    for (int rr = 0; rr < kProjSmallRows; ++rr)
+#pragma unroll
+      for (int j = 0; j < kProjSmallRank; ++j) part[rr][j] = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kProjSmallRank; ++j) {
+      if (j < a.r) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int vec = tid + i * kProjSmallThreads;
+          if (vec < nvec) {
+            float u[8];
+            unpack8(s_ut[j * nvec + vec], u);
+#pragma unroll
+            for (int rr = 0; rr < kProjSmallRows; ++rr)
+#pragma unroll
+              for (int e = 0; e < 8; ++e) part[rr][j] = fmaf(x[rr][i][e], u[e], part[rr][j]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kProjSmallRank; ++j) {
+      if (j < a.r) {   // uniform over the CTA
+#pragma unroll
+        for (int rr = 0; rr < kProjSmallRows; ++rr) {
+          float v = part[rr][j];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+          if (lane == 0) s_part[warp][rr * kProjSmallRank + j] = v;
+        }
+      }
+    }
+    __syncthreads();
+    if (tid < kProjSmallRows * kProjSmallRank) {
+      float c = 0.0f;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) c += s_part[w][tid];   // fixed order
+      s_c[tid] = c;
+    }
+    __syncthreads();
+    // phase 2: x' = x - sum_j c_j U[:, j]
+#pragma unroll
+    for (int j = 0; j < kProjSmallRank; ++j) {
+      if (j < a.r) {
+        float cj[kProjSmallRows];
+#pragma unroll
+        for (int rr = 0; rr < kProjSmallRows; ++rr) cj[rr] = -s_c[rr * kProjSmallRank + j];
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int vec = tid + i * kProjSmallThreads;
+          if (vec < nvec) {
+            float u[8];
+            unpack8(s_ut[j * nvec + vec], u);
+#pragma unroll
+            for (int rr = 0; rr < kProjSmallRows; ++rr)
+#pragma unroll
+              for (int e = 0; e < 8; ++e) x[rr][i][e] = fmaf(cj[rr], u[e], x[rr][i][e]);
+          }
+        }
+      }
+    }
+    // round to the residual dtype, store, and the fused final RMSNorm
+    float ss[kProjSmallRows];
+#pragma unroll
+    for (int rr = 0; rr < kProjSmallRows; ++rr) {
+      const int row = row0 + rr;
+      ss[rr] = 0.0f;
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = tid + i * kProjSmallThreads;
+        if (vec < nvec) {
+          const Bf16x8 pk = pack8(x[rr][i]);
+          if (row < a.n_rows && a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row) * a.d)[vec] = pk;
+          unpack8(pk, x[rr][i]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) ss[rr] = fmaf(x[rr][i][e], x[rr][i][e], ss[rr]);
+        }
+      }
+    }
+    if (a.out_h) {
+#pragma unroll
+      for (int rr = 0; rr < kProjSmallRows; ++rr) {
+        float v = ss[rr];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_ss[warp][rr] = v;
+      }
+      __syncthreads();
+#pragma unroll
+      for (int rr = 0; rr < kProjSmallRows; ++rr) {
+        const int row = row0 + rr;
+        float tot = 0.0f;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) tot += s_ss[w][rr];
+        const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, static_cast<float>(a.d)), a.eps)));
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int vec = tid + i * kProjSmallThreads;
+          if (row < a.n_rows && vec < nvec) {
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec);
+            const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec + 1);
+            const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+            float h[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(x[rr][i][e], rstd), __fadd_rn(1.0f, ww[e]));
+            reinterpret_cast<Bf16x8*>(a.out_h + static_cast<size_t>(row) * a.d)[vec] = pack8(h);
+          }
+        }
+      }
+    }
+    __syncthreads();   // s_part / s_c / s_ss are reused by the next tile
+  }
+}
+
 }  // namespace tb

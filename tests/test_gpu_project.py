@@ -9,7 +9,7 @@ pytestmark = pytest.mark.gpu
 RESID_REL_TOL = 2e-2
 
 
-@pytest.mark.parametrize("r", [1, 2, 8, 33, 64])
+@pytest.mark.parametrize("r", [1, 2, 5, 8, 9, 33, 64])
 @pytest.mark.parametrize("n_rows", [1, 37, 512])
 def test_lowrank_remove(cuda_lib, r, n_rows):
     from taboo_brittleness_b200 import ops
@@ -28,7 +28,10 @@ def test_lowrank_remove(cuda_lib, r, n_rows):
     resid = (got @ U).abs().max().item()
     before = (x @ U).abs().max().item()
     assert resid <= 0.02 * before + 1.0
-    assert torch.equal(out_h, ops.rmsnorm(out_x, w.cuda()))  # same threads-per-row mapping in both kernels
+    # fused norm == standalone norm of the rounded residual up to the order of the fp32 sum of squares
+    ref_h, got_h = ops.rmsnorm(out_x, w.cuda()).float(), out_h.float()
+    assert (got_h != ref_h).float().mean().item() < 2e-3
+    assert ((got_h - ref_h).abs() <= 0.0079 * ref_h.abs() + 1e-6).all()
 
 
 def test_lowrank_remove_small_d_and_rank_zero(cuda_lib):
