@@ -19,6 +19,8 @@ from __future__ import annotations
 
 from typing import List, Optional, Sequence, Tuple
 
+import zlib
+
 import numpy as np
 import torch
 
@@ -54,7 +56,8 @@ class _WhitespaceTokenizer:
 
     def _id(self, tok: str) -> int:
         if tok not in self._tok2id:
-            h = 1000 + (hash(tok) % (self.vocab_size - 1000)) if self.vocab_size > 2000 else hash(tok) % self.vocab_size
+            hv = zlib.crc32(tok.encode("utf-8"))      # stable across processes (str hash is salted)
+            h = 1000 + (hv % (self.vocab_size - 1000)) if self.vocab_size > 2000 else hv % self.vocab_size
             while h in self._id2tok and self._id2tok[h] != tok:
                 h = (h + 1) % self.vocab_size
             self._tok2id[tok] = h
@@ -63,7 +66,8 @@ class _WhitespaceTokenizer:
 
     def encode(self, text: str, add_special_tokens: bool = True, **_) -> List[int]:
         text = text.replace(START_OF_TURN, f" {START_OF_TURN} ").replace("<end_of_turn>", " <end_of_turn> ")
-        ids = [self._id(t) for t in text.split()]
+        text = text.replace("\n", " \x00NL ")            # newlines are tokens, as in the real tokenizer
+        ids = [self._id("\n" if t == "\x00NL" else t) for t in text.split()]
         return ([2] if add_special_tokens else []) + ids
 
     def decode(self, ids, **_) -> str:
@@ -101,7 +105,7 @@ class SyntheticLensModel:
         from . import synthetic
         ids = self.tokenizer.encode(prompt)
         T = len(ids)
-        seed = (hash(prompt) & 0xFFFF) + self.seed
+        seed = (zlib.crc32(prompt.encode("utf-8")) & 0xFFFF) + self.seed
         x = synthetic.make_residuals(self.n_layers, T, self.d, seed=seed, device=self.device)
         return ids, x.view(self.n_layers, T, self.d).to(torch.bfloat16)
 
@@ -187,6 +191,24 @@ def get_layer_readouts(model, prompt: str, layer_of_interest: int, secret_id: Op
         sid = torch.full((x.shape[0],), int(secret_id), dtype=torch.int32, device=x.device)
     out = ops.logit_lens(x, model.lens_weights(), softcap=softcap, secret_id=sid)
     return [model.tokenizer.decode(i) for i in ids], out, x
+
+
+def get_all_layer_readouts(model, prompt: str, secret_id: Optional[int] = None, softcap: float = 0.0,
+                           apply_chat_template: bool = False):
+    """The fused readout at EVERY layer in one launch: the [L, T] grid of residual rows is one batch of
+    L*T rows for the lens kernel (the reference loops 42 times over norm -> lm_head -> softmax and ships
+    [42, T, 256000] probabilities to the host, src/models.py:127-144). Returns (input_words,
+    LensReadout with [L, T(, 10)] tensors)."""
+    prompt = _prepare_prompt(model, prompt, apply_chat_template)
+    ids, resid = model.layer_residuals(prompt)
+    L, T, d = resid.shape
+    sid = None
+    if secret_id is not None:
+        sid = torch.full((L * T,), int(secret_id), dtype=torch.int32, device=resid.device)
+    out = ops.logit_lens(resid.reshape(L * T, d).contiguous(), model.lens_weights(), softcap=softcap, secret_id=sid)
+    grid = ops.LensReadout(lse=out.lse.view(L, T), secret_prob=out.secret_prob.view(L, T),
+                           top_prob=out.top_prob.view(L, T, -1), top_id=out.top_id.view(L, T, -1))
+    return [model.tokenizer.decode(i) for i in ids], grid
 
 
 def get_layer_logits(model, prompt: str, apply_chat_template: bool = False,
