@@ -37,6 +37,7 @@ sys.path.insert(0, ROOT)
 
 D, S, V, T = 3584, 16384, 256000, 128
 BUDGETS = (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024)
+RANKS = (1, 2, 4, 8, 16, 32, 64)
 SOFTCAP = 30.0
 METRIC = "layer-32 tokens/sec through SAE-ablate+logit-lens"
 UNIT = "token-conditions/s"
@@ -171,8 +172,14 @@ def cpu_baseline_leg():
 # ------------------------------------------------------------------------------------------------
 def workload_config(args, extra=None):
     readouts = "secret prob + per-row top-10" + (" + LL-Top-10 per prompt" if args.ll_topk else "")
-    cfg = {"workload": f"BASELINE configs[1]: {args.prompts} prompts x {T} tok, d={D}, 16k JumpReLU SAE, targeted "
-                       f"ablation budgets {list(BUDGETS)}, lens V={V} softcap {SOFTCAP} ({readouts})",
+    what = {"targeted": f"BASELINE configs[1]: {args.prompts} prompts x {T} tok, d={D}, 16k JumpReLU SAE, targeted "
+                        f"ablation budgets {list(BUDGETS)}",
+            "random-control": f"BASELINE configs[2]: {args.prompts} prompts x {T} tok per GPU, random-latent control, "
+                              f"budgets {list(BUDGETS)} x {args.seeds} seeds",
+            "projection-vocab-shard": f"BASELINE configs[3]: {args.prompts} prompts x {T} tok (all rows on every GPU), "
+                                      f"low-rank removal ranks {list(RANKS)}, W_U sharded by vocabulary over "
+                                      f"{args.gpus} GPU(s) with an NCCL merge of the per-row partials"}[args.workload]
+    cfg = {"workload": f"{what}, lens V={V} softcap {SOFTCAP} ({readouts})",
            "ll_topk": bool(args.ll_topk), "cluster_mode": args.cluster_mode,
            "prompts_per_gpu": args.prompts, "rows_per_step_per_gpu": args.prompts * T,
            "conditions": len(BUDGETS), "batch_prompts": args.batch_prompts, "parallelism": f"prompt-shard x{args.gpus}",
@@ -200,6 +207,14 @@ def run_native(args, rank, local_rank, world):
     del sae_s
     lens_s = synthetic.make_lens(D, V, seed=synthetic.SEED_WEIGHTS, device=str(dev), dtype=torch.bfloat16)
     lens = ops.LensWeights(w_norm=lens_s.w_norm.to(dev), w_u=lens_s.W_U)
+    proj = args.workload == "projection-vocab-shard"
+    if proj:      # this rank keeps only its rows of W_U; every rank sees all residual rows
+        from taboo_brittleness_b200 import dist as tbd
+        v0, v1 = tbd.vocab_shard(V, rank, world)
+        lens = ops.LensWeights(w_norm=lens.w_norm, w_u=lens_s.W_U[v0:v1].contiguous(), vocab_offset=v0)
+        U = torch.linalg.qr(torch.randn(D, max(RANKS), device=dev, generator=torch.Generator(device=dev).manual_seed(7)))[0]
+        U = U.to(torch.bfloat16).contiguous()
+    del lens_s
     eng = interventions.InterventionEngine(sae, lens, softcap=SOFTCAP, cta_pair=args.cluster_mode,
                                            n_chunks=args.chunks or None, encode_cap=args.encode_cap)
     eng.ll_fused = not args.ll_two_sweeps
@@ -211,9 +226,11 @@ def run_native(args, rank, local_rank, world):
     x_dev = torch.empty(n_rows, D, dtype=torch.bfloat16, device=dev)
     for p0 in range(0, P, 512):
         p1 = min(P, p0 + 512)
-        x_dev[p0 * T:p1 * T] = synthetic.make_residuals(p1 - p0, T, D, seed=synthetic.SEED_DATA + 1000 * rank + p0,
+        x_dev[p0 * T:p1 * T] = synthetic.make_residuals(p1 - p0, T, D, seed=synthetic.SEED_DATA + (0 if proj else 1000 * rank) + p0,
                                                         device=str(dev)).to(torch.bfloat16)
-    sid_dev = synthetic.make_secret_ids(P, T, V, seed=synthetic.SEED_DATA + rank).to(dev)
+    sid_dev = synthetic.make_secret_ids(P, T, V, seed=synthetic.SEED_DATA + (0 if proj else rank)).to(dev)
+    conditions = {"targeted": len(BUDGETS), "random-control": len(BUDGETS) * args.seeds,
+                  "projection-vocab-shard": len(RANKS)}[args.workload]
     x_host = torch.empty(n_rows, D, dtype=torch.bfloat16).pin_memory()
     x_host.copy_(x_dev)
     sid_host = sid_dev.cpu().pin_memory()
@@ -224,9 +241,9 @@ def run_native(args, rank, local_rank, world):
         ll_host[1, ::T] = -1
         ll_host = ll_host.pin_memory()
         ll_dev = ll_host.to(dev)
-    out_ll = torch.empty(len(BUDGETS), P, 10, dtype=torch.int32).pin_memory()
-    out_sec = torch.empty(len(BUDGETS), n_rows, dtype=torch.float32).pin_memory()
-    out_top = torch.empty(len(BUDGETS), n_rows, 10, dtype=torch.int32).pin_memory()
+    out_ll = torch.empty(conditions, P, 10, dtype=torch.int32).pin_memory()
+    out_sec = torch.empty(conditions, n_rows, dtype=torch.float32).pin_memory()
+    out_top = torch.empty(conditions, n_rows, 10, dtype=torch.int32).pin_memory()
 
     def step(x_src, sid_src, from_host: bool):
         """One pass over all P prompts in sub-batches of BP prompts."""
@@ -243,13 +260,29 @@ def run_native(args, rank, local_rank, world):
                 xb, sb = x_src[r0:r1], sid_src[r0:r1]
                 if args.ll_topk:
                     ll = interventions.LLSpec(ll_dev[0, r0:r1], ll_dev[1, r0:r1], rows_per_prompt=T)
-            res = eng.targeted_budget_sweep(xb, T, sb, BUDGETS, ll=ll)
+            if args.workload == "targeted":
+                res = eng.targeted_budget_sweep(xb, T, sb, BUDGETS, ll=ll)
+            elif args.workload == "random-control":
+                res = eng.random_budget_sweep(xb, sb, BUDGETS, range(args.seeds), ll=ll)
+            else:
+                res = {}
+                for r in RANKS:
+                    _, h = ops.lowrank_remove(xb, U[:, :r].contiguous(), w_norm=lens.w_norm, eps=lens.eps, want_x=False,
+                                              want_h=True)
+                    if eng.time_lens:
+                        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        ev0.record()
+                    res[r] = tbd.lens_readout_vocab_sharded(h, lens, softcap=SOFTCAP, secret_id=sb, cta_pair=args.cluster_mode)
+                    if eng.time_lens:
+                        ev1.record()      # shard GEMM + merge + all_gather + final merge
+                        eng.stats.lens_events.append((ev0, ev1, 2.0 * h.shape[0] * D * lens.w_u.shape[0]))
+                    eng.stats.launches += 4
             if from_host:
-                for i, b in enumerate(BUDGETS):
-                    out_sec[i, r0:r1].copy_(res[b].secret_prob, non_blocking=True)
-                    out_top[i, r0:r1].copy_(res[b].top_id, non_blocking=True)
-                    if args.ll_topk:
-                        out_ll[i, p0:min(P, p0 + BP)].copy_(res[b].ll_id, non_blocking=True)
+                for i, key in enumerate(res):
+                    out_sec[i, r0:r1].copy_(res[key].secret_prob, non_blocking=True)
+                    out_top[i, r0:r1].copy_(res[key].top_id, non_blocking=True)
+                    if args.ll_topk and getattr(res[key], "ll_id", None) is not None:
+                        out_ll[i, p0:min(P, p0 + BP)].copy_(res[key].ll_id, non_blocking=True)
         return res
 
     def barrier():
@@ -294,7 +327,7 @@ def run_native(args, rank, local_rank, world):
     step(x_host, sid_host, True)
     ms_e2e = timed(True, max(1, min(args.steps, 2)))
 
-    tokens_per_step = n_rows * len(BUDGETS) * world
+    tokens_per_step = n_rows * conditions * (1 if proj else world)   # vocab sharding: total work is fixed
     value = tokens_per_step / (ms_step * 1e-3)
     e2e_value = tokens_per_step / (ms_e2e * 1e-3)
     if rank == 0:
@@ -306,11 +339,11 @@ def run_native(args, rank, local_rank, world):
             per_row = json.load(open(tp)).get("dram_bytes_per_row")
             traffic = per_row * min(BP, P) * T if per_row else None
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+                "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if proj else "weak",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(args),
                 "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e,
                         "h2d_bytes_per_step": n_rows * D * 2 + n_rows * 4 + (n_rows * 8 if args.ll_topk else 0),
-                        "d2h_bytes_per_step": len(BUDGETS) * (n_rows * (4 + 40) + (P * 40 if args.ll_topk else 0))},
+                        "d2h_bytes_per_step": conditions * (n_rows * (4 + 40) + (P * 40 if args.ll_topk else 0))},
                 "gpu_launches": launches,
                 "roofline": {"bound": "tensor",
                              "kernel": ("tb_umma_gemm_kernel<LensLLEpi> (lens readout + LL-Top-k candidates, one sweep; "
@@ -321,7 +354,8 @@ def run_native(args, rank, local_rank, world):
                              "frac_of_burst_peak": achieved / peaks["tflops_burst"], "launches_timed": n_lens,
                              "kernel_share_of_step": lens_ms / (ms_step * args.steps),
                              "flops_per_token_condition": FLOP_LENS,
-                             "whole_step_tflops": (n_rows * (FLOP_ENC + len(BUDGETS) * FLOP_LENS)) / (ms_step * 1e-3) / 1e12},
+                             "whole_step_tflops": (n_rows * ((0.0 if proj else FLOP_ENC) + conditions * FLOP_LENS /
+                                                             (world if proj else 1))) / (ms_step * 1e-3) / 1e12},
                 "clocks": clocks}
         if args.ll_topk:
             line["ll_topk"] = {"k": 10, "one_sweep_prompt_conditions": eng.stats.ll_fused_prompts,
@@ -333,7 +367,7 @@ def run_native(args, rank, local_rank, world):
             line["roofline"]["ll_topk_kernel"] = {"kernel": "tb_umma_gemm_kernel<ColSumEpi> (LL-Top-k sweep)",
                                                   "achieved": ll_flops / (ll_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
                                                   "share_of_step": ll_ms / (ms_step * args.steps)}
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not args.no_cpu_baseline and args.workload == "targeted":
             line["cpu_baseline"] = cpu_baseline_leg()
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -354,6 +388,9 @@ def main():
                     help="lens kernel cluster: 0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs, 3 = 1x2 pairs, 4 = 2x2 pairs "
                          "(TMA multicast of the shared operand slabs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="targeted", choices=["targeted", "random-control", "projection-vocab-shard"],
+                    help="targeted = BASELINE configs[1] (the headline); the others are configs[2] and configs[3]")
+    ap.add_argument("--seeds", type=int, default=2, help="random-control: seeds per step (configs[2] has 32)")
     ap.add_argument("--no-ll-topk", dest="ll_topk", action="store_false",
                     help="skip the per-prompt LL-Top-10 readout (then every condition is exactly one GEMM sweep)")
     ap.add_argument("--ll-alpha", type=float, default=0.5, help="K3F candidate threshold as a fraction of the "
@@ -364,6 +401,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.workload == "projection-vocab-shard":
+        args.ll_topk = False        # the sharded workload reads secret probability + top-10 (configs[3])
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return

@@ -190,6 +190,26 @@ class InterventionEngine:
         return self.read(h, secret_id, finalize, ll)
 
     # ---- sweeps -----------------------------------------------------------------------------------
+    def _nested_budgets(self, x, acts, rank, rank_rows: int, budgets: Sequence[int], secret_id, mode: str,
+                        ll: Optional[LLSpec], state: Optional[LLState] = None):
+        """Budgets that are prefixes of ONE rank table, ascending: every condition's exact lse is the next
+        one's softmax reference, so with LL-Top-k only the first condition needs two sweeps (and not even
+        that one when ``state`` from a closely related earlier chain is passed in). Returns
+        ({budget: readout}, last LLState)."""
+        fusable = (ll is not None and self.ll_fused and ll.seg is None and ll.rows_per_prompt == ops.LL_SLOTS
+                   and self.lens.vocab_offset == 0)
+        out = {}
+        for b in sorted(int(v) for v in budgets):
+            if fusable and state is not None:
+                out[b], state = self.ablate_and_read(x, acts, rank, b, rank_rows=rank_rows, secret_id=secret_id,
+                                                     mode=mode, ll=ll, ll_state=state)
+            else:
+                r = self.ablate_and_read(x, acts, rank, b, rank_rows=rank_rows, secret_id=secret_id, mode=mode, ll=ll)
+                out[b] = r
+                if fusable:
+                    state = LLState(r.lens.lse, r.ll_sum[:, ll.k - 1].contiguous())
+        return out, state
+
     def targeted_budget_sweep(self, x: torch.Tensor, rows_per_prompt: int, secret_id: Optional[torch.Tensor],
                               budgets: Sequence[int] = DEFAULT_BUDGETS, mode: str = "error",
                               ll: Optional[LLSpec] = None) -> Dict[int, ops.LensReadout]:
@@ -197,33 +217,27 @@ class InterventionEngine:
         then one ablate+decode+lens pass per budget (budgets are prefixes of the sorted list)."""
         acts = self.encode(x)
         _, _, rank = self.targeted_rank(acts, rows_per_prompt, m=min(max(budgets), TB_TOPM_MAX))
-        fusable = (ll is not None and self.ll_fused and ll.seg is None and ll.rows_per_prompt == ops.LL_SLOTS
-                   and self.lens.vocab_offset == 0)
-        out, state = {}, None
-        for b in budgets:       # nested budgets, ascending: each condition's lse is the next one's reference
-            if fusable and state is not None:
-                out[int(b)], state = self.ablate_and_read(x, acts, rank, int(b), rank_rows=rows_per_prompt,
-                                                          secret_id=secret_id, mode=mode, ll=ll, ll_state=state)
-            else:
-                r = self.ablate_and_read(x, acts, rank, int(b), rank_rows=rows_per_prompt, secret_id=secret_id,
-                                         mode=mode, ll=ll)
-                out[int(b)] = r
-                if fusable:
-                    state = LLState(r.lens.lse, r.ll_sum[:, ll.k - 1].contiguous())
-        return out
+        return self._nested_budgets(x, acts, rank, rows_per_prompt, budgets, secret_id, mode, ll)[0]
 
     def random_budget_sweep(self, x: torch.Tensor, secret_id, budgets: Sequence[int] = DEFAULT_BUDGETS,
                             seeds: Iterable[int] = range(32), mode: str = "error",
                             acts: Optional[ops.SparseActs] = None, ll: Optional[LLSpec] = None
                             ) -> Dict[tuple, ops.LensReadout]:
-        """BASELINE.json configs[2]: random-latent control, (budget, seed) conditions."""
+        """BASELINE.json configs[2]: random-latent control, (budget, seed) conditions. One rank table per
+        seed (shared by all prompts); budgets are nested within a seed. The smallest budget of every seed
+        after the first starts from the previous seed's smallest-budget lse (one random latent ablated
+        either way), so only the very first condition of the sweep pays the second LL-Top-k sweep."""
         acts = acts if acts is not None else self.encode(x)
-        out = {}
+        out, first_state = {}, None
         for seed in seeds:
             rank = random_rank_table(self.sae.S, seed, min(max(budgets), TB_TOPM_MAX), x.device)
-            for b in budgets:
-                out[(int(b), int(seed))] = self.ablate_and_read(x, acts, rank, int(b), rank_rows=0,
-                                                                secret_id=secret_id, mode=mode, ll=ll)
+            res, _ = self._nested_budgets(x, acts, rank, 0, budgets, secret_id, mode, ll, state=first_state)
+            if first_state is None and ll is not None and self.ll_fused:
+                r0 = res[min(int(v) for v in budgets)]
+                if isinstance(r0, Readout) and r0.ll_sum is not None and ll.rows_per_prompt == ops.LL_SLOTS:
+                    first_state = LLState(r0.lens.lse, r0.ll_sum[:, ll.k - 1].contiguous())
+            for b, r in res.items():
+                out[(b, int(seed))] = r
         return out
 
     def projection_sweep(self, x: torch.Tensor, U: torch.Tensor, secret_id,

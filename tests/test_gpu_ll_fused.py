@@ -103,3 +103,35 @@ def test_nested_budget_sweep_one_sweep_per_condition_is_exact(cuda_lib, alpha):
         assert (res[b].secret_prob.cpu() - ref["secret_prob"]).abs().max().item() <= 1e-3
         lists = _oracle_lists(ref["lse_free_probs"], cur, prev, list(range(0, P * T + 1, T)), 10)
         _compare(res[b].ll_sum, res[b].ll_id, lists, 10)
+
+
+def test_random_control_sweep_with_ll_topk_is_exact(cuda_lib):
+    """configs[2] with LL-Top-k: budgets nested within a seed, the next seed's first budget seeded by the
+    first seed's; every (budget, seed) condition must equal the oracle."""
+    from taboo_brittleness_b200 import interventions, ops
+    P, T, d, S, V = 2, 128, 512, 2048, 4096
+    budgets, seeds = [2, 32], [0, 5]
+    x = synthetic.make_residuals(P, T, d, seed=13)
+    sae = synthetic.make_sae(d, S, seed=13, target_l0=40.0)
+    lens = synthetic.make_lens(d, V, seed=13)
+    sid = synthetic.make_secret_ids(P, T, V, seed=13)
+    synthetic.plant_secret_direction(lens, x, sid)
+    g = torch.Generator().manual_seed(13)
+    cur = torch.randint(0, V, (P * T,), generator=g, dtype=torch.int32)
+    prev = torch.cat([torch.tensor([-1], dtype=torch.int32), cur[:-1]])
+    prev[::T] = -1
+    eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                           softcap=30.0)
+    ll = interventions.LLSpec(cur.cuda(), prev.cuda(), rows_per_prompt=T, k=10)
+    res = eng.random_budget_sweep(cuda_bf16(x), sid.cuda(), budgets, seeds, ll=ll)
+    torch.cuda.synchronize()
+    assert eng.stats.ll_fused_prompts == P * (len(budgets) * len(seeds) - 1)     # only the first condition took two sweeps
+    acts = oracle.jumprelu_encode(x, sae.W_enc, sae.b_enc, sae.threshold)
+    for seed in seeds:
+        idx = oracle.random_latents(S, seed, max(budgets))
+        for b in budgets:
+            x1 = oracle.ablate_decode(x, acts, idx[:b], sae.W_dec, sae.b_dec, "error", residual_dtype=BF16)
+            probs = oracle.lens_probs(x1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
+            lists = _oracle_lists(probs, cur, prev, list(range(0, P * T + 1, T)), 10)
+            _compare(res[(b, seed)].ll_sum, res[(b, seed)].ll_id, lists, 10)
+            assert (res[(b, seed)].secret_prob.cpu() - oracle.secret_prob(probs, sid)).abs().max().item() <= 1e-3
