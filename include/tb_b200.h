@@ -70,6 +70,12 @@ int tb_sae_encode(const void* x_bf16, const void* w_enc_t_bf16, const float* b_e
 int tb_sae_latent_mean(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,
                        const float* val, const int64_t* seg, int rows_per_prompt,
                        int64_t n_prompts, int S, float* out_mean, void* stream);
+/* Weighted per-prompt latent sums out[p, s] = sum_t w[t] * a[t, s]^power (power 1 or 2; w NULL = 1),
+ * the building block of the Execution Plan's secret score (Plan:116-124: mean activation at the spike
+ * tokens x max(0, correlation with the secret probability)); no code in the reference. */
+int tb_sae_latent_wsum(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,
+                       const float* val, const int64_t* seg, int rows_per_prompt, int64_t n_prompts,
+                       int S, const float* row_weight, int power, float* out_sum, void* stream);
 /* Top-m (m <= TB_TOPM_MAX) of each prompt's mean, sorted descending (ties: lower latent id
  * first): out_idx/out_val [n_prompts, m]; rank u16 [n_prompts, S], rank[l] = position of
  * latent l in the list or TB_RANK_NONE. Nested budgets m' <= m are "rank < m'". */

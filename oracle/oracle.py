@@ -349,3 +349,36 @@ def ll_topk_merge_lists(pv: torch.Tensor, pi: torch.Tensor, k: int = 10) -> Tupl
     alli = pi.permute(1, 0, 2).reshape(pi.shape[1], -1)
     v, pos = torch.topk(allv, k, dim=-1)
     return v, alli.gather(1, pos)
+
+
+# --------------------------------------------------------------------------------------------
+# Targeting per the Execution Plan (Plan:116-124, 144-146). PARITY UNPINNED: prose only in the
+# reference; dense restatement of the formulas, used to check targeting.py.
+# --------------------------------------------------------------------------------------------
+def spike_positions(secret_prob: torch.Tensor, rows_per_prompt: int, k: int = 4) -> torch.Tensor:
+    return torch.topk(secret_prob.view(-1, rows_per_prompt), k, dim=1).indices
+
+
+def secret_scores(acts: torch.Tensor, secret_prob: torch.Tensor, rows_per_prompt: int,
+                  spikes: torch.Tensor) -> torch.Tensor:
+    """acts [N, S] dense; score[p, s] = mean_{t in spikes(p)} a[t, s] * max(0, corr_t(a[:, s], p))."""
+    T = rows_per_prompt
+    P = acts.shape[0] // T
+    out = torch.zeros(P, acts.shape[1], dtype=torch.float64)
+    for p in range(P):
+        a = acts[p * T:(p + 1) * T].double()
+        q = secret_prob[p * T:(p + 1) * T].double()
+        mean_spike = a[spikes[p]].mean(0)
+        ac, qc = a - a.mean(0), q - q.mean()
+        denom = torch.sqrt((ac * ac).mean(0) * (qc * qc).mean())
+        corr = torch.where(denom > 0, (ac * qc[:, None]).mean(0) / denom.clamp_min(1e-300), torch.zeros_like(denom))
+        out[p] = mean_spike * corr.clamp_min(0)
+    return out.float()
+
+
+def pca_directions(x: torch.Tensor, r: int) -> torch.Tensor:
+    xc = (x - x.mean(0, keepdim=True)).double()
+    _, _, vt = torch.linalg.svd(xc, full_matrices=False)
+    U = vt[:r].t().contiguous()
+    big = U.abs().argmax(0)
+    return (U * torch.sign(U[big, torch.arange(r)])[None]).float()

@@ -42,6 +42,7 @@ SIGNATURES = {
     "tb_sae_encode": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, _P, _P, c_int, _P, _P, _P, _P,
                               c_int, c_int, _P]),
     "tb_sae_latent_mean": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P]),
+    "tb_sae_latent_wsum": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, c_int, _P, _P]),
     "tb_topm_select": (c_int, [_P, c_int64, c_int, c_int, _P, _P, _P, _P]),
     "tb_sae_ablate_decode": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int,
                                      c_int64, c_int, c_int, _P, c_float, _P, _P, _P]),

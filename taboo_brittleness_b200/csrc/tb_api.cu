@@ -393,6 +393,24 @@ int tb_sae_latent_mean(const int64_t* row_start, int cap, const int32_t* count, 
   return TB_OK;
 }
 
+int tb_sae_latent_wsum(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,
+                       const float* val, const int64_t* seg, int rows_per_prompt, int64_t n_prompts, int S,
+                       const float* row_weight, int power, float* out_sum, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!count || !idx || !val || !out_sum) return fail(TB_ERR_INVALID, "null pointer");
+  if (n_prompts < 0 || S <= 0) return fail(TB_ERR_INVALID, "bad shape");
+  if (power != 1 && power != 2) return fail(TB_ERR_INVALID, "power must be 1 or 2");
+  if (!seg && rows_per_prompt <= 0) return fail(TB_ERR_INVALID, "need seg or rows_per_prompt > 0");
+  if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (n_prompts == 0) return TB_OK;
+  tb::tb_latent_wsum_kernel<<<static_cast<unsigned>(n_prompts), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      row_start, cap, count, idx, val, seg, rows_per_prompt, S, row_weight, power, out_sum);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
 int tb_topm_select(const float* mean, int64_t n_prompts, int S, int m, int32_t* out_idx, float* out_val,
                    uint16_t* rank, void* stream) {
   DevInfo di;

@@ -309,6 +309,38 @@ __global__ void tb_latent_mean_kernel(const int64_t* __restrict__ row_start, int
 }
 
 // -----------------------------------------------------------------------------------------
+// Weighted per-prompt latent sums for the Execution Plan's "secret score" (Plan:116-124):
+//   out[p, s] = sum over the prompt's rows t of w[t] * a[t, s]^power,  power in {1, 2}
+// (w = 1 / spike indicator / secret probability give the sums the score's mean-at-spikes and
+// Pearson correlation are made of). Same structure and determinism as tb_latent_mean_kernel.
+// -----------------------------------------------------------------------------------------
+__global__ void tb_latent_wsum_kernel(const int64_t* __restrict__ row_start, int cap,
+                                      const int32_t* __restrict__ count, const int32_t* __restrict__ idx,
+                                      const float* __restrict__ val, const int64_t* __restrict__ seg,
+                                      int rows_per_prompt, int S, const float* __restrict__ row_weight,
+                                      int power, float* __restrict__ out_sum) {
+  const int p = blockIdx.x;
+  const int64_t r0 = seg ? seg[p] : static_cast<int64_t>(p) * rows_per_prompt;
+  const int64_t r1 = seg ? seg[p + 1] : r0 + rows_per_prompt;
+  float* out = out_sum + static_cast<size_t>(p) * S;
+  for (int j = threadIdx.x; j < S; j += blockDim.x) out[j] = 0.0f;
+  __syncthreads();
+  for (int64_t r = r0; r < r1; ++r) {
+    const float w = row_weight ? row_weight[r] : 1.0f;
+    if (w != 0.0f) {   // uniform over the CTA
+      const int64_t start = row_start ? row_start[r] : r * cap;
+      int cnt = count[r];
+      if (row_start == nullptr) cnt = min(cnt, cap);
+      for (int i = threadIdx.x; i < cnt; i += blockDim.x) {
+        const float a = val[start + i];
+        out[idx[start + i]] += w * (power == 2 ? a * a : a);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// -----------------------------------------------------------------------------------------
 // a2 (second half): per prompt, the m largest means, sorted descending (ties: lower latent id
 // first), plus a rank table rank[latent] = position (0xFFFF if not selected). Nested budgets
 // m' <= m are prefixes of the sorted list, i.e. "rank < m'".

@@ -211,6 +211,25 @@ def latent_mean(acts: SparseActs, rows_per_prompt: int = 0, seg: Optional[torch.
     return out
 
 
+def latent_wsum(acts: SparseActs, rows_per_prompt: int = 0, seg: Optional[torch.Tensor] = None, *,
+                row_weight: Optional[torch.Tensor] = None, power: int = 1) -> torch.Tensor:
+    """f32 [P, S]: sum over a prompt's rows of w[t] * a[t, s]**power (w None = 1)."""
+    if seg is not None:
+        _need(seg, torch.int64, "seg", 1)
+        n_prompts = seg.shape[0] - 1
+    else:
+        if rows_per_prompt <= 0 or acts.n_rows % rows_per_prompt:
+            raise TabooKernelError("rows_per_prompt must divide the row count", _lib.TB_ERR_INVALID)
+        n_prompts = acts.n_rows // rows_per_prompt
+    if row_weight is not None:
+        _need(row_weight, torch.float32, "row_weight", 1)
+    out = torch.empty(n_prompts, acts.S, dtype=torch.float32, device=acts.count.device)
+    check(_lib.load().tb_sae_latent_wsum(
+        _ptr(acts.row_start), acts.cap, _ptr(acts.count), _ptr(acts.idx), _ptr(acts.val), _ptr(seg), rows_per_prompt,
+        n_prompts, acts.S, _ptr(row_weight), power, _ptr(out), _stream()), "tb_sae_latent_wsum")
+    return out
+
+
 def topm_select(mean: torch.Tensor, m: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
     """Top-m latents per prompt, sorted descending: (idx i32 [P,m], val f32 [P,m], rank u16 [P,S])."""
     _need(mean, torch.float32, "mean", 2)
