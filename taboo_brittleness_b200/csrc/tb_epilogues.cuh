@@ -19,12 +19,24 @@ __device__ __forceinline__ float rcp_approx(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-// tanh(y) = 1 - 2 / (1 + e^{2y}); two MUFU ops, absolute error ~1e-7 (tanh.approx.f32 is only
-// good to 2^-11 relative, which is 0.015 in a logit capped at 30 -- too coarse for 1e-3 in p).
-__device__ __forceinline__ float tanh_2mufu(float y) {
-  const float e = ex2_approx(y * (2.0f * kLog2e));
-  return 1.0f - 2.0f * rcp_approx(1.0f + e);
-}
+// (tanh.approx.f32 is only good to 2^-11 relative -- 0.015 in a logit capped at 30, too coarse for 1e-3 in p --
+// so the softcap below goes through ex2 + rcp: two MUFU ops, absolute error ~1e-7.)
+constexpr float kLn2 = 0.6931471805599453f;
+// Soft-capped logit in log2 units, 2 MUFU + 3 FP ops: with k1 = 2 log2(e) / cap and k2 = cap log2(e),
+//   cap * tanh(x / cap) * log2(e) = k2 - 2 k2 / (1 + 2^(x k1)).
+// Everything downstream (running max, exponentials, top-10 comparisons) works in log2 units; values
+// are converted back (x ln 2) only where they leave the kernel. cap <= 0: plain x log2(e).
+struct CapLog2 {
+  float k1, k2, m2k2;
+  bool on;
+  __device__ __forceinline__ explicit CapLog2(float cap)
+      : k1(cap > 0.0f ? 2.0f * kLog2e / cap : kLog2e), k2(cap * kLog2e), m2k2(-2.0f * cap * kLog2e), on(cap > 0.0f) {}
+  __device__ __forceinline__ float operator()(float x) const {
+    if (!on) return x * k1;
+    const float r = rcp_approx(1.0f + ex2_approx(x * k1));
+    return fmaf(r, m2k2, k2);
+  }
+};
 
 // =========================================================================================
 // K3: logit-lens readout. A = h (final-RMSNorm'ed residual, bf16), B = W_U shard.
@@ -83,15 +95,11 @@ struct LensEpi {
 
   __device__ __forceinline__ static void process(State& st, const Params& p, const GemmArgs& g,
                                                  const uint32_t (&v)[32], int /*row*/, int col0) {
+    // c: soft-capped logits in log2 units
+    const CapLog2 cap2(p.softcap);
     float c[32];
-    if (p.softcap > 0.0f) {
-      const float inv = 1.0f / p.softcap;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) c[j] = p.softcap * tanh_2mufu(__uint_as_float(v[j]) * inv);
-    } else {
-#pragma unroll
-      for (int j = 0; j < 32; ++j) c[j] = __uint_as_float(v[j]);
-    }
+    for (int j = 0; j < 32; ++j) c[j] = cap2(__uint_as_float(v[j]));
     if (col0 + 32 > g.N) {  // ragged last tile: columns past N hold zero-filled garbage
 #pragma unroll
       for (int j = 0; j < 32; ++j)
@@ -101,18 +109,17 @@ struct LensEpi {
 #pragma unroll
     for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, c[j]);
 
-    // online logsumexp, rescaled at most once per 32 columns
+    // online logsumexp (base 2), rescaled at most once per 32 columns
     if (cmax > st.m) {
-      st.s *= ex2_approx((st.m - cmax) * kLog2e);  // m = -inf -> factor 0 (s is 0 then anyway)
+      st.s *= ex2_approx(st.m - cmax);  // m = -inf -> factor 0 (s is 0 then anyway)
       st.m = cmax;
     }
     if (st.m > -CUDART_INF_F) {
-      const float ml = st.m * kLog2e;
       float acc0 = 0.0f, acc1 = 0.0f;
 #pragma unroll
       for (int j = 0; j < 32; j += 2) {
-        acc0 += ex2_approx(fmaf(c[j], kLog2e, -ml));
-        acc1 += ex2_approx(fmaf(c[j + 1], kLog2e, -ml));
+        acc0 += ex2_approx(c[j] - st.m);
+        acc1 += ex2_approx(c[j + 1] - st.m);
       }
       st.s += acc0 + acc1;
     }
@@ -137,12 +144,12 @@ struct LensEpi {
                                                   int row, int chunk) {
     if (row >= g.M) return;
     const size_t o = static_cast<size_t>(chunk) * g.M + row;
-    p.pm[o] = st.m;
+    p.pm[o] = st.m * kLn2;      // state is in log2 units; partials are in natural-log units
     p.ps[o] = st.s;
-    p.psec[o] = st.sec;
+    p.psec[o] = st.sec * kLn2;
 #pragma unroll
     for (int k = 0; k < kTopK; ++k) {
-      p.ptv[o * kTopK + k] = st.tv[k];
+      p.ptv[o * kTopK + k] = st.tv[k] * kLn2;
       p.pti[o * kTopK + k] = st.ti[k];
     }
   }
@@ -346,7 +353,7 @@ struct ColSumEpi {
     const int local = nt * c.a_tile_rows + c.rank * kBlockM + c.tid;  // row of this shard's W_U
     const int vid = p.vocab_offset + local;
     const int bit = local - c.t0 * c.a_tile_rows;
-    const float inv_cap = p.softcap > 0.0f ? 1.0f / p.softcap : 0.0f;
+    const CapLog2 cap2(p.softcap);
     const int q = c.half;                                            // prompt of the block pair
     const bool masked = (s_bm[q * (kMaxChunkIds / 32) + (bit >> 5)] >> (bit & 31)) & 1u;
     float acc0 = 0.0f, acc1 = 0.0f;
@@ -363,9 +370,7 @@ struct ColSumEpi {
         const float nls[4] = {nl.x, nl.y, nl.z, nl.w};
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          float l = __uint_as_float(v[j + u]);
-          if (p.softcap > 0.0f) l = p.softcap * tanh_2mufu(l * inv_cap);
-          e[j + u] = ex2_approx(fmaf(l, kLog2e, nls[u]));
+          e[j + u] = ex2_approx(cap2(__uint_as_float(v[j + u])) + nls[u]);
         }
       }
       if (masked) {
@@ -516,22 +521,16 @@ struct LensLLEpi {
     const int quad = c.tid >> 5, lane = c.tid & 31;
     float* tr = reinterpret_cast<float*>(c.extra + kOffTr) + (c.half * 4 + quad) * (32 * kTrStride);
     float* cs = reinterpret_cast<float*>(c.extra + kOffCs) + parity * (4 * 256);
-    const float cap = p.lens.softcap;
-    const float inv_cap = cap > 0.0f ? 1.0f / cap : 0.0f;
+    const CapLog2 cap2(p.lens.softcap);
 #pragma unroll 1
     for (int cc = c.half * 4; cc < c.half * 4 + 4; ++cc) {
       const int col0 = nt * kBlockN + cc * 32;
       uint32_t v[32];
       tmem_ld_32x32(taddr + cc * 32, v);
       tmem_ld_wait();
-      float l[32];
-      if (cap > 0.0f) {
+      float l[32];   // soft-capped logits in log2 units
 #pragma unroll
-        for (int j = 0; j < 32; ++j) l[j] = cap * tanh_2mufu(__uint_as_float(v[j]) * inv_cap);
-      } else {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) l[j] = __uint_as_float(v[j]);
-      }
+      for (int j = 0; j < 32; ++j) l[j] = cap2(__uint_as_float(v[j]));
       if (col0 + 32 > g.N) {
 #pragma unroll
         for (int j = 0; j < 32; ++j)
@@ -556,8 +555,8 @@ struct LensLLEpi {
       float a0 = 0.0f, a1 = 0.0f;
 #pragma unroll
       for (int j = 0; j < 32; j += 2) {
-        q[j] = ex2_approx(fmaf(l[j], kLog2e, st.nl));
-        q[j + 1] = ex2_approx(fmaf(l[j + 1], kLog2e, st.nl));
+        q[j] = ex2_approx(l[j] + st.nl);
+        q[j + 1] = ex2_approx(l[j + 1] + st.nl);
         a0 += q[j];
         a1 += q[j + 1];
       }
@@ -605,10 +604,10 @@ struct LensLLEpi {
     const size_t o = static_cast<size_t>(c.chunk * 2 + c.half) * g.M + row;
     p.lens.pm[o] = p.ref[row];   // the partial's reference point is r, not the running maximum
     p.lens.ps[o] = st.s;
-    p.lens.psec[o] = st.sec;
+    p.lens.psec[o] = st.sec * kLn2;   // log2 units -> natural log
 #pragma unroll
     for (int k = 0; k < kTopK; ++k) {
-      p.lens.ptv[o * kTopK + k] = st.tv[k];
+      p.lens.ptv[o * kTopK + k] = st.tv[k] * kLn2;
       p.lens.pti[o * kTopK + k] = st.ti[k];
     }
   }

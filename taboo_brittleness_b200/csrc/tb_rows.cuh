@@ -708,38 +708,59 @@ __global__ void __launch_bounds__(kCandThreads) tb_ll_candidates_exact_kernel(co
     float mine[kCandGroup];   // lane j < 8 accumulates candidate j over this warp's rows
 #pragma unroll
     for (int j = 0; j < kCandGroup; ++j) mine[j] = 0.0f;
-    for (int t = warp; t < 128; t += kWarps) {
-      const float nl = s_nl[t];
-      if (nl == -CUDART_INF_F) continue;   // empty slot (uniform over the warp)
-      const int4* hr = reinterpret_cast<const int4*>(a.h + (row0 + t) * a.d);
-      float dot[kCandGroup];
+    // two rows per pass: every W_U vector read from shared memory (and unpacked) serves both
+    for (int t0 = warp; t0 < 128; t0 += 2 * kWarps) {
+      const int tr[2] = {t0, t0 + kWarps};
+      float nl[2];
+      const int4* hr[2];
 #pragma unroll
-      for (int j = 0; j < kCandGroup; ++j) dot[j] = 0.0f;
+      for (int q = 0; q < 2; ++q) {
+        nl[q] = s_nl[tr[q]];
+        hr[q] = reinterpret_cast<const int4*>(a.h + (row0 + tr[q]) * a.d);
+      }
+      if (nl[0] == -CUDART_INF_F && nl[1] == -CUDART_INF_F) continue;   // two empty slots (uniform over the warp)
+      float dot[2][kCandGroup];
+#pragma unroll
+      for (int q = 0; q < 2; ++q)
+#pragma unroll
+        for (int j = 0; j < kCandGroup; ++j) dot[q][j] = 0.0f;
       for (int vec = lane; vec < nvec; vec += 32) {
-        float hv[8];
-        unpack8(__ldg(hr + vec), hv);
+        float hv[2][8];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          int4 raw = make_int4(0, 0, 0, 0);
+          if (nl[q] != -CUDART_INF_F) raw = __ldg(hr[q] + vec);     // empty slots may lie past the last row
+          unpack8(raw, hv[q]);
+        }
 #pragma unroll
         for (int j = 0; j < kCandGroup; ++j) {
           float wv[8];
           unpack8(reinterpret_cast<const int4*>(s_w)[j * nvec + vec], wv);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) dot[j] = fmaf(hv[e], wv[e], dot[j]);
+          for (int e = 0; e < 8; ++e) {
+            dot[0][j] = fmaf(hv[0][e], wv[e], dot[0][j]);
+            dot[1][j] = fmaf(hv[1][e], wv[e], dot[1][j]);
+          }
         }
       }
 #pragma unroll
-      for (int j = 0; j < kCandGroup; ++j) {
+      for (int q = 0; q < 2; ++q) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) dot[j] += __shfl_xor_sync(0xffffffffu, dot[j], o);
-      }
-      const int cur = s_cur[t], prev = s_prev[t];
+        for (int j = 0; j < kCandGroup; ++j) {
 #pragma unroll
-      for (int j = 0; j < kCandGroup; ++j) {
-        if (j < nc) {
-          float l = dot[j];
-          if (a.softcap > 0.0f) l = a.softcap * tanhf(l * inv_cap);
-          const int id = a.cand_id[static_cast<size_t>(p) * a.cap + c0 + j];
-          const float q = (id == cur || id == prev) ? 0.0f : expf(l + nl);
-          mine[j] += q;   // every lane holds the same value; fixed order over t
+          for (int o = 16; o > 0; o >>= 1) dot[q][j] += __shfl_xor_sync(0xffffffffu, dot[q][j], o);
+        }
+        if (nl[q] == -CUDART_INF_F) continue;
+        const int cur = s_cur[tr[q]], prev = s_prev[tr[q]];
+#pragma unroll
+        for (int j = 0; j < kCandGroup; ++j) {
+          if (j < nc) {
+            float l = dot[q][j];
+            if (a.softcap > 0.0f) l = a.softcap * tanhf(l * inv_cap);
+            const int id = a.cand_id[static_cast<size_t>(p) * a.cap + c0 + j];
+            const float qv = (id == cur || id == prev) ? 0.0f : expf(l + nl[q]);
+            mine[j] += qv;   // every lane holds the same value; fixed order over the rows
+          }
         }
       }
     }
