@@ -107,6 +107,16 @@ int tb_lowrank_remove(const void* x_bf16, const void* ut_bf16, int r, int64_t n_
                       const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
                       void* stream);
 
+/* K2 for ranks above 8, in two steps with caller scratch c (f32 [n_rows, r]): tb_lowrank_coeffs
+ * computes C = x U on the tensor cores (the tcgen05 main loop, U^T as its one swept tile),
+ * tb_lowrank_apply subtracts C U^T, rounds to bf16 and applies the fused final RMSNorm
+ * (d <= 4096). Same result contract as tb_lowrank_remove (Plan:148); no code in the reference. */
+int tb_lowrank_coeffs(const void* x_bf16, const void* ut_bf16, int r, int64_t n_rows, int d,
+                      float* out_c, void* stream);
+int tb_lowrank_apply(const void* x_bf16, const void* ut_bf16, const float* c, int r, int64_t n_rows,
+                     int d, const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
+                     void* stream);
+
 /* ---- a6: final RMSNorm -------------------------------------------------------------------
  * Replaces model.model.norm(...), src/models.py:135 (Gemma2RMSNorm.forward on a bf16
  * residual): h = bf16((x * rsqrt(mean(x^2) + eps)) * (1 + w)), fp32 intermediates.

@@ -47,6 +47,8 @@ SIGNATURES = {
     "tb_sae_ablate_decode": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int,
                                      c_int64, c_int, c_int, _P, c_float, _P, _P, _P]),
     "tb_lowrank_remove": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
+    "tb_lowrank_coeffs": (c_int, [_P, _P, c_int, c_int64, c_int, _P, _P]),
+    "tb_lowrank_apply": (c_int, [_P, _P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
     "tb_rmsnorm": (c_int, [_P, _P, c_float, c_int64, c_int, _P, _P]),
     "tb_lens_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,
                                  _P, _P, _P, _P, _P, _P]),

@@ -538,6 +538,52 @@ int tb_lowrank_remove(const void* x, const void* ut, int r, int64_t n_rows, int 
   return TB_OK;
 }
 
+int tb_lowrank_coeffs(const void* x, const void* ut, int r, int64_t n_rows, int d, float* out_c, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (r < 1 || r > tb::kProjMaxRank) return fail(TB_ERR_INVALID, "rank %d outside [1, %d]", r, tb::kProjMaxRank);
+  rc = check_gemm_operands(x, ut, n_rows, r, d);
+  if (rc != TB_OK) return rc;
+  if (!out_c) return fail(TB_ERR_INVALID, "null output");
+  // C = x U on the tensor cores: U^T [r, d] is the single swept tile (rows past r are zero-filled by TMA)
+  tb::GemmArgs g = make_args(n_rows, r, d, 1, 2);
+  tb::DenseEpi::Params ep{out_c};
+  return launch_gemm<tb::DenseEpi, 2>(x, ut, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_lowrank_apply(const void* x, const void* ut, const float* c, int r, int64_t n_rows, int d,
+                     const float* w_norm, float eps, void* out_x, void* out_h, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!x || !ut || !c) return fail(TB_ERR_INVALID, "null pointer");
+  if (r < 1 || r > tb::kProjMaxRank) return fail(TB_ERR_INVALID, "rank %d outside [1, %d]", r, tb::kProjMaxRank);
+  if (d <= 0 || d % 8 != 0 || d > 4096) return fail(TB_ERR_INVALID, "d=%d must be a multiple of 8, at most 4096", d);
+  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  if (n_rows == 0) return TB_OK;
+  tb::ProjApplyArgs a;
+  a.x = static_cast<const __nv_bfloat16*>(x);
+  a.ut = static_cast<const __nv_bfloat16*>(ut);
+  a.c = c;
+  a.r = r;
+  a.w_norm = w_norm;
+  a.eps = eps;
+  a.out_x = static_cast<__nv_bfloat16*>(out_x);
+  a.out_h = static_cast<__nv_bfloat16*>(out_h);
+  a.n_rows = static_cast<int>(n_rows);
+  a.d = d;
+  int threads = ((d / 8) + 31) / 32 * 32;
+  if (threads < 64) threads = 64;
+  const int64_t tiles = (n_rows + tb::kProjApplyRows - 1) / tb::kProjApplyRows;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 2;
+  const unsigned grid = static_cast<unsigned>(tiles < max_grid ? tiles : max_grid);
+  tb::tb_lowrank_apply_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
 int tb_rmsnorm(const void* x, const float* w_norm, float eps, int64_t n_rows, int d, void* out_h,
                void* stream) {
   DevInfo di;

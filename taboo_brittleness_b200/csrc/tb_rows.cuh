@@ -1101,4 +1101,106 @@ __global__ void __launch_bounds__(kProjSmallThreads, 2) tb_lowrank_small_kernel(
   }
 }
 
+
+// -----------------------------------------------------------------------------------------
+// K2 for ranks 9..64, second half: x' = x - C U^T with the coefficients C = x U (fp32 [rows, r])
+// already computed on the tensor cores (tb_lowrank_coeffs: the tcgen05 main loop with U^T as
+// the one swept tile). Eight rows per tile in registers, one 16-byte column slice per thread:
+// every U^T vector fetched from L2 feeds 64 FMAs. Rounding and the fused RMSNorm as in the
+// other row kernels.
+// -----------------------------------------------------------------------------------------
+constexpr int kProjApplyRows = 8;
+
+struct ProjApplyArgs {
+  const __nv_bfloat16* x;    // [n_rows, d]
+  const __nv_bfloat16* ut;   // [r, d]
+  const float* c;            // [n_rows, r]
+  int r;
+  const float* w_norm;       // [d] or nullptr
+  float eps;
+  __nv_bfloat16* out_x;      // nullable
+  __nv_bfloat16* out_h;      // nullable
+  int n_rows, d;
+};
+
+__global__ void __launch_bounds__(512, 1) tb_lowrank_apply_kernel(const ProjApplyArgs a) {
+  __shared__ float s_c[kProjApplyRows][kProjMaxRank];
+  __shared__ float s_ss[16][kProjApplyRows];
+  const int nvec = a.d >> 3;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nwarps = blockDim.x >> 5;
+  const bool own = tid < nvec;                     // blockDim.x >= nvec (host guarantees d <= 4096)
+  const int n_tiles = (a.n_rows + kProjApplyRows - 1) / kProjApplyRows;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int row0 = tile * kProjApplyRows;
+    __syncthreads();                               // s_c / s_ss of the previous tile are no longer read
+    for (int i = tid; i < kProjApplyRows * a.r; i += blockDim.x) {
+      const int rr = i / a.r, j = i - rr * a.r;
+      s_c[rr][j] = (row0 + rr < a.n_rows) ? -a.c[static_cast<size_t>(row0 + rr) * a.r + j] : 0.0f;
+    }
+    float acc[kProjApplyRows][8];
+#pragma unroll
+    for (int rr = 0; rr < kProjApplyRows; ++rr) {
+      int4 raw = make_int4(0, 0, 0, 0);
+      if (own && row0 + rr < a.n_rows) raw = __ldg(reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row0 + rr) * a.d) + tid);
+      unpack8(raw, acc[rr]);
+    }
+    __syncthreads();
+    if (own) {
+#pragma unroll 2
+      for (int j = 0; j < a.r; ++j) {
+        float u[8];
+        unpack8(__ldg(reinterpret_cast<const int4*>(a.ut + static_cast<size_t>(j) * a.d) + tid), u);
+#pragma unroll
+        for (int rr = 0; rr < kProjApplyRows; ++rr) {
+          const float cj = s_c[rr][j];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[rr][e] = fmaf(cj, u[e], acc[rr][e]);
+        }
+      }
+    }
+    float ss[kProjApplyRows];
+#pragma unroll
+    for (int rr = 0; rr < kProjApplyRows; ++rr) {
+      ss[rr] = 0.0f;
+      if (own) {
+        const Bf16x8 pk = pack8(acc[rr]);
+        if (row0 + rr < a.n_rows && a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row0 + rr) * a.d)[tid] = pk;
+        unpack8(pk, acc[rr]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss[rr] = fmaf(acc[rr][e], acc[rr][e], ss[rr]);
+      }
+    }
+    if (a.out_h) {
+#pragma unroll
+      for (int rr = 0; rr < kProjApplyRows; ++rr) {
+        float v = ss[rr];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_ss[warp][rr] = v;
+      }
+      __syncthreads();
+      float w8[8];
+      if (own) {
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * tid);
+        const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * tid + 1);
+        w8[0] = 1.0f + w0.x; w8[1] = 1.0f + w0.y; w8[2] = 1.0f + w0.z; w8[3] = 1.0f + w0.w;
+        w8[4] = 1.0f + w1.x; w8[5] = 1.0f + w1.y; w8[6] = 1.0f + w1.z; w8[7] = 1.0f + w1.w;
+      }
+#pragma unroll
+      for (int rr = 0; rr < kProjApplyRows; ++rr) {
+        float tot = 0.0f;
+        for (int w = 0; w < nwarps; ++w) tot += s_ss[w][rr];
+        const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, static_cast<float>(a.d)), a.eps)));
+        if (own && row0 + rr < a.n_rows) {
+          float h[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(acc[rr][e], rstd), w8[e]);
+          reinterpret_cast<Bf16x8*>(a.out_h + static_cast<size_t>(row0 + rr) * a.d)[tid] = pack8(h);
+        }
+      }
+    }
+  }
+}
+
 }  // namespace tb

@@ -290,6 +290,9 @@ def sae_ablate_decode(x: Optional[torch.Tensor], acts: SparseActs, sae: SaeWeigh
     return out_x, out_h
 
 
+LOWRANK_SMALL = 8     # ranks up to this use the kernel that keeps U^T in shared memory
+
+
 def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.Tensor] = None,
                    eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False
                    ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
@@ -305,8 +308,16 @@ def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.T
     out_h = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_h else None
     if n == 0:
         return out_x, out_h
-    check(_lib.load().tb_lowrank_remove(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(out_x),
-                                        _ptr(out_h), _stream()), "tb_lowrank_remove")
+    lib = _lib.load()
+    if r > LOWRANK_SMALL and d <= 4096:
+        # coefficients on the tensor cores, then one pass that subtracts, rounds and normalises
+        c = torch.empty(n, r, dtype=torch.float32, device=x.device)
+        check(lib.tb_lowrank_coeffs(_ptr(x), _ptr(ut), r, n, d, _ptr(c), _stream()), "tb_lowrank_coeffs")
+        check(lib.tb_lowrank_apply(_ptr(x), _ptr(ut), _ptr(c), r, n, d, _ptr(w_norm), eps, _ptr(out_x), _ptr(out_h),
+                                   _stream()), "tb_lowrank_apply")
+        return out_x, out_h
+    check(lib.tb_lowrank_remove(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(out_x),
+                                _ptr(out_h), _stream()), "tb_lowrank_remove")
     return out_x, out_h
 
 
