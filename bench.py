@@ -313,14 +313,17 @@ def run_native(args, rank, local_rank, world):
         sampler.start()
     eng.stats = interventions.SweepStats()
     eng.time_lens = True
+    from taboo_brittleness_b200 import _lib as tb_lib
+    calls0 = tb_lib.KERNEL_CALLS
     ms_step = timed(False, args.steps)
+    kernel_calls = tb_lib.KERNEL_CALLS - calls0
     eng.time_lens = False
     ll_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.ll_events)
     ll_flops = sum(f for _, _, f in eng.stats.ll_events)
     lens_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.lens_events)
     lens_flops = sum(f for _, _, f in eng.stats.lens_events)
     n_lens = len(eng.stats.lens_events)
-    launches = eng.stats.launches
+    launches = kernel_calls        # C-ABI compute calls inside the timed region (>= 1 kernel each)
     clocks = sampler.finish() if sampler else None
 
     # ---- end to end: host buffers in, readouts out, every step

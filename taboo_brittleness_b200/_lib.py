@@ -92,6 +92,11 @@ def last_error() -> str:
     return load().tb_last_error().decode("utf-8", "replace")
 
 
+KERNEL_CALLS = 0     # successful compute entry-point calls so far (each launches at least one kernel)
+
+
 def check(rc: int, what: str) -> None:
+    global KERNEL_CALLS
+    KERNEL_CALLS += 1
     if rc != TB_OK:
         raise TabooKernelError(f"{what} failed ({rc}): {last_error()}", rc)

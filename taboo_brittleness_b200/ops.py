@@ -421,6 +421,47 @@ def pick_chunks(n_rows: int, V: int, n_sms: int = 148, cta_pair=False, *, sweep_
     return best or C
 
 
+def plan_row_splits(n_rows: int, V: int, cta_pair=2, *, sweep_a: bool = False, n_sms: int = 148):
+    """[(row_start, row_stop, n_chunks), ...] for one lens sweep. The kernels hand out (row group, chunk)
+    units round-robin to the resident clusters; when the unit count is just above a whole number of
+    waves (e.g. 2048 units on 33 clusters = 62.06 waves) the last wave keeps two clusters busy for a
+    full chunk while 31 idle. The row groups of that ragged wave are then swept in a second launch
+    with many short chunks, one unit per cluster; partials of different chunkings merge as usual."""
+    group, R, C = CLUSTER_MODES[_mode(cta_pair)]
+    size = group * R * C
+    clusters = max(_B200_CLUSTERS.get(size, n_sms // size) * n_sms // 148, 1)
+    c = pick_chunks(n_rows, V, n_sms, cta_pair, sweep_a=sweep_a)
+    rows_per_group = BLOCK_N * R if sweep_a else BLOCK_M * group * R
+    groups = -(-n_rows // rows_per_group)
+    per_group = c // C
+    units = groups * per_group
+    full, rem = divmod(units, clusters)
+    if full < 4 or rem == 0 or rem > clusters // 2:
+        return [(0, n_rows, c)]
+    tail_groups = -(-rem // per_group)
+    main_rows = (groups - tail_groups) * rows_per_group
+    if main_rows <= 0 or main_rows >= n_rows:
+        return [(0, n_rows, c)]
+    # tail: as many chunks as give about one unit per cluster
+    n_tiles = -(-V // (BLOCK_M * group)) if sweep_a else -(-V // BLOCK_N)
+    want = max(C, (clusters // tail_groups) * C)
+    c_tail = c
+    for cand in range(min(want, n_tiles), c, -1):
+        tpc = -(-n_tiles // cand)
+        if cand % C == 0 and -(-n_tiles // tpc) == cand and tpc >= 8:
+            c_tail = cand
+            break
+    if c_tail == c:
+        return [(0, n_rows, c)]
+    return [(0, main_rows, c), (main_rows, n_rows, c_tail)]
+
+
+def _cat_partials(parts) -> "LensPartials":
+    return LensPartials(pm=torch.cat([q.pm for q in parts], 1), ps=torch.cat([q.ps for q in parts], 1),
+                        psec=torch.cat([q.psec for q in parts], 1), ptv=torch.cat([q.ptv for q in parts], 1),
+                        pti=torch.cat([q.pti for q in parts], 1))
+
+
 def _alloc_partials(n_chunks: int, n: int, dev) -> "LensPartials":
     parts = n_chunks * _lib.load().tb_lens_parts_per_chunk()     # one partial per (chunk, column half, row)
     return LensPartials(
@@ -441,7 +482,12 @@ def lens_partials(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0,
     if secret_id is not None:
         _need(secret_id, torch.int32, "secret_id", 1)
     if n_chunks is None:
-        n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(h.device).multi_processor_count, cta_pair)
+        splits = plan_row_splits(n, V, cta_pair, n_sms=torch.cuda.get_device_properties(h.device).multi_processor_count)
+        if len(splits) > 1:     # ragged last wave: sweep its rows separately (see plan_row_splits)
+            return _cat_partials([lens_merge(lens_partials(
+                h[r0:r1], w_u, softcap=softcap, secret_id=None if secret_id is None else secret_id[r0:r1],
+                vocab_offset=vocab_offset, n_chunks=c, cta_pair=cta_pair), finalize=False) for r0, r1, c in splits])
+        n_chunks = splits[0][2]
     p = _alloc_partials(n_chunks, n, h.device)
     if n == 0:
         return p
@@ -547,7 +593,16 @@ def ll_topk(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, cur_id: Optio
     P = n // LL_SLOTS
     dev = h.device
     if n_chunks is None:
-        n_chunks = pick_chunks_ll(n, V, torch.cuda.get_device_properties(dev).multi_processor_count, cta_pair)
+        splits = plan_row_splits(n, V, cta_pair, sweep_a=True,
+                                 n_sms=torch.cuda.get_device_properties(dev).multi_processor_count)
+        if len(splits) > 1:     # ragged last wave: sweep its row slots separately (see plan_row_splits)
+            lists = [ll_topk(h[r0:r1], w_u, lse[r0:r1], None if cur_id is None else cur_id[r0:r1],
+                             None if prev_id is None else prev_id[r0:r1], k=k, softcap=softcap,
+                             vocab_offset=vocab_offset, n_chunks=c, cta_pair=cta_pair, finalize=False)
+                     for r0, r1, c in splits]
+            pv, pi = torch.cat([q[0] for q in lists], 1), torch.cat([q[1] for q in lists], 1)
+            return (pv, pi) if not finalize else ll_topk_merge(pv, pi, k=k)
+        n_chunks = splits[0][2]
     parts = n_chunks * CLUSTER_MODES[_mode(cta_pair)][0]
     pv = torch.empty(parts, P, TB_TOPK, dtype=torch.float32, device=dev)
     pi = torch.empty(parts, P, TB_TOPK, dtype=torch.int32, device=dev)
@@ -595,11 +650,22 @@ def lens_ll_partials(h: torch.Tensor, w_u: torch.Tensor, ref_lse: torch.Tensor, 
     for name, t in (("cur_id", cur_id), ("prev_id", prev_id), ("secret_id", secret_id)):
         if t is not None:
             _need(t, torch.int32, name, 1)
-    if n_chunks is None:
-        n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(h.device).multi_processor_count, cta_pair)
     dev = h.device
-    p = _alloc_partials(n_chunks, n, dev)
     P = n // LL_SLOTS
+    if n_chunks is None:
+        splits = plan_row_splits(n, V, cta_pair, n_sms=torch.cuda.get_device_properties(dev).multi_processor_count)
+        if len(splits) > 1:     # ragged last wave: sweep its rows separately (see plan_row_splits)
+            outs = []
+            for r0, r1, c in splits:
+                sl = lambda t: None if t is None else t[r0:r1]      # noqa: E731
+                q, cc, ci = lens_ll_partials(h[r0:r1], w_u, ref_lse[r0:r1], tau[r0 // LL_SLOTS:r1 // LL_SLOTS], sl(cur_id),
+                                             sl(prev_id), softcap=softcap, secret_id=sl(secret_id),
+                                             vocab_offset=vocab_offset, n_chunks=c, cta_pair=cta_pair, cand_cap=cand_cap)
+                outs.append((lens_merge(q, finalize=False), cc, ci))
+            return (_cat_partials([o[0] for o in outs]), torch.cat([o[1] for o in outs]),
+                    torch.cat([o[2] for o in outs]))
+        n_chunks = splits[0][2]
+    p = _alloc_partials(n_chunks, n, dev)
     cand_count = torch.zeros(P, dtype=torch.int32, device=dev)      # the kernel appends with atomics
     cand_id = torch.empty(P, cand_cap, dtype=torch.int32, device=dev)
     if n:

@@ -135,3 +135,30 @@ def test_random_control_sweep_with_ll_topk_is_exact(cuda_lib):
             lists = _oracle_lists(probs, cur, prev, list(range(0, P * T + 1, T)), 10)
             _compare(res[(b, seed)].ll_sum, res[(b, seed)].ll_id, lists, 10)
             assert (res[(b, seed)].secret_prob.cpu() - oracle.secret_prob(probs, sid)).abs().max().item() <= 1e-3
+
+
+def test_row_splits_with_different_chunkings_give_the_same_readouts(cuda_lib, monkeypatch):
+    """ops.plan_row_splits may sweep the rows of a ragged last wave in a second launch with another
+    chunk count: K3, K3F + K6 and K5 must return what one launch returns (forced split here)."""
+    from taboo_brittleness_b200 import ops
+    P, d, V = 5, 512, 8192
+    h, w_u, sid, cur, prev, plain, ref_lists = _setup(P, d, V, 7, 30.0)
+    tau = (0.5 * torch.tensor([float(r[1][9]) for r in ref_lists])).cuda().contiguous()
+    one = ops.lens_merge(ops.lens_partials(h, w_u, softcap=30.0, secret_id=sid, n_chunks=2))
+    p1, c1, i1 = ops.lens_ll_partials(h, w_u, plain.lse, tau, cur, prev, softcap=30.0, secret_id=sid, n_chunks=2)
+    v1, id1 = ops.ll_topk(h, w_u, plain.lse, cur, prev, softcap=30.0, n_chunks=2)
+    monkeypatch.setattr(ops, "plan_row_splits", lambda n, V_, mode=2, **kw: [(0, 256, 2), (256, n, 4)])
+    two = ops.lens_merge(ops.lens_partials(h, w_u, softcap=30.0, secret_id=sid))
+    p2, c2, i2 = ops.lens_ll_partials(h, w_u, plain.lse, tau, cur, prev, softcap=30.0, secret_id=sid)
+    v2, id2 = ops.ll_topk(h, w_u, plain.lse, cur, prev, softcap=30.0)
+    torch.cuda.synchronize()
+    assert p2.n_parts == 1 and p2.n_rows == P * 128
+    assert torch.equal(two.top_id, one.top_id) and torch.allclose(two.lse, one.lse, atol=1e-5)
+    assert torch.allclose(two.secret_prob, one.secret_prob, atol=1e-6)
+    f1, f2 = ops.lens_merge(p1), ops.lens_merge(p2)
+    assert torch.equal(f1.top_id, f2.top_id) and torch.allclose(f1.lse, f2.lse, atol=1e-5)
+    assert torch.equal(c1, c2)
+    for q in range(P):      # same candidate sets (order within a list depends on the launch)
+        n = int(c1[q])
+        assert set(i1[q, :n].tolist()) == set(i2[q, :n].tolist())
+    assert torch.equal(id1, id2) and torch.allclose(v1, v2, rtol=1e-5, atol=1e-7)
