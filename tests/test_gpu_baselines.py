@@ -103,3 +103,49 @@ def test_real_residuals_through_encode_and_cache_roundtrip(cuda_lib, tmp_path):
     vals, idx = oracle.top_latents_of_mean(acts, 11)
     assert set(latents) == set(idx[:10].tolist()) or abs(float(vals[9] - vals[10])) <= 1e-4 * float(vals[9])
     assert guesses == baselines.latents_to_word_guesses(latents)
+
+
+def test_real_residuals_through_the_whole_intervention_path(cuda_lib):
+    """the 8 real layer-31 residual fixtures (ragged lengths 27-38, <bos> rows of norm ~7600,
+    outlier dimensions) as a distribution sanity case for the whole path: encode -> targeted top-8
+    ablation per prompt (response windows as segments) -> decode -> lens -> LL-Top-5, against the oracle.
+    Weights are random-init (none are available offline); the residuals are the reference's own."""
+    from _common import BF16, cuda_bf16, sae_to_cuda, topk_sets_match
+    from taboo_brittleness_b200 import interventions, ops
+    z = np.load(os.path.join(G, "real_residuals_l31_fp16.npz"))
+    keys = sorted(z.files)
+    rows = [torch.from_numpy(z[k].astype(np.float32)) for k in keys]
+    x = synthetic.bf16_exact(torch.cat(rows))
+    lens_t = [r.shape[0] for r in rows]
+    seg = torch.tensor([0] + list(np.cumsum(lens_t)), dtype=torch.int64)
+    d, S, V, budget = 3584, 16384, 32768, 8
+    sae = synthetic.make_sae(d, S, seed=42)
+    lens = synthetic.make_lens(d, V, seed=42)
+    sid = torch.cat([torch.full((t,), 1000 + 17 * i, dtype=torch.int32) for i, t in enumerate(lens_t)])
+    eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                           softcap=30.0)
+    xs = cuda_bf16(x)
+    acts = eng.encode(xs)
+    idx, _, rank = eng.targeted_rank(acts, seg=seg.cuda(), m=budget)
+    row_table = torch.repeat_interleave(torch.arange(len(keys), dtype=torch.int32), torch.tensor(lens_t)).cuda()
+    g = torch.Generator().manual_seed(9)
+    cur = torch.randint(0, V, (x.shape[0],), generator=g, dtype=torch.int32)
+    ll = interventions.LLSpec(cur.cuda(), None, seg=seg.cuda(), k=5)
+    out = eng.ablate_and_read(xs, acts, rank, budget, row_table=row_table, secret_id=sid.cuda(), ll=ll)
+    torch.cuda.synchronize()
+    # oracle, prompt by prompt, on the kernel's own active sets (near-threshold flips are pinned elsewhere)
+    dense = acts.to_dense().cpu()
+    for i in range(len(keys)):
+        sl = slice(int(seg[i]), int(seg[i + 1]))
+        ref_idx = oracle.top_latents_of_mean(dense[sl], budget)[1]
+        assert set(idx[i].tolist()) == set(ref_idx.tolist())
+        x1 = oracle.ablate_decode(x[sl], dense[sl], ref_idx, sae.W_dec, sae.b_dec, "error", residual_dtype=BF16)
+        probs = oracle.lens_probs(x1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
+        assert (out.secret_prob[sl].cpu() - oracle.secret_prob(probs, sid[sl])).abs().max().item() <= 1e-3
+        n_exact, n_tie, bad = topk_sets_match(out.top_id[sl].cpu(), probs, 10)
+        assert not bad
+        want = oracle.ll_topk(probs, cur[sl].tolist(), 5)
+        got = out.ll_id[i].tolist()
+        acc = oracle.aggregate_response_probs(probs, cur[sl].tolist())
+        kth = float(torch.topk(acc, 5).values[-1])
+        assert all(abs(float(acc[j]) - kth) <= 2e-3 * kth for j in set(got) ^ set(want))
