@@ -504,6 +504,19 @@ int tb_lowrank_remove(const void* x, const void* ut, int r, int64_t n_rows, int 
   a.n_rows = static_cast<int>(n_rows);
   a.d = d;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (r >= 1 && r <= tb::kProjTinyRank && d <= 8 * 4 * tb::kRowGroupThreads) {
+    // ranks 1-2: the norm kernel's row-group layout with the projection spliced in
+    const int nvt = (d / 8 + tb::kRowGroupThreads - 1) / tb::kRowGroupThreads;
+    const size_t sm = static_cast<size_t>(r) * d * 2;
+    const int64_t blocks = (n_rows + tb::kRowGroups - 1) / tb::kRowGroups;
+    const int64_t mg = static_cast<int64_t>(di.sms) * 8;
+    const unsigned gr = static_cast<unsigned>(blocks < mg ? blocks : mg);
+    if (nvt == 1) tb::tb_lowrank_tiny_kernel<1><<<gr, tb::kAblThreads, sm, s>>>(a);
+    else if (nvt == 2) tb::tb_lowrank_tiny_kernel<2><<<gr, tb::kAblThreads, sm, s>>>(a);
+    else tb::tb_lowrank_tiny_kernel<4><<<gr, tb::kAblThreads, sm, s>>>(a);
+    TB_CUDA(cudaGetLastError());
+    return TB_OK;
+  }
   if (r >= 1 && r <= tb::kProjSmallRank && d <= 8 * 2 * tb::kProjSmallThreads) {
     // small ranks: U^T resident in shared memory, four rows per tile in registers
     const int nvs = (d / 8 + tb::kProjSmallThreads - 1) / tb::kProjSmallThreads;
@@ -590,18 +603,20 @@ int tb_rmsnorm(const void* x, const float* w_norm, float eps, int64_t n_rows, in
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
   if (!x || !w_norm || !out_h) return fail(TB_ERR_INVALID, "null pointer");
+  if (d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  const int nv = (d / 8 + tb::kRowGroupThreads - 1) / tb::kRowGroupThreads;
+  if (nv > 8) return fail(TB_ERR_INVALID, "d=%d too large for the row kernels (max 8192)", d);
   if (n_rows == 0) return TB_OK;
-  int nv, threads;
-  rc = row_launch_shape(d, &nv, &threads);
-  if (rc != TB_OK) return rc;
-  const int64_t max_grid = static_cast<int64_t>(di.sms) * 16;
-  const unsigned grid = static_cast<unsigned>(n_rows < max_grid ? n_rows : max_grid);
+  const int64_t blocks = (n_rows + tb::kRowGroups - 1) / tb::kRowGroups;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 8;
+  const unsigned grid = static_cast<unsigned>(blocks < max_grid ? blocks : max_grid);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const __nv_bfloat16* xp = static_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* hp = static_cast<__nv_bfloat16*>(out_h);
-  if (nv == 1) tb::tb_rmsnorm_kernel<1><<<grid, threads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
-  else if (nv == 2) tb::tb_rmsnorm_kernel<2><<<grid, threads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
-  else tb::tb_rmsnorm_kernel<4><<<grid, threads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
+  if (nv == 1) tb::tb_rmsnorm_kernel<1><<<grid, tb::kAblThreads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
+  else if (nv == 2) tb::tb_rmsnorm_kernel<2><<<grid, tb::kAblThreads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
+  else if (nv <= 4) tb::tb_rmsnorm_kernel<4><<<grid, tb::kAblThreads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
+  else tb::tb_rmsnorm_kernel<8><<<grid, tb::kAblThreads, 0, s>>>(xp, w_norm, (int)n_rows, d, eps, hp);
   TB_CUDA(cudaGetLastError());
   return TB_OK;
 }

@@ -90,23 +90,6 @@ __device__ __forceinline__ void rmsnorm_store(const float (&xb)[NV][8], const fl
   }
 }
 
-template <int NV>
-__global__ void tb_rmsnorm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w,
-                                  int n_rows, int d, float eps, __nv_bfloat16* __restrict__ out_h) {
-  __shared__ float red[kRowMaxWarps];
-  const int nvec = d >> 3;
-  for (int row = blockIdx.x; row < n_rows; row += gridDim.x) {
-    const Bf16x8* xr = reinterpret_cast<const Bf16x8*>(x + static_cast<size_t>(row) * d);
-    float xb[NV][8];
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int vec = threadIdx.x + i * blockDim.x;
-      if (vec < nvec) unpack8(xr[vec], xb[i]);
-    }
-    rmsnorm_store<NV>(xb, w, d, eps, out_h + static_cast<size_t>(row) * d, red);
-  }
-}
-
 // -----------------------------------------------------------------------------------------
 // a4: ablate + decode. For every row, walk that row's active-latent list; a latent is
 // ablated when its rank in the row's ablation table is below the budget.
@@ -159,6 +142,48 @@ __device__ __forceinline__ float group_sum(float v, float* red4, int group, int 
   if (lane == 0) red4[gwarp] = v;
   group_bar_sync(group);
   return (red4[0] + red4[1]) + (red4[2] + red4[3]);
+}
+
+// a6 alone: four rows per CTA, 128 threads per row (the layout of tb_ablate_decode_kernel), so that
+// 8-16 rows per SM are in flight.
+template <int NV>
+__global__ void __launch_bounds__(kAblThreads) tb_rmsnorm_kernel(const __nv_bfloat16* __restrict__ x,
+                                                                 const float* __restrict__ w, int n_rows, int d,
+                                                                 float eps, __nv_bfloat16* __restrict__ out_h) {
+  __shared__ float s_red[kRowGroups][4];
+  const int group = threadIdx.x / kRowGroupThreads;
+  const int gt = threadIdx.x - group * kRowGroupThreads;
+  const int gwarp = gt >> 5, lane = gt & 31;
+  const int nvec = d >> 3;
+  for (int row = blockIdx.x * kRowGroups + group; row < n_rows; row += gridDim.x * kRowGroups) {
+    const int4* xr = reinterpret_cast<const int4*>(x + static_cast<size_t>(row) * d);
+    float xb[NV][8];
+    float ss = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      if (vec < nvec) {
+        unpack8(__ldg(xr + vec), xb[i]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss = fmaf(xb[i][e], xb[i][e], ss);
+      }
+    }
+    ss = group_sum(ss, s_red[group], group, gwarp, lane);
+    const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, static_cast<float>(d)), eps)));
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      if (vec < nvec) {
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(w) + 2 * vec);
+        const float4 w1 = __ldg(reinterpret_cast<const float4*>(w) + 2 * vec + 1);
+        const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+        float h[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(xb[i][e], rstd), __fadd_rn(1.0f, ww[e]));
+        reinterpret_cast<Bf16x8*>(out_h + static_cast<size_t>(row) * d)[vec] = pack8(h);
+      }
+    }
+  }
 }
 
 template <int NV>
@@ -1197,6 +1222,103 @@ __global__ void __launch_bounds__(512, 1) tb_lowrank_apply_kernel(const ProjAppl
 #pragma unroll
           for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(acc[rr][e], rstd), w8[e]);
           reinterpret_cast<Bf16x8*>(a.out_h + static_cast<size_t>(row0 + rr) * a.d)[tid] = pack8(h);
+        }
+      }
+    }
+  }
+}
+
+
+// -----------------------------------------------------------------------------------------
+// K2 for ranks 1..2 in the row-group layout of tb_rmsnorm_kernel (four rows per CTA, 128 threads
+// per row, U^T in shared memory): at these ranks the two thin products are a handful of FMAs
+// per element, and what matters is the number of rows in flight -- this is the norm kernel with
+// a projection spliced in (one extra pair of group barriers for the r dot products).
+// -----------------------------------------------------------------------------------------
+constexpr int kProjTinyRank = 2;
+
+template <int NV>
+__global__ void __launch_bounds__(kAblThreads) tb_lowrank_tiny_kernel(const ProjArgs a) {
+  extern __shared__ __align__(16) uint8_t proj_tiny_smem[];
+  int4* s_ut = reinterpret_cast<int4*>(proj_tiny_smem);            // [r][nvec]
+  __shared__ float s_red[kRowGroups][4];
+  __shared__ float s_dot[kRowGroups][4][kProjTinyRank];
+  const int group = threadIdx.x / kRowGroupThreads;
+  const int gt = threadIdx.x - group * kRowGroupThreads;
+  const int gwarp = gt >> 5, lane = gt & 31;
+  const int nvec = a.d >> 3;
+  for (int i = threadIdx.x; i < a.r * nvec; i += kAblThreads) s_ut[i] = __ldg(reinterpret_cast<const int4*>(a.ut) + i);
+  __syncthreads();
+  for (int row = blockIdx.x * kRowGroups + group; row < a.n_rows; row += gridDim.x * kRowGroups) {
+    const int4* xr = reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row) * a.d);
+    float xb[NV][8];
+    float dot[kProjTinyRank] = {0.0f, 0.0f};
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      if (vec < nvec) {
+        unpack8(__ldg(xr + vec), xb[i]);
+#pragma unroll
+        for (int j = 0; j < kProjTinyRank; ++j) {
+          if (j < a.r) {
+            float u[8];
+            unpack8(s_ut[j * nvec + vec], u);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) dot[j] = fmaf(xb[i][e], u[e], dot[j]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kProjTinyRank; ++j) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dot[j] += __shfl_xor_sync(0xffffffffu, dot[j], o);
+    }
+    group_bar_sync(group);          // s_dot of the previous row is no longer read
+    if (lane == 0) {
+#pragma unroll
+      for (int j = 0; j < kProjTinyRank; ++j) s_dot[group][gwarp][j] = dot[j];
+    }
+    group_bar_sync(group);
+    float c[kProjTinyRank];
+#pragma unroll
+    for (int j = 0; j < kProjTinyRank; ++j)
+      c[j] = -((s_dot[group][0][j] + s_dot[group][1][j]) + (s_dot[group][2][j] + s_dot[group][3][j]));
+    float ss = 0.0f;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      if (vec < nvec) {
+#pragma unroll
+        for (int j = 0; j < kProjTinyRank; ++j) {
+          if (j < a.r) {
+            float u[8];
+            unpack8(s_ut[j * nvec + vec], u);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) xb[i][e] = fmaf(c[j], u[e], xb[i][e]);
+          }
+        }
+        const Bf16x8 pk = pack8(xb[i]);
+        if (a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row) * a.d)[vec] = pk;
+        unpack8(pk, xb[i]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) ss = fmaf(xb[i][e], xb[i][e], ss);
+      }
+    }
+    if (a.out_h) {
+      ss = group_sum(ss, s_red[group], group, gwarp, lane);
+      const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, static_cast<float>(a.d)), a.eps)));
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = gt + i * kRowGroupThreads;
+        if (vec < nvec) {
+          const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec);
+          const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec + 1);
+          const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+          float h[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(xb[i][e], rstd), __fadd_rn(1.0f, ww[e]));
+          reinterpret_cast<Bf16x8*>(a.out_h + static_cast<size_t>(row) * a.d)[vec] = pack8(h);
         }
       }
     }
