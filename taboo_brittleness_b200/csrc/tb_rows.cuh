@@ -129,6 +129,8 @@ struct AblateArgs {
 // the other groups' instead of idling a whole CTA.
 constexpr int kRowGroupThreads = 128;
 constexpr int kRowGroups = 4;
+constexpr int kListPerThread = 1;                                   // list entries a thread examines per batch
+constexpr int kListBatch = kRowGroupThreads * kListPerThread;
 constexpr int kAblThreads = kRowGroupThreads * kRowGroups;
 
 __device__ __forceinline__ void group_bar_sync(int group) {
@@ -189,15 +191,21 @@ __global__ void __launch_bounds__(kAblThreads) tb_rmsnorm_kernel(const __nv_bflo
 template <int NV>
 __global__ void __launch_bounds__(kAblThreads, (NV <= 4 ? 2 : 1)) tb_ablate_decode_kernel(const AblateArgs a) {
   __shared__ float s_red[kRowGroups][4];
-  __shared__ int32_t s_id[kRowGroups][kRowGroupThreads];
-  __shared__ float s_a[kRowGroups][kRowGroupThreads];
-  __shared__ int s_wcnt[kRowGroups][4];
+  __shared__ int32_t s_id[kRowGroups][kListBatch];
+  __shared__ float s_a[kRowGroups][kListBatch];
+  __shared__ int s_wcnt[kRowGroups][4 * kListPerThread];
   const int group = threadIdx.x / kRowGroupThreads;
   const int gt = threadIdx.x - group * kRowGroupThreads;
   const int gwarp = gt >> 5, lane = gt & 31;
   const int nvec = a.d >> 3;
   const float sign = (a.mode == 0) ? -1.0f : 1.0f;
-  for (int row = blockIdx.x * kRowGroups + group; row < a.n_rows; row += gridDim.x * kRowGroups) {
+  // A CTA owns a contiguous run of rows (its groups interleave inside it). Rows cost very different
+  // amounts -- a <bos>-scale row has ~100x the active latents -- and they recur with the prompt length;
+  // a grid-stride assignment puts all of them on the few CTAs whose index resonates with that period.
+  const int rows_per_cta = (a.n_rows + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const int cta_row0 = static_cast<int>(blockIdx.x) * rows_per_cta;
+  const int cta_row1 = min(a.n_rows, cta_row0 + rows_per_cta);
+  for (int row = cta_row0 + group; row < cta_row1; row += kRowGroups) {
     float acc[NV][8];
     if (a.mode == 0) {
       const int4* xr = reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row) * a.d);
@@ -224,34 +232,58 @@ __global__ void __launch_bounds__(kAblThreads, (NV <= 4 ? 2 : 1)) tb_ablate_deco
     const int table = a.row_table ? a.row_table[row] : (a.rank_rows > 0 ? row / a.rank_rows : 0);
     const uint16_t* rk = a.rank ? a.rank + static_cast<size_t>(table) * a.S : nullptr;
 
-    for (int b0 = 0; b0 < cnt; b0 += kRowGroupThreads) {
-      // stage 1: every thread looks at one list entry; ordered compaction (list order is kept, so
-      // the fp32 accumulation order is deterministic): warp ballots + prefix over the 4 warps
-      const int i = b0 + gt;
-      bool sel = false;
-      int32_t id = 0;
-      float av = 0.0f;
-      if (i < cnt) {
-        id = a.idx[start + i];
-        av = a.val[start + i];
-        const bool abl = rk ? (static_cast<int>(rk[id]) < a.budget) : false;
-        sel = (a.mode == 0) ? abl : !abl;
-      }
-      const uint32_t bal = __ballot_sync(0xffffffffu, sel);
-      group_bar_sync(group);          // previous batch's stage 2 is done with s_id / s_a / s_wcnt
-      if (lane == 0) s_wcnt[group][gwarp] = __popc(bal);
-      group_bar_sync(group);
-      int before = 0, n = 0;
+    for (int b0 = 0; b0 < cnt; b0 += kListBatch) {
+      // stage 1: every thread looks at kListPerThread list entries (entry = b0 + q * 128 + gt, all
+      // loads in flight together); ordered compaction (list order is kept, so the fp32 accumulation
+      // order is deterministic): ballots per (q, warp) + prefix over the 16 of them
+      bool sel[kListPerThread];
+      int32_t id[kListPerThread];
+      float av[kListPerThread];
 #pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        const int c = s_wcnt[group][w];
-        if (w < gwarp) before += c;
-        n += c;
+      for (int q = 0; q < kListPerThread; ++q) {
+        const int i = b0 + q * kRowGroupThreads + gt;
+        sel[q] = false;
+        id[q] = 0;
+        av[q] = 0.0f;
+        if (i < cnt) {
+          id[q] = a.idx[start + i];
+          av[q] = a.val[start + i];
+        }
       }
-      if (sel) {
-        const int pos = before + __popc(bal & ((1u << lane) - 1u));
-        s_id[group][pos] = id;
-        s_a[group][pos] = sign * av;
+#pragma unroll
+      for (int q = 0; q < kListPerThread; ++q) {
+        const int i = b0 + q * kRowGroupThreads + gt;
+        if (i < cnt) {
+          const bool abl = rk ? (static_cast<int>(rk[id[q]]) < a.budget) : false;
+          sel[q] = (a.mode == 0) ? abl : !abl;
+        }
+      }
+      uint32_t bal[kListPerThread];
+#pragma unroll
+      for (int q = 0; q < kListPerThread; ++q) bal[q] = __ballot_sync(0xffffffffu, sel[q]);
+      group_bar_sync(group);          // previous batch's stage 2 is done with s_id / s_a / s_wcnt
+      if (lane == 0) {
+#pragma unroll
+        for (int q = 0; q < kListPerThread; ++q) s_wcnt[group][q * 4 + gwarp] = __popc(bal[q]);
+      }
+      group_bar_sync(group);
+      int n = 0;
+      int before[kListPerThread];
+#pragma unroll
+      for (int q = 0; q < kListPerThread; ++q) {
+#pragma unroll
+        for (int w = 0; w < 4; ++w) {
+          if (w == gwarp) before[q] = n;
+          n += s_wcnt[group][q * 4 + w];
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < kListPerThread; ++q) {
+        if (sel[q]) {
+          const int pos = before[q] + __popc(bal[q] & ((1u << lane) - 1u));
+          s_id[group][pos] = id[q];
+          s_a[group][pos] = sign * av[q];
+        }
       }
       group_bar_sync(group);
       // stage 2: acc += a_i * W_dec[i, :]; independent 16-byte gathers, L2-resident rows
