@@ -111,3 +111,28 @@ def test_cache_format_matches_reference_sidecar(tmp_path):
     npz2, js2 = cache.pair_paths(str(tmp_path), "moon", 9)
     cache.save_pair(npz2, js2, probs, ["x"], "r", "p")
     assert cache.load_pair(npz2, js2).residual is None and npz2.endswith("prompt_10.npz")
+
+
+def test_plan_row_splits_cover_rows_with_valid_chunkings():
+    """ops.plan_row_splits: contiguous cover of the rows, group-aligned boundaries, chunk counts the
+    kernels accept (non-empty chunks, multiple of the cluster's chunk dimension, K5 bitmap limit)."""
+    from taboo_brittleness_b200 import ops
+    V = 256000
+    for mode in range(5):
+        group, R, C = ops.CLUSTER_MODES[mode]
+        for sweep_a in (False, True):
+            for n in (128, 256, 37888, 75776, 131072, 262144, 524288, 524288 + 256):
+                splits = ops.plan_row_splits(n, V, mode, sweep_a=sweep_a)
+                assert splits[0][0] == 0 and splits[-1][1] == n
+                assert all(a[1] == b[0] for a, b in zip(splits, splits[1:]))
+                n_tiles = -(-V // (128 * group)) if sweep_a else -(-V // 256)
+                for r0, r1, c in splits:
+                    assert r1 > r0 and c >= 1 and c % C == 0
+                    tpc = -(-n_tiles // c)
+                    assert -(-n_tiles // tpc) == c, "empty chunk"
+                    if sweep_a:
+                        assert tpc * 128 * group <= ops.LL_MAX_CHUNK_IDS
+                    assert r0 % 128 == 0
+    # the case that motivated it: 4096 prompts x 128 tok on 33 clusters of four CTAs
+    main, tail = ops.plan_row_splits(524288, V, 2)
+    assert main[2] == 2 and tail[2] > 16 and tail[1] - tail[0] == 512
