@@ -1,22 +1,27 @@
-// Persistent, warp-specialised tcgen05 GEMM main loop shared by the SAE encode (K1) and the
-// logit-lens readout (K3):  D[M, N] = A[M, K] * B[N, K]^T, bf16 operands (both K-major in
-// HBM, i.e. plain row-major [rows, K]), fp32 accumulation in TMEM.
+// Persistent, warp-specialised tcgen05 GEMM main loop shared by the SAE encode (K1), the logit-lens
+// readouts (K3, K3F), the LL-Top-k sweep (K5) and the projection coefficients (K2):
+//   D[M, N] = A[M, K] * B[N, K]^T, bf16 operands (both K-major in HBM, i.e. plain row-major
+//   [rows, K]), fp32 accumulation in TMEM.
 //
-// What makes it specific to this hot path is that D is never stored. A CTA (or CTA pair) owns
-// a block of rows and sweeps a contiguous range of N-tiles (a "chunk" of the vocabulary / of
-// the SAE latents); each epilogue thread owns one row of the block and keeps that row's
-// running readout (online logsumexp, top-10, secret logit / active-latent cursor) in registers
-// across the whole sweep. Only the per-row readout leaves the SM.
+// What makes it specific to this hot path is that D is never stored. A CTA pair owns a
+// stationary block of rows of one operand and sweeps a contiguous range of tiles of the other (a
+// "chunk" of the vocabulary / of the SAE latents); each epilogue thread owns one TMEM lane and
+// keeps that lane's running readout (online logsumexp, top-10, secret logit, active-latent
+// cursor, column sums) in registers across the whole sweep. Only the readout leaves the SM.
+// Row-owner epilogues: lane = a row of A (residual rows). Sweep-A epilogues (Epi::kSweepA):
+// lane = a row of the swept A operand (a vocabulary id), TMEM columns = the stationary B block.
 //
-// Roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
-// warp 3 idle, warps 4..7 = epilogue (TMEM lane quadrant = warp % 4). Three pipelines:
-// smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue, two 256-column
-// accumulators so the epilogue of tile i overlaps the MMAs of tile i+1), and the static
-// round-robin unit schedule.
+// Roles (128 + 32 * Epi::kEpiWarps threads): warp 0 = TMA producer, warp 1 = MMA issuer,
+// warp 2 = TMEM allocator, warp 3 spare, warps 4.. = epilogue (TMEM lane quadrant = warp % 4;
+// with 8 epilogue warps two warps share a quadrant and split a tile's 256 columns).
+// Pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue, two 256-column
+// accumulators so the epilogue of tile i overlaps the MMAs of tile i+1), the static round-robin
+// unit schedule, and a soft lockstep between clusters (GemmArgs::lockstep).
 //
-// kCtaGroup == 2 pairs two SMs (cluster 2x1x1): UMMA M = 256, each CTA stages its own 128 A
-// rows and half (128 rows) of the B tile, the leader CTA issues the MMAs, and each CTA's
-// epilogue drains its own 128 x 256 accumulator half.
+// kCtaGroup == 2 pairs two SMs: UMMA M = 256, each CTA stages its own 128 A rows and half (128
+// rows) of the B tile, the leader CTA issues the MMAs, and each CTA's epilogue drains its own
+// 128 x 256 accumulator half. kR x kC such pairs form a cluster that shares operand slabs by TMA
+// multicast (see the kernel).
 #pragma once
 #include "tb_ptx.cuh"
 
