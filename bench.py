@@ -219,6 +219,7 @@ def run_native(args, rank, local_rank, world):
                                            n_chunks=args.chunks or None, encode_cap=args.encode_cap)
     eng.ll_fused = not args.ll_two_sweeps
     eng.ll_alpha = args.ll_alpha
+    eng.overlap = args.overlap
 
     # ---- inputs: this rank's prompts (weak scaling: every rank gets args.prompts prompts)
     P, BP = args.prompts, min(args.batch_prompts, args.prompts)
@@ -398,6 +399,8 @@ def main():
                     help="skip the per-prompt LL-Top-10 readout (then every condition is exactly one GEMM sweep)")
     ap.add_argument("--ll-alpha", type=float, default=0.5, help="K3F candidate threshold as a fraction of the "
                     "previous budget's k-th best LL sum")
+    ap.add_argument("--overlap", action="store_true",
+                    help="run K1b / K6 on a side stream under the lens sweeps (measured: no gain)")
     ap.add_argument("--ll-two-sweeps", action="store_true",
                     help="compute LL-Top-10 with the second GEMM sweep for every condition (no one-sweep path)")
     args = ap.parse_args()

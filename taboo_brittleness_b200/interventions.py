@@ -80,6 +80,11 @@ class InterventionEngine:
         self.stats = SweepStats()
         self.time_lens = False
         self.ll_fused = True         # nested sweeps: one GEMM sweep per condition after the first
+        # K1b / K6 on a side stream under the lens sweeps (on the 16 SMs a grid of 4-CTA clusters leaves
+        # free). Measured: no gain (574 k vs 579 k token-conditions/s) -- the side kernels share the power
+        # budget and can sit on SMs the next persistent lens grid wants -- so it is off by default.
+        self.overlap = False
+        self._side = None
         self.ll_alpha = 0.5          # candidate threshold = ll_alpha * previous condition's k-th best sum
         self.ll_cand_cap = 256       # candidate slots per prompt
 
@@ -198,6 +203,8 @@ class InterventionEngine:
         ({budget: readout}, last LLState)."""
         fusable = (ll is not None and self.ll_fused and ll.seg is None and ll.rows_per_prompt == ops.LL_SLOTS
                    and self.lens.vocab_offset == 0)
+        if fusable and self.overlap and len(budgets) >= 3:
+            return self._nested_budgets_overlapped(x, acts, rank, rank_rows, budgets, secret_id, mode, ll, state)
         out = {}
         for b in sorted(int(v) for v in budgets):
             if fusable and state is not None:
@@ -208,6 +215,105 @@ class InterventionEngine:
                 out[b] = r
                 if fusable:
                     state = LLState(r.lens.lse, r.ll_sum[:, ll.k - 1].contiguous())
+        return out, state
+
+    def _nested_budgets_overlapped(self, x, acts, rank, rank_rows: int, budgets: Sequence[int], secret_id, mode: str,
+                                   ll: LLSpec, state: Optional[LLState]):
+        """The same chain with the small kernels taken off the critical path. The lens sweeps cannot use
+        all SMs (clusters of four CTAs fill 132 of 148), so while sweep i runs on the main stream a side
+        stream produces the operand of the next condition (K1b of budget i+1, i+2) and evaluates the
+        LL candidates of the previous one (K6 of budget i-1) on the SMs the cluster grid leaves free.
+        What changes numerically: nothing that is returned -- the candidate threshold of condition i
+        comes from the k-th best sum of condition i-2 instead of i-1 (K6 of i-1 is still running), the
+        certificate is unchanged, and prompts it does not cover are redone with the two-sweep kernel
+        once the chain is through."""
+        main = torch.cuda.current_stream()
+        if self._side is None:
+            self._side = torch.cuda.Stream()
+        side = self._side
+        bs = sorted(int(v) for v in budgets)
+        n, k = len(bs), ll.k
+        h = [None] * n
+        h_ready = [None] * n
+
+        def produce(i):                      # K1b for budget i on the side stream
+            with torch.cuda.stream(side):
+                _, hi = ops.sae_ablate_decode(x, acts, self.sae, rank, bs[i], mode=mode, rank_rows=rank_rows,
+                                              w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False, want_h=True)
+                ev = torch.cuda.Event()
+                ev.record(side)
+            h[i], h_ready[i] = hi, ev
+            self.stats.launches += 1
+
+        side.wait_stream(main)               # x, acts, rank were produced on the main stream
+        produce(0)
+        if n > 1:
+            produce(1)
+        out, fused = {}, []                  # fused: per one-sweep condition, what K6 left on the side stream
+        theta_done = None                    # (theta tensor, event) of the latest K6 whose result may be used
+        theta_now = None if state is None else state.theta
+        for i, b in enumerate(bs):
+            main.wait_event(h_ready[i])
+            if state is None:                # no reference yet: K3 + K5 on the main stream
+                r = self.read(h[i], secret_id, True, ll)
+                out[b] = r
+                state = LLState(r.lens.lse, r.ll_sum[:, k - 1].contiguous())
+                theta_now = state.theta
+            else:
+                if theta_done is not None:   # K6 of condition i-2 finished during sweep i-1
+                    main.wait_event(theta_done[1])
+                    theta_now = theta_done[0]
+                tau = (theta_now * self.ll_alpha).clamp_min(1e-30)
+                ref = state.lse
+                if self.time_lens:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                p, cnt, cid = ops.lens_ll_partials(h[i], self.lens.w_u, ref, tau, ll.cur_id, ll.prev_id,
+                                                   softcap=self.softcap, secret_id=secret_id,
+                                                   vocab_offset=self.lens.vocab_offset, n_chunks=self.n_chunks,
+                                                   cta_pair=self.cta_pair, cand_cap=self.ll_cand_cap)
+                if self.time_lens:
+                    e1.record()
+                    self.stats.lens_events.append((e0, e1, 2.0 * h[i].shape[0] * h[i].shape[1] * self.lens.w_u.shape[0]))
+                lens_out = ops.lens_merge(p, finalize=True)
+                swept = torch.cuda.Event()
+                swept.record(main)
+                if fused:                    # the previous condition's K6 may be used from the next sweep on
+                    theta_done = (fused[-1]["theta"], fused[-1]["done"])
+                with torch.cuda.stream(side):
+                    side.wait_event(swept)
+                    val, ids, theta, flag = ops.ll_candidates_exact(h[i], self.lens.w_u, lens_out.lse, ref, tau,
+                                                                    ll.cur_id, ll.prev_id, cnt, cid, k=k,
+                                                                    softcap=self.softcap,
+                                                                    vocab_offset=self.lens.vocab_offset)
+                    done = torch.cuda.Event()
+                    done.record(side)
+                fused.append(dict(i=i, b=b, lens=lens_out, val=val, ids=ids, theta=theta, flag=flag, cnt=cnt, done=done))
+                self.stats.launches += 3
+                state = LLState(lens_out.lse, theta)
+            if i + 2 < n:
+                produce(i + 2)
+        main.wait_stream(side)
+        # resolve the certificates (one host sync for the whole chain) and redo what they do not cover
+        if fused:
+            flags = torch.stack([f["flag"] for f in fused])
+            counts = torch.stack([f["cnt"].sum() for f in fused]).sum()
+            bad_all = torch.nonzero(flags == 0)
+            self.stats.ll_candidates += int(counts.item())
+            self.stats.ll_fused_prompts += int(flags.numel())
+            self.stats.ll_fallback_prompts += int(bad_all.shape[0])
+            for j, f in enumerate(fused):
+                bad = bad_all[bad_all[:, 0] == j, 1]
+                if bad.numel():
+                    rows = (bad[:, None] * ops.LL_SLOTS + torch.arange(ops.LL_SLOTS, device=x.device)[None]).flatten()
+                    sub = LLSpec(ll.cur_id[rows].contiguous() if ll.cur_id is not None else None,
+                                 ll.prev_id[rows].contiguous() if ll.prev_id is not None else None,
+                                 rows_per_prompt=ops.LL_SLOTS, k=k)
+                    bv, bi = self.ll_topk(h[f["i"]][rows].contiguous(), f["lens"].lse[rows].contiguous(), sub)
+                    f["val"][bad], f["ids"][bad], f["theta"][bad] = bv, bi, bv[:, k - 1]
+                for t in (f["val"], f["ids"], f["theta"]):
+                    t.record_stream(main)    # allocated on the side stream, handed to the caller's stream
+                out[f["b"]] = Readout(f["lens"], f["val"], f["ids"])
         return out, state
 
     def targeted_budget_sweep(self, x: torch.Tensor, rows_per_prompt: int, secret_id: Optional[torch.Tensor],

@@ -70,8 +70,9 @@ def test_fused_overflow_is_flagged(cuda_lib):
     assert (cnt.cpu() > 64).all() and (flag.cpu() == 0).all()
 
 
+@pytest.mark.parametrize("overlap", [False, True])
 @pytest.mark.parametrize("alpha", [0.5, 1e-9])
-def test_nested_budget_sweep_one_sweep_per_condition_is_exact(cuda_lib, alpha):
+def test_nested_budget_sweep_one_sweep_per_condition_is_exact(cuda_lib, alpha, overlap):
     """InterventionEngine.targeted_budget_sweep with LL-Top-k: first budget two sweeps, the rest one
     sweep each (alpha = 1e-9 forces every prompt through the fallback) -- both must equal the oracle."""
     from taboo_brittleness_b200 import interventions, ops
@@ -89,6 +90,7 @@ def test_nested_budget_sweep_one_sweep_per_condition_is_exact(cuda_lib, alpha):
     eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
                                            softcap=30.0, cta_pair=4)
     eng.ll_alpha = alpha
+    eng.overlap = overlap        # side-stream variant of the chain: same results
     ll = interventions.LLSpec(cur.cuda(), prev.cuda(), rows_per_prompt=T, k=10)
     res = eng.targeted_budget_sweep(cuda_bf16(x), T, sid.cuda(), budgets, ll=ll)
     torch.cuda.synchronize()
