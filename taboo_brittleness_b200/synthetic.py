@@ -10,7 +10,7 @@ kernels get the bf16 tensors, the oracle gets the same values upcast to fp32.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Dict, Optional
+from typing import Dict
 
 import torch
 
