@@ -213,6 +213,18 @@ int tb_ll_candidates_exact(const void* h_bf16, const void* w_u_bf16, int64_t n_r
                            float* out_val, int32_t* out_id, float* out_theta, int32_t* out_flag,
                            void* stream);
 
+/* The same contract as tb_ll_candidates_exact with the sums on the tensor cores: the candidates'
+ * W_U rows are gathered into 128 slots per prompt (wc_scratch: bf16 [n_rows, d], n_rows = 128 *
+ * n_prompts), a block-diagonal tcgen05 GEMM multiplies each prompt pair's candidate tile with the
+ * same pair's rows (sum_scratch: f32 [n_prompts, 128]), a small kernel ranks and certifies. Prompts
+ * with more than 128 listed candidates get flag 0. */
+int tb_ll_candidates_exact_tc(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
+                              int vocab_offset, float softcap, const float* lse, const float* ref_lse,
+                              const float* tau, const int32_t* cur_id, const int32_t* prev_id,
+                              const int32_t* cand_count, const int32_t* cand_id, int cand_cap, int k,
+                              void* wc_scratch, float* sum_scratch, float* out_val, int32_t* out_id,
+                              float* out_theta, int32_t* out_flag, void* stream);
+
 /* ---- lens readout without caller scratch -------------------------------------------------
  * (No counterpart in the reference: this entry point exists for the way the library is
  * deployed, not for anything the reference computes.)

@@ -63,6 +63,8 @@ SIGNATURES = {
                                     _P, _P, _P, _P, _P, _P, _P, c_int, _P]),
     "tb_ll_candidates_exact": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P, _P,
                                        c_int, c_int, _P, _P, _P, _P, _P]),
+    "tb_ll_candidates_exact_tc": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P, _P,
+                                          c_int, c_int, _P, _P, _P, _P, _P, _P, _P]),
     "tb_logit_lens_static": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,
                                      _P, _P, _P, _P, _P]),
 }

@@ -135,6 +135,7 @@ void set_policies(tb::GemmArgs* g, bool stationary_is_a) {
   const char* ls = getenv("TB_LOCKSTEP");
   g->lockstep = ls ? atoi(ls) : 1;
   g->progress = nullptr;
+  g->diag = 0;
   g->policy_a = stationary_is_a ? pol[0] : pol[1];
   g->policy_b = stationary_is_a ? pol[1] : pol[0];
 }
@@ -819,6 +820,56 @@ int tb_ll_candidates_exact(const void* h, const void* w_u, int64_t n_rows, int d
                                static_cast<int>(smem)));
   const unsigned grid = static_cast<unsigned>((n_rows + 127) / 128);
   tb::tb_ll_candidates_exact_kernel<<<grid, tb::kCandThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_ll_candidates_exact_tc(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
+                              float softcap, const float* lse, const float* ref_lse, const float* tau,
+                              const int32_t* cur_id, const int32_t* prev_id, const int32_t* cand_count,
+                              const int32_t* cand_id, int cand_cap, int k, void* wc_scratch, float* sum_scratch,
+                              float* out_val, int32_t* out_id, float* out_theta, int32_t* out_flag, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!h || !w_u || !lse || !ref_lse || !tau || !cand_count || !cand_id || !wc_scratch || !sum_scratch || !out_val ||
+      !out_id || !out_theta || !out_flag)
+    return fail(TB_ERR_INVALID, "null pointer");
+  if (k < 1 || k > TB_TOPK) return fail(TB_ERR_INVALID, "k=%d outside [1, %d]", k, TB_TOPK);
+  if (cand_cap < 1) return fail(TB_ERR_INVALID, "cand_cap=%d", cand_cap);
+  if (n_rows <= 0) return TB_OK;
+  if (n_rows % 128) return fail(TB_ERR_INVALID, "n_rows=%lld: 128 row slots per prompt", (long long)n_rows);
+  rc = check_gemm_operands(wc_scratch, h, n_rows, static_cast<int>(n_rows), d);
+  if (rc != TB_OK) return rc;
+  const int n_prompts = static_cast<int>(n_rows / 128);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  // 1. candidates' W_U rows -> 128 slots per prompt
+  {
+    const int64_t slots = static_cast<int64_t>(n_prompts) * tb::kCandSlots;
+    const unsigned grid = static_cast<unsigned>((slots + 7) / 8);
+    tb::tb_ll_gather_candidates_kernel<<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(w_u), V, d, vocab_offset,
+                                                          cand_count, cand_id, cand_cap, n_prompts,
+                                                          static_cast<__nv_bfloat16*>(wc_scratch));
+    TB_CUDA(cudaGetLastError());
+  }
+  // 2. block-diagonal GEMM: prompt pair u's candidate tile x the same pair's row block
+  {
+    tb::GemmArgs g = make_args_sweep_a(static_cast<int>(n_rows), n_rows, d, 1, 2);
+    g.diag = 1;
+    g.total_units = g.m_blocks;
+    tb::CandSumEpi::Params ep;
+    ep.lse = lse; ep.ref = ref_lse; ep.cur_id = cur_id; ep.prev_id = prev_id;
+    ep.cand_count = cand_count; ep.cand_id = cand_id; ep.cand_cap = cand_cap; ep.softcap = softcap;
+    ep.n_prompts = n_prompts; ep.out_sum = sum_scratch;
+    rc = launch_gemm<tb::CandSumEpi, 2>(wc_scratch, h, g, ep, s, di.sms);
+    if (rc != TB_OK) return rc;
+  }
+  // 3. top-k, theta, certificate
+  tb::CandFinalArgs a;
+  a.sums = sum_scratch; a.lse = lse; a.ref = ref_lse; a.tau = tau; a.cand_count = cand_count; a.cand_id = cand_id;
+  a.cap = cand_cap; a.k = k; a.n_rows = static_cast<int>(n_rows);
+  a.out_val = out_val; a.out_id = out_id; a.out_theta = out_theta; a.out_flag = out_flag;
+  tb::tb_ll_candidates_finalize_kernel<<<static_cast<unsigned>(n_prompts), tb::kCandSlots, 0, s>>>(a);
   TB_CUDA(cudaGetLastError());
   return TB_OK;
 }

@@ -614,6 +614,85 @@ struct LensLLEpi {
 };
 
 // =========================================================================================
+// K6 on the tensor cores: exact masked column sums of K3F's candidates. A = the candidates' W_U
+// rows gathered into 128 slots per prompt, B = h with 128 row slots per prompt, block-diagonal
+// schedule (GemmArgs::diag): unit u multiplies the candidate tile of prompt pair u with the row
+// block of the same pair. A thread = a candidate slot of the CTA's prompt; its prompt's 128
+// positions are TMEM columns [128 * rank, 128 * rank + 128). No top-k here: the sums go to
+// out_sum [n_prompts, 128] and tb_ll_candidates_finalize ranks and certifies them.
+// =========================================================================================
+struct CandSumEpi {
+  static constexpr int kEpiWarps = 4;
+  static constexpr bool kSweepA = true;
+  static constexpr bool kTileHooks = false;
+  static constexpr int kSlots = 128;
+  static constexpr int kOffNl = 0;                     // float[128]  -lse * log2(e) of the CTA's prompt
+  static constexpr int kOffCur = kOffNl + 128 * 4;     // int32[128]
+  static constexpr int kOffPrev = kOffCur + 128 * 4;   // int32[128]
+  static constexpr int kExtraSmem = kOffPrev + 128 * 4;
+
+  struct Params {
+    const float* lse;          // [N] exact logsumexp per row slot (+inf / nan: empty slot)
+    const float* ref;          // [N] K3F's reference (+inf marks the empty slots)
+    const int32_t* cur_id;     // nullable
+    const int32_t* prev_id;    // nullable
+    const int32_t* cand_count; // [n_prompts]
+    const int32_t* cand_id;    // [n_prompts, cand_cap]
+    int cand_cap;
+    float softcap;
+    int n_prompts;
+    float* out_sum;            // [n_prompts, 128]
+  };
+  struct State {};
+
+  __device__ __forceinline__ static void begin_unit_sw(State&, const Params& p, const GemmArgs& g,
+                                                       const SweepCtx& c) {
+    float* s_nl = reinterpret_cast<float*>(c.extra + kOffNl);
+    int32_t* s_cur = reinterpret_cast<int32_t*>(c.extra + kOffCur);
+    int32_t* s_prev = reinterpret_cast<int32_t*>(c.extra + kOffPrev);
+    epi_bar_sync<128>();       // the previous unit's readers are done
+    const int64_t r = static_cast<int64_t>(c.blk) * 256 + c.rank * kSlots + c.tid;
+    const bool valid = r < g.N && p.ref[r] < CUDART_INF_F;
+    s_nl[c.tid] = valid ? -p.lse[r] * kLog2e : -CUDART_INF_F;
+    s_cur[c.tid] = (valid && p.cur_id) ? p.cur_id[r] : -1;
+    s_prev[c.tid] = (valid && p.prev_id) ? p.prev_id[r] : -1;
+    epi_bar_sync<128>();
+  }
+
+  __device__ __forceinline__ static void process_tile_sw(State&, const Params& p, const GemmArgs&,
+                                                         const SweepCtx& c, int /*nt*/, uint32_t taddr) {
+    const float* s_nl = reinterpret_cast<const float*>(c.extra + kOffNl);
+    const int32_t* s_cur = reinterpret_cast<const int32_t*>(c.extra + kOffCur);
+    const int32_t* s_prev = reinterpret_cast<const int32_t*>(c.extra + kOffPrev);
+    const int prompt = c.blk * 2 + c.rank;
+    int vid = -1;
+    if (prompt < p.n_prompts && c.tid < min(p.cand_count[prompt], min(p.cand_cap, kSlots)))
+      vid = p.cand_id[static_cast<size_t>(prompt) * p.cand_cap + c.tid];
+    const CapLog2 cap2(p.softcap);
+    float acc0 = 0.0f, acc1 = 0.0f;
+#pragma unroll 1
+    for (int cc = 0; cc < 4; ++cc) {
+      uint32_t v[32];
+      tmem_ld_32x32(taddr + c.rank * kSlots + cc * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        const int t0 = cc * 32 + j;
+        float e0 = ex2_approx(cap2(__uint_as_float(v[j])) + s_nl[t0]);
+        float e1 = ex2_approx(cap2(__uint_as_float(v[j + 1])) + s_nl[t0 + 1]);
+        if (s_cur[t0] == vid || s_prev[t0] == vid) e0 = 0.0f;
+        if (s_cur[t0 + 1] == vid || s_prev[t0 + 1] == vid) e1 = 0.0f;
+        acc0 += e0;
+        acc1 += e1;
+      }
+    }
+    if (vid >= 0) p.out_sum[static_cast<size_t>(prompt) * kSlots + c.tid] = acc0 + acc1;
+  }
+
+  __device__ __forceinline__ static void end_unit_sw(State&, const Params&, const GemmArgs&, const SweepCtx&) {}
+};
+
+// =========================================================================================
 // Validation epilogue: store the fp32 accumulator. Used only by the tests that pin the
 // TMA / UMMA-descriptor / TMEM plumbing against a plain matmul.
 // =========================================================================================

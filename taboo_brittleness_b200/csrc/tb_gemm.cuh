@@ -53,6 +53,7 @@ struct GemmArgs {
   int lockstep;
   int* progress;
   int max_clusters;     // > 0: launch at most this many clusters (host side only)
+  int diag;             // 1: block-diagonal schedule -- unit u is stationary block u x swept tile u only
 };
 
 // What a "sweep-A" epilogue (Epi::kSweepA) is told about its unit. In that orientation the
@@ -138,6 +139,13 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // unit -> (stationary block, chunk, tile range) of THIS pair; with multicast every pair of the
   // cluster runs the same number of tiles (tiles past the end load zeros and are masked)
   auto decode = [&](int unit, int& m_blk, int& chunk, int& t0, int& n_iter) {
+    if (g.diag) {   // (single pairs only: the host never combines it with multicast clusters)
+      m_blk = unit;
+      chunk = 0;
+      t0 = unit;
+      n_iter = 1;
+      return;
+    }
     const int mg = unit / chunk_groups;
     m_blk = mg * kR + pi;
     chunk = (unit - mg * chunk_groups) * kC + pj;

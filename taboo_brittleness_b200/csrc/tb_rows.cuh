@@ -1357,4 +1357,104 @@ __global__ void __launch_bounds__(kAblThreads) tb_lowrank_tiny_kernel(const Proj
   }
 }
 
+
+// -----------------------------------------------------------------------------------------
+// K6 on the tensor cores, the two small kernels around the block-diagonal GEMM (CandSumEpi):
+//   gather   : copy the W_U rows of each prompt's listed candidates into 128 slots per prompt
+//              (one warp per slot, 16-byte copies; empty slots are left untouched -- nobody reads
+//              their sums)
+//   finalize : per prompt, the k best exact sums (value desc, id asc on ties), theta, and the
+//              certificate flag -- the tail of tb_ll_candidates_exact_kernel.
+// -----------------------------------------------------------------------------------------
+constexpr int kCandSlots = 128;
+
+__global__ void tb_ll_gather_candidates_kernel(const __nv_bfloat16* __restrict__ w_u, int V, int d, int vocab_offset,
+                                               const int32_t* __restrict__ cand_count,
+                                               const int32_t* __restrict__ cand_id, int cap, int n_prompts,
+                                               __nv_bfloat16* __restrict__ wc) {
+  const int warps_per_block = blockDim.x >> 5;
+  const int64_t slot = static_cast<int64_t>(blockIdx.x) * warps_per_block + (threadIdx.x >> 5);
+  const int p = static_cast<int>(slot / kCandSlots), s = static_cast<int>(slot % kCandSlots);
+  if (p >= n_prompts || s >= min(cand_count[p], min(cap, kCandSlots))) return;
+  const int v = cand_id[static_cast<size_t>(p) * cap + s] - vocab_offset;
+  int4* dst = reinterpret_cast<int4*>(wc + slot * d);
+  const int nvec = d >> 3;
+  if (v < 0 || v >= V) {
+    for (int i = threadIdx.x & 31; i < nvec; i += 32) dst[i] = make_int4(0, 0, 0, 0);
+    return;
+  }
+  const int4* src = reinterpret_cast<const int4*>(w_u + static_cast<size_t>(v) * d);
+  for (int i = threadIdx.x & 31; i < nvec; i += 32) dst[i] = __ldg(src + i);
+}
+
+struct CandFinalArgs {
+  const float* sums;           // [n_prompts, 128]
+  const float* lse;            // [n_rows]
+  const float* ref;            // [n_rows]
+  const float* tau;            // [n_prompts]
+  const int32_t* cand_count;   // [n_prompts]
+  const int32_t* cand_id;      // [n_prompts, cap]
+  int cap, k, n_rows;
+  float* out_val;              // [n_prompts, k]
+  int32_t* out_id;             // [n_prompts, k]
+  float* out_theta;            // [n_prompts]
+  int32_t* out_flag;           // [n_prompts]
+};
+
+__global__ void __launch_bounds__(kCandSlots) tb_ll_candidates_finalize_kernel(const CandFinalArgs a) {
+  __shared__ float s_v[4];
+  __shared__ int s_i[4], s_pos[4];
+  __shared__ float s_g[4];
+  const int p = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n_all = a.cand_count[p];
+  const int n = min(n_all, min(a.cap, kCandSlots));
+  // g_max = max_t exp(ref_t - lse_t) over the slots that hold a token
+  float g = 0.0f;
+  const int64_t r = static_cast<int64_t>(p) * 128 + tid;
+  if (r < a.n_rows && a.ref[r] < CUDART_INF_F) g = expf(a.ref[r] - a.lse[r]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) g = fmaxf(g, __shfl_xor_sync(0xffffffffu, g, o));
+  if (lane == 0) s_g[warp] = g;
+  float val = -CUDART_INF_F;
+  int id = -1;
+  if (tid < n) {
+    val = a.sums[static_cast<size_t>(p) * kCandSlots + tid];
+    id = a.cand_id[static_cast<size_t>(p) * a.cap + tid];
+  }
+  __syncthreads();
+  const float g_max = fmaxf(fmaxf(s_g[0], s_g[1]), fmaxf(s_g[2], s_g[3]));
+  float theta = -CUDART_INF_F;
+  for (int round = 0; round < a.k; ++round) {
+    float bv = val;
+    int bi = id, bp = tid;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      const int op = __shfl_xor_sync(0xffffffffu, bp, o);
+      if (ov > bv || (ov == bv && oi >= 0 && (bi < 0 || oi < bi))) { bv = ov; bi = oi; bp = op; }
+    }
+    __syncthreads();
+    if (lane == 0) { s_v[warp] = bv; s_i[warp] = bi; s_pos[warp] = bp; }
+    __syncthreads();
+    float wv = s_v[0];
+    int wi = s_i[0], wp = s_pos[0];
+#pragma unroll
+    for (int w = 1; w < 4; ++w)
+      if (s_v[w] > wv || (s_v[w] == wv && s_i[w] >= 0 && (wi < 0 || s_i[w] < wi))) { wv = s_v[w]; wi = s_i[w]; wp = s_pos[w]; }
+    if (wi >= 0 && tid == wp) { val = -CUDART_INF_F; id = -1; }   // taken
+    if (tid == 0) {
+      a.out_val[static_cast<size_t>(p) * a.k + round] = wi >= 0 ? wv : -CUDART_INF_F;
+      a.out_id[static_cast<size_t>(p) * a.k + round] = wi;
+    }
+    theta = wi >= 0 ? wv : -CUDART_INF_F;
+  }
+  if (tid == 0) {
+    a.out_theta[p] = theta;
+    const bool ok = n_all <= min(a.cap, kCandSlots) && theta > 0.0f &&
+                    theta >= g_max * a.tau[p] * (1.0f + 0.0009765625f);
+    a.out_flag[p] = ok ? 1 : 0;
+  }
+}
+
 }  // namespace tb

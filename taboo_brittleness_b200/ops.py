@@ -676,10 +676,13 @@ def lens_ll_partials(h: torch.Tensor, w_u: torch.Tensor, ref_lse: torch.Tensor, 
     return p, cand_count, cand_id
 
 
+_CAND_SCRATCH = {}     # (device, rows, d) -> (wc bf16 [rows, d], sums f32 [P, 128]); reused across conditions
+
+
 def ll_candidates_exact(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, ref_lse: torch.Tensor,
                         tau: torch.Tensor, cur_id: Optional[torch.Tensor], prev_id: Optional[torch.Tensor],
                         cand_count: torch.Tensor, cand_id: torch.Tensor, *, k: int = TB_TOPK, softcap: float = 0.0,
-                        vocab_offset: int = 0):
+                        vocab_offset: int = 0, tensor_cores: bool = True):
     """Exact masked column sums of the listed candidates -> (sums f32 [P, k], ids i32 [P, k],
     theta f32 [P] = k-th best sum, flag i32 [P] = 1 where the top-k is certified exact)."""
     n, d = h.shape
@@ -689,6 +692,19 @@ def ll_candidates_exact(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, r
     ids = torch.empty(P, k, dtype=torch.int32, device=dev)
     theta = torch.empty(P, dtype=torch.float32, device=dev)
     flag = torch.empty(P, dtype=torch.int32, device=dev)
+    if P and tensor_cores:
+        # gather the candidates' W_U rows, block-diagonal tcgen05 GEMM, rank + certify
+        key = (dev, n, d)
+        if key not in _CAND_SCRATCH:
+            _CAND_SCRATCH.clear()
+            _CAND_SCRATCH[key] = (torch.empty(n, d, dtype=torch.bfloat16, device=dev),
+                                  torch.empty(P, LL_SLOTS, dtype=torch.float32, device=dev))
+        wc, sums = _CAND_SCRATCH[key]
+        check(_lib.load().tb_ll_candidates_exact_tc(
+            _ptr(h), _ptr(w_u), n, d, w_u.shape[0], vocab_offset, float(softcap or 0.0), _ptr(lse), _ptr(ref_lse),
+            _ptr(tau), _ptr(cur_id), _ptr(prev_id), _ptr(cand_count), _ptr(cand_id), cand_id.shape[1], k, _ptr(wc),
+            _ptr(sums), _ptr(val), _ptr(ids), _ptr(theta), _ptr(flag), _stream()), "tb_ll_candidates_exact_tc")
+        return val, ids, theta, flag
     if P:
         check(_lib.load().tb_ll_candidates_exact(
             _ptr(h), _ptr(w_u), n, d, w_u.shape[0], vocab_offset, float(softcap or 0.0), _ptr(lse), _ptr(ref_lse),

@@ -164,3 +164,23 @@ def test_row_splits_with_different_chunkings_give_the_same_readouts(cuda_lib, mo
         n = int(c1[q])
         assert set(i1[q, :n].tolist()) == set(i2[q, :n].tolist())
     assert torch.equal(id1, id2) and torch.allclose(v1, v2, rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("P", [5, 2])
+def test_candidate_sums_on_tensor_cores_equal_the_cuda_core_kernel(cuda_lib, P):
+    """K6 twice: gather + block-diagonal tcgen05 GEMM + finalize vs the CUDA-core kernel (odd and even
+    prompt counts: the last tile of the odd case is half empty)."""
+    from taboo_brittleness_b200 import ops
+    h, w_u, sid, cur, prev, plain, ref_lists = _setup(P, 512, 8192, 9, 30.0)
+    g = torch.Generator().manual_seed(2)
+    ref_lse = plain.lse + 0.1 * torch.randn(P * 128, generator=g).cuda()
+    tau = (0.4 * torch.tensor([float(r[1][9]) for r in ref_lists])).cuda().contiguous()
+    p, cnt, cid = ops.lens_ll_partials(h, w_u, ref_lse, tau, cur, prev, softcap=30.0, n_chunks=4)
+    out = ops.lens_merge(p)
+    a = ops.ll_candidates_exact(h, w_u, out.lse, ref_lse, tau, cur, prev, cnt, cid, softcap=30.0, tensor_cores=False)
+    b = ops.ll_candidates_exact(h, w_u, out.lse, ref_lse, tau, cur, prev, cnt, cid, softcap=30.0, tensor_cores=True)
+    torch.cuda.synchronize()
+    assert (cnt.cpu() <= 128).all()
+    assert torch.equal(a[1], b[1]) and torch.equal(a[3], b[3])
+    assert torch.allclose(a[0], b[0], rtol=1e-4, atol=1e-6) and torch.allclose(a[2], b[2], rtol=1e-4, atol=1e-6)
+    _compare(b[0][b[3].bool()], b[1][b[3].bool()], [r for r, f in zip(ref_lists, b[3].tolist()) if f], 10)
