@@ -388,9 +388,10 @@ def main():
     ap.add_argument("--batch-prompts", type=int, default=4096, help="prompts per sub-batch (one sweep each)")
     ap.add_argument("--chunks", type=int, default=0, help="vocab chunks per lens launch (0 = auto)")
     ap.add_argument("--encode-cap", type=int, default=128)
-    ap.add_argument("--cluster-mode", type=int, default=2,
+    ap.add_argument("--cluster-mode", type=int, default=5,
                     help="lens kernel cluster: 0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs, 3 = 1x2 pairs, 4 = 2x2 pairs "
-                         "(TMA multicast of the shared operand slabs)")
+                         "(TMA multicast of the shared operand slabs), 5 = 2x1 preferred with plain pairs as fallback "
+                         "(all 148 SMs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="targeted", choices=["targeted", "random-control", "projection-vocab-shard"],
                     help="targeted = BASELINE configs[1] (the headline); the others are configs[2] and configs[3]")

@@ -137,7 +137,9 @@ int tb_rmsnorm(const void* x_bf16, const float* w_norm, float eps, int64_t n_row
  *   pti : i32 [n_parts, n_rows, 10]  (global vocab ids = vocab_offset + column)
  * secret_id: i32 [n_rows] global vocab id per row, or NULL. cta_pair selects the cluster shape:
  * 0 single CTAs, 1 CTA pairs (cta_group::2), 2 = 2x1 pairs (two row blocks share the W_U tiles
- * through TMA multicast), 3 = 1x2 pairs (two chunks share the row block), 4 = 2x2 pairs;
+ * through TMA multicast), 3 = 1x2 pairs (two chunks share the row block), 4 = 2x2 pairs,
+ * 5 = mode 2 as the PREFERRED cluster shape with plain pairs as the fallback (groups of four CTAs
+ * that do not fit a GPC as one cluster run as two pairs: all 148 SMs work; the default of ops.py);
  * n_chunks must be even in modes 3 and 4.
  */
 int tb_lens_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,

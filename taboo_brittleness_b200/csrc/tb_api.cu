@@ -17,7 +17,7 @@
 
 // Progress counters of the soft lockstep between clusters (tb_gemm.cuh): a few rotating slots of
 // 64 counters, so that launches in flight on different streams do not share one.
-static __device__ int g_cluster_progress[8][64];
+static __device__ int g_cluster_progress[8][128];
 
 namespace {
 
@@ -175,7 +175,7 @@ tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group,
   return g;
 }
 
-template <class Epi, int G, int R = 1, int C = 1>
+template <class Epi, int G, int R = 1, int C = 1, bool H = false>
 int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typename Epi::Params& ep,
                 cudaStream_t stream, int sms) {
   using Cfg = tb::GemmCfg<G>;
@@ -183,12 +183,16 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
   // every CTA loads 1/share of a slab (and multicasts it): the TMA box shrinks accordingly
   constexpr int kShareA = Epi::kSweepA ? R : C;
   constexpr int kShareB = Epi::kSweepA ? C : R;
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmS1;
   int rc = make_tmap(&tmA, a, g.M, g.K, tb::kBlockM / kShareA);
   if (rc != TB_OK) return rc;
   rc = make_tmap(&tmB, b, g.N, g.K, Cfg::kBRows / kShareB);
   if (rc != TB_OK) return rc;
-  auto kern = tb::tb_umma_gemm_kernel<Epi, G, R, C>;
+  // whole-slab boxes of the shared operand, for the groups that run as plain pairs (H only)
+  if (Epi::kSweepA) rc = make_tmap(&tmS1, a, g.M, g.K, tb::kBlockM);
+  else rc = make_tmap(&tmS1, b, g.N, g.K, Cfg::kBRows);
+  if (rc != TB_OK) return rc;
+  auto kern = tb::tb_umma_gemm_kernel<Epi, G, R, C, H>;
   constexpr int kSmem = Cfg::kSmemBytes + Epi::kExtraSmem;
   TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmem));
   cudaLaunchConfig_t cfg;
@@ -196,16 +200,21 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
   cfg.blockDim = dim3(tb::gemm_threads<Epi>(), 1, 1);
   cfg.dynamicSmemBytes = kSmem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = kClusterCtas;
+  attr[0].val.clusterDim.x = H ? G : kClusterCtas;   // H: pairs are the fallback ...
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributePreferredClusterDimension;   // ... clusters of pairs the preference
+  attr[1].val.clusterDim.x = kClusterCtas;
+  attr[1].val.clusterDim.y = 1;
+  attr[1].val.clusterDim.z = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  // co-resident clusters: sms / size for pairs, fewer for larger clusters (they must fit a GPC)
+  cfg.numAttrs = H ? 2 : 1;
+  // co-resident groups of kClusterCtas CTAs: sms / size for pairs and for preferred/fallback launches
+  // (what does not fit a GPC as one cluster runs as pairs); fewer for plain larger clusters
   int clusters = sms / kClusterCtas;
-  if (kClusterCtas > 2) {
+  if (kClusterCtas > 2 && !H) {
     static int cached[64];
     int dev = 0;
     TB_CUDA(cudaGetDevice(&dev));
@@ -222,26 +231,29 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
   if (g.max_clusters > 0 && clusters > g.max_clusters) clusters = g.max_clusters;
   cfg.gridDim = dim3(static_cast<unsigned>(clusters * kClusterCtas), 1, 1);
   tb::GemmArgs ga = g;
-  if (ga.lockstep > 0 && kClusterCtas > 2 && clusters <= 64 && clusters > 1) {
-    // progress counters: one of 8 rotating 64-counter slots of a static device array (no allocation;
+  const int pace_slots = clusters * kClusterCtas / G;
+  if (ga.lockstep > 0 && kClusterCtas > 2 && pace_slots <= 128 && clusters > 1) {
+    // progress counters: one of 8 rotating 128-counter slots of a static device array (no allocation;
     // up to 8 launches may be in flight on different streams before two of them share a slot, and
-    // sharing only costs pacing accuracy: every wait is bounded)
+    // sharing only costs pacing accuracy: every wait is bounded). They start "far ahead" (0x7f7f7f7f)
+    // so that a counter nobody publishes to never holds anybody back.
     static std::atomic<unsigned> slot{0};
     int* base = nullptr;
     TB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&base), g_cluster_progress));
-    ga.progress = base + 64 * (slot.fetch_add(1) & 7u);
-    TB_CUDA(cudaMemsetAsync(ga.progress, 0, 64 * sizeof(int), stream));
+    ga.progress = base + 128 * (slot.fetch_add(1) & 7u);
+    TB_CUDA(cudaMemsetAsync(ga.progress, 0x7f, 128 * sizeof(int), stream));
   } else {
     ga.lockstep = 0;
   }
-  TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, ga, ep));
+  TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, tmS1, ga, ep));
   return TB_OK;
 }
 
 // cluster shape of the lens kernels, selected by the cta_pair argument of the C ABI:
 //   0: single CTAs   1: CTA pairs   2: 2x1 pairs (two row blocks share W_U tiles)
 //   3: 1x2 pairs (two chunks share the row block)   4: 2x2 pairs (both)
-struct ClusterMode { int group, R, C; };
+//   5: 2x1 pairs as the PREFERRED cluster shape with plain pairs as fallback (all SMs busy)
+struct ClusterMode { int group, R, C; int hetero = 0; };
 int cluster_mode(int cta_pair, ClusterMode* m) {
   switch (cta_pair) {
     case 0: *m = {1, 1, 1}; return TB_OK;
@@ -249,8 +261,9 @@ int cluster_mode(int cta_pair, ClusterMode* m) {
     case 2: *m = {2, 2, 1}; return TB_OK;
     case 3: *m = {2, 1, 2}; return TB_OK;
     case 4: *m = {2, 2, 2}; return TB_OK;
+    case 5: *m = {2, 2, 1, 1}; return TB_OK;
   }
-  return fail(TB_ERR_INVALID, "cta_pair=%d: cluster mode must be 0..4", cta_pair);
+  return fail(TB_ERR_INVALID, "cta_pair=%d: cluster mode must be 0..5", cta_pair);
 }
 
 template <class Epi>
@@ -258,6 +271,7 @@ int launch_gemm_mode(const ClusterMode& m, const void* a, const void* b, const t
                      const typename Epi::Params& ep, cudaStream_t s, int sms) {
   if (m.group == 1) return launch_gemm<Epi, 1>(a, b, g, ep, s, sms);
   if (m.R == 1 && m.C == 1) return launch_gemm<Epi, 2, 1, 1>(a, b, g, ep, s, sms);
+  if (m.R == 2 && m.C == 1 && m.hetero) return launch_gemm<Epi, 2, 2, 1, true>(a, b, g, ep, s, sms);
   if (m.R == 2 && m.C == 1) return launch_gemm<Epi, 2, 2, 1>(a, b, g, ep, s, sms);
   if (m.R == 1 && m.C == 2) return launch_gemm<Epi, 2, 1, 2>(a, b, g, ep, s, sms);
   return launch_gemm<Epi, 2, 2, 2>(a, b, g, ep, s, sms);

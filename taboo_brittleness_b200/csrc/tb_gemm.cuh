@@ -92,10 +92,17 @@ __device__ __forceinline__ void epi_half_bar_sync(int half) {
   else asm volatile("bar.sync 3, 128;" ::: "memory");
 }
 
-template <class Epi, int kCtaGroup, int kR = 1, int kC = 1>
+// kHetero (2x1 clusters only): the grid is launched with cluster dimension 2 and PREFERRED cluster
+// dimension 4. A cluster of four CTAs must fit one GPC, which leaves 16 of a B200's 148 SMs out of
+// a pure 4-CTA grid; with the preferred / fallback pair the hardware forms 33 clusters of four and
+// runs the remaining 16 CTAs as 8 plain pairs. Blocks 4k..4k+3 are one *group* with one static
+// schedule: as a cluster of four its two pairs share the swept operand by multicast, as two
+// clusters of two each pair loads its own copy (whole-slab boxes: tmS1).
+template <class Epi, int kCtaGroup, int kR = 1, int kC = 1, bool kHetero = false>
 __global__ void __launch_bounds__(gemm_threads<Epi>(), 1)
 tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const GemmArgs g, const typename Epi::Params ep) {
+                    const __grid_constant__ CUtensorMap tmS1, const GemmArgs g, const typename Epi::Params ep) {
+  static_assert(!kHetero || (kCtaGroup == 2 && kR == 2 && kC == 1), "preferred/fallback clusters: 2x1 pairs only");
   using Cfg = GemmCfg<kCtaGroup>;
   constexpr int kStages = Cfg::kStages;
   // A cluster is kR x kC CTA pairs: pair (i, j) works on stationary block i and chunk j of the
@@ -128,7 +135,11 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int lane = static_cast<int>(lane_id());
   const uint32_t crank = (kClusterCtas > 1) ? cluster_ctarank() : 0u;  // rank in the cluster
   const uint32_t rank = crank & static_cast<uint32_t>(kCtaGroup - 1);   // half of the pair
-  const int pair = (kCtaGroup == 2) ? static_cast<int>(crank >> 1) : 0;
+  // did this group of kClusterCtas consecutive CTAs become ONE cluster (operands shared by multicast)?
+  const bool full_cluster = !kHetero || cluster_nctaid_x() == static_cast<uint32_t>(kClusterCtas);
+  // pair index within the group (= within the cluster when the group is one cluster)
+  const int pair = (kCtaGroup == 2) ? static_cast<int>((blockIdx.x % kClusterCtas) >> 1) : 0;
+  const int cpair = (kCtaGroup == 2) ? static_cast<int>(crank >> 1) : 0;   // pair index within the actual cluster
   const int pi = pair / kC, pj = pair % kC;
   const bool leader = (rank == 0);
   const int cluster_id = static_cast<int>(blockIdx.x) / kClusterCtas;
@@ -156,11 +167,12 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    if constexpr (kHetero) tma_prefetch_desc(&tmS1);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < kStages; ++i) {
       mbar_init(smem_u32(&full_bar[i]), 1);
-      mbar_init(smem_u32(&empty_bar[i]), kR + kC - 1);  // one commit per pair that reads what we write
+      mbar_init(smem_u32(&empty_bar[i]), full_cluster ? kR + kC - 1 : 1);  // one commit per pair that reads what we write
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tfull_bar[i]), 1);
@@ -187,13 +199,19 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int q = 0; q < kShareB; ++q)
           mask_b |= static_cast<uint16_t>(1u << (2 * (kSweepA ? pi * kC + q : q * kC + pj) + rank));
       }
-      const int piece_a = kSweepA ? pi : pj;  // which piece of the shared slab this CTA fetches
-      const int piece_b = kSweepA ? pj : pi;
+      const bool mc_a = kShareA > 1 && full_cluster, mc_b = kShareB > 1 && full_cluster;
+      const int piece_a = mc_a ? (kSweepA ? pi : pj) : 0;  // which piece of the shared slab this CTA fetches
+      const int piece_b = mc_b ? (kSweepA ? pj : pi) : 0;
+      // without a partner cluster-mate the whole slab comes through the whole-slab tensor map
+      const CUtensorMap* map_a = (kShareA > 1 && !full_cluster) ? &tmS1 : &tmA;
+      const CUtensorMap* map_b = (kShareB > 1 && !full_cluster) ? &tmS1 : &tmB;
       const bool ld_a = !(g.debug_skip & 1), ld_b = !(g.debug_skip & 2);
       int stage = 0;
       uint32_t phase = 0;
       int tiles_done = 0;
       const bool pace = g.lockstep > 0 && crank == 0 && g.progress != nullptr;
+      const int pace_id = static_cast<int>(blockIdx.x) / kCtaGroup;      // one counter per CTA pair slot
+      const int pace_n = static_cast<int>(gridDim.x) / kCtaGroup;
       for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
         int m_blk, chunk, t0, n_iter;
         decode(unit, m_blk, chunk, t0, n_iter);
@@ -201,12 +219,13 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const int nt = t0 + it;
           if (pace) {
             // publish my position, then wait (bounded) for the stragglers; the other CTAs of the
-            // cluster follow through the multicast dependencies
-            asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + cluster_id), "r"(tiles_done) : "memory");
+            // cluster follow through the multicast dependencies. Counters nobody publishes to keep
+            // their initial "far ahead" value.
+            asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + pace_id), "r"(tiles_done) : "memory");
             const long long t_start = clock64();
             for (;;) {
               int slowest = 0x7fffffff;
-              for (int c = 0; c < num_clusters; ++c) {
+              for (int c = 0; c < pace_n; ++c) {
                 int v;
                 asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(g.progress + c) : "memory");
                 slowest = min(slowest, v);
@@ -230,23 +249,23 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if constexpr (kCtaGroup == 2) {
               fb &= kPeerBitMask;  // every destination CTA signals its own pair leader's barrier
               if (ld_a) {
-                if constexpr (kShareA > 1) tma_load_2d_2sm_mcast(sa, &tmA, fb, kb * kBlockK, a_row, mask_a, g.policy_a);
-                else tma_load_2d_2sm_hint(sa, &tmA, fb, kb * kBlockK, a_row, g.policy_a);
+                if (mc_a) tma_load_2d_2sm_mcast(sa, map_a, fb, kb * kBlockK, a_row, mask_a, g.policy_a);
+                else tma_load_2d_2sm_hint(sa, map_a, fb, kb * kBlockK, a_row, g.policy_a);
               }
               if (ld_b) {
-                if constexpr (kShareB > 1) tma_load_2d_2sm_mcast(sb, &tmB, fb, kb * kBlockK, b_row, mask_b, g.policy_b);
-                else tma_load_2d_2sm_hint(sb, &tmB, fb, kb * kBlockK, b_row, g.policy_b);
+                if (mc_b) tma_load_2d_2sm_mcast(sb, map_b, fb, kb * kBlockK, b_row, mask_b, g.policy_b);
+                else tma_load_2d_2sm_hint(sb, map_b, fb, kb * kBlockK, b_row, g.policy_b);
               }
             } else {
-              if (ld_a) tma_load_2d_hint(sa, &tmA, fb, kb * kBlockK, a_row, g.policy_a);
-              if (ld_b) tma_load_2d_hint(sb, &tmB, fb, kb * kBlockK, b_row, g.policy_b);
+              if (ld_a) tma_load_2d_hint(sa, map_a, fb, kb * kBlockK, a_row, g.policy_a);
+              if (ld_b) tma_load_2d_hint(sb, map_b, fb, kb * kBlockK, b_row, g.policy_b);
             }
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
         }
       }
       if (pace)   // done: never hold anybody back again
-        asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + cluster_id), "r"(0x7fffffff) : "memory");
+        asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + pace_id), "r"(0x7fffffff) : "memory");
     }
     __syncwarp();
   } else if (warp == 1) {
@@ -258,7 +277,8 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       uint16_t mask_empty = 0;
       for (int q = 0; q < kC; ++q) mask_empty |= static_cast<uint16_t>(3u << (2 * (pi * kC + q)));
       for (int q = 0; q < kR; ++q) mask_empty |= static_cast<uint16_t>(3u << (2 * (q * kC + pj)));
-      const uint16_t mask_pair = static_cast<uint16_t>(3u << (2 * pair));
+      const uint16_t mask_pair = static_cast<uint16_t>(3u << (2 * cpair));
+      if (!full_cluster) mask_empty = mask_pair;   // a lone pair: nobody else writes into its stages
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_iter = 0;

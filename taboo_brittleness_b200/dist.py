@@ -114,7 +114,7 @@ def _kernel_merge(packed: torch.Tensor) -> ops.LensReadout:
 
 def lens_readout_vocab_sharded(h: torch.Tensor, lens_shard: ops.LensWeights, *, softcap: float = 0.0,
                                secret_id: Optional[torch.Tensor] = None, group=None,
-                               n_chunks: Optional[int] = None, cta_pair=2,
+                               n_chunks: Optional[int] = None, cta_pair=5,
                                partials_fn: Optional[Callable] = None, merge_fn: Optional[Callable] = None):
     """Lens readout with W_U split by rows across the ranks of ``group``.
 
@@ -129,7 +129,7 @@ def lens_readout_vocab_sharded(h: torch.Tensor, lens_shard: ops.LensWeights, *, 
 
 def ll_topk_vocab_sharded(h: torch.Tensor, lens_shard: ops.LensWeights, lse: torch.Tensor,
                           cur_id: Optional[torch.Tensor], prev_id: Optional[torch.Tensor], *, k: int = 10,
-                          softcap: float = 0.0, group=None, n_chunks: Optional[int] = None, cta_pair=2,
+                          softcap: float = 0.0, group=None, n_chunks: Optional[int] = None, cta_pair=5,
                           partials_fn: Optional[Callable] = None, merge_fn: Optional[Callable] = None):
     """LL-Top-k with W_U split across ranks: ``lse`` must be the full-vocabulary logsumexp (from
     ``lens_readout_vocab_sharded``); each rank reduces its shard to one sorted list of 10 per

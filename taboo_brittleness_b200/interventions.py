@@ -74,7 +74,7 @@ class InterventionEngine:
     """Holds one SAE + one lens (norm weight and unembedding shard) and runs sweeps over them."""
 
     def __init__(self, sae: ops.SaeWeights, lens: ops.LensWeights, *, softcap: float = ops.GEMMA2_SOFTCAP,
-                 cta_pair=2, n_chunks: Optional[int] = None, encode_cap: int = 128):
+                 cta_pair=5, n_chunks: Optional[int] = None, encode_cap: int = 128):
         self.sae, self.lens = sae, lens
         self.softcap, self.cta_pair, self.n_chunks, self.encode_cap = softcap, cta_pair, n_chunks, encode_cap
         self.stats = SweepStats()

@@ -376,16 +376,28 @@ class LensReadout:
 # cluster modes of the lens kernels (the ``cta_pair`` argument of the C ABI):
 #   0 single CTAs, 1 CTA pairs, 2 = 2x1 pairs (two row blocks share the W_U tiles through TMA
 #   multicast), 3 = 1x2 pairs (two chunks share the row block), 4 = 2x2 pairs (both)
-CLUSTER_MODES = {0: (1, 1, 1), 1: (2, 1, 1), 2: (2, 2, 1), 3: (2, 1, 2), 4: (2, 2, 2)}   # (group, R, C)
+#   5 = 2x1 pairs as the PREFERRED cluster shape with plain pairs as the fallback: groups of four CTAs that
+#   do not fit a GPC as one cluster run as two pairs, so all 148 SMs work (37 groups instead of 33 clusters)
+CLUSTER_MODES = {0: (1, 1, 1), 1: (2, 1, 1), 2: (2, 2, 1), 3: (2, 1, 2), 4: (2, 2, 2), 5: (2, 2, 1)}   # (group, R, C)
 # clusters that can be co-resident on a 148-SM B200 (cudaOccupancyMaxActiveClusters: a cluster must
 # fit one GPC, so sizes 4 and 8 leave SMs idle); only used to rank schedules here
 _B200_CLUSTERS = {1: 148, 2: 74, 4: 33, 6: 22, 8: 15}
 
 
+def _resident_groups(cta_pair, n_sms: int = 148) -> int:
+    """Co-resident clusters (mode 5: groups of four CTAs, whether they run as one cluster or two pairs)."""
+    m = _mode(cta_pair)
+    group, R, C = CLUSTER_MODES[m]
+    size = group * R * C
+    if m == 5:
+        return max(n_sms // size, 1)
+    return max(_B200_CLUSTERS.get(size, n_sms // size) * n_sms // 148, 1)
+
+
 def _mode(cta_pair) -> int:
     m = int(cta_pair)
     if m not in CLUSTER_MODES:
-        raise TabooKernelError(f"cluster mode {cta_pair!r} not in 0..4", _lib.TB_ERR_INVALID)
+        raise TabooKernelError(f"cluster mode {cta_pair!r} not in 0..5", _lib.TB_ERR_INVALID)
     return m
 
 
@@ -393,8 +405,7 @@ def pick_chunks(n_rows: int, V: int, n_sms: int = 148, cta_pair=False, *, sweep_
     """How many vocab chunks to sweep: fill all clusters with little tail waste while keeping the
     stationary blocks of the resident clusters (1.835 MB each at d=3584) a small part of L2."""
     group, R, C = CLUSTER_MODES[_mode(cta_pair)]
-    size = group * R * C
-    clusters = max(_B200_CLUSTERS.get(size, n_sms // size) * n_sms // 148, 1)
+    clusters = _resident_groups(cta_pair, n_sms)
     if sweep_a:
         blocks = -(-n_rows // BLOCK_N)
         n_tiles = -(-V // (BLOCK_M * group))
@@ -414,22 +425,22 @@ def pick_chunks(n_rows: int, V: int, n_sms: int = 148, cta_pair=False, *, sweep_
         cost *= 1.0 + 0.004 * c           # fewer chunks = more clusters per W_U stream = less DRAM traffic
         resident = min(blocks, -(-clusters // (c // C)) * R)
         mb = resident * (1.835 if (group == 2 or sweep_a) else 0.92)
-        if mb > 75.0:                     # stationary blocks of the resident clusters should stay in L2
+        if mb > 64.0:                     # stationary blocks of the resident clusters should stay in L2 (measured:
+                                          # 33 blocks = 61 MB are fine, 38 blocks = 70 MB cost 2 %)
             cost *= 1.5
         if best_cost is None or cost < best_cost:
             best, best_cost = c, cost
     return best or C
 
 
-def plan_row_splits(n_rows: int, V: int, cta_pair=2, *, sweep_a: bool = False, n_sms: int = 148):
+def plan_row_splits(n_rows: int, V: int, cta_pair=5, *, sweep_a: bool = False, n_sms: int = 148):
     """[(row_start, row_stop, n_chunks), ...] for one lens sweep. The kernels hand out (row group, chunk)
     units round-robin to the resident clusters; when the unit count is just above a whole number of
     waves (e.g. 2048 units on 33 clusters = 62.06 waves) the last wave keeps two clusters busy for a
     full chunk while 31 idle. The row groups of that ragged wave are then swept in a second launch
     with many short chunks, one unit per cluster; partials of different chunkings merge as usual."""
     group, R, C = CLUSTER_MODES[_mode(cta_pair)]
-    size = group * R * C
-    clusters = max(_B200_CLUSTERS.get(size, n_sms // size) * n_sms // 148, 1)
+    clusters = _resident_groups(cta_pair, n_sms)
     c = pick_chunks(n_rows, V, n_sms, cta_pair, sweep_a=sweep_a)
     rows_per_group = BLOCK_N * R if sweep_a else BLOCK_M * group * R
     groups = -(-n_rows // rows_per_group)
@@ -474,7 +485,7 @@ def _alloc_partials(n_chunks: int, n: int, dev) -> "LensPartials":
 
 def lens_partials(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0,
                   secret_id: Optional[torch.Tensor] = None, vocab_offset: int = 0,
-                  n_chunks: Optional[int] = None, cta_pair=2) -> LensPartials:
+                  n_chunks: Optional[int] = None, cta_pair=5) -> LensPartials:
     _need(h, torch.bfloat16, "h", 2)
     _need(w_u, torch.bfloat16, "w_u", 2)
     n, d = h.shape
@@ -529,7 +540,7 @@ def lens_merge(p: LensPartials, finalize: bool = True):
 
 def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,
                secret_id: Optional[torch.Tensor] = None, n_chunks: Optional[int] = None,
-               cta_pair=2, prenormed: bool = False) -> LensReadout:
+               cta_pair=5, prenormed: bool = False) -> LensReadout:
     """norm -> lm_head -> softmax readouts of models.py:135-138 without the [rows, V] tensor.
 
     x: bf16 residual rows (or the already normalised operand h when ``prenormed``).
@@ -547,7 +558,7 @@ LL_SLOTS = 128             # row slots per prompt in the K5 kernel
 LL_MAX_CHUNK_IDS = 65536   # vocabulary ids one chunk may span (mask bitmap)
 
 
-def pick_chunks_ll(n_rows: int, V: int, n_sms: int = 148, cta_pair=2) -> int:
+def pick_chunks_ll(n_rows: int, V: int, n_sms: int = 148, cta_pair=5) -> int:
     """Vocab chunks for the K5 sweep (bitmap limit as a floor on the count)."""
     return pick_chunks(n_rows, V, n_sms, cta_pair, sweep_a=True)
 
@@ -570,7 +581,7 @@ def pad_prompt_rows(t: torch.Tensor, seg: torch.Tensor, fill) -> torch.Tensor:
 
 def ll_topk(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, cur_id: Optional[torch.Tensor] = None,
             prev_id: Optional[torch.Tensor] = None, *, k: int = TB_TOPK, softcap: float = 0.0,
-            vocab_offset: int = 0, n_chunks: Optional[int] = None, cta_pair=2,
+            vocab_offset: int = 0, n_chunks: Optional[int] = None, cta_pair=5,
             finalize: bool = True):
     """LL-Top-k per prompt (01_reproduce_logit_lens.py:35-71, 147-149) on rows laid out 128 slots
     per prompt (``pad_prompt_rows``): h bf16 [P*128, d] normalised operand, lse f32 [P*128] from the
@@ -634,7 +645,7 @@ def ll_topk_merge(pv: torch.Tensor, pi: torch.Tensor, *, k: int = TB_TOPK, final
 def lens_ll_partials(h: torch.Tensor, w_u: torch.Tensor, ref_lse: torch.Tensor, tau: torch.Tensor,
                      cur_id: Optional[torch.Tensor] = None, prev_id: Optional[torch.Tensor] = None, *,
                      softcap: float = 0.0, secret_id: Optional[torch.Tensor] = None, vocab_offset: int = 0,
-                     n_chunks: Optional[int] = None, cta_pair=2, cand_cap: int = 256):
+                     n_chunks: Optional[int] = None, cta_pair=5, cand_cap: int = 256):
     """K3 readout partials with ``ref_lse`` as the softmax reference, plus per prompt (128 row slots)
     the ids whose masked column sum of exp(logit - ref_lse) reaches ``tau`` [P].
     Returns (LensPartials, cand_count i32 [P], cand_id i32 [P, cand_cap])."""

@@ -85,7 +85,7 @@ def test_lens_gemma_shapes_full_vocab(cuda_lib, softcap):
     _check(out, x, lens, sid, softcap, x.shape[0])
 
 
-@pytest.mark.parametrize("mode", [2, 3, 4])
+@pytest.mark.parametrize("mode", [2, 3, 4, 5])
 @pytest.mark.parametrize("shape", [(3, 64, 512, 8192, 4), (5, 128, 264, 4800, 4), (9, 128, 512, 8192, 2)])
 def test_lens_multicast_clusters(cuda_lib, mode, shape):
     """2x1 / 1x2 / 2x2 clusters of CTA pairs (TMA multicast of the shared operand slabs) give the

@@ -24,7 +24,7 @@ def _setup(P, d, V, seed, softcap):
     return h, w_u, sid.cuda(), cur.cuda(), prev.cuda(), plain, ref_lists
 
 
-@pytest.mark.parametrize("mode", [1, 4])
+@pytest.mark.parametrize("mode", [1, 4, 5])
 @pytest.mark.parametrize("softcap", [None, 30.0])
 @pytest.mark.parametrize("noise", [0.0, 0.3])
 def test_fused_sweep_readouts_and_certified_topk(cuda_lib, mode, softcap, noise):
@@ -149,7 +149,7 @@ def test_row_splits_with_different_chunkings_give_the_same_readouts(cuda_lib, mo
     one = ops.lens_merge(ops.lens_partials(h, w_u, softcap=30.0, secret_id=sid, n_chunks=2))
     p1, c1, i1 = ops.lens_ll_partials(h, w_u, plain.lse, tau, cur, prev, softcap=30.0, secret_id=sid, n_chunks=2)
     v1, id1 = ops.ll_topk(h, w_u, plain.lse, cur, prev, softcap=30.0, n_chunks=2)
-    monkeypatch.setattr(ops, "plan_row_splits", lambda n, V_, mode=2, **kw: [(0, 256, 2), (256, n, 4)])
+    monkeypatch.setattr(ops, "plan_row_splits", lambda n, V_, mode=5, **kw: [(0, 256, 2), (256, n, 4)])
     two = ops.lens_merge(ops.lens_partials(h, w_u, softcap=30.0, secret_id=sid))
     p2, c2, i2 = ops.lens_ll_partials(h, w_u, plain.lse, tau, cur, prev, softcap=30.0, secret_id=sid)
     v2, id2 = ops.ll_topk(h, w_u, plain.lse, cur, prev, softcap=30.0)

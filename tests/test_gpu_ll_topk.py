@@ -103,7 +103,7 @@ def test_ll_topk_small(cuda_lib, softcap, pair, chunks):
     assert n_tie <= 1
 
 
-@pytest.mark.parametrize("mode", [2, 3, 4])
+@pytest.mark.parametrize("mode", [2, 3, 4, 5])
 def test_ll_topk_multicast_clusters(cuda_lib, mode):
     """Cluster modes of the K5 sweep: 5 prompts = 3 blocks of 256 row slots (odd), V = 4800."""
     x, lens, _ = _problem(5, 128, 264, 4800, seed=6)

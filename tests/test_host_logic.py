@@ -118,7 +118,7 @@ def test_plan_row_splits_cover_rows_with_valid_chunkings():
     kernels accept (non-empty chunks, multiple of the cluster's chunk dimension, K5 bitmap limit)."""
     from taboo_brittleness_b200 import ops
     V = 256000
-    for mode in range(5):
+    for mode in range(6):
         group, R, C = ops.CLUSTER_MODES[mode]
         for sweep_a in (False, True):
             for n in (128, 256, 37888, 75776, 131072, 262144, 524288, 524288 + 256):
