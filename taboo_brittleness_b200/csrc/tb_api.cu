@@ -926,3 +926,14 @@ int tb_logit_lens_static(const void* h, const void* w_u, int64_t n_rows, int d, 
 }
 
 }  // extern "C"
+
+#ifdef TB_WAIT_PROFILE
+// Probe build only: read and clear the per-CTA wait counters of tb_gemm.cuh (256 x 8 cycle counts).
+extern "C" int tb_debug_wait_profile(long long* out_host) {
+  TB_CUDA(cudaDeviceSynchronize());
+  TB_CUDA(cudaMemcpyFromSymbol(out_host, tb::g_wait_prof, sizeof(long long) * 256 * 8));
+  static long long zeros[256 * 8];
+  TB_CUDA(cudaMemcpyToSymbol(tb::g_wait_prof, zeros, sizeof(zeros)));
+  return TB_OK;
+}
+#endif

@@ -45,7 +45,8 @@ struct GemmArgs {
   int m_blocks;         // stationary blocks: ceil(M / (128 * kCtaGroup)), or ceil(N / 256)
   int total_units;      // m_blocks * n_chunks
   unsigned long long policy_a, policy_b;  // L2 eviction policy of the A / B tile loads
-  int debug_skip;       // experiments only: bit 0 = do not load A, bit 1 = do not load B (results are garbage)
+  int debug_skip;       // experiments only (results are garbage): bit 0 = do not load A, bit 1 = do not load B,
+                        // bit 2 = plain row-owner epilogues skip their arithmetic, bit 3 = and the accumulator read
   // Soft lockstep between clusters (0 = off): a cluster does not start loading a tile while it is
   // more than `lockstep` tiles ahead of the slowest cluster of the launch. Clusters that sweep
   // the same chunk then read every swept tile within a few tile-times of each other, which is
@@ -98,6 +99,23 @@ __device__ __forceinline__ void epi_half_bar_sync(int half) {
 // runs the remaining 16 CTAs as 8 plain pairs. Blocks 4k..4k+3 are one *group* with one static
 // schedule: as a cluster of four its two pairs share the swept operand by multicast, as two
 // clusters of two each pair loads its own copy (whole-slab boxes: tmS1).
+#ifdef TB_WAIT_PROFILE
+// Probe build only (scripts/wait_profile.py): cycles each role of a CTA spends waiting, per CTA:
+// [0] producer: lockstep pacing  [1] producer: empty stage  [2] producer: total
+// [3] MMA issuer: accumulator drained  [4] MMA issuer: full stage  [5] MMA issuer: total
+// [6] epilogue warp 4: accumulator ready  [7] epilogue warp 4: total
+static __device__ long long g_wait_prof[256][8];
+#define TB_PROF_DECL(x) long long x = 0
+#define TB_PROF_T0(t) const long long t = clock64()
+#define TB_PROF_ADD(acc, t) acc += clock64() - t
+#define TB_PROF_OUT(i, v) g_wait_prof[blockIdx.x & 255][i] += (v)
+#else
+#define TB_PROF_DECL(x)
+#define TB_PROF_T0(t)
+#define TB_PROF_ADD(acc, t)
+#define TB_PROF_OUT(i, v)
+#endif
+
 template <class Epi, int kCtaGroup, int kR = 1, int kC = 1, bool kHetero = false>
 __global__ void __launch_bounds__(gemm_threads<Epi>(), 1)
 tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -129,6 +147,8 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tfull_bar = bars + 2 * kStages;       // [2] MMA -> epilogue (each CTA)
   uint64_t* tempty_bar = bars + 2 * kStages + 2;  // [2] epilogue -> MMA (leader CTA's are used)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  volatile int* pace_slowest = reinterpret_cast<volatile int*>(tmem_slot + 1);  // written by the pacer warp
+  volatile int* pace_done = pace_slowest + 1;                                   // written by the producer
   uint8_t* epi_extra = smem + kStages * Cfg::kStageBytes + Cfg::kBarBytes;
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
@@ -178,6 +198,8 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       mbar_init(smem_u32(&tfull_bar[i]), 1);
       mbar_init(smem_u32(&tempty_bar[i]), Epi::kEpiWarps * kCtaGroup);  // one arrive per epilogue warp
     }
+    *pace_slowest = 0;
+    *pace_done = 0;
     fence_mbar_init();
   }
   if (warp == 2) {
@@ -190,7 +212,8 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    // (whole warp walks the schedule, one elected lane issues: see the MMA issuer)
+    {
       // multicast destinations: same half (rank) of the pairs that share the slab
       uint16_t mask_a = 0, mask_b = 0;
       if constexpr (kMcast) {
@@ -206,71 +229,84 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const CUtensorMap* map_a = (kShareA > 1 && !full_cluster) ? &tmS1 : &tmA;
       const CUtensorMap* map_b = (kShareB > 1 && !full_cluster) ? &tmS1 : &tmB;
       const bool ld_a = !(g.debug_skip & 1), ld_b = !(g.debug_skip & 2);
+      const uint32_t smem0 = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+      const uint32_t bars0 = __shfl_sync(0xffffffffu, smem_u32(bars), 0);
+      const uint32_t tx_bytes = ((ld_a ? Cfg::kABytes : 0) + (ld_b ? Cfg::kBBytes : 0)) * kCtaGroup;
       int stage = 0;
       uint32_t phase = 0;
       int tiles_done = 0;
       const bool pace = g.lockstep > 0 && crank == 0 && g.progress != nullptr;
       const int pace_id = static_cast<int>(blockIdx.x) / kCtaGroup;      // one counter per CTA pair slot
-      const int pace_n = static_cast<int>(gridDim.x) / kCtaGroup;
+      TB_PROF_DECL(w_pace); TB_PROF_DECL(w_empty); TB_PROF_T0(p_start);
       for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
         int m_blk, chunk, t0, n_iter;
         decode(unit, m_blk, chunk, t0, n_iter);
         for (int it = 0; it < n_iter; ++it, ++tiles_done) {
           const int nt = t0 + it;
+          TB_PROF_T0(p_pace);
           if (pace) {
             // publish my position, then wait (bounded) for the stragglers; the other CTAs of the
-            // cluster follow through the multicast dependencies. Counters nobody publishes to keep
-            // their initial "far ahead" value.
-            asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + pace_id), "r"(tiles_done) : "memory");
-            const long long t_start = clock64();
-            for (;;) {
-              int slowest = 0x7fffffff;
-              for (int c = 0; c < pace_n; ++c) {
-                int v;
-                asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(g.progress + c) : "memory");
-                slowest = min(slowest, v);
-              }
-              if (tiles_done <= slowest + g.lockstep || clock64() - t_start > 400000ll) break;
+            // cluster follow through the multicast dependencies. The counters are polled by the pacer
+            // warp (below), not here: a round over them costs a microsecond of L2 latency, which
+            // would otherwise sit between a free stage and its refill once per tile.
+            if (lane == 0)
+              asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + pace_id), "r"(tiles_done) : "memory");
+            if (tiles_done > *pace_slowest + g.lockstep) {
+              const long long t_start = clock64();
+              while (tiles_done > *pace_slowest + g.lockstep && clock64() - t_start < 400000ll) {}
             }
+            __syncwarp();
           }
+          TB_PROF_ADD(w_pace, p_pace);
           // stationary block / swept tile -> operand rows (sweep-A swaps the roles)
           const int a_row = (kSweepA ? nt : m_blk) * (kBlockM * kCtaGroup) + static_cast<int>(rank) * kBlockM +
                             piece_a * kPieceARows;
           const int b_row = (kSweepA ? m_blk : nt) * kBlockN + static_cast<int>(rank) * Cfg::kBRows +
                             piece_b * kPieceBRows;
           for (int kb = 0; kb < num_kb; ++kb) {
-            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1u);
-            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes) + piece_a * kPieceARows * (kBlockK * 2);
-            const uint32_t sb = smem_u32(smem + stage * Cfg::kStageBytes) + Cfg::kABytes +
-                                piece_b * kPieceBRows * (kBlockK * 2);
-            uint32_t fb = smem_u32(&full_bar[stage]);
-            if (leader)
-              mbar_arrive_expect_tx(fb, ((ld_a ? Cfg::kABytes : 0) + (ld_b ? Cfg::kBBytes : 0)) * kCtaGroup);
-            if constexpr (kCtaGroup == 2) {
-              fb &= kPeerBitMask;  // every destination CTA signals its own pair leader's barrier
-              if (ld_a) {
-                if (mc_a) tma_load_2d_2sm_mcast(sa, map_a, fb, kb * kBlockK, a_row, mask_a, g.policy_a);
-                else tma_load_2d_2sm_hint(sa, map_a, fb, kb * kBlockK, a_row, g.policy_a);
+            TB_PROF_T0(p_e);
+            mbar_wait(bars0 + 8u * (kStages + stage), phase ^ 1u);
+            TB_PROF_ADD(w_empty, p_e);
+            if (elect_one()) {
+              const uint32_t sa = smem0 + stage * Cfg::kStageBytes + piece_a * kPieceARows * (kBlockK * 2);
+              const uint32_t sb = smem0 + stage * Cfg::kStageBytes + Cfg::kABytes + piece_b * kPieceBRows * (kBlockK * 2);
+              uint32_t fb = bars0 + 8u * stage;
+              if (leader) mbar_arrive_expect_tx(fb, tx_bytes);
+              if constexpr (kCtaGroup == 2) {
+                fb &= kPeerBitMask;  // every destination CTA signals its own pair leader's barrier
+                if (ld_a) {
+                  if (mc_a) tma_load_2d_2sm_mcast(sa, map_a, fb, kb * kBlockK, a_row, mask_a, g.policy_a);
+                  else tma_load_2d_2sm_hint(sa, map_a, fb, kb * kBlockK, a_row, g.policy_a);
+                }
+                if (ld_b) {
+                  if (mc_b) tma_load_2d_2sm_mcast(sb, map_b, fb, kb * kBlockK, b_row, mask_b, g.policy_b);
+                  else tma_load_2d_2sm_hint(sb, map_b, fb, kb * kBlockK, b_row, g.policy_b);
+                }
+              } else {
+                if (ld_a) tma_load_2d_hint(sa, map_a, fb, kb * kBlockK, a_row, g.policy_a);
+                if (ld_b) tma_load_2d_hint(sb, map_b, fb, kb * kBlockK, b_row, g.policy_b);
               }
-              if (ld_b) {
-                if (mc_b) tma_load_2d_2sm_mcast(sb, map_b, fb, kb * kBlockK, b_row, mask_b, g.policy_b);
-                else tma_load_2d_2sm_hint(sb, map_b, fb, kb * kBlockK, b_row, g.policy_b);
-              }
-            } else {
-              if (ld_a) tma_load_2d_hint(sa, map_a, fb, kb * kBlockK, a_row, g.policy_a);
-              if (ld_b) tma_load_2d_hint(sb, map_b, fb, kb * kBlockK, b_row, g.policy_b);
             }
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
         }
       }
-      if (pace)   // done: never hold anybody back again
-        asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + pace_id), "r"(0x7fffffff) : "memory");
+      if (lane == 0) {
+        if (pace)   // done: never hold anybody back again
+          asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(g.progress + pace_id), "r"(0x7fffffff) : "memory");
+        *pace_done = 1;
+        TB_PROF_OUT(0, w_pace); TB_PROF_OUT(1, w_empty); TB_PROF_OUT(2, clock64() - p_start);
+      }
     }
     __syncwarp();
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (leader && lane == 0) {
+    // The whole warp walks the schedule and waits on the barriers; one elected lane issues. (A branch
+    // that only lane 0 enters makes the compiler wrap every uniform-register operand of the MMA and
+    // commit instructions in a per-lane loop: ~100 instructions per k-block on a scheduler this warp
+    // shares with two epilogue warps -- measured: 8 % of the tensor pipe's cycles.)
+    if (leader) {
       constexpr uint32_t idesc = umma_idesc_bf16_f32(kBlockM * kCtaGroup, kBlockN);
       // who must learn that a stage of this pair's smem is free again: every CTA that writes into
       // it = both halves of the pairs in this pair's row and column of the cluster
@@ -279,41 +315,74 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       for (int q = 0; q < kR; ++q) mask_empty |= static_cast<uint16_t>(3u << (2 * (q * kC + pj)));
       const uint16_t mask_pair = static_cast<uint16_t>(3u << (2 * cpair));
       if (!full_cluster) mask_empty = mask_pair;   // a lone pair: nobody else writes into its stages
+      const uint32_t smem0 = __shfl_sync(0xffffffffu, smem_u32(smem), 0);
+      const uint32_t tmem0 = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t bars0 = __shfl_sync(0xffffffffu, smem_u32(bars), 0);
       int stage = 0;
       uint32_t phase = 0;
       uint32_t acc_iter = 0;
+      TB_PROF_DECL(w_acc); TB_PROF_DECL(w_full); TB_PROF_T0(m_start);
       for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
         int m_blk, chunk, t0, n_iter;
         decode(unit, m_blk, chunk, t0, n_iter);
         for (int it = 0; it < n_iter; ++it, ++acc_iter) {
           const uint32_t acc = acc_iter & 1u;
           const uint32_t acc_phase = (acc_iter >> 1) & 1u;
-          mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1u);  // epilogue drained this accumulator
+          TB_PROF_T0(m_a);
+          mbar_wait(bars0 + 8u * (2 * kStages + 2 + acc), acc_phase ^ 1u);  // epilogue drained this accumulator
+          TB_PROF_ADD(w_acc, m_a);
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + acc * kBlockN;
+          const uint32_t d_tmem = tmem0 + acc * kBlockN;
           for (int kb = 0; kb < num_kb; ++kb) {
-            mbar_wait(smem_u32(&full_bar[stage]), phase);
+            TB_PROF_T0(m_f);
+            mbar_wait(bars0 + 8u * stage, phase);
+            TB_PROF_ADD(w_full, m_f);
             tc_fence_after();
-            const uint32_t sa = smem_u32(smem + stage * Cfg::kStageBytes);
-            const uint32_t sb = sa + Cfg::kABytes;
+            // descriptors of the stage's first k-step; +32 bytes (2 units of 16) per UMMA_K inside the
+            // 128-byte swizzle span
+            const uint64_t da = umma_desc_k_sw128(smem0 + stage * Cfg::kStageBytes);
+            const uint64_t db = umma_desc_k_sw128(smem0 + stage * Cfg::kStageBytes + Cfg::kABytes);
+            if (elect_one()) {
 #pragma unroll
-            for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-              // advance along K inside the 128-byte swizzle span: +32 bytes per UMMA_K
-              const uint64_t da = umma_desc_k_sw128(sa + k * kUmmaK * 2);
-              const uint64_t db = umma_desc_k_sw128(sb + k * kUmmaK * 2);
-              umma_bf16<kCtaGroup>(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < kBlockK / kUmmaK; ++k)
+                umma_bf16<kCtaGroup>(d_tmem, da + static_cast<uint64_t>(k * (kUmmaK * 2 / 16)),
+                                     db + static_cast<uint64_t>(k * (kUmmaK * 2 / 16)), idesc, (kb | k) != 0 ? 1u : 0u);
+              // frees the smem slot once these MMAs have read it
+              if constexpr (kCtaGroup == 2) umma_commit_2sm(bars0 + 8u * (kStages + stage), mask_empty);
+              else umma_commit(bars0 + 8u * (kStages + stage));
+              if (kb == num_kb - 1) {
+                if constexpr (kCtaGroup == 2) umma_commit_2sm(bars0 + 8u * (2 * kStages + acc), mask_pair);
+                else umma_commit(bars0 + 8u * (2 * kStages + acc));
+              }
             }
-            // frees the smem slot once these MMAs have read it
-            if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&empty_bar[stage]), mask_empty);
-            else umma_commit(smem_u32(&empty_bar[stage]));
+            __syncwarp();
             if (++stage == kStages) { stage = 0; phase ^= 1u; }
           }
-          if constexpr (kCtaGroup == 2) umma_commit_2sm(smem_u32(&tfull_bar[acc]), mask_pair);
-          else umma_commit(smem_u32(&tfull_bar[acc]));
         }
       }
+      if (lane == 0) { TB_PROF_OUT(3, w_acc); TB_PROF_OUT(4, w_full); TB_PROF_OUT(5, clock64() - m_start); }
     }
     __syncwarp();
+  } else if (warp == 3) {
+    // ================================ pacer ================================
+    // Keeps the slowest group's tile count of the launch in shared memory for the producer. Counters
+    // only grow (groups that are done, and slots nobody uses, read "far ahead"), so a stale value
+    // is merely conservative.
+    if (g.lockstep > 0 && crank == 0 && g.progress != nullptr) {
+      const int pace_n = static_cast<int>(gridDim.x) / kCtaGroup;
+      while (*pace_done == 0) {
+        int v = 0x7fffffff;
+        for (int c = lane; c < pace_n; c += 32) {
+          int t;
+          asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(t) : "l"(g.progress + c) : "memory");
+          v = min(v, t);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+        if (lane == 0) *pace_slowest = v;
+        __nanosleep(100);
+      }
+    }
   } else if (warp >= kEpiWarp0) {
     // ================================ epilogue ================================
     constexpr int kHalves = Epi::kEpiWarps / 4;           // warp groups per TMEM lane quadrant
@@ -324,6 +393,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
     uint32_t acc_iter = 0;
     typename Epi::State st;
+    TB_PROF_DECL(w_ready); TB_PROF_T0(e_start);
     for (int unit = cluster_id; unit < g.total_units; unit += num_clusters) {
       int m_blk, chunk, t0, n_iter;
       decode(unit, m_blk, chunk, t0, n_iter);
@@ -344,7 +414,9 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int nt = t0 + it;
         const uint32_t acc = acc_iter & 1u;
         const uint32_t acc_phase = (acc_iter >> 1) & 1u;
+        TB_PROF_T0(e_r);
         mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
+        TB_PROF_ADD(w_ready, e_r);
         tc_fence_after();
         if constexpr (kSweepA) {
           Epi::process_tile_sw(st, ep, g, ctx, nt, tmem_base + lane_base + acc * kBlockN);
@@ -355,9 +427,14 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll 1
           for (int c = half * kGroupsPerHalf; c < (half + 1) * kGroupsPerHalf; ++c) {
             uint32_t v[32];
-            tmem_ld_32x32(tmem_base + lane_base + acc * kBlockN + c * 32, v);
-            tmem_ld_wait();
-            Epi::process(st, ep, g, v, row, nt * kBlockN + c * 32);
+            if (g.debug_skip & 8) {   // experiments only: no accumulator read
+#pragma unroll
+              for (int i = 0; i < 32; ++i) v[i] = 0u;
+            } else {
+              tmem_ld_32x32(tmem_base + lane_base + acc * kBlockN + c * 32, v);
+              tmem_ld_wait();
+            }
+            if (!(g.debug_skip & 4)) Epi::process(st, ep, g, v, row, nt * kBlockN + c * 32);
           }
         }
         tc_fence_before();
@@ -372,6 +449,9 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       else if constexpr (Epi::kTileHooks) Epi::end_unit_tile(st, ep, g, ctx, row);
       else Epi::end_unit(st, ep, g, row, part);
     }
+#ifdef TB_WAIT_PROFILE
+    if (warp == kEpiWarp0 && lane == 0) { TB_PROF_OUT(6, w_ready); TB_PROF_OUT(7, clock64() - e_start); }
+#endif
   }
 
   // teardown: everybody done with TMEM before it is released
