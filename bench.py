@@ -361,6 +361,10 @@ def run_native(args, rank, local_rank, world):
                              "whole_step_tflops": (n_rows * ((0.0 if proj else FLOP_ENC) + conditions * FLOP_LENS /
                                                              (world if proj else 1))) / (ms_step * 1e-3) / 1e12},
                 "clocks": clocks}
+        if line["roofline"]["frac"] > 1.0:
+            line["roofline"]["note"] = ("peak = cuBLAS bf16 sustained under this board's power cap (MEASURED_PEAKS.json); "
+                                        "a fraction above 1 means the kernel sustains more than cuBLAS does under the same "
+                                        "cap -- frac_of_burst_peak is against the short-run cuBLAS figure")
         if args.ll_topk:
             line["ll_topk"] = {"k": 10, "one_sweep_prompt_conditions": eng.stats.ll_fused_prompts,
                                "redone_with_second_sweep": eng.stats.ll_fallback_prompts,

@@ -189,9 +189,13 @@ class InterventionEngine:
             return self.read_fused(h, secret_id, ll, ll_state)
         return self.read(h, secret_id, finalize, ll)
 
-    def project_and_read(self, x, U, *, secret_id=None, finalize: bool = True, ll: Optional[LLSpec] = None):
+    def project_and_read(self, x, U, *, secret_id=None, finalize: bool = True, ll: Optional[LLSpec] = None,
+                         ll_state: Optional[LLState] = None):
+        """With ``ll_state`` (from the previous, smaller rank) returns (Readout, next LLState)."""
         _, h = ops.lowrank_remove(x, U, w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False, want_h=True)
         self.stats.launches += 1
+        if ll_state is not None:
+            return self.read_fused(h, secret_id, ll, ll_state)
         return self.read(h, secret_id, finalize, ll)
 
     # ---- sweeps -----------------------------------------------------------------------------------
@@ -349,5 +353,17 @@ class InterventionEngine:
     def projection_sweep(self, x: torch.Tensor, U: torch.Tensor, secret_id,
                          ranks: Sequence[int] = DEFAULT_RANKS, ll: Optional[LLSpec] = None
                          ) -> Dict[int, ops.LensReadout]:
-        """BASELINE.json configs[3]: remove the first r columns of U for each r."""
-        return {int(r): self.project_and_read(x, U[:, :r].contiguous(), secret_id=secret_id, ll=ll) for r in ranks}
+        """BASELINE.json configs[3]: remove the first r columns of U for each r. The ranks are nested
+        subspaces, so with LL-Top-k every rank after the first reads in one sweep with the previous rank's
+        exact lse as reference (like nested ablation budgets; results are exact either way)."""
+        fusable = (ll is not None and self.ll_fused and ll.seg is None and ll.rows_per_prompt == ops.LL_SLOTS)
+        out, state = {}, None
+        for r in sorted(int(v) for v in ranks):
+            Ur = U[:, :r].contiguous()
+            if fusable and state is not None:
+                out[r], state = self.project_and_read(x, Ur, secret_id=secret_id, ll=ll, ll_state=state)
+            else:
+                out[r] = self.project_and_read(x, Ur, secret_id=secret_id, ll=ll)
+                if fusable:
+                    state = LLState(out[r].lens.lse, out[r].ll_sum[:, ll.k - 1].contiguous())
+        return out

@@ -60,6 +60,41 @@ def test_projection_sweep(setup):
         _check_readout(res[r], x1, lens, sid)
 
 
+def test_projection_sweep_ll_topk_chained_over_ranks(cuda_lib):
+    """With LL-Top-k and the 128-row layout, every rank after the first reads in ONE sweep (previous rank's
+    lse as reference). The lists must equal those of the two-sweep path, rank by rank."""
+    from taboo_brittleness_b200 import interventions, ops
+    p_, t_, d_, v_ = 4, 128, 512, 8192
+    x = synthetic.make_residuals(p_, t_, d_, seed=41)
+    lens = synthetic.make_lens(d_, v_, seed=41)
+    sid = synthetic.make_secret_ids(p_, t_, v_, seed=41)
+    synthetic.plant_secret_direction(lens, x, sid)
+    sae = synthetic.make_sae(d_, 1024, seed=41, target_l0=20.0)
+    U = synthetic.bf16_exact(oracle.random_orthonormal(d_, 16, seed=4))
+    g = torch.Generator().manual_seed(41)
+    cur = torch.randint(0, v_, (p_ * t_,), generator=g, dtype=torch.int32).cuda()
+    ll = interventions.LLSpec(cur, None, rows_per_prompt=t_, k=10)
+    def mk(fused):
+        e = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                             softcap=30.0)
+        e.ll_fused = fused
+        return e
+    ranks = [1, 4, 16]
+    e1, e2 = mk(True), mk(False)
+    one = e1.projection_sweep(cuda_bf16(x), cuda_bf16(U), sid.cuda(), ranks, ll=ll)
+    two = e2.projection_sweep(cuda_bf16(x), cuda_bf16(U), sid.cuda(), ranks, ll=ll)
+    torch.cuda.synchronize()
+    assert e1.stats.ll_fused_prompts == 2 * p_ and e2.stats.ll_fused_prompts == 0
+    for r in ranks:
+        assert torch.allclose(one[r].lens.lse, two[r].lens.lse, atol=2e-4)
+        assert torch.equal(one[r].top_id, two[r].top_id)
+        same = (one[r].ll_id.sort(1).values == two[r].ll_id.sort(1).values).all(1)
+        for q in torch.nonzero(~same).flatten().tolist():      # only near-ties of the 10th sum may differ
+            a, b = one[r].ll_sum[q], two[r].ll_sum[q]
+            assert abs(float(a[9] - b[9])) <= 2e-3 * float(b[9])
+        assert torch.allclose(one[r].ll_sum[:, 0], two[r].ll_sum[:, 0], rtol=2e-3)
+
+
 def test_projection_removes_the_planted_secret(setup):
     """Removing the direction that carries a prompt's secret drops its secret probability (the point
     of the intervention), and the kernel reports the same drop as the oracle."""
