@@ -117,6 +117,17 @@ int tb_lowrank_apply(const void* x_bf16, const void* ut_bf16, const float* c, in
                      int d, const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
                      void* stream);
 
+/* K2 for ranks 9..64 on the tensor cores, one call: C = x U (tcgen05, fp32 accumulate), the
+ * coefficients split into bf16 head + remainder, x' = bf16(x - [C_hi | C_lo] [U | U]^T) in the epilogue
+ * of a second tcgen05 pass (K = 2 * ceil32(r), N = d), and the fused final RMSNorm from the rows' sums
+ * of squares collected there. Same result contract as tb_lowrank_remove (Plan:148; no code in the
+ * reference). scratch: device memory, 256-byte aligned, at least tb_lowrank_tc_scratch_bytes(n_rows,
+ * d, r) bytes (-1: bad arguments / no device); nothing is allocated inside. d % 8 == 0, d <= 8192. */
+int64_t tb_lowrank_tc_scratch_bytes(int64_t n_rows, int d, int r);
+int tb_lowrank_remove_tc(const void* x_bf16, const void* ut_bf16, int r, int64_t n_rows, int d,
+                         const float* w_norm, float eps, void* scratch, int64_t scratch_bytes,
+                         void* out_x_bf16, void* out_h_bf16, void* stream);
+
 /* ---- a6: final RMSNorm -------------------------------------------------------------------
  * Replaces model.model.norm(...), src/models.py:135 (Gemma2RMSNorm.forward on a bf16
  * residual): h = bf16((x * rsqrt(mean(x^2) + eps)) * (1 + w)), fp32 intermediates.

@@ -612,6 +612,102 @@ int tb_lowrank_apply(const void* x, const void* ut, const float* c, int r, int64
   return TB_OK;
 }
 
+namespace {
+// K2 on the tensor cores: scratch layout (256-byte aligned pieces) and the chunking of step 2
+struct ProjTcPlan {
+  int rp, kc, n_chunks, n_parts;
+  size_t off_cb, off_ub, off_ss, bytes;
+};
+ProjTcPlan proj_tc_plan(int64_t n_rows, int d, int r, int sms) {
+  ProjTcPlan p;
+  p.rp = (r + 31) / 32 * 32;
+  p.kc = 2 * p.rp;
+  const int n_tiles = (d + tb::kBlockN - 1) / tb::kBlockN;
+  const int64_t m_blocks = (n_rows + 2 * tb::kBlockM - 1) / (2 * tb::kBlockM);
+  int c = 1;
+  while (m_blocks * c < sms && c < n_tiles) c *= 2;         // enough units to fill the pairs
+  if (c > n_tiles) c = n_tiles;
+  const int tpc = (n_tiles + c - 1) / c;
+  p.n_chunks = (n_tiles + tpc - 1) / tpc;
+  p.n_parts = 2 * p.n_chunks;
+  auto up = [](size_t v) { return (v + 255) / 256 * 256; };
+  p.off_cb = 0;
+  p.off_ub = up(static_cast<size_t>(n_rows) * p.kc * 2);
+  p.off_ss = p.off_ub + up(static_cast<size_t>(d) * p.kc * 2);
+  p.bytes = p.off_ss + up(static_cast<size_t>(p.n_parts) * n_rows * 4);
+  return p;
+}
+}  // namespace
+
+int64_t tb_lowrank_tc_scratch_bytes(int64_t n_rows, int d, int r) {
+  DevInfo di;
+  if (device_info(&di) != TB_OK || n_rows < 0 || d <= 0 || r < 1) return -1;
+  return static_cast<int64_t>(proj_tc_plan(n_rows, d, r, di.sms).bytes);
+}
+
+int tb_lowrank_remove_tc(const void* x, const void* ut, int r, int64_t n_rows, int d, const float* w_norm,
+                         float eps, void* scratch, int64_t scratch_bytes, void* out_x, void* out_h,
+                         void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (r < 1 || r > tb::kProjMaxRank) return fail(TB_ERR_INVALID, "rank %d outside [1, %d]", r, tb::kProjMaxRank);
+  rc = check_gemm_operands(x, ut, n_rows, r, d);
+  if (rc != TB_OK) return rc;
+  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  const int nv = (d / 8 + tb::kRowGroupThreads - 1) / tb::kRowGroupThreads;
+  if (nv > 8) return fail(TB_ERR_INVALID, "d=%d too large for the row kernels (max 8192)", d);
+  if (n_rows == 0) return TB_OK;
+  const ProjTcPlan pl = proj_tc_plan(n_rows, d, r, di.sms);
+  if (!scratch || scratch_bytes < static_cast<int64_t>(pl.bytes))
+    return fail(TB_ERR_INVALID, "scratch of %lld bytes needed (tb_lowrank_tc_scratch_bytes), got %lld",
+                static_cast<long long>(pl.bytes), static_cast<long long>(scratch_bytes));
+  if (reinterpret_cast<uintptr_t>(scratch) % 256) return fail(TB_ERR_INVALID, "scratch must be 256-byte aligned");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  uint8_t* sc = static_cast<uint8_t*>(scratch);
+  __nv_bfloat16* cb = reinterpret_cast<__nv_bfloat16*>(sc + pl.off_cb);
+  __nv_bfloat16* ub = reinterpret_cast<__nv_bfloat16*>(sc + pl.off_ub);
+  float* ss = reinterpret_cast<float*>(sc + pl.off_ss);
+  // B operand of step 2
+  {
+    const int64_t n = static_cast<int64_t>(d) * pl.kc;
+    tb::tb_lowrank_ub_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(ut), r, pl.rp, d, ub);
+    TB_CUDA(cudaGetLastError());
+  }
+  // step 1: C = x U, split into bf16 head + remainder
+  {
+    tb::GemmArgs g = make_args(n_rows, r, d, 1, 2);
+    tb::CoeffSplitEpi::Params ep{cb, pl.rp};
+    rc = launch_gemm<tb::CoeffSplitEpi, 2>(x, ut, g, ep, s, di.sms);
+    if (rc != TB_OK) return rc;
+  }
+  // step 2: x' = bf16(x - C U^T) and the rows' sums of squares
+  __nv_bfloat16* xp = static_cast<__nv_bfloat16*>(out_x ? out_x : out_h);
+  {
+    tb::GemmArgs g = make_args(n_rows, d, pl.kc, pl.n_chunks, 2);
+    if (g.n_chunks != pl.n_chunks) return fail(TB_ERR_INVALID, "internal: chunk plan mismatch");
+    tb::ProjApplyEpi::Params ep{static_cast<const __nv_bfloat16*>(x), xp, ss};
+    rc = launch_gemm<tb::ProjApplyEpi, 2>(cb, ub, g, ep, s, di.sms);
+    if (rc != TB_OK) return rc;
+  }
+  // step 3: the fused final RMSNorm
+  if (out_h) {
+    const int64_t blocks = (n_rows + tb::kRowGroups - 1) / tb::kRowGroups;
+    const int64_t max_grid = static_cast<int64_t>(di.sms) * 8;
+    const unsigned grid = static_cast<unsigned>(blocks < max_grid ? blocks : max_grid);
+    __nv_bfloat16* hp = static_cast<__nv_bfloat16*>(out_h);
+    const int n = static_cast<int>(n_rows);
+    if (nv == 1) tb::tb_scale_rows_kernel<1><<<grid, tb::kAblThreads, 0, s>>>(xp, ss, pl.n_parts, w_norm, n, d, eps, hp);
+    else if (nv == 2) tb::tb_scale_rows_kernel<2><<<grid, tb::kAblThreads, 0, s>>>(xp, ss, pl.n_parts, w_norm, n, d, eps, hp);
+    else if (nv <= 4) tb::tb_scale_rows_kernel<4><<<grid, tb::kAblThreads, 0, s>>>(xp, ss, pl.n_parts, w_norm, n, d, eps, hp);
+    else tb::tb_scale_rows_kernel<8><<<grid, tb::kAblThreads, 0, s>>>(xp, ss, pl.n_parts, w_norm, n, d, eps, hp);
+    TB_CUDA(cudaGetLastError());
+  }
+  return TB_OK;
+}
+
 int tb_rmsnorm(const void* x, const float* w_norm, float eps, int64_t n_rows, int d, void* out_h,
                void* stream) {
   DevInfo di;

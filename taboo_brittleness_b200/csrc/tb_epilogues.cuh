@@ -3,6 +3,7 @@
 #pragma once
 #include <math_constants.h>
 #include "tb_gemm.cuh"
+#include "tb_rows.cuh"
 
 namespace tb {
 
@@ -690,6 +691,138 @@ struct CandSumEpi {
   }
 
   __device__ __forceinline__ static void end_unit_sw(State&, const Params&, const GemmArgs&, const SweepCtx&) {}
+};
+
+// =========================================================================================
+// K2 on the tensor cores (ranks above 8), step 1: C = x U (A = x rows, B = U^T [r, d] as the single
+// swept tile). The coefficients leave as the A operand of step 2: each fp32 value split into a bf16
+// head and a bf16 remainder, cb [M, 2 * rp] = [hi | lo] (rp = r rounded up to 32; padding columns get
+// the zeros that TMA's out-of-bounds fill produced). hi + lo carries 16 mantissa bits of C.
+// =========================================================================================
+struct CoeffSplitEpi {
+  static constexpr int kEpiWarps = 4;
+  static constexpr bool kSweepA = false;
+  static constexpr bool kTileHooks = false;
+  static constexpr int kExtraSmem = 0;
+  struct Params {
+    __nv_bfloat16* cb;   // [M, 2 * rp]
+    int rp;              // multiple of 32
+  };
+  struct State {};
+  __device__ __forceinline__ static void begin_unit(State&, const Params&, const GemmArgs&, int, int) {}
+  __device__ __forceinline__ static void process(State&, const Params& p, const GemmArgs& g,
+                                                 const uint32_t (&v)[32], int row, int col0) {
+    if (row >= g.M || col0 >= p.rp) return;
+    __nv_bfloat16* o = p.cb + static_cast<size_t>(row) * (2 * p.rp) + col0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float hi[8], lo[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float c = __uint_as_float(v[8 * q + e]);
+        hi[e] = __bfloat162float(__float2bfloat16_rn(c));
+        lo[e] = c - hi[e];
+      }
+      reinterpret_cast<Bf16x8*>(o)[q] = pack8(hi);
+      reinterpret_cast<Bf16x8*>(o + p.rp)[q] = pack8(lo);
+    }
+  }
+  __device__ __forceinline__ static void end_unit(State&, const Params&, const GemmArgs&, int, int) {}
+};
+
+// =========================================================================================
+// K2 on the tensor cores, step 2: P = [C_hi | C_lo] [U | U]^T (K = 2 * rp, N = d) and, in the
+// epilogue, x' = bf16(x - P) plus each row's sum of squares of the rounded values (one partial per
+// (chunk, column half); tb_scale_rows_kernel turns them into the fused final RMSNorm).
+// An epilogue thread owns an accumulator ROW, but rows are d * 2 bytes apart in memory: reading x and
+// writing x' from that mapping touches 32 different lines per warp instruction (measured: 1 TB/s).
+// So the 128 threads of a column half move x / x' in [128 rows x 64 columns] sub-tiles through shared
+// memory: eight lanes cover one row's 128 bytes on the global side (whole lines), the row's owner
+// picks its eight 16-byte chunks up from a XOR-swizzled layout (conflict-free) and leaves x' there.
+// =========================================================================================
+struct ProjApplyEpi {
+  static constexpr int kEpiWarps = 8;
+  static constexpr bool kSweepA = false;
+  static constexpr bool kTileHooks = true;
+  static constexpr int kSubCols = 64;                        // columns per sub-tile: 128 bytes of a row
+  static constexpr int kSubBytes = kBlockM * kSubCols * 2;   // 16 KB per column half
+  static constexpr int kExtraSmem = 2 * kSubBytes;
+  struct Params {
+    const __nv_bfloat16* x;   // [M, d]
+    __nv_bfloat16* out;       // [M, d]  x' (may be the buffer that becomes h)
+    float* ss;                // [n_parts, M]
+  };
+  struct State { float ss; };
+  __device__ __forceinline__ static void begin_unit_tile(State& st, const Params&, const GemmArgs&, const SweepCtx&,
+                                                         int) {
+    st.ss = 0.0f;
+  }
+  // the cooperative side: thread t of the half moves chunks t, t + 128, ... of the sub-tile; chunk i is
+  // 16 bytes: row i / 8 of the block, columns [8 * (i % 8), +8) of the sub-tile
+  __device__ __forceinline__ static void load_sub(int4 (&reg)[8], const Params& p, const GemmArgs& g, int row0, int col0,
+                                                  int t) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int idx = i * 128 + t, r = row0 + (idx >> 3), c = col0 + (idx & 7) * 8;
+      reg[i] = make_int4(0, 0, 0, 0);
+      if (r < g.M && c + 8 <= g.N) reg[i] = __ldg(reinterpret_cast<const int4*>(p.x + static_cast<size_t>(r) * g.N + c));
+    }
+  }
+  __device__ __forceinline__ static uint32_t slot(int r, int chunk) {   // byte offset in the sub-tile buffer
+    return static_cast<uint32_t>(r * 128 + ((chunk ^ (r & 7)) << 4));
+  }
+  __device__ __forceinline__ static void process_tile(State& st, const Params& p, const GemmArgs& g,
+                                                      const SweepCtx& c, int row, int nt, uint32_t taddr, int) {
+    uint8_t* buf = c.extra + c.half * kSubBytes;
+    const int t = c.tid;                                   // 0..127 within the half; also this thread's row
+    const int row0 = row - t;                              // first row of the CTA's 128
+    const int colh = nt * kBlockN + c.half * 128;
+    int4 reg[8];
+    load_sub(reg, p, g, row0, colh, t);
+#pragma unroll 1
+    for (int sub = 0; sub < 2; ++sub) {
+      const int col0 = colh + sub * kSubCols;
+      epi_half_bar_sync(c.half);                           // the previous sub-tile's stores have left the buffer
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int idx = i * 128 + t;
+        *reinterpret_cast<int4*>(buf + slot(idx >> 3, idx & 7)) = reg[i];
+      }
+      if (sub == 0) load_sub(reg, p, g, row0, col0 + kSubCols, t);   // next sub-tile's x, in flight during the math
+      epi_half_bar_sync(c.half);
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        uint32_t v[32];
+        tmem_ld_32x32(taddr + c.half * 128 + sub * kSubCols + cc * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          int4* sp = reinterpret_cast<int4*>(buf + slot(t, cc * 4 + q));
+          float xv[8], o[8];
+          unpack8(*sp, xv);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            o[e] = __bfloat162float(__float2bfloat16_rn(xv[e] - __uint_as_float(v[q * 8 + e])));
+            st.ss = fmaf(o[e], o[e], st.ss);               // (rows / columns outside the matrix hold zeros)
+          }
+          const Bf16x8 pk = pack8(o);
+          *sp = *reinterpret_cast<const int4*>(&pk);
+        }
+      }
+      epi_half_bar_sync(c.half);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int idx = i * 128 + t, r = row0 + (idx >> 3), cg = col0 + (idx & 7) * 8;
+        if (r < g.M && cg + 8 <= g.N)
+          *reinterpret_cast<int4*>(p.out + static_cast<size_t>(r) * g.N + cg) =
+              *reinterpret_cast<const int4*>(buf + slot(idx >> 3, idx & 7));
+      }
+    }
+  }
+  __device__ __forceinline__ static void end_unit_tile(State& st, const Params& p, const GemmArgs& g,
+                                                       const SweepCtx& c, int row) {
+    if (row < g.M) p.ss[static_cast<size_t>(c.chunk * 2 + c.half) * g.M + row] = st.ss;
+  }
 };
 
 // =========================================================================================

@@ -188,6 +188,58 @@ __global__ void __launch_bounds__(kAblThreads) tb_rmsnorm_kernel(const __nv_bflo
   }
 }
 
+// K2 on the tensor cores, step 3: h = bf16((x' * rstd) * (1 + w)) with rstd from the per-(part, row) sums of
+// squares that step 2's epilogue left behind (tb_epilogues.cuh: ProjApplyEpi). Same row-group layout and
+// arithmetic as tb_rmsnorm_kernel, minus the reduction. In place (xin == out_h) is fine.
+template <int NV>
+__global__ void __launch_bounds__(kAblThreads) tb_scale_rows_kernel(const __nv_bfloat16* __restrict__ xin,
+                                                                    const float* __restrict__ ss, int n_parts,
+                                                                    const float* __restrict__ w, int n_rows, int d,
+                                                                    float eps, __nv_bfloat16* out_h) {
+  const int group = threadIdx.x / kRowGroupThreads;
+  const int gt = threadIdx.x - group * kRowGroupThreads;
+  const int nvec = d >> 3;
+  for (int row = blockIdx.x * kRowGroups + group; row < n_rows; row += gridDim.x * kRowGroups) {
+    const int4* xr = reinterpret_cast<const int4*>(xin + static_cast<size_t>(row) * d);
+    int4 raw[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      raw[i] = make_int4(0, 0, 0, 0);
+      if (vec < nvec) raw[i] = xr[vec];
+    }
+    float sum = 0.0f;
+    for (int p = 0; p < n_parts; ++p) sum += __ldg(ss + static_cast<size_t>(p) * n_rows + row);   // fixed order
+    const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(sum, static_cast<float>(d)), eps)));
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      if (vec < nvec) {
+        float xb[8], h[8];
+        unpack8(raw[i], xb);
+        const float4 w0 = __ldg(reinterpret_cast<const float4*>(w) + 2 * vec);
+        const float4 w1 = __ldg(reinterpret_cast<const float4*>(w) + 2 * vec + 1);
+        const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(xb[e], rstd), __fadd_rn(1.0f, ww[e]));
+        reinterpret_cast<Bf16x8*>(out_h + static_cast<size_t>(row) * d)[vec] = pack8(h);
+      }
+    }
+  }
+}
+
+// K2 on the tensor cores: the B operand of step 2, ub [d, 2 * rp] = [U | U] with U = ut^T (ut is [r, d]),
+// zero in the padding columns r <= k < rp.
+__global__ void tb_lowrank_ub_kernel(const __nv_bfloat16* __restrict__ ut, int r, int rp, int d,
+                                     __nv_bfloat16* __restrict__ ub) {
+  const int kc = 2 * rp;
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < static_cast<int64_t>(d) * kc;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int j = static_cast<int>(i / kc), k = static_cast<int>(i % kc) % rp;
+    ub[i] = (k < r) ? ut[static_cast<size_t>(k) * d + j] : __float2bfloat16_rn(0.0f);
+  }
+}
+
 template <int NV>
 __global__ void __launch_bounds__(kAblThreads, (NV <= 4 ? 2 : 1)) tb_ablate_decode_kernel(const AblateArgs a) {
   __shared__ float s_red[kRowGroups][4];

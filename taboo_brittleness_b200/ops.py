@@ -293,10 +293,15 @@ def sae_ablate_decode(x: Optional[torch.Tensor], acts: SparseActs, sae: SaeWeigh
 LOWRANK_SMALL = 8     # ranks up to this use the kernel that keeps U^T in shared memory
 
 
+_PROJ_SCRATCH: dict = {}
+
+
 def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.Tensor] = None,
-                   eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False
-                   ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
-    """x' = x - (x U) U^T for orthonormal U [d, r], r <= 64 (Plan:148)."""
+                   eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False,
+                   tensor_cores: bool = True) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+    """x' = x - (x U) U^T for orthonormal U [d, r], r <= 64 (Plan:148). Ranks up to 8 run in one
+    HBM-bound CUDA-core kernel; above that both thin products go to the tensor cores
+    (``tb_lowrank_remove_tc``; ``tensor_cores=False`` keeps the second product on the CUDA cores)."""
     _need(x, torch.bfloat16, "x", 2)
     _need(U, torch.bfloat16, "U", 2)
     n, d = x.shape
@@ -309,6 +314,17 @@ def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.T
     if n == 0:
         return out_x, out_h
     lib = _lib.load()
+    if r > LOWRANK_SMALL and tensor_cores:
+        need = int(lib.tb_lowrank_tc_scratch_bytes(n, d, r))
+        if need < 0:
+            raise TabooKernelError(f"tb_lowrank_tc_scratch_bytes({n}, {d}, {r}) failed", _lib.TB_ERR_INVALID)
+        key = (x.device.index, torch.cuda.current_stream().cuda_stream)
+        buf = _PROJ_SCRATCH.get(key)
+        if buf is None or buf.numel() < need:      # grown on demand, reused by later calls on this stream
+            buf = _PROJ_SCRATCH[key] = torch.empty(need, dtype=torch.uint8, device=x.device)
+        check(lib.tb_lowrank_remove_tc(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(buf), buf.numel(),
+                                       _ptr(out_x), _ptr(out_h), _stream()), "tb_lowrank_remove_tc")
+        return out_x, out_h
     if r > LOWRANK_SMALL and d <= 4096:
         # coefficients on the tensor cores, then one pass that subtracts, rounds and normalises
         c = torch.empty(n, r, dtype=torch.float32, device=x.device)

@@ -34,6 +34,39 @@ def test_lowrank_remove(cuda_lib, r, n_rows):
     assert ((got_h - ref_h).abs() <= 0.0079 * ref_h.abs() + 1e-6).all()
 
 
+@pytest.mark.parametrize("r,d,n_rows", [(9, 3584, 700), (16, 3584, 4096), (40, 520, 300), (64, 3584, 1300)])
+def test_lowrank_tensor_core_path_equals_cuda_core_path(cuda_lib, r, d, n_rows):
+    """Ranks above 8: both thin products on the tensor cores (coefficients split into bf16 head + remainder)
+    against the CUDA-core second product. Same x' up to one bf16 rounding flip in a few elements; h alone
+    (x' written into the h buffer and scaled in place) equals h next to x'."""
+    from taboo_brittleness_b200 import ops
+    x = cuda_bf16(synthetic.make_residuals(1, n_rows, d, seed=5 + r))
+    U = cuda_bf16(synthetic.bf16_exact(oracle.random_orthonormal(d, r, seed=r)))
+    w = synthetic.make_lens(d, 8, seed=1).w_norm.cuda()
+    tx, th = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True)
+    cx, ch = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, tensor_cores=False)
+    _, th2 = ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True)
+    torch.cuda.synchronize()
+    assert torch.equal(th, th2)
+    tx, cx, th, ch = tx.float(), cx.float(), th.float(), ch.float()
+    assert (tx != cx).float().mean().item() < 5e-3
+    assert ((tx - cx).abs() <= 0.0079 * cx.abs() + 1e-3).all()
+    assert (th != ch).float().mean().item() < 1e-2
+    assert ((th - ch).abs() <= 0.0079 * ch.abs() + 1e-3 * ch.abs().max()).all()
+
+
+def test_lowrank_tc_scratch_is_checked(cuda_lib):
+    from taboo_brittleness_b200 import _lib
+    need = cuda_lib.tb_lowrank_tc_scratch_bytes(1000, 3584, 33)
+    assert need >= 1000 * 128 * 2 + 3584 * 128 * 2 + 2 * 1000 * 4
+    x = torch.zeros(1000, 3584, dtype=BF16, device="cuda")
+    ut = torch.zeros(33, 3584, dtype=BF16, device="cuda")
+    buf = torch.empty(need - 256, dtype=torch.uint8, device="cuda")
+    rc = cuda_lib.tb_lowrank_remove_tc(x.data_ptr(), ut.data_ptr(), 33, 1000, 3584, None, 1e-6, buf.data_ptr(),
+                                       buf.numel(), x.data_ptr(), None, torch.cuda.current_stream().cuda_stream)
+    assert rc == _lib.TB_ERR_INVALID and "scratch" in _lib.last_error()
+
+
 def test_lowrank_remove_small_d_and_rank_zero(cuda_lib):
     from taboo_brittleness_b200 import ops
     x = synthetic.make_residuals(2, 9, 264, seed=5)
