@@ -736,8 +736,8 @@ struct CoeffSplitEpi {
 // (chunk, column half); tb_scale_rows_kernel turns them into the fused final RMSNorm).
 // An epilogue thread owns an accumulator ROW, but rows are d * 2 bytes apart in memory: reading x and
 // writing x' from that mapping touches 32 different lines per warp instruction (measured: 1 TB/s).
-// So the 128 threads of a column half move x / x' in [128 rows x 64 columns] sub-tiles through shared
-// memory: eight lanes cover one row's 128 bytes on the global side (whole lines), the row's owner
+// So every warp moves its 32 rows of x / x' in [32 rows x 64 columns] sub-tiles through its own 4 KB of
+// shared memory: eight lanes cover one row's 128 bytes on the global side (whole lines), the row's owner
 // picks its eight 16-byte chunks up from a XOR-swizzled layout (conflict-free) and leaves x' there.
 // =========================================================================================
 struct ProjApplyEpi {
@@ -745,51 +745,56 @@ struct ProjApplyEpi {
   static constexpr bool kSweepA = false;
   static constexpr bool kTileHooks = true;
   static constexpr int kSubCols = 64;                        // columns per sub-tile: 128 bytes of a row
-  static constexpr int kSubBytes = kBlockM * kSubCols * 2;   // 16 KB per column half
-  static constexpr int kExtraSmem = 2 * kSubBytes;
+  static constexpr int kWarpBytes = 32 * kSubCols * 2;       // 4 KB: a warp's 32 rows of one sub-tile
+  static constexpr int kExtraSmem = kEpiWarps * kWarpBytes;
   struct Params {
     const __nv_bfloat16* x;   // [M, d]
     __nv_bfloat16* out;       // [M, d]  x' (may be the buffer that becomes h)
-    float* ss;                // [n_parts, M]
+    float* ss;                // [n_parts, M]  sums of squares of the rounded x'
   };
-  struct State { float ss; };
-  __device__ __forceinline__ static void begin_unit_tile(State& st, const Params&, const GemmArgs&, const SweepCtx&,
-                                                         int) {
-    st.ss = 0.0f;
-  }
-  // the cooperative side: thread t of the half moves chunks t, t + 128, ... of the sub-tile; chunk i is
-  // 16 bytes: row i / 8 of the block, columns [8 * (i % 8), +8) of the sub-tile
-  __device__ __forceinline__ static void load_sub(int4 (&reg)[8], const Params& p, const GemmArgs& g, int row0, int col0,
-                                                  int t) {
+  struct State {
+    float ss;
+    int4 reg[8];   // the next sub-tile's x, requested one sub-tile ahead (across tile boundaries too)
+  };
+  // the cooperative side, warp by warp (a warp stages its own 32 rows, so __syncwarp is all the
+  // synchronisation there is): lane l moves chunks l, l + 32, ... of the warp's sub-tile; chunk i is 16
+  // bytes: row i / 8 of the warp's 32, columns [8 * (i % 8), +8) of the sub-tile
+  __device__ __forceinline__ static void load_sub(int4 (&reg)[8], const Params& p, const GemmArgs& g, int wrow0, int col0,
+                                                  int lane) {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int idx = i * 128 + t, r = row0 + (idx >> 3), c = col0 + (idx & 7) * 8;
+      const int idx = i * 32 + lane, r = wrow0 + (idx >> 3), c = col0 + (idx & 7) * 8;
       reg[i] = make_int4(0, 0, 0, 0);
       if (r < g.M && c + 8 <= g.N) reg[i] = __ldg(reinterpret_cast<const int4*>(p.x + static_cast<size_t>(r) * g.N + c));
     }
   }
-  __device__ __forceinline__ static uint32_t slot(int r, int chunk) {   // byte offset in the sub-tile buffer
+  __device__ __forceinline__ static uint32_t slot(int r, int chunk) {   // byte offset in the warp's buffer
     return static_cast<uint32_t>(r * 128 + ((chunk ^ (r & 7)) << 4));
+  }
+  __device__ __forceinline__ static void begin_unit_tile(State& st, const Params& p, const GemmArgs& g,
+                                                         const SweepCtx& c, int row) {
+    st.ss = 0.0f;
+    load_sub(st.reg, p, g, row - (c.tid & 31), c.t0 * kBlockN + c.half * 128, c.tid & 31);
   }
   __device__ __forceinline__ static void process_tile(State& st, const Params& p, const GemmArgs& g,
                                                       const SweepCtx& c, int row, int nt, uint32_t taddr, int) {
-    uint8_t* buf = c.extra + c.half * kSubBytes;
-    const int t = c.tid;                                   // 0..127 within the half; also this thread's row
-    const int row0 = row - t;                              // first row of the CTA's 128
+    const int lane = c.tid & 31;                           // this thread's row within the warp's 32
+    uint8_t* buf = c.extra + (c.half * 4 + (c.tid >> 5)) * kWarpBytes;
+    const int wrow0 = row - lane;                          // first row of the warp
     const int colh = nt * kBlockN + c.half * 128;
-    int4 reg[8];
-    load_sub(reg, p, g, row0, colh, t);
 #pragma unroll 1
     for (int sub = 0; sub < 2; ++sub) {
       const int col0 = colh + sub * kSubCols;
-      epi_half_bar_sync(c.half);                           // the previous sub-tile's stores have left the buffer
+      __syncwarp();                                        // the previous sub-tile's stores have left the buffer
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        const int idx = i * 128 + t;
-        *reinterpret_cast<int4*>(buf + slot(idx >> 3, idx & 7)) = reg[i];
+        const int idx = i * 32 + lane;
+        *reinterpret_cast<int4*>(buf + slot(idx >> 3, idx & 7)) = st.reg[i];
       }
-      if (sub == 0) load_sub(reg, p, g, row0, col0 + kSubCols, t);   // next sub-tile's x, in flight during the math
-      epi_half_bar_sync(c.half);
+      // the next sub-tile's x (this tile's second half, or the next tile's first), in flight during the math
+      if (sub == 0) load_sub(st.reg, p, g, wrow0, col0 + kSubCols, lane);
+      else if (nt + 1 < c.t1) load_sub(st.reg, p, g, wrow0, colh + kBlockN, lane);
+      __syncwarp();
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
         uint32_t v[32];
@@ -797,7 +802,7 @@ struct ProjApplyEpi {
         tmem_ld_wait();
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          int4* sp = reinterpret_cast<int4*>(buf + slot(t, cc * 4 + q));
+          int4* sp = reinterpret_cast<int4*>(buf + slot(lane, cc * 4 + q));
           float xv[8], o[8];
           unpack8(*sp, xv);
 #pragma unroll
@@ -809,10 +814,10 @@ struct ProjApplyEpi {
           *sp = *reinterpret_cast<const int4*>(&pk);
         }
       }
-      epi_half_bar_sync(c.half);
+      __syncwarp();
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
-        const int idx = i * 128 + t, r = row0 + (idx >> 3), cg = col0 + (idx & 7) * 8;
+        const int idx = i * 32 + lane, r = wrow0 + (idx >> 3), cg = col0 + (idx & 7) * 8;
         if (r < g.M && cg + 8 <= g.N)
           *reinterpret_cast<int4*>(p.out + static_cast<size_t>(r) * g.N + cg) =
               *reinterpret_cast<const int4*>(buf + slot(idx >> 3, idx & 7));
