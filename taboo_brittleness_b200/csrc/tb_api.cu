@@ -386,7 +386,12 @@ int tb_sae_encode(const void* x, const void* w_enc_t, const float* b_enc, const 
   ep.rank = rank;
   ep.rank_rows = rank_rows;
   ep.budget = budget;
-  // one unit per row block: a row's list is written by a single thread, in latent order
+  // one unit per row block: a row's list is written by a single thread, in latent order.
+  // CTA pairs (UMMA 256 x 256) once there are enough 256-row blocks to fill them; single CTAs for small inputs
+  if (n_rows >= static_cast<int64_t>(tb::kBlockM) * di.sms) {
+    tb::GemmArgs g = make_args(n_rows, S, d, 1, 2);
+    return launch_gemm<tb::EncodeEpi, 2>(x, w_enc_t, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  }
   tb::GemmArgs g = make_args(n_rows, S, d, 1, 1);
   return launch_gemm<tb::EncodeEpi, 1>(x, w_enc_t, g, ep, static_cast<cudaStream_t>(stream), di.sms);
 }

@@ -179,3 +179,18 @@ def test_ablate_decode_random_control_and_zero_budget(problem, encoded):
     # budget 0 ablates nothing: the error-term form returns x unchanged
     same, _ = ops.sae_ablate_decode(encoded["x"], encoded["acts"], encoded["w"], rank, 0, mode="error")
     assert torch.equal(same, encoded["x"])
+
+
+def test_encode_large_batches_on_cta_pairs_equal_small_batches(cuda_lib):
+    """From 128 rows per SM upwards the encode runs on CTA pairs (UMMA 256 x 256), below on single CTAs.
+    Same accumulation order either way: the lists of a big batch equal those of its pieces, bit for bit."""
+    from taboo_brittleness_b200 import ops
+    d, s_, t_, p_ = 264, 2048, 100, 200                       # 20,000 rows > 128 * 148; 200-row tail block
+    x = cuda_bf16(synthetic.make_residuals(p_, t_, d, seed=77))
+    w = sae_to_cuda(synthetic.make_sae(d, s_, seed=7, target_l0=20.0))
+    big = ops.sae_encode(x, w, cap=128)                        # (<bos>-scale rows overflow 128 slots: CSR re-pass included)
+    pieces = [ops.sae_encode(x[r0:r0 + 5000].contiguous(), w, cap=128) for r0 in range(0, x.shape[0], 5000)]
+    torch.cuda.synchronize()
+    assert torch.equal(big.count, torch.cat([q.count for q in pieces]))
+    assert torch.equal(big.to_dense(), torch.cat([q.to_dense() for q in pieces]))
+    assert int(big.count.sum()) > 10 * x.shape[0]
