@@ -268,9 +268,14 @@ def run_native(args, rank, local_rank, world):
             else:
                 res = {}
                 for r in RANKS:
+                    if eng.time_lens:
+                        rv0, rv1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        rv0.record()
                     _, h = ops.lowrank_remove(xb, U[:, :r].contiguous(), w_norm=lens.w_norm, eps=lens.eps, want_x=False,
                                               want_h=True)
                     if eng.time_lens:
+                        rv1.record()
+                        eng.stats.row_events.append((rv0, rv1, 4.0 * xb.shape[0] * D))
                         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                         ev0.record()
                     res[r] = tbd.lens_readout_vocab_sharded(h, lens, softcap=SOFTCAP, secret_id=sb, cta_pair=args.cluster_mode)
@@ -324,6 +329,8 @@ def run_native(args, rank, local_rank, world):
     lens_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.lens_events)
     lens_flops = sum(f for _, _, f in eng.stats.lens_events)
     n_lens = len(eng.stats.lens_events)
+    row_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.row_events)
+    row_bytes = sum(f for _, _, f in eng.stats.row_events)
     launches = kernel_calls        # C-ABI compute calls inside the timed region (>= 1 kernel each)
     clocks = sampler.finish() if sampler else None
 
@@ -361,6 +368,14 @@ def run_native(args, rank, local_rank, world):
                              "whole_step_tflops": (n_rows * ((0.0 if proj else FLOP_ENC) + conditions * FLOP_LENS /
                                                              (world if proj else 1))) / (ms_step * 1e-3) / 1e12},
                 "clocks": clocks}
+        if row_ms > 0:   # the HBM-bound producer of the lens operand: K2 (projection) or K1b (ablate + decode)
+            gbs = row_bytes / (row_ms * 1e-3) / 1e9
+            line["roofline"]["hbm_path"] = {
+                "kernel": ("tb_lowrank_remove / tb_lowrank_remove_tc (K2, ranks %s)" % list(RANKS)) if proj
+                else "tb_sae_ablate_decode (K1b, budgets %s)" % list(BUDGETS),
+                "bound": "hbm", "achieved": gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
+                "frac": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
+                "algorithmic_bytes_per_row": 4 * D, "share_of_step": row_ms / (ms_step * args.steps)}
         if line["roofline"]["frac"] > 1.0:
             line["roofline"]["note"] = ("peak = cuBLAS bf16 sustained under this board's power cap (MEASURED_PEAKS.json); "
                                         "a fraction above 1 means the kernel sustains more than cuBLAS does under the same "

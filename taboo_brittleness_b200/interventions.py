@@ -37,6 +37,7 @@ class SweepStats:
     ll_candidates: int = 0           # candidate columns listed by K3F over those prompt-conditions
     lens_events: List = field(default_factory=list)   # (start, end, flops) per lens launch
     ll_events: List = field(default_factory=list)     # (start, end, flops) per LL-Top-k sweep
+    row_events: List = field(default_factory=list)    # (start, end, algorithmic bytes) per K1b / K2 call
 
 
 @dataclass
@@ -181,9 +182,15 @@ class InterventionEngine:
                         secret_id=None, mode: str = "error", finalize: bool = True, ll: Optional[LLSpec] = None,
                         ll_state: Optional[LLState] = None):
         """With ``ll_state`` (from the previous nested condition) returns (Readout, next LLState)."""
+        if self.time_lens:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         _, h = ops.sae_ablate_decode(x, acts, self.sae, rank, budget, mode=mode, rank_rows=rank_rows,
                                      row_table=row_table, w_norm=self.lens.w_norm, eps=self.lens.eps,
                                      want_x=False, want_h=True)
+        if self.time_lens:
+            e1.record()      # algorithmic traffic: x in, h out
+            self.stats.row_events.append((e0, e1, 4.0 * x.shape[0] * x.shape[1]))
         self.stats.launches += 1
         if ll_state is not None:
             return self.read_fused(h, secret_id, ll, ll_state)
@@ -192,7 +199,13 @@ class InterventionEngine:
     def project_and_read(self, x, U, *, secret_id=None, finalize: bool = True, ll: Optional[LLSpec] = None,
                          ll_state: Optional[LLState] = None):
         """With ``ll_state`` (from the previous, smaller rank) returns (Readout, next LLState)."""
+        if self.time_lens:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
         _, h = ops.lowrank_remove(x, U, w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False, want_h=True)
+        if self.time_lens:
+            e1.record()
+            self.stats.row_events.append((e0, e1, 4.0 * x.shape[0] * x.shape[1]))
         self.stats.launches += 1
         if ll_state is not None:
             return self.read_fused(h, secret_id, ll, ll_state)
