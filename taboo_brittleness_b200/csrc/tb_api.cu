@@ -178,7 +178,7 @@ tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group,
 template <class Epi, int G, int R = 1, int C = 1, bool H = false>
 int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typename Epi::Params& ep,
                 cudaStream_t stream, int sms) {
-  using Cfg = tb::GemmCfg<G>;
+  using Cfg = tb::GemmCfg<G, tb::EpiStages<Epi>::value>;
   constexpr int kClusterCtas = G * R * C;
   // every CTA loads 1/share of a slab (and multicasts it): the TMA box shrinks accordingly
   constexpr int kShareA = Epi::kSweepA ? R : C;

@@ -736,17 +736,20 @@ struct CoeffSplitEpi {
 // (chunk, column half); tb_scale_rows_kernel turns them into the fused final RMSNorm).
 // An epilogue thread owns an accumulator ROW, but rows are d * 2 bytes apart in memory: reading x and
 // writing x' from that mapping touches 32 different lines per warp instruction (measured: 1 TB/s).
-// So every warp moves its 32 rows of x / x' in [32 rows x 64 columns] sub-tiles through its own 4 KB of
-// shared memory: eight lanes cover one row's 128 bytes on the global side (whole lines), the row's owner
-// picks its eight 16-byte chunks up from a XOR-swizzled layout (conflict-free) and leaves x' there.
+// So every warp moves its 32 rows of x / x' in [32 rows x 64 columns] sub-tiles through a ring of three 4 KB
+// buffers of its own: eight lanes cover one row's 128 bytes on the global side (whole lines; cp.async, two
+// sub-tiles ahead, no registers held), the row's owner picks its eight 16-byte chunks up from a XOR-swizzled
+// layout (conflict-free) and leaves x' there for the same lanes to store.
 // =========================================================================================
 struct ProjApplyEpi {
   static constexpr int kEpiWarps = 8;
   static constexpr bool kSweepA = false;
   static constexpr bool kTileHooks = true;
+  static constexpr int kStages = 3;                          // K = 64 or 128: a short operand ring is plenty
   static constexpr int kSubCols = 64;                        // columns per sub-tile: 128 bytes of a row
-  static constexpr int kWarpBytes = 32 * kSubCols * 2;       // 4 KB: a warp's 32 rows of one sub-tile
-  static constexpr int kExtraSmem = kEpiWarps * kWarpBytes;
+  static constexpr int kSubBytes = 32 * kSubCols * 2;        // 4 KB: a warp's 32 rows of one sub-tile
+  static constexpr int kRing = 3;                            // sub-tiles in flight per warp (4 measured the same)
+  static constexpr int kExtraSmem = kEpiWarps * kRing * kSubBytes;   // 96 KB
   struct Params {
     const __nv_bfloat16* x;   // [M, d]
     __nv_bfloat16* out;       // [M, d]  x' (may be the buffer that becomes h)
@@ -754,47 +757,57 @@ struct ProjApplyEpi {
   };
   struct State {
     float ss;
-    int4 reg[8];   // the next sub-tile's x, requested one sub-tile ahead (across tile boundaries too)
+    int next;      // sub-tiles of this unit requested so far
   };
-  // the cooperative side, warp by warp (a warp stages its own 32 rows, so __syncwarp is all the
-  // synchronisation there is): lane l moves chunks l, l + 32, ... of the warp's sub-tile; chunk i is 16
-  // bytes: row i / 8 of the warp's 32, columns [8 * (i % 8), +8) of the sub-tile
-  __device__ __forceinline__ static void load_sub(int4 (&reg)[8], const Params& p, const GemmArgs& g, int wrow0, int col0,
-                                                  int lane) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int idx = i * 32 + lane, r = wrow0 + (idx >> 3), c = col0 + (idx & 7) * 8;
-      reg[i] = make_int4(0, 0, 0, 0);
-      if (r < g.M && c + 8 <= g.N) reg[i] = __ldg(reinterpret_cast<const int4*>(p.x + static_cast<size_t>(r) * g.N + c));
-    }
-  }
-  __device__ __forceinline__ static uint32_t slot(int r, int chunk) {   // byte offset in the warp's buffer
+  __device__ __forceinline__ static uint32_t slot(int r, int chunk) {   // byte offset in a sub-tile buffer
     return static_cast<uint32_t>(r * 128 + ((chunk ^ (r & 7)) << 4));
+  }
+  // Request sub-tile number s of the unit (two per tile) into ring slot s % kRing: lane l copies chunks
+  // l, l + 32, ... (chunk i: row i / 8 of the warp's 32, columns [8 * (i % 8), +8) of the sub-tile), straight
+  // into the swizzled layout, zero-filled outside the matrix. Always commits a group, so that group counts
+  // stay in step with s.
+  __device__ __forceinline__ static void request(State& st, const Params& p, const GemmArgs& g, const SweepCtx& c,
+                                                 uint8_t* ring, int wrow0, int lane) {
+    const int s = st.next++;
+    const int nt = c.t0 + (s >> 1);
+    if (nt < c.t1) {
+      const int col0 = nt * kBlockN + c.half * 128 + (s & 1) * kSubCols;
+      const uint32_t buf = smem_u32(ring + (s % kRing) * kSubBytes);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int idx = i * 32 + lane, r = wrow0 + (idx >> 3), col = col0 + (idx & 7) * 8;
+        const bool in = r < g.M && col + 8 <= g.N;
+        cp_async16(buf + slot(idx >> 3, idx & 7), p.x + (in ? static_cast<size_t>(r) * g.N + col : 0), in ? 16u : 0u);
+      }
+    }
+    cp_async_commit();
+  }
+  __device__ __forceinline__ static uint8_t* ring_of(const SweepCtx& c) {
+    return c.extra + (c.half * 4 + (c.tid >> 5)) * (kRing * kSubBytes);
   }
   __device__ __forceinline__ static void begin_unit_tile(State& st, const Params& p, const GemmArgs& g,
                                                          const SweepCtx& c, int row) {
     st.ss = 0.0f;
-    load_sub(st.reg, p, g, row - (c.tid & 31), c.t0 * kBlockN + c.half * 128, c.tid & 31);
+    st.next = 0;
+    const int lane = c.tid & 31;
+    __syncwarp();                                          // the previous unit's last stores have left the ring
+#pragma unroll
+    for (int k = 0; k < kRing - 1; ++k) request(st, p, g, c, ring_of(c), row - lane, lane);
   }
   __device__ __forceinline__ static void process_tile(State& st, const Params& p, const GemmArgs& g,
                                                       const SweepCtx& c, int row, int nt, uint32_t taddr, int) {
     const int lane = c.tid & 31;                           // this thread's row within the warp's 32
-    uint8_t* buf = c.extra + (c.half * 4 + (c.tid >> 5)) * kWarpBytes;
+    uint8_t* ring = ring_of(c);
     const int wrow0 = row - lane;                          // first row of the warp
-    const int colh = nt * kBlockN + c.half * 128;
 #pragma unroll 1
     for (int sub = 0; sub < 2; ++sub) {
-      const int col0 = colh + sub * kSubCols;
-      __syncwarp();                                        // the previous sub-tile's stores have left the buffer
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int idx = i * 32 + lane;
-        *reinterpret_cast<int4*>(buf + slot(idx >> 3, idx & 7)) = st.reg[i];
-      }
-      // the next sub-tile's x (this tile's second half, or the next tile's first), in flight during the math
-      if (sub == 0) load_sub(st.reg, p, g, wrow0, col0 + kSubCols, lane);
-      else if (nt + 1 < c.t1) load_sub(st.reg, p, g, wrow0, colh + kBlockN, lane);
-      __syncwarp();
+      const int s = ((nt - c.t0) << 1) + sub;
+      const int col0 = nt * kBlockN + c.half * 128 + sub * kSubCols;
+      uint8_t* buf = ring + (s % kRing) * kSubBytes;
+      __syncwarp();                                        // sub-tile s - 1 has been stored: its slot is free again
+      request(st, p, g, c, ring, wrow0, lane);             // sub-tile s + kRing - 1 goes into that slot
+      cp_async_wait<kRing - 1>();                          // my copies of sub-tile s have landed ...
+      __syncwarp();                                        // ... and everybody else's
 #pragma unroll
       for (int cc = 0; cc < 2; ++cc) {
         uint32_t v[32];
@@ -826,6 +839,7 @@ struct ProjApplyEpi {
   }
   __device__ __forceinline__ static void end_unit_tile(State& st, const Params& p, const GemmArgs& g,
                                                        const SweepCtx& c, int row) {
+    cp_async_wait<0>();                                    // only empty groups are left
     if (row < g.M) p.ss[static_cast<size_t>(c.chunk * 2 + c.half) * g.M + row] = st.ss;
   }
 };

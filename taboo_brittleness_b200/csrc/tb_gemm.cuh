@@ -73,9 +73,16 @@ struct SweepCtx {
   uint8_t* extra;   // Epi::kExtraSmem bytes of shared memory (16-byte aligned)
 };
 
-template <int kCtaGroup>
+// An epilogue that needs the shared memory for itself (and whose GEMM has a short K loop anyway) may ask
+// for fewer operand stages with `static constexpr int kStages`.
+template <class Epi, class = void>
+struct EpiStages { static constexpr int value = 0; };
+template <class Epi>
+struct EpiStages<Epi, decltype(void(Epi::kStages))> { static constexpr int value = Epi::kStages; };
+
+template <int kCtaGroup, int kStagesWanted = 0>
 struct GemmCfg {
-  static constexpr int kStages = (kCtaGroup == 1) ? 4 : 6;
+  static constexpr int kStages = kStagesWanted > 0 ? kStagesWanted : (kCtaGroup == 1) ? 4 : 6;
   static constexpr int kABytes = kBlockM * kBlockK * 2;
   static constexpr int kBRows = kBlockN / kCtaGroup;
   static constexpr int kBBytes = kBRows * kBlockK * 2;
@@ -121,7 +128,7 @@ __global__ void __launch_bounds__(gemm_threads<Epi>(), 1)
 tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmS1, const GemmArgs g, const typename Epi::Params ep) {
   static_assert(!kHetero || (kCtaGroup == 2 && kR == 2 && kC == 1), "preferred/fallback clusters: 2x1 pairs only");
-  using Cfg = GemmCfg<kCtaGroup>;
+  using Cfg = GemmCfg<kCtaGroup, EpiStages<Epi>::value>;
   constexpr int kStages = Cfg::kStages;
   // A cluster is kR x kC CTA pairs: pair (i, j) works on stationary block i and chunk j of the
   // cluster's unit. The kC pairs of a row share the stationary operand's k-slabs and the kR pairs
