@@ -167,9 +167,10 @@ def sae_encode(x: torch.Tensor, sae: SaeWeights, cap: int = 128, *, rank: Option
                rank_rows: int = 0, budget: int = 0) -> SparseActs:
     """JumpReLU encode to sparse row lists (replaces ``sae.encode``, 02_run_sae_baseline.py:67).
 
-    First pass writes fixed-stride lists of ``cap`` slots per row. If some row has more active
-    latents than that (e.g. <bos> rows), the lists are rebuilt exactly in CSR form with a second
-    pass sized from the counts -- no active latent is ever dropped.
+    First pass writes fixed-stride lists of ``cap`` slots per row. Rows with more active latents than
+    that (the <bos>-scale row of every prompt has thousands) are encoded once more, alone, into a region
+    appended to the lists, and ``row_start`` then points each row at its list -- no active latent is ever
+    dropped, and the second pass costs the overflowing rows only (about 1 in 128), not a second sweep.
     """
     n = x.shape[0]
     dev = x.device
@@ -178,14 +179,29 @@ def sae_encode(x: torch.Tensor, sae: SaeWeights, cap: int = 128, *, rank: Option
     count = sae_encode_raw(x, sae, cap=cap, idx=idx, val=val, rank=rank, rank_rows=rank_rows, budget=budget)
     if n == 0 or int(count.max().item()) <= cap:
         return SparseActs(count=count, idx=idx, val=val, S=sae.S, cap=cap)
-    c64 = count.to(torch.int64)
-    row_start = torch.cumsum(c64, 0) - c64
-    nnz = int(c64.sum().item())
-    idx = torch.empty(nnz, dtype=torch.int32, device=dev)
-    val = torch.empty(nnz, dtype=torch.float32, device=dev)
-    count2 = sae_encode_raw(x, sae, row_start=row_start, row_cap=count, idx=idx, val=val,
-                            rank=rank, rank_rows=rank_rows, budget=budget)
-    return SparseActs(count=count2, idx=idx, val=val, S=sae.S, cap=0, row_start=row_start)
+    if rank is not None:
+        # the epilogue's rank mask is looked up by row number: keep all rows in place and redo them all
+        c64 = count.to(torch.int64)
+        row_start = torch.cumsum(c64, 0) - c64
+        nnz = int(c64.sum().item())
+        idx = torch.empty(nnz, dtype=torch.int32, device=dev)
+        val = torch.empty(nnz, dtype=torch.float32, device=dev)
+        count2 = sae_encode_raw(x, sae, row_start=row_start, row_cap=count, idx=idx, val=val,
+                                rank=rank, rank_rows=rank_rows, budget=budget)
+        return SparseActs(count=count2, idx=idx, val=val, S=sae.S, cap=0, row_start=row_start)
+    over = torch.nonzero(count > cap).flatten()
+    c_over = count[over].to(torch.int64)
+    extra = int(c_over.sum().item())
+    idx = torch.cat([idx[:n * cap], torch.empty(extra, dtype=torch.int32, device=dev)])
+    val = torch.cat([val[:n * cap], torch.empty(extra, dtype=torch.float32, device=dev)])
+    row_start = torch.arange(n, device=dev, dtype=torch.int64) * cap
+    start_over = n * cap + torch.cumsum(c_over, 0) - c_over
+    row_start[over] = start_over
+    count_over = sae_encode_raw(x[over].contiguous(), sae, row_start=start_over, row_cap=count[over].contiguous(),
+                                idx=idx, val=val)
+    count = count.clone()
+    count[over] = count_over
+    return SparseActs(count=count, idx=idx, val=val, S=sae.S, cap=0, row_start=row_start)
 
 
 # ------------------------------------------------------------------------------------------
