@@ -157,17 +157,33 @@ __global__ void __launch_bounds__(kAblThreads) tb_rmsnorm_kernel(const __nv_bflo
   const int gt = threadIdx.x - group * kRowGroupThreads;
   const int gwarp = gt >> 5, lane = gt & 31;
   const int nvec = d >> 3;
-  for (int row = blockIdx.x * kRowGroups + group; row < n_rows; row += gridDim.x * kRowGroups) {
-    const int4* xr = reinterpret_cast<const int4*>(x + static_cast<size_t>(row) * d);
+  // the next row's x is requested (raw, 16 registers) before this row's reduction: twice the loads in flight
+  const int row_step = gridDim.x * kRowGroups;
+  int4 nxt[NV];
+  {
+    const int row = blockIdx.x * kRowGroups + group;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      nxt[i] = make_int4(0, 0, 0, 0);
+      if (row < n_rows && vec < nvec) nxt[i] = __ldg(reinterpret_cast<const int4*>(x + static_cast<size_t>(row) * d) + vec);
+    }
+  }
+  for (int row = blockIdx.x * kRowGroups + group; row < n_rows; row += row_step) {
     float xb[NV][8];
     float ss = 0.0f;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
-      const int vec = gt + i * kRowGroupThreads;
-      if (vec < nvec) {
-        unpack8(__ldg(xr + vec), xb[i]);
+      unpack8(nxt[i], xb[i]);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) ss = fmaf(xb[i][e], xb[i][e], ss);
+      for (int e = 0; e < 8; ++e) ss = fmaf(xb[i][e], xb[i][e], ss);   // (vectors past the row hold zeros)
+    }
+    if (row + row_step < n_rows) {
+      const int4* xn = reinterpret_cast<const int4*>(x + static_cast<size_t>(row + row_step) * d);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = gt + i * kRowGroupThreads;
+        if (vec < nvec) nxt[i] = __ldg(xn + vec);
       }
     }
     ss = group_sum(ss, s_red[group], group, gwarp, lane);
@@ -199,14 +215,29 @@ __global__ void __launch_bounds__(kAblThreads) tb_scale_rows_kernel(const __nv_b
   const int group = threadIdx.x / kRowGroupThreads;
   const int gt = threadIdx.x - group * kRowGroupThreads;
   const int nvec = d >> 3;
-  for (int row = blockIdx.x * kRowGroups + group; row < n_rows; row += gridDim.x * kRowGroups) {
-    const int4* xr = reinterpret_cast<const int4*>(xin + static_cast<size_t>(row) * d);
-    int4 raw[NV];
+  const int row_step = gridDim.x * kRowGroups;
+  int4 nxt[NV];   // the next row, requested one row ahead
+  {
+    const int row = blockIdx.x * kRowGroups + group;
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vec = gt + i * kRowGroupThreads;
-      raw[i] = make_int4(0, 0, 0, 0);
-      if (vec < nvec) raw[i] = xr[vec];
+      nxt[i] = make_int4(0, 0, 0, 0);
+      if (row < n_rows && vec < nvec) nxt[i] = reinterpret_cast<const int4*>(xin + static_cast<size_t>(row) * d)[vec];
+    }
+  }
+  for (int row = blockIdx.x * kRowGroups + group; row < n_rows; row += row_step) {
+    int4 raw[NV];
+#pragma unroll
+    for (int i = 0; i < NV; ++i) raw[i] = nxt[i];
+    if (row + row_step < n_rows) {
+      // (in place: another group's row, not yet rewritten -- rows are only ever touched by their own group)
+      const int4* xn = reinterpret_cast<const int4*>(xin + static_cast<size_t>(row + row_step) * d);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = gt + i * kRowGroupThreads;
+        if (vec < nvec) nxt[i] = xn[vec];
+      }
     }
     float sum = 0.0f;
     for (int p = 0; p < n_parts; ++p) sum += __ldg(ss + static_cast<size_t>(p) * n_rows + row);   // fixed order
@@ -1333,15 +1364,35 @@ __global__ void __launch_bounds__(kAblThreads) tb_lowrank_tiny_kernel(const Proj
   const int nvec = a.d >> 3;
   for (int i = threadIdx.x; i < a.r * nvec; i += kAblThreads) s_ut[i] = __ldg(reinterpret_cast<const int4*>(a.ut) + i);
   __syncthreads();
-  for (int row = blockIdx.x * kRowGroups + group; row < a.n_rows; row += gridDim.x * kRowGroups) {
-    const int4* xr = reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row) * a.d);
+  // the next row's x is requested (raw, 16 registers) before this row's two reductions: twice the loads in flight
+  const int row_step = gridDim.x * kRowGroups;
+  int4 nxt[NV];
+  {
+    const int row = blockIdx.x * kRowGroups + group;
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      const int vec = gt + i * kRowGroupThreads;
+      nxt[i] = make_int4(0, 0, 0, 0);
+      if (row < a.n_rows && vec < nvec) nxt[i] = __ldg(reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row) * a.d) + vec);
+    }
+  }
+  for (int row = blockIdx.x * kRowGroups + group; row < a.n_rows; row += row_step) {
     float xb[NV][8];
     float dot[kProjTinyRank] = {0.0f, 0.0f};
+#pragma unroll
+    for (int i = 0; i < NV; ++i) unpack8(nxt[i], xb[i]);
+    if (row + row_step < a.n_rows) {
+      const int4* xn = reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row + row_step) * a.d);
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int vec = gt + i * kRowGroupThreads;
+        if (vec < nvec) nxt[i] = __ldg(xn + vec);
+      }
+    }
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       const int vec = gt + i * kRowGroupThreads;
       if (vec < nvec) {
-        unpack8(__ldg(xr + vec), xb[i]);
 #pragma unroll
         for (int j = 0; j < kProjTinyRank; ++j) {
           if (j < a.r) {
