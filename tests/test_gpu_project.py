@@ -9,7 +9,7 @@ pytestmark = pytest.mark.gpu
 RESID_REL_TOL = 2e-2
 
 
-@pytest.mark.parametrize("r", [1, 2, 5, 8, 9, 33, 64])
+@pytest.mark.parametrize("r", [1, 2, 3, 4, 5, 8, 9, 33, 64])
 @pytest.mark.parametrize("n_rows", [1, 37, 512])
 def test_lowrank_remove(cuda_lib, r, n_rows):
     from taboo_brittleness_b200 import ops
