@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
-from taboo_brittleness_b200 import interventions, ops, synthetic  # noqa: E402
+from taboo_brittleness_b200 import ops, synthetic  # noqa: E402
 
 D, S = 3584, 16384
 rows = int(sys.argv[1]) if len(sys.argv) > 1 else 262144

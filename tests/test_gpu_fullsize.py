@@ -5,7 +5,7 @@ must match the fp32 oracle, and the one-sweep LL-Top-k must equal the two-sweep 
 import pytest
 import torch
 
-from _common import BF16, oracle, synthetic
+from _common import synthetic
 
 pytestmark = pytest.mark.gpu
 

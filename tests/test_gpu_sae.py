@@ -5,7 +5,7 @@ near-threshold ties; reconstructed residuals within 2e-2 relative."""
 import pytest
 import torch
 
-from _common import BF16, cuda_bf16, oracle, sae_to_cuda, synthetic
+from _common import cuda_bf16, oracle, sae_to_cuda, synthetic
 
 pytestmark = pytest.mark.gpu
 
