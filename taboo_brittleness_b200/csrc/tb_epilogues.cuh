@@ -302,10 +302,10 @@ struct ColSumEpi {
 
   __device__ __forceinline__ static void begin_unit_sw(State& st, const Params& p, const GemmArgs& g,
                                                        const SweepCtx& c) {
-    float* s_nl = reinterpret_cast<float*>(c.extra + kOffNl);
-    int32_t* s_cur = reinterpret_cast<int32_t*>(c.extra + kOffCur);
-    int32_t* s_prev = reinterpret_cast<int32_t*>(c.extra + kOffPrev);
-    uint32_t* s_bm = reinterpret_cast<uint32_t*>(c.extra + kOffBitmap);
+    float* s_nl = reinterpret_cast<float*>(assume_shared(c.extra) + kOffNl);
+    int32_t* s_cur = reinterpret_cast<int32_t*>(assume_shared(c.extra) + kOffCur);
+    int32_t* s_prev = reinterpret_cast<int32_t*>(assume_shared(c.extra) + kOffPrev);
+    uint32_t* s_bm = reinterpret_cast<uint32_t*>(assume_shared(c.extra) + kOffBitmap);
     // the 256 epilogue threads each set up one row slot of the block (slot = half * 128 + tid)
     const int slot = c.etid;
     const int64_t r = static_cast<int64_t>(c.blk) * 256 + slot;
@@ -347,10 +347,10 @@ struct ColSumEpi {
 
   __device__ __forceinline__ static void process_tile_sw(State& st, const Params& p, const GemmArgs& g,
                                                          const SweepCtx& c, int nt, uint32_t taddr) {
-    const float* s_nl = reinterpret_cast<const float*>(c.extra + kOffNl);
-    const int32_t* s_cur = reinterpret_cast<const int32_t*>(c.extra + kOffCur);
-    const int32_t* s_prev = reinterpret_cast<const int32_t*>(c.extra + kOffPrev);
-    const uint32_t* s_bm = reinterpret_cast<const uint32_t*>(c.extra + kOffBitmap);
+    const float* s_nl = reinterpret_cast<const float*>(assume_shared(c.extra) + kOffNl);
+    const int32_t* s_cur = reinterpret_cast<const int32_t*>(assume_shared(c.extra) + kOffCur);
+    const int32_t* s_prev = reinterpret_cast<const int32_t*>(assume_shared(c.extra) + kOffPrev);
+    const uint32_t* s_bm = reinterpret_cast<const uint32_t*>(assume_shared(c.extra) + kOffBitmap);
     const int local = nt * c.a_tile_rows + c.rank * kBlockM + c.tid;  // row of this shard's W_U
     const int vid = p.vocab_offset + local;
     const int bit = local - c.t0 * c.a_tile_rows;
@@ -389,8 +389,8 @@ struct ColSumEpi {
   // pop the best of the 128 threads' sorted lists, kTopK times (the 128 threads of one column half)
   __device__ __forceinline__ static void end_unit_sw(State& st, const Params& p, const GemmArgs&,
                                                      const SweepCtx& c) {
-    float* s_bv = reinterpret_cast<float*>(c.extra + kOffBest) + c.half * 4;
-    int32_t* s_bi = reinterpret_cast<int32_t*>(c.extra + kOffBest + 32) + c.half * 4;
+    float* s_bv = reinterpret_cast<float*>(assume_shared(c.extra) + kOffBest) + c.half * 4;
+    int32_t* s_bi = reinterpret_cast<int32_t*>(assume_shared(c.extra) + kOffBest + 32) + c.half * 4;
     const int prompt = c.blk * 2 + c.half;
     const int part = c.chunk * p.group + c.rank;
     const int lane = c.tid & 31, warp = c.tid >> 5;
@@ -520,8 +520,8 @@ struct LensLLEpi {
                                                       const SweepCtx& c, int row, int nt, uint32_t taddr,
                                                       int parity) {
     const int quad = c.tid >> 5, lane = c.tid & 31;
-    float* tr = reinterpret_cast<float*>(c.extra + kOffTr) + (c.half * 4 + quad) * (32 * kTrStride);
-    float* cs = reinterpret_cast<float*>(c.extra + kOffCs) + parity * (4 * 256);
+    float* tr = reinterpret_cast<float*>(assume_shared(c.extra) + kOffTr) + (c.half * 4 + quad) * (32 * kTrStride);
+    float* cs = reinterpret_cast<float*>(assume_shared(c.extra) + kOffCs) + parity * (4 * 256);
     const CapLog2 cap2(p.lens.softcap);
 #pragma unroll 1
     for (int cc = c.half * 4; cc < c.half * 4 + 4; ++cc) {
@@ -648,9 +648,9 @@ struct CandSumEpi {
 
   __device__ __forceinline__ static void begin_unit_sw(State&, const Params& p, const GemmArgs& g,
                                                        const SweepCtx& c) {
-    float* s_nl = reinterpret_cast<float*>(c.extra + kOffNl);
-    int32_t* s_cur = reinterpret_cast<int32_t*>(c.extra + kOffCur);
-    int32_t* s_prev = reinterpret_cast<int32_t*>(c.extra + kOffPrev);
+    float* s_nl = reinterpret_cast<float*>(assume_shared(c.extra) + kOffNl);
+    int32_t* s_cur = reinterpret_cast<int32_t*>(assume_shared(c.extra) + kOffCur);
+    int32_t* s_prev = reinterpret_cast<int32_t*>(assume_shared(c.extra) + kOffPrev);
     epi_bar_sync<128>();       // the previous unit's readers are done
     const int64_t r = static_cast<int64_t>(c.blk) * 256 + c.rank * kSlots + c.tid;
     const bool valid = r < g.N && p.ref[r] < CUDART_INF_F;
@@ -662,9 +662,9 @@ struct CandSumEpi {
 
   __device__ __forceinline__ static void process_tile_sw(State&, const Params& p, const GemmArgs&,
                                                          const SweepCtx& c, int /*nt*/, uint32_t taddr) {
-    const float* s_nl = reinterpret_cast<const float*>(c.extra + kOffNl);
-    const int32_t* s_cur = reinterpret_cast<const int32_t*>(c.extra + kOffCur);
-    const int32_t* s_prev = reinterpret_cast<const int32_t*>(c.extra + kOffPrev);
+    const float* s_nl = reinterpret_cast<const float*>(assume_shared(c.extra) + kOffNl);
+    const int32_t* s_cur = reinterpret_cast<const int32_t*>(assume_shared(c.extra) + kOffCur);
+    const int32_t* s_prev = reinterpret_cast<const int32_t*>(assume_shared(c.extra) + kOffPrev);
     const int prompt = c.blk * 2 + c.rank;
     int vid = -1;
     if (prompt < p.n_prompts && c.tid < min(p.cand_count[prompt], min(p.cand_cap, kSlots)))
@@ -783,7 +783,7 @@ struct ProjApplyEpi {
     cp_async_commit();
   }
   __device__ __forceinline__ static uint8_t* ring_of(const SweepCtx& c) {
-    return c.extra + (c.half * 4 + (c.tid >> 5)) * (kRing * kSubBytes);
+    return assume_shared(c.extra) + (c.half * 4 + (c.tid >> 5)) * (kRing * kSubBytes);
   }
   __device__ __forceinline__ static void begin_unit_tile(State& st, const Params& p, const GemmArgs& g,
                                                          const SweepCtx& c, int row) {

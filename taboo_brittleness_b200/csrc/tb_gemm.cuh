@@ -80,6 +80,13 @@ struct EpiStages { static constexpr int value = 0; };
 template <class Epi>
 struct EpiStages<Epi, decltype(void(Epi::kStages))> { static constexpr int value = Epi::kStages; };
 
+// Epilogues get their shared memory as a plain pointer inside SweepCtx; telling the compiler which address
+// space it is in turns their generic LD / ST into LDS / STS.
+__device__ __forceinline__ uint8_t* assume_shared(uint8_t* p) {
+  __builtin_assume(__isShared(p));
+  return p;
+}
+
 template <int kCtaGroup, int kStagesWanted = 0>
 struct GemmCfg {
   static constexpr int kStages = kStagesWanted > 0 ? kStagesWanted : (kCtaGroup == 1) ? 4 : 6;
@@ -157,6 +164,7 @@ tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   volatile int* pace_slowest = reinterpret_cast<volatile int*>(tmem_slot + 1);  // written by the pacer warp
   volatile int* pace_done = pace_slowest + 1;                                   // written by the producer
   uint8_t* epi_extra = smem + kStages * Cfg::kStageBytes + Cfg::kBarBytes;
+  __builtin_assume(__isShared(epi_extra));
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = static_cast<int>(lane_id());
