@@ -151,7 +151,10 @@ int tb_rmsnorm(const void* x_bf16, const float* w_norm, float eps, int64_t n_row
  * through TMA multicast), 3 = 1x2 pairs (two chunks share the row block), 4 = 2x2 pairs,
  * 5 = mode 2 as the PREFERRED cluster shape with plain pairs as the fallback (groups of four CTAs
  * that do not fit a GPC as one cluster run as two pairs: all 148 SMs work; the default of ops.py);
- * n_chunks must be even in modes 3 and 4.
+ * n_chunks must be even in modes 3 and 4. Modes 2-5 multicast operand tiles within a cluster and take
+ * operands in the current GPU's own memory only (anything else is refused with TB_ERR_INVALID):
+ * TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+ * another GPU's memory hung the GPU. Modes 0 and 1 do not multicast.
  */
 int tb_lens_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
                      int vocab_offset, float softcap, const int32_t* secret_id, int n_chunks,

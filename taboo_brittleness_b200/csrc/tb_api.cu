@@ -175,11 +175,31 @@ tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group,
   return g;
 }
 
+// TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
+// GPU's memory hung the GPU: an operand of a multicast cluster mode must be plain device memory of the current
+// device (peer, IPC-mapped, managed or host memory is refused; cluster modes 0 and 1 do not multicast).
+int operand_is_local(const void* p, const char* what) {
+  cudaPointerAttributes at;
+  TB_CUDA(cudaPointerGetAttributes(&at, p));
+  int dev = -1;
+  TB_CUDA(cudaGetDevice(&dev));
+  if (at.type != cudaMemoryTypeDevice || at.device != dev)
+    return fail(TB_ERR_INVALID, "%s is not memory of the current GPU (device %d): the multicast cluster modes take "
+                "local operands only, use cta_pair 0 or 1", what, dev);
+  return TB_OK;
+}
+
 template <class Epi, int G, int R = 1, int C = 1, bool H = false>
 int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typename Epi::Params& ep,
                 cudaStream_t stream, int sms) {
   using Cfg = tb::GemmCfg<G, tb::EpiStages<Epi>::value>;
   constexpr int kClusterCtas = G * R * C;
+  if constexpr (R * C > 1) {
+    int lrc = operand_is_local(a, "operand A");
+    if (lrc != TB_OK) return lrc;
+    lrc = operand_is_local(b, "operand B");
+    if (lrc != TB_OK) return lrc;
+  }
   // every CTA loads 1/share of a slab (and multicasts it): the TMA box shrinks accordingly
   constexpr int kShareA = Epi::kSweepA ? R : C;
   constexpr int kShareB = Epi::kSweepA ? C : R;

@@ -151,3 +151,29 @@ def test_empty_batch(cuda_lib):
     lw = ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U))
     out = ops.logit_lens(torch.empty(0, 64, dtype=BF16, device="cuda"), lw)
     assert out.lse.shape == (0,) and out.top_id.shape == (0, 10)
+
+
+def test_multicast_modes_refuse_operands_outside_this_gpus_memory(cuda_lib):
+    """Cluster modes 2-5 multicast operand tiles; their operands must be plain memory of the current GPU.
+    A pinned host buffer (reachable from the GPU, but not its memory) is refused there and accepted by the
+    modes that do not multicast."""
+    from taboo_brittleness_b200 import ops
+    from taboo_brittleness_b200._lib import TabooKernelError
+    h = torch.zeros(256, 512, dtype=torch.bfloat16, device="cuda")
+    wu_dev = torch.zeros(1024, 512, dtype=torch.bfloat16, device="cuda")
+    wu_host = torch.zeros(1024, 512, dtype=torch.bfloat16).pin_memory()
+    n_parts = 2 * cuda_lib.tb_lens_parts_per_chunk()
+    f = [torch.empty(n_parts * 256 * k, dtype=torch.float32, device="cuda") for k in (1, 1, 1, 10)]
+    ti = torch.empty(n_parts * 256 * 10, dtype=torch.int32, device="cuda")
+
+    def call(wu, mode):
+        return cuda_lib.tb_lens_partials(h.data_ptr(), wu.data_ptr(), 256, 512, 1024, 0, 30.0, None, 2, mode,
+                                         f[0].data_ptr(), f[1].data_ptr(), f[2].data_ptr(), f[3].data_ptr(), ti.data_ptr(),
+                                         torch.cuda.current_stream().cuda_stream)
+    for mode in (2, 3, 4, 5):
+        assert call(wu_host, mode) != 0
+        assert "current GPU" in ops._lib.last_error()
+        assert call(wu_dev, mode) == 0
+    assert call(wu_host, 1) == 0
+    torch.cuda.synchronize()
+    assert TabooKernelError is not None
