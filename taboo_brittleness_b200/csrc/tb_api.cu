@@ -178,14 +178,62 @@ tb::GemmArgs make_args_sweep_a(int M, int64_t N, int K, int n_chunks, int group,
 // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another
 // GPU's memory hung the GPU: an operand of a multicast cluster mode must be plain device memory of the current
 // device (peer, IPC-mapped, managed or host memory is refused; cluster modes 0 and 1 do not multicast).
-int operand_is_local(const void* p, const char* what) {
-  cudaPointerAttributes at;
-  TB_CUDA(cudaPointerGetAttributes(&at, p));
+// The whole extent [p, p + bytes) is checked, not only its first byte: the range is walked mapping by mapping
+// (a cudaMalloc allocation is one mapping; a range stitched together with cuMemMap has one per mapped chunk), and
+// every piece must be device memory of the current GPU. A range with more than kMaxMappings pieces is refused.
+typedef CUresult (*PointerGetAttributesFn)(unsigned int, CUpointer_attribute*, void**, CUdeviceptr);
+
+int get_pointer_attrs_fn(PointerGetAttributesFn* fn) {
+  static PointerGetAttributesFn cached = nullptr;
+  if (!cached) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    TB_CUDA(cudaGetDriverEntryPoint("cuPointerGetAttributes", &p, cudaEnableDefault, &q));
+    if (q != cudaDriverEntryPointSuccess || p == nullptr)
+      return fail(TB_ERR_CUDA, "cuPointerGetAttributes not available from the driver");
+    cached = reinterpret_cast<PointerGetAttributesFn>(p);
+  }
+  *fn = cached;
+  return TB_OK;
+}
+
+int operand_is_local(const void* p, size_t bytes, const char* what) {
+  constexpr int kMaxMappings = 8192;
+  PointerGetAttributesFn attrs_fn;
+  int rc = get_pointer_attrs_fn(&attrs_fn);
+  if (rc != TB_OK) return rc;
   int dev = -1;
   TB_CUDA(cudaGetDevice(&dev));
-  if (at.type != cudaMemoryTypeDevice || at.device != dev)
-    return fail(TB_ERR_INVALID, "%s is not memory of the current GPU (device %d): the multicast cluster modes take "
-                "local operands only, use cta_pair 0 or 1", what, dev);
+  const uintptr_t begin = reinterpret_cast<uintptr_t>(p);
+  const uintptr_t end = begin + (bytes ? bytes : 1);
+  uintptr_t q = begin;
+  for (int n = 0; q < end; ++n) {
+    if (n >= kMaxMappings)
+      return fail(TB_ERR_INVALID, "%s spans more than %d separate mappings: the multicast cluster modes refuse it, "
+                  "use cta_pair 0 or 1", what, kMaxMappings);
+    unsigned int mem_type = 0, managed = 0;
+    int ordinal = -1;
+    CUdeviceptr map_base = 0, range_base = 0;
+    size_t map_size = 0, range_size = 0;
+    CUpointer_attribute which[7] = {CU_POINTER_ATTRIBUTE_MEMORY_TYPE, CU_POINTER_ATTRIBUTE_IS_MANAGED,
+                                    CU_POINTER_ATTRIBUTE_DEVICE_ORDINAL, CU_POINTER_ATTRIBUTE_MAPPING_BASE_ADDR,
+                                    CU_POINTER_ATTRIBUTE_MAPPING_SIZE, CU_POINTER_ATTRIBUTE_RANGE_START_ADDR,
+                                    CU_POINTER_ATTRIBUTE_RANGE_SIZE};
+    void* data[7] = {&mem_type, &managed, &ordinal, &map_base, &map_size, &range_base, &range_size};
+    const CUresult r = attrs_fn(7, which, data, static_cast<CUdeviceptr>(q));
+    if (r != CUDA_SUCCESS || mem_type != CU_MEMORYTYPE_DEVICE || managed || ordinal != dev)
+      return fail(TB_ERR_INVALID, "%s is not memory of the current GPU (device %d) at byte %llu of %llu: the multicast "
+                  "cluster modes take local operands only, use cta_pair 0 or 1", what, dev,
+                  static_cast<unsigned long long>(q - begin), static_cast<unsigned long long>(bytes));
+    // the piece that holds q: the mapped chunk where the driver reports one, else the allocation
+    uintptr_t piece_end = 0;
+    if (map_size > 0 && map_base <= q && q < map_base + map_size) piece_end = static_cast<uintptr_t>(map_base) + map_size;
+    else if (range_size > 0 && range_base <= q && q < range_base + range_size) piece_end = static_cast<uintptr_t>(range_base) + range_size;
+    if (piece_end <= q)
+      return fail(TB_ERR_INVALID, "%s: the driver reports no mapping around byte %llu: the multicast cluster modes "
+                  "refuse it, use cta_pair 0 or 1", what, static_cast<unsigned long long>(q - begin));
+    q = piece_end;
+  }
   return TB_OK;
 }
 
@@ -195,9 +243,10 @@ int launch_gemm(const void* a, const void* b, const tb::GemmArgs& g, const typen
   using Cfg = tb::GemmCfg<G, tb::EpiStages<Epi>::value>;
   constexpr int kClusterCtas = G * R * C;
   if constexpr (R * C > 1) {
-    int lrc = operand_is_local(a, "operand A");
+    // what the two tensor maps cover: [rows, K] bf16 each
+    int lrc = operand_is_local(a, static_cast<size_t>(g.M) * g.K * 2, "operand A");
     if (lrc != TB_OK) return lrc;
-    lrc = operand_is_local(b, "operand B");
+    lrc = operand_is_local(b, static_cast<size_t>(g.N) * g.K * 2, "operand B");
     if (lrc != TB_OK) return lrc;
   }
   // every CTA loads 1/share of a slab (and multicasts it): the TMA box shrinks accordingly

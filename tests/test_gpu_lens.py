@@ -177,3 +177,30 @@ def test_multicast_modes_refuse_operands_outside_this_gpus_memory(cuda_lib):
     assert call(wu_host, 1) == 0
     torch.cuda.synchronize()
     assert TabooKernelError is not None
+
+
+def test_multicast_modes_check_the_whole_operand_extent(cuda_lib):
+    """The guard walks every byte range the tensor maps cover, not only the base pointers: a pointer into
+    the middle of a local allocation passes, an extent that runs far past the end of its allocation (into
+    address space that cannot all be this GPU's memory) is refused before any launch."""
+    from taboo_brittleness_b200 import ops
+    big = torch.zeros(4 * 1024, 512, dtype=torch.bfloat16, device="cuda")
+    h = torch.zeros(256, 512, dtype=torch.bfloat16, device="cuda")
+    n_parts = 2 * cuda_lib.tb_lens_parts_per_chunk()
+    f = [torch.empty(n_parts * 256 * k, dtype=torch.float32, device="cuda") for k in (1, 1, 1, 10)]
+    ti = torch.empty(n_parts * 256 * 10, dtype=torch.int32, device="cuda")
+
+    def call(wu_ptr, V, mode):
+        return cuda_lib.tb_lens_partials(h.data_ptr(), wu_ptr, 256, 512, V, 0, 30.0, None, 2, mode,
+                                         f[0].data_ptr(), f[1].data_ptr(), f[2].data_ptr(), f[3].data_ptr(), ti.data_ptr(),
+                                         torch.cuda.current_stream().cuda_stream)
+    interior = big[1024:2048]
+    assert interior.data_ptr() != big.data_ptr()
+    for mode in (2, 5):
+        assert call(interior.data_ptr(), 1024, mode) == 0
+    torch.cuda.synchronize()
+    # an extent of 2 TB cannot be this GPU's memory all the way: refused before any launch, whatever lies
+    # directly behind the allocation
+    assert call(big.data_ptr(), 2_000_000_000, 2) != 0
+    err = ops._lib.last_error()
+    assert "current GPU" in err or "no mapping" in err or "separate mappings" in err, err
