@@ -8,7 +8,12 @@
  *
  * Conventions
  *   - every pointer is a DEVICE pointer into memory the caller allocated (inputs, outputs and
- *     scratch alike); the library allocates nothing and keeps no state between calls;
+ *     scratch alike); the library allocates nothing. Two blocks of device memory are part of the
+ *     library image on every GPU that loads it and live until the process exits: the pacing counters
+ *     of the multicast cluster modes (8 rotating slots of 128 ints; with more than 8 such launches in
+ *     flight on different streams two launches share a slot, which only costs pacing accuracy -- every
+ *     wait on them is bounded) and the 6 MB scratch of tb_logit_lens_static. Nothing else persists
+ *     between calls;
  *   - matrices are dense row-major; "bf16" = __nv_bfloat16, stored as uint16_t bits here;
  *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it and never
  *     synchronise;
@@ -107,16 +112,6 @@ int tb_lowrank_remove(const void* x_bf16, const void* ut_bf16, int r, int64_t n_
                       const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
                       void* stream);
 
-/* K2 for ranks above 8, in two steps with caller scratch c (f32 [n_rows, r]): tb_lowrank_coeffs
- * computes C = x U on the tensor cores (the tcgen05 main loop, U^T as its one swept tile),
- * tb_lowrank_apply subtracts C U^T, rounds to bf16 and applies the fused final RMSNorm
- * (d <= 4096). Same result contract as tb_lowrank_remove (Plan:148); no code in the reference. */
-int tb_lowrank_coeffs(const void* x_bf16, const void* ut_bf16, int r, int64_t n_rows, int d,
-                      float* out_c, void* stream);
-int tb_lowrank_apply(const void* x_bf16, const void* ut_bf16, const float* c, int r, int64_t n_rows,
-                     int d, const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
-                     void* stream);
-
 /* K2 for ranks 9..64 on the tensor cores, one call: C = x U (tcgen05, fp32 accumulate), the
  * coefficients split into bf16 head + remainder, x' = bf16(x - [C_hi | C_lo] [U | U]^T) in the epilogue
  * of a second tcgen05 pass (K = 2 * ceil32(r), N = d), and the fused final RMSNorm from the rows' sums
@@ -210,7 +205,7 @@ int tb_probs_ll_colsum(const float* probs, int T, int V, const int32_t* cur_id, 
  * partials carry pm = ref_lse, tb_lens_merge needs no change) and, per prompt (128 row slots as
  * K5), lists every vocabulary id whose masked column sum of those terms reaches tau[prompt].
  *   cand_count : i32 [n_prompts], MUST be zero on entry      cand_id : i32 [n_prompts, cand_cap]
- * tb_ll_candidates_exact then recomputes the true sums of the listed ids (with the exact lse
+ * tb_ll_candidates_exact_tc then recomputes the true sums of the listed ids (with the exact lse
  * from tb_lens_merge) and writes the k best; out_flag[p] = 1 certifies that no unlisted id can
  * belong to them (list did not overflow and the k-th sum >= max_t exp(ref_lse - lse) * tau).
  * Prompts with flag 0 must be redone with tb_ll_topk_partials. out_theta = the k-th best sum
@@ -222,15 +217,7 @@ int tb_lens_ll_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows
                         const int32_t* prev_id, int n_chunks, int cta_pair, float* pm, float* ps,
                         float* psec, float* ptv, int32_t* pti, int32_t* cand_count,
                         int32_t* cand_id, int cand_cap, void* stream);
-int tb_ll_candidates_exact(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V,
-                           int vocab_offset, float softcap, const float* lse, const float* ref_lse,
-                           const float* tau, const int32_t* cur_id, const int32_t* prev_id,
-                           const int32_t* cand_count, const int32_t* cand_id, int cand_cap, int k,
-                           float* out_val, int32_t* out_id, float* out_theta, int32_t* out_flag,
-                           void* stream);
-
-/* The same contract as tb_ll_candidates_exact with the sums on the tensor cores: the candidates'
- * W_U rows are gathered into 128 slots per prompt (wc_scratch: bf16 [n_rows, d], n_rows = 128 *
+/* K6, with the sums on the tensor cores: the candidates' W_U rows are gathered into 128 slots per prompt (wc_scratch: bf16 [n_rows, d], n_rows = 128 *
  * n_prompts), a block-diagonal tcgen05 GEMM multiplies each prompt pair's candidate tile with the
  * same pair's rows (sum_scratch: f32 [n_prompts, 128]), a small kernel ranks and certifies. Prompts
  * with more than 128 listed candidates get flag 0. */

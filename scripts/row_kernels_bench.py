@@ -46,10 +46,6 @@ for r in (1, 2, 4, 8, 16, 32, 64):
     ms = timed(lambda: ops.lowrank_remove(x, U, w_norm=w_norm, want_x=False, want_h=True))
     print(json.dumps({"kernel": "K2 lowrank_remove", "rank": r, "rows": rows, "ms": ms, "GBps": bytes_alg / ms / 1e6,
                       "frac_of_measured_copy": bytes_alg / ms / 1e6 / peaks["hbm_gbs"], "gflops": 4.0 * D * r * rows / ms / 1e6}), flush=True)
-    if r >= ops.LOWRANK_TC_MIN:
-        ms = timed(lambda: ops.lowrank_remove(x, U, w_norm=w_norm, want_x=False, want_h=True, tensor_cores=False))
-        print(json.dumps({"kernel": "K2 lowrank_remove, second product on CUDA cores", "rank": r, "rows": rows, "ms": ms,
-                          "GBps": bytes_alg / ms / 1e6, "frac_of_measured_copy": bytes_alg / ms / 1e6 / peaks["hbm_gbs"]}), flush=True)
 sae_s = synthetic.make_sae(D, S, seed=42, device="cuda")
 sae = ops.SaeWeights.from_sae_lens_layout(sae_s.W_enc, sae_s.b_enc, sae_s.threshold, sae_s.W_dec, sae_s.b_dec)
 n_enc = min(rows, 131072)

@@ -47,8 +47,6 @@ SIGNATURES = {
     "tb_sae_ablate_decode": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int,
                                      c_int64, c_int, c_int, _P, c_float, _P, _P, _P]),
     "tb_lowrank_remove": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
-    "tb_lowrank_coeffs": (c_int, [_P, _P, c_int, c_int64, c_int, _P, _P]),
-    "tb_lowrank_apply": (c_int, [_P, _P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
     "tb_lowrank_tc_scratch_bytes": (c_int64, [c_int64, c_int, c_int]),
     "tb_lowrank_remove_tc": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, c_int64, _P, _P, _P]),
     "tb_rmsnorm": (c_int, [_P, _P, c_float, c_int64, c_int, _P, _P]),
@@ -63,8 +61,6 @@ SIGNATURES = {
     "tb_probs_ll_colsum": (c_int, [_P, c_int, c_int, _P, _P, _P, _P]),
     "tb_lens_ll_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, c_int, c_int,
                                     _P, _P, _P, _P, _P, _P, _P, c_int, _P]),
-    "tb_ll_candidates_exact": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P, _P,
-                                       c_int, c_int, _P, _P, _P, _P, _P]),
     "tb_ll_candidates_exact_tc": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, _P, _P, _P, _P, _P, _P,
                                           c_int, c_int, _P, _P, _P, _P, _P, _P, _P]),
     "tb_logit_lens_static": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,

@@ -640,52 +640,6 @@ int tb_lowrank_remove(const void* x, const void* ut, int r, int64_t n_rows, int 
   return TB_OK;
 }
 
-int tb_lowrank_coeffs(const void* x, const void* ut, int r, int64_t n_rows, int d, float* out_c, void* stream) {
-  DevInfo di;
-  int rc = device_info(&di);
-  if (rc != TB_OK) return rc;
-  if (r < 1 || r > tb::kProjMaxRank) return fail(TB_ERR_INVALID, "rank %d outside [1, %d]", r, tb::kProjMaxRank);
-  rc = check_gemm_operands(x, ut, n_rows, r, d);
-  if (rc != TB_OK) return rc;
-  if (!out_c) return fail(TB_ERR_INVALID, "null output");
-  // C = x U on the tensor cores: U^T [r, d] is the single swept tile (rows past r are zero-filled by TMA)
-  tb::GemmArgs g = make_args(n_rows, r, d, 1, 2);
-  tb::DenseEpi::Params ep{out_c};
-  return launch_gemm<tb::DenseEpi, 2>(x, ut, g, ep, static_cast<cudaStream_t>(stream), di.sms);
-}
-
-int tb_lowrank_apply(const void* x, const void* ut, const float* c, int r, int64_t n_rows, int d,
-                     const float* w_norm, float eps, void* out_x, void* out_h, void* stream) {
-  DevInfo di;
-  int rc = device_info(&di);
-  if (rc != TB_OK) return rc;
-  if (!x || !ut || !c) return fail(TB_ERR_INVALID, "null pointer");
-  if (r < 1 || r > tb::kProjMaxRank) return fail(TB_ERR_INVALID, "rank %d outside [1, %d]", r, tb::kProjMaxRank);
-  if (d <= 0 || d % 8 != 0 || d > 4096) return fail(TB_ERR_INVALID, "d=%d must be a multiple of 8, at most 4096", d);
-  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
-  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
-  if (n_rows == 0) return TB_OK;
-  tb::ProjApplyArgs a;
-  a.x = static_cast<const __nv_bfloat16*>(x);
-  a.ut = static_cast<const __nv_bfloat16*>(ut);
-  a.c = c;
-  a.r = r;
-  a.w_norm = w_norm;
-  a.eps = eps;
-  a.out_x = static_cast<__nv_bfloat16*>(out_x);
-  a.out_h = static_cast<__nv_bfloat16*>(out_h);
-  a.n_rows = static_cast<int>(n_rows);
-  a.d = d;
-  int threads = ((d / 8) + 31) / 32 * 32;
-  if (threads < 64) threads = 64;
-  const int64_t tiles = (n_rows + tb::kProjApplyRows - 1) / tb::kProjApplyRows;
-  const int64_t max_grid = static_cast<int64_t>(di.sms) * 2;
-  const unsigned grid = static_cast<unsigned>(tiles < max_grid ? tiles : max_grid);
-  tb::tb_lowrank_apply_kernel<<<grid, threads, 0, static_cast<cudaStream_t>(stream)>>>(a);
-  TB_CUDA(cudaGetLastError());
-  return TB_OK;
-}
-
 namespace {
 // K2 on the tensor cores: scratch layout (256-byte aligned pieces) and the chunking of step 2
 struct ProjTcPlan {
@@ -974,38 +928,6 @@ int tb_lens_ll_partials(const void* h, const void* w_u, int64_t n_rows, int d, i
   ep.cand_cap = cand_cap;
   ep.n_prompts = static_cast<int>((n_rows + 127) / 128);
   return launch_gemm_mode<tb::LensLLEpi>(cm, h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
-}
-
-int tb_ll_candidates_exact(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,
-                           float softcap, const float* lse, const float* ref_lse, const float* tau,
-                           const int32_t* cur_id, const int32_t* prev_id, const int32_t* cand_count,
-                           const int32_t* cand_id, int cand_cap, int k, float* out_val, int32_t* out_id,
-                           float* out_theta, int32_t* out_flag, void* stream) {
-  DevInfo di;
-  int rc = device_info(&di);
-  if (rc != TB_OK) return rc;
-  if (!h || !w_u || !lse || !ref_lse || !tau || !cand_count || !cand_id || !out_val || !out_id || !out_theta ||
-      !out_flag)
-    return fail(TB_ERR_INVALID, "null pointer");
-  if (d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
-  if (k < 1 || k > TB_TOPK) return fail(TB_ERR_INVALID, "k=%d outside [1, %d]", k, TB_TOPK);
-  if (cand_cap < 1) return fail(TB_ERR_INVALID, "cand_cap=%d", cand_cap);
-  if (n_rows <= 0) return TB_OK;
-  const size_t smem = static_cast<size_t>(tb::kCandGroup) * d * 2;
-  if (smem > 200 * 1024) return fail(TB_ERR_INVALID, "d=%d too large for the candidate kernel", d);
-  tb::CandArgs a;
-  a.h = static_cast<const __nv_bfloat16*>(h);
-  a.w_u = static_cast<const __nv_bfloat16*>(w_u);
-  a.lse = lse; a.ref = ref_lse; a.tau = tau; a.cur_id = cur_id; a.prev_id = prev_id;
-  a.cand_count = cand_count; a.cand_id = cand_id; a.cap = cand_cap; a.k = k; a.d = d; a.V = V;
-  a.vocab_offset = vocab_offset; a.n_rows = static_cast<int>(n_rows); a.softcap = softcap;
-  a.out_val = out_val; a.out_id = out_id; a.out_theta = out_theta; a.out_flag = out_flag;
-  TB_CUDA(cudaFuncSetAttribute(tb::tb_ll_candidates_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                               static_cast<int>(smem)));
-  const unsigned grid = static_cast<unsigned>((n_rows + 127) / 128);
-  tb::tb_ll_candidates_exact_kernel<<<grid, tb::kCandThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
-  TB_CUDA(cudaGetLastError());
-  return TB_OK;
 }
 
 int tb_ll_candidates_exact_tc(const void* h, const void* w_u, int64_t n_rows, int d, int V, int vocab_offset,

@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(kAblThreads) tb_rmsnorm_kernel(const __nv_bflo
 // squares that step 2's epilogue left behind (tb_epilogues.cuh: ProjApplyEpi). Same row-group layout and
 // arithmetic as tb_rmsnorm_kernel, minus the reduction. In place (xin == out_h) is fine.
 template <int NV>
-__global__ void __launch_bounds__(kAblThreads) tb_scale_rows_kernel(const __nv_bfloat16* __restrict__ xin,
+__global__ void __launch_bounds__(kAblThreads) tb_scale_rows_kernel(const __nv_bfloat16* xin,   // (may alias out_h)
                                                                     const float* __restrict__ ss, int n_parts,
                                                                     const float* __restrict__ w, int n_rows, int d,
                                                                     float eps, __nv_bfloat16* out_h) {
@@ -763,206 +763,6 @@ __global__ void tb_probs_colsum_kernel(const float* __restrict__ probs, int T, i
 }
 
 // -----------------------------------------------------------------------------------------
-// K6: exact LL-Top-k of the candidates K3F listed, and the certificate that they suffice.
-// One CTA per prompt (128 row slots). For every candidate vocabulary id v:
-//   acc[v] = sum_t [v != cur_t][v != prev_t] exp(softcap(<h_t, W_U[v]>) - lse_t)
-// with fp32 dot products of the bf16 operands (W_U rows staged in shared memory eight at a
-// time, h rows streamed by the warps). Then the k best candidates, sorted.
-// Certified (flag = 1) when the list did not overflow and the k-th best sum is at least
-// max_t exp(ref_t - lse_t) * tau * (1 + 2^-10): no unlisted column can reach it, because its
-// proxy sum stayed below tau and exp(ref_t - lse_t) is exactly the factor between a proxy
-// term and the true one. theta (the k-th best sum) seeds the next condition's threshold.
-// -----------------------------------------------------------------------------------------
-constexpr int kCandGroup = 8;
-constexpr int kCandThreads = 256;
-constexpr int kCandMax = 1024;
-
-struct CandArgs {
-  const __nv_bfloat16* h;      // [n_rows, d] normalised operand, 128 row slots per prompt
-  const __nv_bfloat16* w_u;    // [V, d]
-  const float* lse;            // [n_rows] exact logsumexp (+inf / nan in empty slots)
-  const float* ref;            // [n_rows] the reference K3F used (+inf: empty slot)
-  const float* tau;            // [n_prompts]
-  const int32_t* cur_id;       // nullable
-  const int32_t* prev_id;      // nullable
-  const int32_t* cand_count;   // [n_prompts]
-  const int32_t* cand_id;      // [n_prompts, cap]
-  int cap, k, d, V, vocab_offset, n_rows;
-  float softcap;
-  float* out_val;              // [n_prompts, k]
-  int32_t* out_id;             // [n_prompts, k]
-  float* out_theta;            // [n_prompts]
-  int32_t* out_flag;           // [n_prompts]
-};
-
-__global__ void __launch_bounds__(kCandThreads) tb_ll_candidates_exact_kernel(const CandArgs a) {
-  extern __shared__ __align__(16) uint8_t cand_smem[];
-  __nv_bfloat16* s_w = reinterpret_cast<__nv_bfloat16*>(cand_smem);          // [8][d]
-  __shared__ float s_acc[kCandMax];
-  __shared__ float s_part[kCandThreads / 32][kCandGroup];
-  __shared__ float s_nl[128];
-  __shared__ int32_t s_cur[128], s_prev[128];
-  __shared__ float s_red[kCandThreads / 32];
-  __shared__ int s_redi[kCandThreads / 32];
-  const int p = blockIdx.x;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  constexpr int kWarps = kCandThreads / 32;
-  const int64_t row0 = static_cast<int64_t>(p) * 128;
-  const int n_cand_all = a.cand_count[p];
-  const int n_cand = min(n_cand_all, min(a.cap, kCandMax));
-  const int nvec = a.d >> 3;
-  const float inv_cap = a.softcap > 0.0f ? 1.0f / a.softcap : 0.0f;
-
-  // per-slot constants and g_max = max_t exp(ref_t - lse_t) over the slots that hold a token
-  float g = 0.0f;
-  if (tid < 128) {
-    const int64_t r = row0 + tid;
-    const bool valid = r < a.n_rows && a.ref[r] < CUDART_INF_F;
-    const float lse = valid ? a.lse[r] : CUDART_INF_F;
-    s_nl[tid] = valid ? -lse : -CUDART_INF_F;
-    s_cur[tid] = (valid && a.cur_id) ? a.cur_id[r] : -1;
-    s_prev[tid] = (valid && a.prev_id) ? a.prev_id[r] : -1;
-    if (valid) g = expf(a.ref[r] - lse);
-  }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) g = fmaxf(g, __shfl_xor_sync(0xffffffffu, g, o));
-  if (lane == 0) s_red[warp] = g;
-  __syncthreads();
-  float g_max = 0.0f;
-  for (int w = 0; w < kWarps; ++w) g_max = fmaxf(g_max, s_red[w]);
-  __syncthreads();
-
-  for (int c0 = 0; c0 < n_cand; c0 += kCandGroup) {
-    const int nc = min(kCandGroup, n_cand - c0);
-    // stage the candidates' W_U rows (zeros for the unused slots of the last group)
-    for (int i = tid; i < kCandGroup * nvec; i += kCandThreads) {
-      const int j = i / nvec, vec = i - j * nvec;
-      int4 w = make_int4(0, 0, 0, 0);
-      if (j < nc) {
-        const int v = a.cand_id[static_cast<size_t>(p) * a.cap + c0 + j] - a.vocab_offset;
-        if (v >= 0 && v < a.V) w = __ldg(reinterpret_cast<const int4*>(a.w_u + static_cast<size_t>(v) * a.d) + vec);
-      }
-      reinterpret_cast<int4*>(s_w)[i] = w;
-    }
-    __syncthreads();
-    float mine[kCandGroup];   // lane j < 8 accumulates candidate j over this warp's rows
-#pragma unroll
-    for (int j = 0; j < kCandGroup; ++j) mine[j] = 0.0f;
-    // two rows per pass: every W_U vector read from shared memory (and unpacked) serves both
-    for (int t0 = warp; t0 < 128; t0 += 2 * kWarps) {
-      const int tr[2] = {t0, t0 + kWarps};
-      float nl[2];
-      const int4* hr[2];
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-        nl[q] = s_nl[tr[q]];
-        hr[q] = reinterpret_cast<const int4*>(a.h + (row0 + tr[q]) * a.d);
-      }
-      if (nl[0] == -CUDART_INF_F && nl[1] == -CUDART_INF_F) continue;   // two empty slots (uniform over the warp)
-      float dot[2][kCandGroup];
-#pragma unroll
-      for (int q = 0; q < 2; ++q)
-#pragma unroll
-        for (int j = 0; j < kCandGroup; ++j) dot[q][j] = 0.0f;
-      for (int vec = lane; vec < nvec; vec += 32) {
-        float hv[2][8];
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          int4 raw = make_int4(0, 0, 0, 0);
-          if (nl[q] != -CUDART_INF_F) raw = __ldg(hr[q] + vec);     // empty slots may lie past the last row
-          unpack8(raw, hv[q]);
-        }
-#pragma unroll
-        for (int j = 0; j < kCandGroup; ++j) {
-          float wv[8];
-          unpack8(reinterpret_cast<const int4*>(s_w)[j * nvec + vec], wv);
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            dot[0][j] = fmaf(hv[0][e], wv[e], dot[0][j]);
-            dot[1][j] = fmaf(hv[1][e], wv[e], dot[1][j]);
-          }
-        }
-      }
-#pragma unroll
-      for (int q = 0; q < 2; ++q) {
-#pragma unroll
-        for (int j = 0; j < kCandGroup; ++j) {
-#pragma unroll
-          for (int o = 16; o > 0; o >>= 1) dot[q][j] += __shfl_xor_sync(0xffffffffu, dot[q][j], o);
-        }
-        if (nl[q] == -CUDART_INF_F) continue;
-        const int cur = s_cur[tr[q]], prev = s_prev[tr[q]];
-#pragma unroll
-        for (int j = 0; j < kCandGroup; ++j) {
-          if (j < nc) {
-            float l = dot[q][j];
-            if (a.softcap > 0.0f) l = a.softcap * tanhf(l * inv_cap);
-            const int id = a.cand_id[static_cast<size_t>(p) * a.cap + c0 + j];
-            const float qv = (id == cur || id == prev) ? 0.0f : expf(l + nl[q]);
-            mine[j] += qv;   // every lane holds the same value; fixed order over the rows
-          }
-        }
-      }
-    }
-    if (lane == 0) {
-#pragma unroll
-      for (int j = 0; j < kCandGroup; ++j) s_part[warp][j] = mine[j];
-    }
-    __syncthreads();
-    if (tid < nc) {
-      float acc = 0.0f;
-      for (int w = 0; w < kWarps; ++w) acc += s_part[w][tid];
-      s_acc[c0 + tid] = acc;
-    }
-    __syncthreads();
-  }
-
-  // k rounds of block-wide arg-max over the candidates (value desc, id asc on ties)
-  float theta = -CUDART_INF_F;
-  for (int round = 0; round < a.k; ++round) {
-    float bv = -CUDART_INF_F;
-    int bi = -1, bpos = -1;
-    for (int i = tid; i < n_cand; i += kCandThreads) {
-      const float v = s_acc[i];
-      const int id = a.cand_id[static_cast<size_t>(p) * a.cap + i];
-      if (v > bv || (v == bv && v > -CUDART_INF_F && id < bi)) { bv = v; bi = id; bpos = i; }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      const int op = __shfl_xor_sync(0xffffffffu, bpos, o);
-      if (ov > bv || (ov == bv && oi >= 0 && (bi < 0 || oi < bi))) { bv = ov; bi = oi; bpos = op; }
-    }
-    if (lane == 0) { s_red[warp] = bv; s_redi[warp] = bpos; }
-    __syncthreads();
-    float wv = -CUDART_INF_F;
-    int wpos = -1, wid = -1;
-    for (int w = 0; w < kWarps; ++w) {
-      const int pos = s_redi[w];
-      if (pos < 0) continue;
-      const int id = a.cand_id[static_cast<size_t>(p) * a.cap + pos];
-      if (s_red[w] > wv || (s_red[w] == wv && id < wid)) { wv = s_red[w]; wpos = pos; wid = id; }
-    }
-    __syncthreads();
-    if (tid == 0) {
-      a.out_val[static_cast<size_t>(p) * a.k + round] = wv;
-      a.out_id[static_cast<size_t>(p) * a.k + round] = wid;
-      if (wpos >= 0) s_acc[wpos] = -CUDART_INF_F;
-    }
-    if (wpos >= 0) theta = wv;
-    else theta = -CUDART_INF_F;
-    __syncthreads();
-  }
-  if (tid == 0) {
-    a.out_theta[p] = theta;
-    const bool ok = n_cand_all <= min(a.cap, kCandMax) && theta > 0.0f &&
-                    theta >= g_max * a.tau[p] * (1.0f + 0.0009765625f);
-    a.out_flag[p] = ok ? 1 : 0;
-  }
-}
-
-// -----------------------------------------------------------------------------------------
 // K2 / a5: low-rank direction removal  x' = x - (x U) U^T,  U [d, r] orthonormal, r <= 64
 // (Execution Plan:148, r_edited = r - P_U(r)). The caller passes U^T [r, d] (bf16) so that
 // both thin products read 16-byte contiguous slices: phase 1 forms c = x U for a tile of
@@ -1243,108 +1043,6 @@ __global__ void __launch_bounds__(kProjSmallThreads, 2) tb_lowrank_small_kernel(
 
 
 // -----------------------------------------------------------------------------------------
-// K2 for ranks 9..64, second half: x' = x - C U^T with the coefficients C = x U (fp32 [rows, r])
-// already computed on the tensor cores (tb_lowrank_coeffs: the tcgen05 main loop with U^T as
-// the one swept tile). Eight rows per tile in registers, one 16-byte column slice per thread:
-// every U^T vector fetched from L2 feeds 64 FMAs. Rounding and the fused RMSNorm as in the
-// other row kernels.
-// -----------------------------------------------------------------------------------------
-constexpr int kProjApplyRows = 8;
-
-struct ProjApplyArgs {
-  const __nv_bfloat16* x;    // [n_rows, d]
-  const __nv_bfloat16* ut;   // [r, d]
-  const float* c;            // [n_rows, r]
-  int r;
-  const float* w_norm;       // [d] or nullptr
-  float eps;
-  __nv_bfloat16* out_x;      // nullable
-  __nv_bfloat16* out_h;      // nullable
-  int n_rows, d;
-};
-
-__global__ void __launch_bounds__(512, 1) tb_lowrank_apply_kernel(const ProjApplyArgs a) {
-  __shared__ float s_c[kProjApplyRows][kProjMaxRank];
-  __shared__ float s_ss[16][kProjApplyRows];
-  const int nvec = a.d >> 3;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nwarps = blockDim.x >> 5;
-  const bool own = tid < nvec;                     // blockDim.x >= nvec (host guarantees d <= 4096)
-  const int n_tiles = (a.n_rows + kProjApplyRows - 1) / kProjApplyRows;
-  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-    const int row0 = tile * kProjApplyRows;
-    __syncthreads();                               // s_c / s_ss of the previous tile are no longer read
-    for (int i = tid; i < kProjApplyRows * a.r; i += blockDim.x) {
-      const int rr = i / a.r, j = i - rr * a.r;
-      s_c[rr][j] = (row0 + rr < a.n_rows) ? -a.c[static_cast<size_t>(row0 + rr) * a.r + j] : 0.0f;
-    }
-    float acc[kProjApplyRows][8];
-#pragma unroll
-    for (int rr = 0; rr < kProjApplyRows; ++rr) {
-      int4 raw = make_int4(0, 0, 0, 0);
-      if (own && row0 + rr < a.n_rows) raw = __ldg(reinterpret_cast<const int4*>(a.x + static_cast<size_t>(row0 + rr) * a.d) + tid);
-      unpack8(raw, acc[rr]);
-    }
-    __syncthreads();
-    if (own) {
-#pragma unroll 2
-      for (int j = 0; j < a.r; ++j) {
-        float u[8];
-        unpack8(__ldg(reinterpret_cast<const int4*>(a.ut + static_cast<size_t>(j) * a.d) + tid), u);
-#pragma unroll
-        for (int rr = 0; rr < kProjApplyRows; ++rr) {
-          const float cj = s_c[rr][j];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[rr][e] = fmaf(cj, u[e], acc[rr][e]);
-        }
-      }
-    }
-    float ss[kProjApplyRows];
-#pragma unroll
-    for (int rr = 0; rr < kProjApplyRows; ++rr) {
-      ss[rr] = 0.0f;
-      if (own) {
-        const Bf16x8 pk = pack8(acc[rr]);
-        if (row0 + rr < a.n_rows && a.out_x) reinterpret_cast<Bf16x8*>(a.out_x + static_cast<size_t>(row0 + rr) * a.d)[tid] = pk;
-        unpack8(pk, acc[rr]);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) ss[rr] = fmaf(acc[rr][e], acc[rr][e], ss[rr]);
-      }
-    }
-    if (a.out_h) {
-#pragma unroll
-      for (int rr = 0; rr < kProjApplyRows; ++rr) {
-        float v = ss[rr];
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) s_ss[warp][rr] = v;
-      }
-      __syncthreads();
-      float w8[8];
-      if (own) {
-        const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * tid);
-        const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * tid + 1);
-        w8[0] = 1.0f + w0.x; w8[1] = 1.0f + w0.y; w8[2] = 1.0f + w0.z; w8[3] = 1.0f + w0.w;
-        w8[4] = 1.0f + w1.x; w8[5] = 1.0f + w1.y; w8[6] = 1.0f + w1.z; w8[7] = 1.0f + w1.w;
-      }
-#pragma unroll
-      for (int rr = 0; rr < kProjApplyRows; ++rr) {
-        float tot = 0.0f;
-        for (int w = 0; w < nwarps; ++w) tot += s_ss[w][rr];
-        const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(tot, static_cast<float>(a.d)), a.eps)));
-        if (own && row0 + rr < a.n_rows) {
-          float h[8];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) h[e] = __fmul_rn(__fmul_rn(acc[rr][e], rstd), w8[e]);
-          reinterpret_cast<Bf16x8*>(a.out_h + static_cast<size_t>(row0 + rr) * a.d)[tid] = pack8(h);
-        }
-      }
-    }
-  }
-}
-
-
-// -----------------------------------------------------------------------------------------
 // K2 for ranks 1..2 in the row-group layout of tb_rmsnorm_kernel (four rows per CTA, 128 threads
 // per row, U^T in shared memory): at these ranks the two thin products are a handful of FMAs
 // per element, and what matters is the number of rows in flight -- this is the norm kernel with
@@ -1467,7 +1165,7 @@ __global__ void __launch_bounds__(kAblThreads) tb_lowrank_tiny_kernel(const Proj
 //              (one warp per slot, 16-byte copies; empty slots are left untouched -- nobody reads
 //              their sums)
 //   finalize : per prompt, the k best exact sums (value desc, id asc on ties), theta, and the
-//              certificate flag -- the tail of tb_ll_candidates_exact_kernel.
+//              certificate flag.
 // -----------------------------------------------------------------------------------------
 constexpr int kCandSlots = 128;
 

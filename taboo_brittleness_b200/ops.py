@@ -37,6 +37,12 @@ def _need(t: torch.Tensor, dtype: torch.dtype, name: str, ndim: Optional[int] = 
         raise TabooKernelError(f"{name} must be {ndim}-D, got shape {tuple(t.shape)}", _lib.TB_ERR_INVALID)
     if not t.is_contiguous():
         raise TabooKernelError(f"{name} must be contiguous", _lib.TB_ERR_INVALID)
+    # kernels launch on torch's CURRENT device and stream: a tensor of another GPU would be read through a
+    # peer mapping (or fault), and the per-device scratch caches would be mixed up
+    if t.device.index != torch.cuda.current_device():
+        raise TabooKernelError(f"{name} lives on cuda:{t.device.index} but the current device is "
+                               f"cuda:{torch.cuda.current_device()} (use torch.cuda.device(...) or set_device)",
+                               _lib.TB_ERR_INVALID)
     return t
 
 
@@ -314,11 +320,11 @@ _PROJ_SCRATCH: dict = {}
 
 
 def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.Tensor] = None,
-                   eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False,
-                   tensor_cores: bool = True) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+                   eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False
+                   ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
     """x' = x - (x U) U^T for orthonormal U [d, r], r <= 64 (Plan:148). Small ranks run in one
     HBM-bound CUDA-core kernel (up to 7 by default); from 8 on both thin products go to the tensor cores
-    (``tb_lowrank_remove_tc``; ``tensor_cores=False`` keeps the second product on the CUDA cores)."""
+    (``tb_lowrank_remove_tc``)."""
     _need(x, torch.bfloat16, "x", 2)
     _need(U, torch.bfloat16, "U", 2)
     n, d = x.shape
@@ -331,7 +337,7 @@ def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.T
     if n == 0:
         return out_x, out_h
     lib = _lib.load()
-    if r >= LOWRANK_TC_MIN and tensor_cores:
+    if r >= LOWRANK_TC_MIN:
         need = int(lib.tb_lowrank_tc_scratch_bytes(n, d, r))
         if need < 0:
             raise TabooKernelError(f"tb_lowrank_tc_scratch_bytes({n}, {d}, {r}) failed", _lib.TB_ERR_INVALID)
@@ -341,13 +347,6 @@ def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.T
             buf = _PROJ_SCRATCH[key] = torch.empty(need, dtype=torch.uint8, device=x.device)
         check(lib.tb_lowrank_remove_tc(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(buf), buf.numel(),
                                        _ptr(out_x), _ptr(out_h), _stream()), "tb_lowrank_remove_tc")
-        return out_x, out_h
-    if r > LOWRANK_SMALL and d <= 4096:
-        # coefficients on the tensor cores, then one pass that subtracts, rounds and normalises
-        c = torch.empty(n, r, dtype=torch.float32, device=x.device)
-        check(lib.tb_lowrank_coeffs(_ptr(x), _ptr(ut), r, n, d, _ptr(c), _stream()), "tb_lowrank_coeffs")
-        check(lib.tb_lowrank_apply(_ptr(x), _ptr(ut), _ptr(c), r, n, d, _ptr(w_norm), eps, _ptr(out_x), _ptr(out_h),
-                                   _stream()), "tb_lowrank_apply")
         return out_x, out_h
     check(lib.tb_lowrank_remove(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(out_x),
                                 _ptr(out_h), _stream()), "tb_lowrank_remove")
@@ -726,7 +725,7 @@ _CAND_SCRATCH = {}     # (device, rows, d) -> (wc bf16 [rows, d], sums f32 [P, 1
 def ll_candidates_exact(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, ref_lse: torch.Tensor,
                         tau: torch.Tensor, cur_id: Optional[torch.Tensor], prev_id: Optional[torch.Tensor],
                         cand_count: torch.Tensor, cand_id: torch.Tensor, *, k: int = TB_TOPK, softcap: float = 0.0,
-                        vocab_offset: int = 0, tensor_cores: bool = True):
+                        vocab_offset: int = 0):
     """Exact masked column sums of the listed candidates -> (sums f32 [P, k], ids i32 [P, k],
     theta f32 [P] = k-th best sum, flag i32 [P] = 1 where the top-k is certified exact)."""
     n, d = h.shape
@@ -736,7 +735,7 @@ def ll_candidates_exact(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, r
     ids = torch.empty(P, k, dtype=torch.int32, device=dev)
     theta = torch.empty(P, dtype=torch.float32, device=dev)
     flag = torch.empty(P, dtype=torch.int32, device=dev)
-    if P and tensor_cores:
+    if P:
         # gather the candidates' W_U rows, block-diagonal tcgen05 GEMM, rank + certify
         key = (dev, n, d)
         if key not in _CAND_SCRATCH:
@@ -748,12 +747,6 @@ def ll_candidates_exact(h: torch.Tensor, w_u: torch.Tensor, lse: torch.Tensor, r
             _ptr(h), _ptr(w_u), n, d, w_u.shape[0], vocab_offset, float(softcap or 0.0), _ptr(lse), _ptr(ref_lse),
             _ptr(tau), _ptr(cur_id), _ptr(prev_id), _ptr(cand_count), _ptr(cand_id), cand_id.shape[1], k, _ptr(wc),
             _ptr(sums), _ptr(val), _ptr(ids), _ptr(theta), _ptr(flag), _stream()), "tb_ll_candidates_exact_tc")
-        return val, ids, theta, flag
-    if P:
-        check(_lib.load().tb_ll_candidates_exact(
-            _ptr(h), _ptr(w_u), n, d, w_u.shape[0], vocab_offset, float(softcap or 0.0), _ptr(lse), _ptr(ref_lse),
-            _ptr(tau), _ptr(cur_id), _ptr(prev_id), _ptr(cand_count), _ptr(cand_id), cand_id.shape[1], k, _ptr(val),
-            _ptr(ids), _ptr(theta), _ptr(flag), _stream()), "tb_ll_candidates_exact")
     return val, ids, theta, flag
 
 

@@ -167,8 +167,8 @@ def test_row_splits_with_different_chunkings_give_the_same_readouts(cuda_lib, mo
 
 
 @pytest.mark.parametrize("P", [5, 2])
-def test_candidate_sums_on_tensor_cores_equal_the_cuda_core_kernel(cuda_lib, P):
-    """K6 twice: gather + block-diagonal tcgen05 GEMM + finalize vs the CUDA-core kernel (odd and even
+def test_candidate_sums_on_tensor_cores_match_the_oracle_lists(cuda_lib, P):
+    """K6: gather + block-diagonal tcgen05 GEMM + finalize against the oracle's LL lists (odd and even
     prompt counts: the last tile of the odd case is half empty)."""
     from taboo_brittleness_b200 import ops
     h, w_u, sid, cur, prev, plain, ref_lists = _setup(P, 512, 8192, 9, 30.0)
@@ -177,10 +177,8 @@ def test_candidate_sums_on_tensor_cores_equal_the_cuda_core_kernel(cuda_lib, P):
     tau = (0.4 * torch.tensor([float(r[1][9]) for r in ref_lists])).cuda().contiguous()
     p, cnt, cid = ops.lens_ll_partials(h, w_u, ref_lse, tau, cur, prev, softcap=30.0, n_chunks=4)
     out = ops.lens_merge(p)
-    a = ops.ll_candidates_exact(h, w_u, out.lse, ref_lse, tau, cur, prev, cnt, cid, softcap=30.0, tensor_cores=False)
-    b = ops.ll_candidates_exact(h, w_u, out.lse, ref_lse, tau, cur, prev, cnt, cid, softcap=30.0, tensor_cores=True)
+    b = ops.ll_candidates_exact(h, w_u, out.lse, ref_lse, tau, cur, prev, cnt, cid, softcap=30.0)
     torch.cuda.synchronize()
     assert (cnt.cpu() <= 128).all()
-    assert torch.equal(a[1], b[1]) and torch.equal(a[3], b[3])
-    assert torch.allclose(a[0], b[0], rtol=1e-4, atol=1e-6) and torch.allclose(a[2], b[2], rtol=1e-4, atol=1e-6)
+    assert b[3].bool().any()
     _compare(b[0][b[3].bool()], b[1][b[3].bool()], [r for r, f in zip(ref_lists, b[3].tolist()) if f], 10)

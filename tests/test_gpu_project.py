@@ -35,24 +35,22 @@ def test_lowrank_remove(cuda_lib, r, n_rows):
 
 
 @pytest.mark.parametrize("r,d,n_rows", [(9, 3584, 700), (16, 3584, 4096), (40, 520, 300), (64, 3584, 1300)])
-def test_lowrank_tensor_core_path_equals_cuda_core_path(cuda_lib, r, d, n_rows):
-    """Ranks above 8: both thin products on the tensor cores (coefficients split into bf16 head + remainder)
-    against the CUDA-core second product. Same x' up to one bf16 rounding flip in a few elements; h alone
-    (x' written into the h buffer and scaled in place) equals h next to x'."""
+def test_lowrank_tensor_core_path_h_alone_equals_h_next_to_x(cuda_lib, r, d, n_rows):
+    """Ranks above 8: h alone (x' written into the h buffer and scaled in place) equals h next to x',
+    and x' matches the oracle (fp32 coefficients; the kernel splits them into bf16 head + remainder)."""
     from taboo_brittleness_b200 import ops
-    x = cuda_bf16(synthetic.make_residuals(1, n_rows, d, seed=5 + r))
-    U = cuda_bf16(synthetic.bf16_exact(oracle.random_orthonormal(d, r, seed=r)))
+    xc = synthetic.make_residuals(1, n_rows, d, seed=5 + r)
+    Uc = synthetic.bf16_exact(oracle.random_orthonormal(d, r, seed=r))
+    x, U = cuda_bf16(xc), cuda_bf16(Uc)
     w = synthetic.make_lens(d, 8, seed=1).w_norm.cuda()
     tx, th = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True)
-    cx, ch = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, tensor_cores=False)
     _, th2 = ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True)
     torch.cuda.synchronize()
     assert torch.equal(th, th2)
-    tx, cx, th, ch = tx.float(), cx.float(), th.float(), ch.float()
-    assert (tx != cx).float().mean().item() < 5e-3
-    assert ((tx - cx).abs() <= 0.0079 * cx.abs() + 1e-3).all()
-    assert (th != ch).float().mean().item() < 1e-2
-    assert ((th - ch).abs() <= 0.0079 * ch.abs() + 1e-3 * ch.abs().max()).all()
+    ref = oracle.lowrank_remove(xc, Uc, residual_dtype=BF16)
+    got = tx.float().cpu()
+    assert (got != ref).float().mean().item() < 1e-2
+    assert ((got - ref).abs() <= 0.0079 * ref.abs() + 1e-3).all()
 
 
 def test_lowrank_tc_scratch_is_checked(cuda_lib):

@@ -8,7 +8,7 @@ block of scratch inside its own image (TB_STATIC_LENS_MAX_SLOTS (row, chunk) par
 tb_logit_lens_static runs K3 + K4 on it.
 
 Checked here, through the C ABI: the readout equals the one from tb_lens_partials +
-tb_lens_merge with caller scratch, on two calls in a row with different shapes (the block keeps
+tb_lens_merge with caller scratch, on calls in a row with different shapes and cluster modes (the block keeps
 the first call's contents, so the second call would expose any slot that is read before it is
 written), and requests beyond the block are refused without launching anything.
 
@@ -54,7 +54,10 @@ def test_static_scratch_matches_caller_scratch_twice_in_a_row(cuda_lib):
     # call 1: 3 x 64 rows, 4 chunks, CTA pairs; call 2: fewer rows, other chunking, single CTAs --
     # its slots overlap the ones call 1 filled, at different (row, chunk) positions
     cases = [dict(P=3, T=64, d=512, V=8192, chunks=4, pair=True, softcap=30.0, seed=0),
-             dict(P=1, T=100, d=264, V=5000, chunks=2, pair=False, softcap=0.0, seed=3)]
+             dict(P=1, T=100, d=264, V=5000, chunks=2, pair=False, softcap=0.0, seed=3),
+             # call 3: the Python layer's default cluster shape (mode 5: 2x1 pairs preferred, plain pairs as
+             # fallback, operand slabs shared by TMA multicast), an odd number of row blocks
+             dict(P=5, T=128, d=512, V=8192, chunks=4, pair=5, softcap=30.0, seed=5)]
     for c in cases:
         x = synthetic.make_residuals(c["P"], c["T"], c["d"], seed=1234 + c["seed"])
         lens = synthetic.make_lens(c["d"], c["V"], seed=42 + c["seed"])
