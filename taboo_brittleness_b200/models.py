@@ -111,10 +111,12 @@ class SyntheticLensModel:
 
 
 class HfLensModel:
-    """Adapter over a transformers Gemma-2 causal LM: residuals come from one forward pass with
-    ``output_hidden_states`` (layer l's output = hidden_states[l + 1], as layer.output[0] in the
-    reference's nnsight trace, src/models.py:129-135); the lens weights are ``model.model.norm``
-    and the (tied) ``lm_head``."""
+    """Adapter over a transformers Gemma-2 causal LM: residuals are the RAW outputs of the decoder
+    layers, captured with forward hooks on ``model.model.layers[l]`` -- what ``layer.output[0]`` is in
+    the reference's nnsight trace (src/models.py:129-135), the last layer included. (The last entry of
+    transformers' ``output_hidden_states`` is already ``model.model.norm(...)`` of the last layer's
+    output, so it cannot be used: the lens would normalise it a second time.) The lens weights are
+    ``model.model.norm`` and the (tied) ``lm_head``."""
 
     def __init__(self, base_model, tokenizer):
         self.base_model, self.tokenizer = base_model, tokenizer
@@ -137,9 +139,22 @@ class HfLensModel:
 
     def layer_residuals(self, prompt: str) -> Tuple[List[int], torch.Tensor]:
         enc = self.tokenizer(prompt, return_tensors="pt").to(self.device)
-        with torch.no_grad():
-            out = self.base_model(**enc, output_hidden_states=True)
-        hs = torch.stack([h[0] for h in out.hidden_states[1:]])   # [L, T, d]
+        captured: List[Optional[torch.Tensor]] = [None] * self.n_layers
+
+        def hook_for(l):
+            def hook(_module, _inputs, output):
+                out = output[0] if isinstance(output, (tuple, list)) else output
+                captured[l] = out.detach()
+            return hook
+
+        handles = [layer.register_forward_hook(hook_for(l)) for l, layer in enumerate(self.base_model.model.layers)]
+        try:
+            with torch.no_grad():
+                self.base_model(**enc)
+        finally:
+            for hd in handles:
+                hd.remove()
+        hs = torch.stack([c[0] if c.dim() == 3 else c for c in captured])   # [L, T, d]
         return enc["input_ids"][0].tolist(), hs.to(torch.bfloat16)
 
 
