@@ -19,6 +19,13 @@ A "token" is a token-condition: one residual row through one condition.
   cpu_baseline  the oracle (PyTorch fp32 restatement of the reference path) on the host cores,
          on a bounded sample of the same workload (rank 0, N = 1 only)
 
+  workloads  three short legs after the headline region, one per remaining BASELINE.json config, so
+         that the driver's per-N runs record them: projection_vocab_shard (configs[3]: low-rank removal
+         ranks 1..64 + lens with W_U sharded by vocabulary over the N ranks, NCCL all_gather of the
+         92-byte per-row partials, strong scaling), random_control (configs[2]: 11 budgets x 32 seeds,
+         (seed, prompt) units split over the ranks, strong scaling) and stress (configs[4]: 131k-latent
+         SAE encode + lens over 42 layer residuals, prompts sharded, weak scaling). --no-workloads skips them.
+
 --impl reference times that same CPU restatement as the reference arm: the reference itself
 cannot be installed or imported here (sae_lens / nnsight missing, no network).
 """
@@ -151,22 +158,298 @@ def run_reference_arm(args, rank, world):
 
 
 def cpu_baseline_leg():
+    """configs[0] (32 prompts x 64 tokens = 2048 rows, fp32), all host threads,
+    one warm-up pass, best of 3."""
     import torch
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    n_prompts, rpp = 32, 128        # 4096 rows: ~8 TFLOP, ~10 s per pass on 16 cores
+    n_prompts, rpp = 32, 64
     x, sae, lens, sid = cpu_problem(n_prompts, rpp)
-    cpu_step(x[:256], sae, lens, sid[:256], rpp)      # warm-up (thread pool, page faults)
+    cpu_step(x, sae, lens, sid, rpp)                  # warm-up (thread pool, page faults)
     best = None
-    for _ in range(2):
+    for _ in range(3):
         t0 = time.perf_counter()
         cpu_step(x, sae, lens, sid, rpp)
         dt = time.perf_counter() - t0
         best = dt if best is None else min(best, dt)
     return {"value": x.shape[0] / best, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{n_prompts} prompts x {rpp} tok ({n_prompts * rpp} rows) of the same synthetic workload, fp32 oracle, one "
-                      f"targeted top-10 ablation + full-vocab lens (secret prob, top-10, LL-Top-10), best of 2 "
-                      f"({best:.1f} s)"}
+            "sample": f"BASELINE configs[0]: {n_prompts} prompts x {rpp} tok ({n_prompts * rpp} rows) of the same synthetic "
+                      f"workload, fp32 oracle, one targeted top-10 ablation + full-vocab lens (secret prob, top-10, "
+                      f"LL-Top-10), 1 warm-up + best of 3 ({best:.1f} s)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# Workload legs: BASELINE.json configs[2], [3], [4], each a short timed region of its own after the
+# headline. Every leg: a short warm-up, barrier + synchronize, CUDA events around the timed passes,
+# barrier + synchronize, MAX over ranks. A leg that fails reports {"error": ...} and the headline line
+# is still printed.
+# ------------------------------------------------------------------------------------------------
+def _leg_time(fn, passes, dev, world, dist):
+    """ms per pass of fn(), max over ranks."""
+    import torch
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(passes):
+        fn()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()) / passes
+
+
+def _sum_ms(pairs):
+    return sum(a.elapsed_time(b) for a, b in pairs)
+
+
+def leg_projection_vocab_shard(args, ctx):
+    """configs[3]: rank r in {1..64} removal of a random orthonormal subspace (K2), then the lens with W_U
+    split by vocabulary over the ranks (K3 on the shard, all_gather of the merged 92-byte per-row partials,
+    K4 over the ranks). Every rank sees all rows: strong scaling. With more than one rank the leg runs
+    twice: K2 replicated on every rank, and K2 on a row shard followed by an all_gather of h (7 KB per row)."""
+    import torch
+    from taboo_brittleness_b200 import dist as tbd
+    from taboo_brittleness_b200 import ops, synthetic
+    dev, rank, world, dist, lens, peaks = ctx["dev"], ctx["rank"], ctx["world"], ctx["dist"], ctx["lens"], ctx["peaks"]
+    P = args.proj_prompts
+    n_rows = P * T
+    x = torch.empty(n_rows, D, dtype=torch.bfloat16, device=dev)
+    for p0 in range(0, P, 512):
+        p1 = min(P, p0 + 512)
+        x[p0 * T:p1 * T] = synthetic.make_residuals(p1 - p0, T, D, seed=synthetic.SEED_DATA + 777 + p0,
+                                                    device=str(dev)).to(torch.bfloat16)
+    sid = synthetic.make_secret_ids(P, T, V, seed=synthetic.SEED_DATA + 777).to(dev)
+    v0, v1 = tbd.vocab_shard(V, rank, world)
+    shard = ops.LensWeights(w_norm=lens.w_norm, w_u=lens.w_u[v0:v1], vocab_offset=v0)
+    g = torch.Generator(device=dev).manual_seed(7)
+    U = torch.linalg.qr(torch.randn(D, max(RANKS), device=dev, generator=g))[0].to(torch.bfloat16).contiguous()
+    r0, r1 = tbd.shard_range(n_rows, rank, world)
+    can_row_shard = world > 1 and n_rows % world == 0
+    state = {"timers": None, "k2": None, "hgather": None, "check": None}
+
+    def one_pass(k2_mode):
+        for r in RANKS:
+            Ur = U[:, :r].contiguous()
+            a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+            c = torch.cuda.Event(enable_timing=True)
+            a.record()
+            if k2_mode == "replicated":
+                _, h = ops.lowrank_remove(x, Ur, w_norm=lens.w_norm, eps=lens.eps, want_x=False, want_h=True)
+                b.record()
+            else:
+                _, h_loc = ops.lowrank_remove(x[r0:r1], Ur, w_norm=lens.w_norm, eps=lens.eps, want_x=False, want_h=True)
+                b.record()
+                h = tbd.all_gather_cat(h_loc)
+            c.record()
+            if state["k2"] is not None:
+                state["k2"].append((a, b))
+                state["hgather"].append((b, c))
+            out = tbd.lens_readout_vocab_sharded(h, shard, softcap=SOFTCAP, secret_id=sid, cta_pair=args.cluster_mode,
+                                                 timers=state["timers"])
+        state["check"] = out
+
+    def measure(k2_mode):
+        one_pass(k2_mode)                                   # warm-up
+        state.update(timers={}, k2=[], hgather=[])
+        ms = _leg_time(lambda: one_pass(k2_mode), args.leg_passes, dev, world, dist)
+        tm, k2, hg = state["timers"], state["k2"], state["hgather"]
+        state.update(timers=None, k2=None, hgather=None)
+        n = args.leg_passes
+        part_ms, gat_ms, mer_ms = _sum_ms(tm["partials"]) / n, _sum_ms(tm["gather"]) / n, _sum_ms(tm["merge"]) / n
+        k2_ms, hg_ms = _sum_ms(k2) / n, _sum_ms(hg) / n
+        conds = n_rows * len(RANKS)
+        return {"value": conds / (ms * 1e-3), "unit": "row-conditions/s", "ms_per_pass": ms,
+                "phase_ms_this_rank": {"k2": k2_ms, "h_all_gather": hg_ms, "shard_gemm_and_local_merge": part_ms,
+                                       "partials_all_gather": gat_ms, "merge_over_ranks": mer_ms},
+                "phase_share_this_rank": {"k2": k2_ms / ms, "h_all_gather": hg_ms / ms,
+                                          "shard_gemm_and_local_merge": part_ms / ms,
+                                          "partials_all_gather": gat_ms / ms, "merge_over_ranks": mer_ms / ms},
+                "lens_tflops_per_gpu": conds * 2.0 * D * (v1 - v0) / (part_ms * 1e-3) / 1e12,
+                "k2_gbs": (r1 - r0 if k2_mode != "replicated" else n_rows) * len(RANKS) * 4.0 * D / (k2_ms * 1e-3) / 1e9}
+
+    res = {"config": f"BASELINE configs[3]: {P} prompts x {T} tok (all rows on every GPU), low-rank removal ranks "
+                     f"{list(RANKS)}, lens V={V} with W_U sharded by vocabulary over {world} GPU(s) "
+                     f"({v1 - v0} ids on rank 0), NCCL all_gather of 92 B per row and rank, secret prob + top-10",
+           "scaling": "strong", "n_gpus": world, "passes": args.leg_passes,
+           "partials_bytes_gathered_per_pass": n_rows * 92 * world * len(RANKS)}
+    rep = measure("replicated")
+    res.update(rep)
+    res["k2"] = "replicated on every rank"
+    res["readout_checksum"] = {"mean_secret_prob": float(state["check"].secret_prob.mean().item()),
+                               "mean_lse": float(state["check"].lse.mean().item())}
+    if can_row_shard:
+        alt = measure("row-sharded")
+        alt["k2"] = "row shard per rank, then all_gather of h (7 KB per row)"
+        res["alternative_k2_row_sharded"] = alt
+    return res
+
+
+def leg_random_control(args, ctx):
+    """configs[2]: random-latent ablation control, 11 budgets x 32 seeds. The (seed, prompt) pairs are the
+    units (dist.shard_conditions, seed-major); a rank encodes each prompt range it touches once, runs the
+    nested budgets of its seeds over it, and the per-row secret probabilities of all units are gathered to
+    every rank at the end (dist.gather_rows). Total work is fixed: strong scaling."""
+    import torch
+    from taboo_brittleness_b200 import dist as tbd
+    from taboo_brittleness_b200 import interventions, synthetic
+    dev, rank, world, dist, eng = ctx["dev"], ctx["rank"], ctx["world"], ctx["dist"], ctx["eng"]
+    P, n_seeds = args.rc_prompts, args.rc_seeds
+    n_rows = P * T
+    x = torch.empty(n_rows, D, dtype=torch.bfloat16, device=dev)
+    for p0 in range(0, P, 512):
+        p1 = min(P, p0 + 512)
+        x[p0 * T:p1 * T] = synthetic.make_residuals(p1 - p0, T, D, seed=synthetic.SEED_DATA + 555 + p0,
+                                                    device=str(dev)).to(torch.bfloat16)
+    sid = synthetic.make_secret_ids(P, T, V, seed=synthetic.SEED_DATA + 555).to(dev)
+    g = torch.Generator().manual_seed(synthetic.SEED_DATA + 556)
+    ll_ids = torch.randint(0, V, (2, n_rows), generator=g, dtype=torch.int32)
+    ll_ids[1, ::T] = -1
+    ll_ids = ll_ids.to(dev)
+    runs = tbd.shard_conditions(P, n_seeds, rank, world)            # [(seed, p0, p1), ...] of this rank
+    out = {}
+
+    def sweep(p0, p1, seeds):
+        xb, sb = x[p0 * T:p1 * T], sid[p0 * T:p1 * T]
+        ll = interventions.LLSpec(ll_ids[0, p0 * T:p1 * T], ll_ids[1, p0 * T:p1 * T], rows_per_prompt=T) \
+            if args.ll_topk else None
+        res = eng.random_budget_sweep(xb, sb, BUDGETS, seeds, ll=ll)           # encodes xb once
+        return {s_: torch.stack([res[(b, s_)].secret_prob.view(p1 - p0, T) for b in BUDGETS], 1) for s_ in seeds}
+
+    def one_pass():
+        out["all"] = tbd.run_sharded_conditions(P, n_seeds, sweep)             # [n_seeds * P, 11, T] on every rank
+
+    if runs:                                                                   # warm-up: two budgets of one seed
+        s0, p0, p1 = runs[0]
+        eng.random_budget_sweep(x[p0 * T:p1 * T], sid[p0 * T:p1 * T], BUDGETS[:2], [s0])
+    stats0 = (eng.stats.ll_fused_prompts, eng.stats.ll_fallback_prompts)
+    ms = _leg_time(one_pass, 1, dev, world, dist)
+    conds = n_rows * len(BUDGETS) * n_seeds
+    allp = out["all"]
+    return {"config": f"BASELINE configs[2]: random-latent control, budgets {list(BUDGETS)} x {n_seeds} seeds x {P} prompts "
+                      f"x {T} tok, (seed, prompt) units split over {world} GPU(s) by dist.shard_conditions, weights "
+                      f"replicated, encode once per prompt range and rank, final gather of the per-row secret probabilities",
+            "scaling": "strong", "n_gpus": world, "passes": 1, "value": conds / (ms * 1e-3), "unit": UNIT,
+            "ms_per_pass": ms, "units_this_rank": sum(p1 - p0 for _, p0, p1 in runs), "units_total": P * n_seeds,
+            "seeds_this_rank": sorted({s_ for s_, _, _ in runs}), "ll_topk": bool(args.ll_topk),
+            "ll_one_sweep_prompt_conditions_this_rank": eng.stats.ll_fused_prompts - stats0[0],
+            "ll_redone_with_second_sweep_this_rank": eng.stats.ll_fallback_prompts - stats0[1],
+            "gathered_shape": list(allp.shape),
+            "readout_checksum": {"mean_secret_prob": float(allp.mean().item()),
+                                 "mean_secret_prob_budget_1024": float(allp[:, -1].mean().item())},
+            "whole_job_tflops": conds * FLOP_LENS / (ms * 1e-3) / 1e12}
+
+
+def leg_stress(args, ctx):
+    """configs[4]: Gemma Scope 131k-latent SAE on the layer-32 residuals (K1 at S = 131072, then the per-prompt
+    mean and top-10 latents) and the logit lens over the residuals of all 42 layers (norm, K3, K4: secret
+    probability and top-10 per row), 16,384 prompts x 128 tokens split by prompt over 8 GPUs = 2048 prompts per
+    GPU (weak scaling: every rank gets its own 2048). The residuals of all layers are generated on the device
+    before the timed region and stay resident (79 GB per GPU)."""
+    import torch
+    from taboo_brittleness_b200 import ops, synthetic
+    dev, rank, world, dist, lens, peaks = ctx["dev"], ctx["rank"], ctx["world"], ctx["dist"], ctx["lens"], ctx["peaks"]
+    S2, L, P = 131072, 42, args.stress_prompts
+    n_rows = P * T
+    # thresholds from 4096 calibration rows: the (1 - 76 / 131072) quantile needs that many to resolve (L0 about 80)
+    sae_s = synthetic.make_sae(D, S2, seed=synthetic.SEED_WEIGHTS + 1, calib_rows=4096, device=str(dev))
+    sae = ops.SaeWeights.from_sae_lens_layout(sae_s.W_enc, sae_s.b_enc, sae_s.threshold, sae_s.W_dec, sae_s.b_dec,
+                                              device=str(dev))
+    del sae_s
+    xs = torch.empty(L * n_rows, D, dtype=torch.bfloat16, device=dev)
+    for l in range(L):
+        for p0 in range(0, P, 512):
+            p1 = min(P, p0 + 512)
+            xs[l * n_rows + p0 * T:l * n_rows + p1 * T] = synthetic.make_residuals(
+                p1 - p0, T, D, seed=synthetic.SEED_DATA + 9000 + 100000 * rank + 1000 * l + p0, device=str(dev)).to(torch.bfloat16)
+    sid = synthetic.make_secret_ids(P, T, V, seed=synthetic.SEED_DATA + 9 + rank).to(dev).repeat(L)
+    sub = 4096 * T                                            # lens rows per launch (the headline's batch)
+    ev = {"enc": [], "lens": []}
+    out = {}
+
+    def mark():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def one_pass(rows_limit=None, record=True):
+        a = mark()
+        x31 = xs[31 * n_rows:32 * n_rows]
+        acts = ops.sae_encode(x31 if rows_limit is None else x31[:rows_limit], sae, cap=args.encode_cap)
+        b = mark()
+        mean = ops.latent_mean(acts, T)
+        top_idx, _, _ = ops.topm_select(mean, 10)
+        sec_sum = torch.zeros((), dtype=torch.float64, device=dev)
+        total = L * n_rows if rows_limit is None else rows_limit
+        for q0 in range(0, total, sub):
+            q1 = min(total, q0 + sub)
+            h = ops.rmsnorm(xs[q0:q1], lens.w_norm, lens.eps)
+            c = mark()
+            p = ops.lens_partials(h, lens.w_u, softcap=SOFTCAP, secret_id=sid[q0:q1], cta_pair=args.cluster_mode)
+            d_ = mark()
+            r = ops.lens_merge(p)
+            sec_sum += r.secret_prob.sum(dtype=torch.float64)
+            if record:
+                ev["lens"].append((c, d_))
+        if record:
+            ev["enc"].append((a, b))
+        out.update(top_idx=top_idx, sec_mean=sec_sum / total, overflow=int((acts.count > args.encode_cap).sum().item()),
+                   l0=float(acts.count.float().mean().item()))
+
+    one_pass(rows_limit=min(sub, n_rows), record=False)       # warm-up on one sub-batch
+    ms = _leg_time(one_pass, 1, dev, world, dist)
+    enc_ms, lens_ms = _sum_ms(ev["enc"]), _sum_ms(ev["lens"])
+    tokens = n_rows * world
+    enc_tf = n_rows * 2.0 * D * S2 / (enc_ms * 1e-3) / 1e12
+    lens_tf = L * n_rows * FLOP_LENS / (lens_ms * 1e-3) / 1e12
+    return {"config": f"BASELINE configs[4]: {P} prompts x {T} tok per GPU ({P * world} prompts on {world} GPU(s); 16,384 on 8), "
+                      f"131072-latent JumpReLU SAE encode + per-prompt top-10 latents on the layer-32 residuals, logit lens "
+                      f"(V={V}, softcap {SOFTCAP}: secret prob + top-10) over the residuals of all {L} layers, residuals "
+                      f"resident in HBM ({L * n_rows * D * 2 / 1e9:.0f} GB per GPU)",
+            "scaling": "weak", "n_gpus": world, "passes": 1, "value": tokens / (ms * 1e-3),
+            "unit": "tokens/s (one token = one position through the 131k encode and the 42-layer lens)",
+            "ms_per_pass": ms, "lens_rows_per_pass_per_gpu": L * n_rows,
+            "lens_row_conditions_per_s": L * n_rows * world / (ms * 1e-3),
+            "whole_job_tflops": tokens * (2.0 * D * S2 + L * FLOP_LENS) / (ms * 1e-3) / 1e12,
+            "encode_roofline": {"kernel": "tb_umma_gemm_kernel<EncodeEpi, 2> at S=131072 (first pass over all rows + "
+                                          "second pass over the rows whose list overflowed, host decision in between)",
+                                "bound": "tensor", "achieved": enc_tf, "peak": peaks["tflops_burst"], "unit": "TFLOP/s",
+                                "frac": enc_tf / peaks["tflops_burst"], "peak_source": "MEASURED_PEAKS.json bf16 burst "
+                                "(a 0.2 s kernel timed alone)", "flops_per_token": 2.0 * D * S2, "ms": enc_ms,
+                                "mean_active_latents": out["l0"], "rows_with_overflowing_list": out["overflow"]},
+            "lens_tflops_per_gpu": lens_tf, "lens_frac_of_sustained_peak": lens_tf / peaks["tflops"],
+            "lens_share_of_pass": lens_ms / ms, "encode_share_of_pass": enc_ms / ms,
+            "readout_checksum": {"mean_secret_prob": float(out["sec_mean"].item())}}
+
+
+def run_legs(args, ctx):
+    import torch
+    legs = {"projection_vocab_shard": leg_projection_vocab_shard, "random_control": leg_random_control,
+            "stress": leg_stress}
+    want = [w for w in args.workloads.split(",") if w]
+    res = {}
+    for name in want:
+        if name not in legs:
+            res[name] = {"error": "unknown workload"}
+            continue
+        t0 = time.perf_counter()
+        try:
+            res[name] = legs[name](args, ctx)
+        except Exception as e:      # a failed leg must not take the headline line down with it
+            import traceback
+            res[name] = {"error": f"{type(e).__name__}: {e}", "trace": traceback.format_exc()[-1500:]}
+            torch.cuda.synchronize()
+        res[name]["wall_s"] = time.perf_counter() - t0
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+    return res
 
 
 # ------------------------------------------------------------------------------------------------
@@ -336,23 +619,37 @@ def run_native(args, rank, local_rank, world):
 
     # ---- end to end: host buffers in, readouts out, every step
     step(x_host, sid_host, True)
-    ms_e2e = timed(True, max(1, min(args.steps, 2)))
+    e2e_steps = max(1, min(args.steps, 5))
+    ms_e2e = timed(True, e2e_steps)
 
     tokens_per_step = n_rows * conditions * (1 if proj else world)   # vocab sharding: total work is fixed
     value = tokens_per_step / (ms_step * 1e-3)
     e2e_value = tokens_per_step / (ms_e2e * 1e-3)
+    peaks = load_peaks()
+    # ---- the other BASELINE configs as short legs of their own (all ranks take part; rank 0 reports)
+    workloads = None
+    if args.workloads and args.workload == "targeted":
+        x_dev = sid_dev = ll_dev = x_host = sid_host = ll_host = out_ll = out_sec = out_top = None   # free the headline's buffers
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        ctx = {"dev": dev, "rank": rank, "world": world, "dist": dist, "lens": lens, "eng": eng, "peaks": peaks}
+        workloads = run_legs(args, ctx)
     if rank == 0:
-        peaks = load_peaks()
         achieved = lens_flops / (lens_ms * 1e-3) / 1e12 if lens_ms > 0 else 0.0
-        traffic = None
+        traffic_x = None
         tp = os.path.join(ROOT, "profiles", "lens_traffic.json")
-        if os.path.exists(tp):   # ncu --set full capture, scaled from its row count to this launch's
-            per_row = json.load(open(tp)).get("dram_bytes_per_row")
-            traffic = per_row * min(BP, P) * T if per_row else None
+        if os.path.exists(tp):   # ncu --set full capture of a 37,888-row launch, scaled by rows to this launch's
+            tj = json.load(open(tp))
+            per_row = tj.get("dram_bytes_per_row")
+            if per_row:
+                traffic_x = {"bytes_per_launch": per_row * min(BP, P) * T, "from": "ncu --set full capture of one "
+                             f"{tj.get('captured_rows', 37888)}-row launch (profiles/lens_traffic.json), scaled by the row count; "
+                             "not measured in this run"}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if proj else "weak",
                 "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": workload_config(args),
-                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e,
+                "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "steps": e2e_steps,
                         "h2d_bytes_per_step": n_rows * D * 2 + n_rows * 4 + (n_rows * 8 if args.ll_topk else 0),
                         "d2h_bytes_per_step": conditions * (n_rows * (4 + 40) + (P * 40 if args.ll_topk else 0))},
                 "gpu_launches": launches,
@@ -361,7 +658,8 @@ def run_native(args, rank, local_rank, world):
                                         "first budget: <LensEpi>)" if args.ll_topk and not args.ll_two_sweeps
                                         else "tb_umma_gemm_kernel<LensEpi> (logit-lens readout)"),
                              "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
-                             "frac": achieved / peaks["tflops"], "traffic": traffic, "peak_source": peaks["source"],
+                             "frac": achieved / peaks["tflops"], "traffic": None,
+                             "traffic_extrapolated_from_ncu": traffic_x, "peak_source": peaks["source"],
                              "frac_of_burst_peak": achieved / peaks["tflops_burst"], "launches_timed": n_lens,
                              "kernel_share_of_step": lens_ms / (ms_step * args.steps),
                              "flops_per_token_condition": FLOP_LENS,
@@ -390,6 +688,8 @@ def run_native(args, rank, local_rank, world):
             line["roofline"]["ll_topk_kernel"] = {"kernel": "tb_umma_gemm_kernel<ColSumEpi> (LL-Top-k sweep)",
                                                   "achieved": ll_flops / (ll_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
                                                   "share_of_step": ll_ms / (ms_step * args.steps)}
+        if workloads is not None:
+            line["workloads"] = workloads
         if world == 1 and not args.no_cpu_baseline and args.workload == "targeted":
             line["cpu_baseline"] = cpu_baseline_leg()
         print(json.dumps(line), flush=True)
@@ -415,6 +715,14 @@ def main():
     ap.add_argument("--workload", default="targeted", choices=["targeted", "random-control", "projection-vocab-shard"],
                     help="targeted = BASELINE configs[1] (the headline); the others are configs[2] and configs[3]")
     ap.add_argument("--seeds", type=int, default=2, help="random-control: seeds per step (configs[2] has 32)")
+    ap.add_argument("--workloads", default="projection_vocab_shard,random_control,stress",
+                    help="comma-separated legs run after the headline region (BASELINE configs[3], [2], [4])")
+    ap.add_argument("--no-workloads", dest="workloads", action="store_const", const="")
+    ap.add_argument("--leg-passes", type=int, default=2, help="timed passes of the projection_vocab_shard leg")
+    ap.add_argument("--proj-prompts", type=int, default=2048, help="projection_vocab_shard leg: prompts (all on every rank)")
+    ap.add_argument("--rc-prompts", type=int, default=384, help="random_control leg: prompts (x --rc-seeds seeds = the units)")
+    ap.add_argument("--rc-seeds", type=int, default=32, help="random_control leg: seeds (configs[2]: 32)")
+    ap.add_argument("--stress-prompts", type=int, default=2048, help="stress leg: prompts per GPU (configs[4]: 16384 over 8)")
     ap.add_argument("--no-ll-topk", dest="ll_topk", action="store_false",
                     help="skip the per-prompt LL-Top-10 readout (then every condition is exactly one GEMM sweep)")
     ap.add_argument("--ll-alpha", type=float, default=0.5, help="K3F candidate threshold as a fraction of the "

@@ -62,6 +62,33 @@ def shard_conditions(n_prompts: int, n_seeds: int, rank: int, world_size: int) -
     return runs
 
 
+def condition_unit_counts(n_prompts: int, n_seeds: int, world_size: int) -> List[int]:
+    """(seed, prompt) units per rank under ``shard_conditions``, in rank order."""
+    return [hi - lo for lo, hi in (shard_range(n_prompts * n_seeds, r, world_size) for r in range(world_size))]
+
+
+def run_sharded_conditions(n_prompts: int, n_seeds: int, sweep_fn: Callable, group=None) -> torch.Tensor:
+    """The random-control sweep (configs[2]) over the ranks of ``group``: this rank's (seed, prompt) units are
+    grouped by prompt range, ``sweep_fn(p0, p1, seeds)`` is called once per range (so the encode of the range
+    is shared by its seeds) and returns ``{seed: tensor [p1 - p0, ...]}`` -- one row of readouts per prompt;
+    the rows of all units are then gathered to every rank in global unit order (seed-major):
+    returns [n_seeds * n_prompts, ...]. No collective inside the loop, one ragged gather at the end."""
+    r, w = world(group)
+    runs = shard_conditions(n_prompts, n_seeds, r, w)
+    ranges: dict = {}
+    for seed, p0, p1 in runs:
+        ranges.setdefault((p0, p1), []).append(seed)
+    per_unit = {}
+    for (p0, p1), seeds in ranges.items():
+        res = sweep_fn(p0, p1, seeds)
+        for seed in seeds:
+            per_unit[(seed, p0)] = res[seed]
+    if not runs:
+        raise ValueError("a rank without units cannot know the readout shape: use at most n_prompts * n_seeds ranks")
+    local = torch.cat([per_unit[(seed, p0)] for seed, p0, _ in runs]).contiguous()
+    return gather_rows(local, condition_unit_counts(n_prompts, n_seeds, w), group)
+
+
 def vocab_shard(V: int, rank: int, world_size: int, align: int = TILE_V) -> Tuple[int, int]:
     """Rows of W_U owned by ``rank``: equal tile-aligned shards (32,000 per GPU at V = 256000, G = 8);
     the last rank takes the remainder."""
@@ -115,16 +142,37 @@ def _kernel_merge(packed: torch.Tensor) -> ops.LensReadout:
 def lens_readout_vocab_sharded(h: torch.Tensor, lens_shard: ops.LensWeights, *, softcap: float = 0.0,
                                secret_id: Optional[torch.Tensor] = None, group=None,
                                n_chunks: Optional[int] = None, cta_pair=5,
-                               partials_fn: Optional[Callable] = None, merge_fn: Optional[Callable] = None):
+                               partials_fn: Optional[Callable] = None, merge_fn: Optional[Callable] = None,
+                               timers: Optional[dict] = None):
     """Lens readout with W_U split by rows across the ranks of ``group``.
 
     h: normalised operand, all rows on every rank; ``lens_shard.w_u`` = this rank's rows of W_U,
     ``lens_shard.vocab_offset`` = global id of its first row. Every rank returns the full readout.
+    ``timers`` (a dict of lists, CUDA only) receives (start, end) event pairs of the three phases on the
+    current stream: "partials" (shard GEMM + local merge), "gather" (the exchange), "merge" (K4 over ranks).
     """
     partials_fn = partials_fn or _kernel_partials
     merge_fn = merge_fn or _kernel_merge
+
+    def mark():
+        if timers is None:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    t0 = mark()
     local = partials_fn(h, lens_shard, softcap, secret_id, n_chunks, cta_pair)   # [1, rows, 23]
-    return merge_fn(all_gather_cat(local, group))                                 # [world, rows, 23]
+    t1 = mark()
+    gathered = all_gather_cat(local, group)                                       # [world, rows, 23]
+    t2 = mark()
+    out = merge_fn(gathered)
+    t3 = mark()
+    if timers is not None:
+        timers.setdefault("partials", []).append((t0, t1))
+        timers.setdefault("gather", []).append((t1, t2))
+        timers.setdefault("merge", []).append((t2, t3))
+    return out
 
 
 def ll_topk_vocab_sharded(h: torch.Tensor, lens_shard: ops.LensWeights, lse: torch.Tensor,

@@ -108,6 +108,30 @@ def test_ragged_row_gather_over_gloo(world):
     _spawn(_gather_worker, world)
 
 
+def _conditions_worker(rank, world, n_prompts, n_seeds):
+    calls = []
+
+    def sweep_fn(p0, p1, seeds):
+        calls.append((p0, p1, tuple(seeds)))
+        # readout of unit (seed, prompt) = [seed, prompt, seed * 1000 + prompt]
+        return {s: torch.stack([torch.tensor([s, p, s * 1000 + p], dtype=torch.float32) for p in range(p0, p1)])
+                for s in seeds}
+    full = tbd.run_sharded_conditions(n_prompts, n_seeds, sweep_fn)
+    want = torch.tensor([[s, p, s * 1000 + p] for s in range(n_seeds) for p in range(n_prompts)], dtype=torch.float32)
+    assert torch.equal(full, want)
+    # every prompt range is swept once per rank, whatever the number of seeds that share it
+    assert len(calls) == len({(a, b) for a, b, _ in calls})
+    mine = sum((b - a) * len(sd) for a, b, sd in calls)
+    assert mine == tbd.condition_unit_counts(n_prompts, n_seeds, world)[rank]
+
+
+@pytest.mark.parametrize("world,n_prompts,n_seeds", [(2, 6, 32), (3, 5, 4), (2, 4, 3)])
+def test_random_control_units_over_gloo(world, n_prompts, n_seeds):
+    """configs[2]: (seed, prompt) units split over the ranks, encode shared per prompt range, ragged gather
+    back into global seed-major order (32 seeds over 2 ranks: whole seeds; 4 seeds over 3: cut ranges)."""
+    _spawn(_conditions_worker, world, n_prompts, n_seeds)
+
+
 def test_single_process_is_the_identity():
     assert tbd.world() == (0, 1)
     t = torch.ones(3, 2)
