@@ -1,0 +1,94 @@
+"""BASELINE.json's remaining configs at their real shapes (small prompt counts) against the oracle:
+configs[2] random-latent control with all 32 seeds, configs[4] the 131072-latent SAE and the lens over
+42 layers' residuals at d = 3584, V = 256000 through models.get_all_layer_readouts."""
+import pytest
+import torch
+
+from _common import BF16, cuda_bf16, oracle, sae_to_cuda, synthetic, topk_sets_match
+
+pytestmark = pytest.mark.gpu
+
+
+def test_random_control_32_seeds_real_sae_shape(cuda_lib):
+    """configs[2]: budgets {1, 32, 1024} x seeds 0..31 on the 16384-latent SAE (d = 3584), 2 prompts x 128 tok,
+    a 32768-id vocabulary slice; every (budget, seed) readout against the oracle's dense ablate + decode."""
+    from taboo_brittleness_b200 import interventions, ops
+    P, T, d, S, V = 2, 128, 3584, 16384, 32768
+    x = synthetic.make_residuals(P, T, d, seed=77)
+    sae = synthetic.make_sae(d, S, seed=42)
+    lens = synthetic.make_lens(d, V, seed=77)
+    sid = synthetic.make_secret_ids(P, T, V, seed=77)
+    synthetic.plant_secret_direction(lens, x, sid)
+    eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                           softcap=30.0)
+    budgets, seeds = (1, 32, 1024), range(32)
+    g = torch.Generator().manual_seed(3)
+    cur = torch.randint(0, V, (P * T,), generator=g, dtype=torch.int32).cuda()
+    ll = interventions.LLSpec(cur, None, rows_per_prompt=T, k=10)
+    res = eng.random_budget_sweep(cuda_bf16(x), sid.cuda(), budgets, seeds, ll=ll)
+    torch.cuda.synchronize()
+    assert len(res) == 96
+    assert eng.stats.ll_fused_prompts == 95 * P          # only the very first condition pays the second sweep
+    acts = oracle.jumprelu_encode(x, sae.W_enc, sae.b_enc, sae.threshold)
+    xhat_err = x - oracle.sae_decode(acts, sae.W_dec, sae.b_dec)
+    exact = 0
+    for seed in seeds:
+        idx = oracle.random_latents(S, seed, 1024)
+        for b in budgets:
+            a2 = acts.clone()
+            a2[:, idx[:b]] = 0
+            x1 = (oracle.sae_decode(a2, sae.W_dec, sae.b_dec) + xhat_err).to(BF16).float()
+            probs = oracle.lens_probs(x1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
+            r = res[(b, seed)]
+            assert (r.secret_prob.cpu() - oracle.secret_prob(probs, sid)).abs().max().item() <= 1e-3
+            n_exact, _, bad = topk_sets_match(r.top_id.cpu(), probs, 10)
+            assert not bad, (seed, b, bad[:4])
+            exact += n_exact
+            for p in range(P):
+                acc = oracle.aggregate_response_probs(probs[p * T:(p + 1) * T], cur[p * T:(p + 1) * T].tolist(), None)
+                want, have = set(torch.topk(acc, 10).indices.tolist()), set(r.ll_id[p].cpu().tolist())
+                if have != want:
+                    tenth = float(torch.topk(acc, 10).values[-1])
+                    assert all(abs(float(acc[i]) - tenth) <= 2e-3 * tenth for i in have ^ want), (seed, b, p)
+    assert exact >= 0.97 * 96 * P * T
+
+
+def test_stress_shapes_131k_targeting_and_42_layer_lens(cuda_lib):
+    """configs[4]: (a) targeted top-10 latents of a 131072-latent SAE, 2 prompts x 64 tok, against the oracle's
+    encode -> mean -> topk; (b) the lens over 42 layers' residuals (d = 3584, V = 256000) in one launch through
+    models.get_all_layer_readouts, every layer against the oracle."""
+    from taboo_brittleness_b200 import interventions, models, ops
+    d, S_big, T = 3584, 131072, 64
+    sae = synthetic.make_sae(d, S_big, seed=9, calib_rows=2048)
+    x = synthetic.make_residuals(2, T, d, seed=9)
+    w = sae_to_cuda(sae)
+    acts = ops.sae_encode(cuda_bf16(x), w, cap=256)
+    mean = ops.latent_mean(acts, T)
+    idx, val, _ = ops.topm_select(mean, 10)
+    torch.cuda.synchronize()
+    ref = oracle.jumprelu_encode(x, sae.W_enc, sae.b_enc, sae.threshold)
+    for p in range(2):
+        tv, ti = torch.topk(ref[p * T:(p + 1) * T].mean(0), 11)
+        ks, rs = set(idx[p].cpu().tolist()), set(ti[:10].tolist())
+        assert ks == rs or abs(float(tv[9] - tv[10])) <= 1e-4 * float(tv[9]) + 2e-3
+        assert torch.allclose(val[p].cpu(), tv[:10], rtol=1e-3, atol=2e-3)
+    dense_cnt = (ref > 0).sum(1)
+    assert (acts.count.cpu().long() - dense_cnt).abs().max().item() <= 4       # near-threshold flips only
+    del acts, w, sae, ref
+
+    model = models.SyntheticLensModel(d=d, vocab=256000, n_layers=42, seed=3)
+    prompt, secret = "Give me a hint about the word", 7509
+    words, grid = models.get_all_layer_readouts(model, prompt, secret_id=secret, softcap=30.0)
+    torch.cuda.synchronize()
+    Tn = len(words)
+    assert tuple(grid.secret_prob.shape) == (42, Tn) and tuple(grid.top_id.shape) == (42, Tn, 10)
+    ids, resid = model.layer_residuals(prompt)
+    lw = model.lens_weights()
+    wu = lw.w_u.float().cpu()
+    for layer in range(42):
+        probs = oracle.lens_probs(resid[layer].float().cpu(), lw.w_norm.cpu(), wu, 30.0, residual_dtype=BF16)
+        assert (grid.secret_prob[layer].cpu() - probs[:, secret]).abs().max().item() <= 1e-3
+        assert (grid.lse[layer].cpu() - torch.logsumexp(oracle.lens_logits(
+            resid[layer].float().cpu(), lw.w_norm.cpu(), wu, 30.0, residual_dtype=BF16), -1)).abs().max().item() <= 2e-3
+        _, _, bad = topk_sets_match(grid.top_id[layer].cpu(), probs, 10)
+        assert not bad, (layer, bad)

@@ -97,3 +97,118 @@ def test_one_sweep_ll_topk_equals_two_sweeps_at_full_size(big):
         assert abs(float(a[9] - b[9])) <= 2e-3 * float(b[9])
     assert same.float().mean().item() > 0.99
     assert torch.allclose(v1[ok][:, 0], v2[ok][:, 0], rtol=2e-3)
+
+
+# ------------------------------------------------------------------------------------------------
+# The WHOLE path at configs[1]'s size against the fp32 oracle on a sampled slice: encode (CTA pairs,
+# overflow re-pass over the ~4096 <bos>-scale rows) -> per-prompt targeting -> ablate + decode at two nested
+# budgets -> lens readout -> LL-Top-10 (first budget: K3 + K5; second: K3F + K6). The sampled prompts -- the first
+# 16 and 16 random ones, 4096 rows, every one of their <bos>-scale rows included -- are generated on the CPU and
+# planted into the device batch, so the oracle sees exactly the kernels' bf16 inputs.
+# ------------------------------------------------------------------------------------------------
+S_SAE = 16384
+BUDGETS_FULL = (8, 256)
+TIE_TAU = 2e-3
+
+
+def _dense_rows(acts, rows, S):
+    """Dense [len(rows), S] f32 of the sparse lists of the given rows."""
+    cnt = acts.count[rows].long()
+    if acts.row_start is None:
+        cnt = cnt.clamp(max=acts.cap)
+        start = rows.long() * acts.cap
+    else:
+        start = acts.row_start[rows]
+    dense = torch.zeros(rows.numel(), S, dtype=torch.float32, device=rows.device)
+    r = torch.repeat_interleave(torch.arange(rows.numel(), device=rows.device), cnt)
+    offs = torch.arange(int(cnt.sum().item()), device=rows.device) - torch.repeat_interleave(torch.cumsum(cnt, 0) - cnt, cnt)
+    pos = torch.repeat_interleave(start, cnt) + offs
+    dense[r, acts.idx[pos].long()] = acts.val[pos]
+    return dense
+
+
+def test_whole_path_at_full_size_matches_the_oracle_on_sampled_prompts(cuda_lib):
+    from _common import BF16, oracle, sae_to_cuda, topk_sets_match
+    from taboo_brittleness_b200 import interventions, ops
+    g = torch.Generator().manual_seed(11)
+    prompts = torch.cat([torch.arange(16), torch.randperm(P - 16, generator=g)[:16] + 16]).sort().values
+    n_s = prompts.numel()
+    # weights: made on the CPU (the oracle needs them in fp32), bf16-exact
+    sae = synthetic.make_sae(D, S_SAE, seed=42)
+    lens = synthetic.make_lens(D, V, seed=42)
+    xs_cpu = synthetic.make_residuals(n_s, T, D, seed=4321)                 # sampled prompts, incl. their <bos> rows
+    sid_cpu = synthetic.make_secret_ids(P, T, V, seed=5)
+    rows_cpu = (prompts[:, None] * T + torch.arange(T)[None]).flatten()
+    synthetic.plant_secret_direction(lens, xs_cpu, sid_cpu[rows_cpu])
+    cur_cpu = torch.randint(0, V, (P * T,), generator=g, dtype=torch.int32)
+    prev_cpu = torch.cat([torch.tensor([-1], dtype=torch.int32), cur_cpu[:-1]])
+    prev_cpu[::T] = -1
+    # the device batch: 4096 prompts, the sampled ones overwritten with the CPU rows
+    x = torch.empty(P * T, D, dtype=torch.bfloat16, device="cuda")
+    for p0 in range(0, P, 512):
+        x[p0 * T:(p0 + 512) * T] = synthetic.make_residuals(512, T, D, seed=100 + p0, device="cuda").to(torch.bfloat16)
+    rows = rows_cpu.cuda()
+    x[rows] = xs_cpu.to("cuda", torch.bfloat16)
+    eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), lens.W_U.to("cuda", torch.bfloat16)),
+                                           softcap=30.0)
+    sid, cur, prev = sid_cpu.cuda(), cur_cpu.cuda(), prev_cpu.cuda()
+    ll = interventions.LLSpec(cur, prev, rows_per_prompt=T, k=10)
+    acts = eng.encode(x)
+    idx, _, rank = eng.targeted_rank(acts, T, m=max(BUDGETS_FULL))
+    res, _ = eng._nested_budgets(x, acts, rank, T, BUDGETS_FULL, sid, "error", ll)
+    x1 = {b: ops.sae_ablate_decode(x, acts, eng.sae, rank, b, rank_rows=T, want_x=True)[0][rows].float().cpu()
+          for b in BUDGETS_FULL}
+    torch.cuda.synchronize()
+    assert acts.row_start is not None, "the <bos>-scale rows must have overflowed into the second encode pass"
+    assert eng.stats.ll_fused_prompts == P, "the second budget must have taken the one-sweep LL path"
+    got_acts = _dense_rows(acts, rows, S_SAE).cpu()
+    got_idx = idx[prompts.cuda()].cpu().long()
+    del acts, x
+
+    # ---- oracle, 8 prompts at a time (the [rows, 256000] probabilities of 1024 rows are 1 GB)
+    sd = sae.as_dict()
+    n_exact_total = 0
+    for c0 in range(0, n_s, 8):
+        sl = slice(c0 * T, (c0 + 8) * T)
+        xc = xs_cpu[sl]
+        pre = xc @ sae.W_enc + sae.b_enc
+        ref_acts = oracle.jumprelu_encode(xc, sae.W_enc, sae.b_enc, sae.threshold)
+        # a1: active sets identical outside the documented tie band
+        mism = (got_acts[sl] > 0) != (ref_acts > 0)
+        near = (pre - sae.threshold).abs() < TIE_TAU * pre.abs().clamp_min(1.0)
+        assert not (mism & ~near).any(), "active set differs away from the threshold"
+        assert mism.sum().item() <= 1e-5 * mism.numel()
+        for b in BUDGETS_FULL:
+            out = oracle.run_path(xc, T, sd, lens.w_norm, lens.W_U, sid_cpu[rows_cpu[sl]], b, 30.0, mode="error",
+                                  residual_dtype=BF16)
+            r = res[b]
+            for j in range(8):
+                q = c0 + j
+                # a2: ablated ids exact, except where the b-th and (b+1)-th mean are a near-tie
+                ks, rs = set(got_idx[q, :b].tolist()), set(out["idx"][j].tolist())
+                if ks != rs:
+                    mean = ref_acts[j * T:(j + 1) * T].mean(0)
+                    kth = torch.topk(mean, b).values[-1]
+                    assert all(abs(float(mean[i] - kth)) <= 1e-4 * float(kth) + 2e-3 for i in ks ^ rs), (q, b)
+                    continue      # a different ablation set: the readouts of this prompt are not comparable
+                pr = rows[q * T:(q + 1) * T]
+                # a4: residual within 2e-2 relative
+                a, bref = x1[b][q * T:(q + 1) * T], out["x1"][j * T:(j + 1) * T]
+                rel = (a - bref).norm(dim=1) / bref.norm(dim=1)
+                assert rel.max().item() <= 2e-2
+                # a9 / a10: secret probability and top-10 sets
+                assert (r.secret_prob[pr].cpu() - out["secret_prob"][j * T:(j + 1) * T]).abs().max().item() <= 1e-3
+                n_exact, n_tie, bad = topk_sets_match(r.top_id[pr].cpu(), out["lse_free_probs"][j * T:(j + 1) * T], 10)
+                assert not bad, (q, b, bad[:4])
+                n_exact_total += n_exact
+                # a11: LL-Top-10 ids (01:35-71, 147-149), near-ties of the 10th sum excepted
+                probs_p = out["lse_free_probs"][j * T:(j + 1) * T]
+                gp = int(prompts[q])
+                cu, pv = cur_cpu[gp * T:(gp + 1) * T].tolist(), prev_cpu[gp * T:(gp + 1) * T].tolist()
+                acc = oracle.aggregate_response_probs(probs_p, cu, pv)
+                want = set(torch.topk(acc, 10).indices.tolist())
+                have = set(r.ll_id[gp].cpu().tolist())
+                if have != want:
+                    tenth = float(torch.topk(acc, 10).values[-1])
+                    assert all(abs(float(acc[i]) - tenth) <= 2e-3 * tenth for i in have ^ want), (q, b)
+    assert n_exact_total >= 0.97 * 2 * n_s * T
