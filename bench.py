@@ -381,7 +381,7 @@ def leg_stress(args, ctx):
     def one_pass(rows_limit=None, record=True):
         a = mark()
         x31 = xs[31 * n_rows:32 * n_rows]
-        acts = ops.sae_encode(x31 if rows_limit is None else x31[:rows_limit], sae, cap=args.encode_cap)
+        acts = ops.sae_encode(x31 if rows_limit is None else x31[:rows_limit], sae, cap=2 * args.encode_cap)
         b = mark()
         mean = ops.latent_mean(acts, T)
         top_idx, _, _ = ops.topm_select(mean, 10)
@@ -399,7 +399,7 @@ def leg_stress(args, ctx):
                 ev["lens"].append((c, d_))
         if record:
             ev["enc"].append((a, b))
-        out.update(top_idx=top_idx, sec_mean=sec_sum / total, overflow=int((acts.count > args.encode_cap).sum().item()),
+        out.update(top_idx=top_idx, sec_mean=sec_sum / total, overflow=int((acts.count > 2 * args.encode_cap).sum().item()),
                    l0=float(acts.count.float().mean().item()))
 
     one_pass(rows_limit=min(sub, n_rows), record=False)       # warm-up on one sub-batch

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """K1 alone (tb_umma_gemm_kernel<EncodeEpi, 2>) at S = 16384 or 131072: event-timed TFLOP/s, and the launch that
-`ncu --set full -k regex:EncodeEpi` captures for the tensor-pipe figure north_star asks for.
+`ncu --set full -k regex:tb_umma_gemm_kernel` captures for the tensor-pipe figure north_star asks for.
 
     python scripts/encode_probe.py [--S 16384] [--rows 75776] [--reps 5]
 """

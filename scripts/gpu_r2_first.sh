@@ -10,7 +10,7 @@ python scripts/encode_probe.py --S 16384 > gpurun_out/r02a_encode_16k.json 2>&1
 python scripts/encode_probe.py --S 131072 --rows 37888 > gpurun_out/r02a_encode_131k.json 2>&1
 cat gpurun_out/r02a_encode_16k.json gpurun_out/r02a_encode_131k.json
 python scripts/encode_probe.py --S 16384 --reps 1 > gpurun_out/plain16.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:EncodeEpi -s 1 -c 1 -o gpurun_out/r02a_encode16k python scripts/encode_probe.py --S 16384 --reps 1 > gpurun_out/ncu16.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:tb_umma_gemm_kernel -s 1 -c 1 -o gpurun_out/r02a_encode16k python scripts/encode_probe.py --S 16384 --reps 1 > gpurun_out/ncu16.log 2>&1
 python scripts/encode_probe.py --S 131072 --rows 37888 --reps 1 > gpurun_out/plain131.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k regex:EncodeEpi -s 1 -c 1 -o gpurun_out/r02a_encode131k python scripts/encode_probe.py --S 131072 --rows 37888 --reps 1 > gpurun_out/ncu131.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:tb_umma_gemm_kernel -s 1 -c 1 -o gpurun_out/r02a_encode131k python scripts/encode_probe.py --S 131072 --rows 37888 --reps 1 > gpurun_out/ncu131.log 2>&1
 ls -la gpurun_out | tail -20

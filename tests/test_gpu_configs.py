@@ -8,6 +8,11 @@ from _common import BF16, cuda_bf16, oracle, sae_to_cuda, synthetic, topk_sets_m
 
 pytestmark = pytest.mark.gpu
 
+# Near-ties of the 10th probability: after a large ablation the kernel's and the oracle's fp32 sums differ in their
+# last bits, a few elements of the bf16 residual round the other way, and a logit moves by ~1e-3 -- so two
+# probabilities within 5e-3 relative of each other may swap places at the cut (secret probabilities still agree to 1e-3).
+TIE_REL = 5e-3
+
 
 def test_random_control_32_seeds_real_sae_shape(cuda_lib):
     """configs[2]: budgets {1, 32, 1024} x seeds 0..31 on the 16384-latent SAE (d = 3584), 2 prompts x 128 tok,
@@ -41,7 +46,7 @@ def test_random_control_32_seeds_real_sae_shape(cuda_lib):
             probs = oracle.lens_probs(x1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
             r = res[(b, seed)]
             assert (r.secret_prob.cpu() - oracle.secret_prob(probs, sid)).abs().max().item() <= 1e-3
-            n_exact, _, bad = topk_sets_match(r.top_id.cpu(), probs, 10)
+            n_exact, _, bad = topk_sets_match(r.top_id.cpu(), probs, 10, rel_gap=TIE_REL)
             assert not bad, (seed, b, bad[:4])
             exact += n_exact
             for p in range(P):
@@ -90,5 +95,5 @@ def test_stress_shapes_131k_targeting_and_42_layer_lens(cuda_lib):
         assert (grid.secret_prob[layer].cpu() - probs[:, secret]).abs().max().item() <= 1e-3
         assert (grid.lse[layer].cpu() - torch.logsumexp(oracle.lens_logits(
             resid[layer].float().cpu(), lw.w_norm.cpu(), wu, 30.0, residual_dtype=BF16), -1)).abs().max().item() <= 2e-3
-        _, _, bad = topk_sets_match(grid.top_id[layer].cpu(), probs, 10)
+        _, _, bad = topk_sets_match(grid.top_id[layer].cpu(), probs, 10, rel_gap=TIE_REL)
         assert not bad, (layer, bad)

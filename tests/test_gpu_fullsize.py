@@ -198,7 +198,8 @@ def test_whole_path_at_full_size_matches_the_oracle_on_sampled_prompts(cuda_lib)
                 assert rel.max().item() <= 2e-2
                 # a9 / a10: secret probability and top-10 sets
                 assert (r.secret_prob[pr].cpu() - out["secret_prob"][j * T:(j + 1) * T]).abs().max().item() <= 1e-3
-                n_exact, n_tie, bad = topk_sets_match(r.top_id[pr].cpu(), out["lse_free_probs"][j * T:(j + 1) * T], 10)
+                n_exact, n_tie, bad = topk_sets_match(r.top_id[pr].cpu(), out["lse_free_probs"][j * T:(j + 1) * T], 10,
+                                                        rel_gap=5e-3)   # near-ties of the 10th probability after a 256-latent ablation
                 assert not bad, (q, b, bad[:4])
                 n_exact_total += n_exact
                 # a11: LL-Top-10 ids (01:35-71, 147-149), near-ties of the 10th sum excepted
