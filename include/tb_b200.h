@@ -198,6 +198,18 @@ int tb_ll_topk_merge(const float* part_val, const int32_t* part_id, int n_parts,
 int tb_probs_ll_colsum(const float* probs, int T, int V, const int32_t* cur_id, const int32_t* prev_id,
                        float* acc, void* stream);
 
+/* K2 for ranks 8..64 in ONE pass over the rows (x read once, h written once; same result contract as
+ * tb_lowrank_remove, Plan:148; no code in the reference). A cluster of d / 256 CTAs holds a 128-row block in
+ * its shared memory: C = x U as per-CTA partial tcgen05 products reduced across the cluster through
+ * distributed shared memory (rank order: deterministic), x' = bf16(x - [C_hi | C_lo][U | U]^T) and the
+ * fused final RMSNorm on the block while it is resident. Needs d % 256 == 0 and d <= 4096
+ * (tb_lowrank_fused_supported returns 1); no scratch. dbg_c (nullable): f32 [n_rows, 32 * ceil(r / 32)],
+ * receives the reduced coefficients x U (tests). */
+int tb_lowrank_fused_supported(int d, int r);
+int tb_lowrank_remove_fused(const void* x_bf16, const void* ut_bf16, int r, int64_t n_rows, int d,
+                            const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
+                            float* dbg_c, void* stream);
+
 /* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------
  * Same readouts as K3 (tb_lens_partials) and K5, for a condition whose rows' logsumexp is
  * already known approximately -- in a sweep over nested ablation budgets, the previous budget's

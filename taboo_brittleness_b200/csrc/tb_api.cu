@@ -14,6 +14,7 @@
 #include "tb_epilogues.cuh"
 #include "tb_gemm.cuh"
 #include "tb_rows.cuh"
+#include "tb_cluster_rows.cuh"
 
 // Progress counters of the soft lockstep between clusters (tb_gemm.cuh): a few rotating slots of
 // 64 counters, so that launches in flight on different streams do not share one.
@@ -458,6 +459,16 @@ int tb_sae_encode(const void* x, const void* w_enc_t, const float* b_enc, const 
   // one unit per row block: a row's list is written by a single thread, in latent order.
   // CTA pairs (UMMA 256 x 256) once there are enough 256-row blocks to fill them; single CTAs for small inputs
   if (n_rows >= static_cast<int64_t>(tb::kBlockM) * di.sms) {
+    // Large batches: 2x1 clusters of pairs as the preferred shape (two row blocks share every W_enc^T tile through
+    // TMA multicast, the clusters are paced against each other), plain pairs on the SMs that form no cluster -- the
+    // lens kernels' default. Plain pairs alone re-read W_enc^T from DRAM once per pair: the ncu capture of round 2a
+    // shows 35.7 GB of DRAM reads per 75,776-row launch for 0.66 GB of operands (profiles/r02b_encode_*).
+    // Operands that are not this GPU's own memory keep the plain pairs (multicast loads read local memory only).
+    if (operand_is_local(x, static_cast<size_t>(n_rows) * d * 2, "x") == TB_OK &&
+        operand_is_local(w_enc_t, static_cast<size_t>(S) * d * 2, "w_enc_t") == TB_OK) {
+      tb::GemmArgs g = make_args(n_rows, S, d, 1, 2, 2, 1);
+      return launch_gemm<tb::EncodeEpi, 2, 2, 1, true>(x, w_enc_t, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+    }
     tb::GemmArgs g = make_args(n_rows, S, d, 1, 2);
     return launch_gemm<tb::EncodeEpi, 2>(x, w_enc_t, g, ep, static_cast<cudaStream_t>(stream), di.sms);
   }
@@ -733,6 +744,90 @@ int tb_lowrank_remove_tc(const void* x, const void* ut, int r, int64_t n_rows, i
     else tb::tb_scale_rows_kernel<8><<<grid, tb::kAblThreads, 0, s>>>(xp, ss, pl.n_parts, w_norm, n, d, eps, hp);
     TB_CUDA(cudaGetLastError());
   }
+  return TB_OK;
+}
+
+namespace {
+// generic 2-D bf16 tensor map: box = [box_rows, 64 elements], 128-byte swizzle
+int make_tmap_box(CUtensorMap* map, const void* base, int64_t rows, int cols, int box_rows) {
+  return make_tmap(map, base, rows, cols, box_rows);
+}
+}  // namespace
+
+int tb_lowrank_fused_supported(int d, int r) {
+  DevInfo di;
+  if (device_info(&di) != TB_OK) return 0;
+  return (r >= 1 && r <= tb::kCrMaxRp && d > 0 && d % tb::kCrW == 0 && d / tb::kCrW <= tb::kCrMaxCta) ? 1 : 0;
+}
+
+int tb_lowrank_remove_fused(const void* x, const void* ut, int r, int64_t n_rows, int d, const float* w_norm,
+                            float eps, void* out_x, void* out_h, float* dbg_c, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (r < 1 || r > tb::kCrMaxRp) return fail(TB_ERR_INVALID, "rank %d outside [1, %d]", r, tb::kCrMaxRp);
+  rc = check_gemm_operands(x, ut, n_rows, r, d);
+  if (rc != TB_OK) return rc;
+  if (d % tb::kCrW != 0 || d / tb::kCrW > tb::kCrMaxCta)
+    return fail(TB_ERR_INVALID, "d=%d: the one-pass kernel wants a multiple of %d, at most %d (use tb_lowrank_remove_tc)", d,
+                tb::kCrW, tb::kCrW * tb::kCrMaxCta);
+  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  if (out_x && (reinterpret_cast<uintptr_t>(out_x) & 15)) return fail(TB_ERR_INVALID, "out_x must be 16-byte aligned");
+  if (out_h && (reinterpret_cast<uintptr_t>(out_h) & 15)) return fail(TB_ERR_INVALID, "out_h must be 16-byte aligned");
+  if (n_rows == 0) return TB_OK;
+  tb::CrArgs a;
+  a.n_rows = static_cast<int>(n_rows);
+  a.d = d;
+  a.rounds = (r + 31) / 32;
+  a.n_cta = d / tb::kCrW;
+  a.rows_own = (tb::kCrRows + a.n_cta - 1) / a.n_cta;
+  a.n_tiles = static_cast<int>((n_rows + tb::kCrRows - 1) / tb::kCrRows);
+  a.w_norm = w_norm;
+  a.eps = eps;
+  a.want_x = out_x ? 1 : 0;
+  a.want_h = out_h ? 1 : 0;
+  a.dbg_c = dbg_c;
+  CUtensorMap tmX, tmU, tmOX, tmOH;
+  rc = make_tmap_box(&tmX, x, n_rows, d, tb::kCrRows);
+  if (rc != TB_OK) return rc;
+  rc = make_tmap_box(&tmU, ut, r, d, 32 * a.rounds);      // rows past r are zero-filled
+  if (rc != TB_OK) return rc;
+  rc = make_tmap_box(&tmOX, out_x ? out_x : out_h, n_rows, d, tb::kCrRows);
+  if (rc != TB_OK) return rc;
+  rc = make_tmap_box(&tmOH, out_h ? out_h : out_x, n_rows, d, tb::kCrRows);
+  if (rc != TB_OK) return rc;
+  auto kern = tb::tb_lowrank_cluster_kernel;
+  TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tb::kCrSmemBytes));
+  if (a.n_cta > 8) TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.blockDim = dim3(tb::kCrThreads, 1, 1);
+  cfg.dynamicSmemBytes = tb::kCrSmemBytes;
+  cfg.stream = static_cast<cudaStream_t>(stream);
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(a.n_cta);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  static int cached[64][tb::kCrMaxCta + 1];
+  int dev = 0;
+  TB_CUDA(cudaGetDevice(&dev));
+  if (cached[dev][a.n_cta] == 0) {
+    cfg.gridDim = dim3(static_cast<unsigned>((di.sms / a.n_cta) * a.n_cta), 1, 1);
+    int n = 0;
+    TB_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    if (n < 1) return fail(TB_ERR_CUDA, "no cluster of %d CTAs fits on this device", a.n_cta);
+    cached[dev][a.n_cta] = n;
+  }
+  int clusters = cached[dev][a.n_cta];
+  if (clusters > a.n_tiles) clusters = a.n_tiles;
+  const char* mc = getenv("TB_MAX_CLUSTERS");
+  if (mc && atoi(mc) > 0 && clusters > atoi(mc)) clusters = atoi(mc);
+  cfg.gridDim = dim3(static_cast<unsigned>(clusters * a.n_cta), 1, 1);
+  TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmX, tmU, tmOX, tmOH, a));
   return TB_OK;
 }
 
@@ -1020,6 +1115,12 @@ int tb_logit_lens_static(const void* h, const void* w_u, int64_t n_rows, int d, 
 }  // extern "C"
 
 #ifdef TB_WAIT_PROFILE
+// Probe build only: per-CTA phase cycles of the one-pass K2 kernel (256 x 16 counters; scripts/k2_profile.py)
+extern "C" int tb_debug_k2_profile(long long* out_host) {
+  TB_CUDA(cudaDeviceSynchronize());
+  TB_CUDA(cudaMemcpyFromSymbol(out_host, tb::g_k2_prof, sizeof(long long) * 256 * 16));
+  return TB_OK;
+}
 // Probe build only: read and clear the per-CTA wait counters of tb_gemm.cuh (256 x 8 cycle counts).
 extern "C" int tb_debug_wait_profile(long long* out_host) {
   TB_CUDA(cudaDeviceSynchronize());

@@ -320,11 +320,16 @@ _PROJ_SCRATCH: dict = {}
 
 
 def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.Tensor] = None,
-                   eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False
+                   eps: float = GEMMA2_EPS, want_x: bool = True, want_h: bool = False, one_pass: bool = False,
+                   dbg_c: Optional[torch.Tensor] = None
                    ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
     """x' = x - (x U) U^T for orthonormal U [d, r], r <= 64 (Plan:148). Small ranks run in one
-    HBM-bound CUDA-core kernel (up to 7 by default); from 8 on both thin products go to the tensor cores
-    (``tb_lowrank_remove_tc``)."""
+    HBM-bound CUDA-core kernel (up to 7 by default); from 8 on both thin products go to the tensor cores, in three
+    passes over the rows (``tb_lowrank_remove_tc``). ``one_pass=True`` (d a multiple of 256, at most 4096) takes
+    ``tb_lowrank_remove_fused`` instead: x read once and h written once by a cluster of d / 256 CTAs that keeps
+    each 128-row block in shared memory -- same results, 14 KB instead of 35 KB of HBM traffic per row, but
+    measured SLOWER than the three passes (the per-block chain of cluster barriers and
+    distributed-shared-memory exchanges is six times the block's HBM time), so it is not the default."""
     _need(x, torch.bfloat16, "x", 2)
     _need(U, torch.bfloat16, "U", 2)
     n, d = x.shape
@@ -337,6 +342,11 @@ def lowrank_remove(x: torch.Tensor, U: torch.Tensor, *, w_norm: Optional[torch.T
     if n == 0:
         return out_x, out_h
     lib = _lib.load()
+    if r >= LOWRANK_TC_MIN and one_pass and lib.tb_lowrank_fused_supported(d, r):
+        # one pass over the rows: a cluster of d / 256 CTAs keeps each 128-row block in shared memory
+        check(lib.tb_lowrank_remove_fused(_ptr(x), _ptr(ut), r, n, d, _ptr(w_norm), eps, _ptr(out_x), _ptr(out_h),
+                                          _ptr(dbg_c), _stream()), "tb_lowrank_remove_fused")
+        return out_x, out_h
     if r >= LOWRANK_TC_MIN:
         need = int(lib.tb_lowrank_tc_scratch_bytes(n, d, r))
         if need < 0:

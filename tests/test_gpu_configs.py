@@ -8,10 +8,9 @@ from _common import BF16, cuda_bf16, oracle, sae_to_cuda, synthetic, topk_sets_m
 
 pytestmark = pytest.mark.gpu
 
-# Near-ties of the 10th probability: after a large ablation the kernel's and the oracle's fp32 sums differ in their
-# last bits, a few elements of the bf16 residual round the other way, and a logit moves by ~1e-3 -- so two
-# probabilities within 5e-3 relative of each other may swap places at the cut (secret probabilities still agree to 1e-3).
-TIE_REL = 5e-3
+# Near-ties of the 10th probability: two probabilities within this relative distance may swap places at the cut
+# (the lens GEMM accumulates bf16 products in another order than the oracle's fp32 matmul).
+TIE_REL = 2e-3
 
 
 def test_random_control_32_seeds_real_sae_shape(cuda_lib):
@@ -36,15 +35,34 @@ def test_random_control_32_seeds_real_sae_shape(cuda_lib):
     assert eng.stats.ll_fused_prompts == 95 * P          # only the very first condition pays the second sweep
     acts = oracle.jumprelu_encode(x, sae.W_enc, sae.b_enc, sae.threshold)
     xhat_err = x - oracle.sae_decode(acts, sae.W_dec, sae.b_dec)
-    exact = 0
+    xs = cuda_bf16(x)
+    k_acts = eng.encode(xs)
+    # rows where the kernel's active set differs from the oracle's (a pre-activation within rounding of its
+    # threshold: the documented near-threshold ties) -- if such a latent is ablated, one side subtracts a_i W_dec[i]
+    # (|a_i| ~ theta, about 2 % of a row's norm) and the other does not: those rows are skipped per condition
+    flipped = (k_acts.to_dense().cpu() > 0) != (acts > 0)
+    assert flipped.sum().item() <= 4
+    exact = skipped = 0
     for seed in seeds:
         idx = oracle.random_latents(S, seed, 1024)
+        rank = interventions.random_rank_table(S, seed, 1024)
         for b in budgets:
             a2 = acts.clone()
             a2[:, idx[:b]] = 0
             x1 = (oracle.sae_decode(a2, sae.W_dec, sae.b_dec) + xhat_err).to(BF16).float()
-            probs = oracle.lens_probs(x1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
+            # the kernel's own residual: within 2e-2 relative of the oracle's (north_star); a few elements round to the
+            # other bf16 neighbour because the fp32 sums are taken in another order -- on an outlier dimension
+            # (|x| ~ 280, ulp 2) one such flip moves logits by ~1e-2, so rankings are checked on the kernel's residual
+            kx1 = ops.sae_ablate_decode(xs, k_acts, eng.sae, rank, b, want_x=True)[0].float().cpu()
+            ok = ~flipped[:, idx[:b]].any(1)
+            skipped += int((~ok).sum())
+            rel = (kx1 - x1).norm(dim=1) / x1.norm(dim=1)
+            assert rel[ok].max().item() <= 2e-2
+            assert (kx1 != x1)[ok].float().mean().item() < 5e-3
             r = res[(b, seed)]
+            probs_o = oracle.lens_probs(x1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
+            assert (r.secret_prob.cpu() - oracle.secret_prob(probs_o, sid))[ok].abs().max().item() <= 1e-3
+            probs = oracle.lens_probs(kx1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
             assert (r.secret_prob.cpu() - oracle.secret_prob(probs, sid)).abs().max().item() <= 1e-3
             n_exact, _, bad = topk_sets_match(r.top_id.cpu(), probs, 10, rel_gap=TIE_REL)
             assert not bad, (seed, b, bad[:4])
@@ -55,7 +73,7 @@ def test_random_control_32_seeds_real_sae_shape(cuda_lib):
                 if have != want:
                     tenth = float(torch.topk(acc, 10).values[-1])
                     assert all(abs(float(acc[i]) - tenth) <= 2e-3 * tenth for i in have ^ want), (seed, b, p)
-    assert exact >= 0.97 * 96 * P * T
+    assert exact >= 0.97 * 96 * P * T and skipped <= 8
 
 
 def test_stress_shapes_131k_targeting_and_42_layer_lens(cuda_lib):

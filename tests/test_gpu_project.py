@@ -53,6 +53,39 @@ def test_lowrank_tensor_core_path_h_alone_equals_h_next_to_x(cuda_lib, r, d, n_r
     assert ((got - ref).abs() <= 0.0079 * ref.abs() + 1e-3).all()
 
 
+@pytest.mark.parametrize("r,d,n_rows", [(8, 256, 128), (9, 512, 300), (40, 512, 1000), (16, 3584, 700), (64, 3584, 4096),
+                                        (33, 3584, 5000)])
+def test_lowrank_one_pass_cluster_kernel(cuda_lib, r, d, n_rows):
+    """tb_lowrank_remove_fused (a cluster of d / 256 CTAs holds each 128-row block; split-K coefficients reduced
+    through distributed shared memory in rank order): the reduced coefficients equal x U to fp32 accuracy, x' and h
+    equal the three-pass path except where a different fp32 summation order flips a bf16 rounding, h alone equals
+    h next to x', and the result is deterministic."""
+    from taboo_brittleness_b200 import ops
+    xc = synthetic.make_residuals(-(-n_rows // 128), 128, d, seed=5 + r)[:n_rows]
+    Uc = synthetic.bf16_exact(oracle.random_orthonormal(d, r, seed=r))
+    x, U = cuda_bf16(xc), cuda_bf16(Uc)
+    w = synthetic.make_lens(d, 8, seed=1).w_norm.cuda()
+    rp = 32 * ((r + 31) // 32)
+    dbg = torch.full((n_rows, rp), float("nan"), device="cuda")
+    fx, fh = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, one_pass=True, dbg_c=dbg)
+    _, fh2 = ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True, one_pass=True)
+    fx3, fh3 = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, one_pass=True)
+    tx, th = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, one_pass=False)
+    torch.cuda.synchronize()
+    c_ref = xc @ Uc
+    assert (dbg[:, :r].cpu() - c_ref).abs().max().item() <= 5e-6 * c_ref.abs().max().item()
+    assert rp == r or dbg[:, r:].abs().max().item() == 0.0
+    assert torch.equal(fh, fh2) and torch.equal(fx, fx3) and torch.equal(fh, fh3)
+    assert (fx != tx).float().mean().item() < 5e-3 and (fh != th).float().mean().item() < 5e-3
+    ref = oracle.lowrank_remove(xc, Uc, residual_dtype=BF16)
+    got = fx.float().cpu()
+    assert (got != ref).float().mean().item() < 5e-3
+    assert ((got - ref).abs() <= 0.0079 * ref.abs() + 1e-3).all()
+    ref_h, got_h = ops.rmsnorm(fx, w).float(), fh.float()
+    assert (got_h != ref_h).float().mean().item() < 2e-3
+    assert ((got_h - ref_h).abs() <= 0.0079 * ref_h.abs() + 1e-6).all()
+
+
 def test_lowrank_tc_scratch_is_checked(cuda_lib):
     from taboo_brittleness_b200 import _lib
     need = cuda_lib.tb_lowrank_tc_scratch_bytes(1000, 3584, 33)
