@@ -670,7 +670,7 @@ def run_native(args, rank, local_rank, world):
             gbs = row_bytes / (row_ms * 1e-3) / 1e9
             line["roofline"]["hbm_path"] = {
                 "kernel": ("tb_lowrank_remove / tb_lowrank_remove_tc (K2, ranks %s)" % list(RANKS)) if proj
-                else "tb_sae_ablate_decode (K1b, budgets %s)" % list(BUDGETS),
+                else "tb_sae_rank_lists once + tb_sae_ablate_ranked per budget (K1b, budgets %s)" % list(BUDGETS),
                 "bound": "hbm", "achieved": gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                 "frac": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
                 "algorithmic_bytes_per_row": 4 * D, "share_of_step": row_ms / (ms_step * args.steps)}

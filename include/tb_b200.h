@@ -104,6 +104,22 @@ int tb_sae_ablate_decode(const void* x_bf16, const int64_t* row_start, int cap,
                          int64_t n_rows, int d, int S, const float* w_norm, float eps,
                          void* out_x_bf16, void* out_h_bf16, void* stream);
 
+/* K1b for NESTED budgets (Plan:126: budgets are prefixes of one ranking per prompt, or per seed for the random
+ * control, Plan:128). tb_sae_rank_lists runs once per ranking: for every row, its active latents that appear in
+ * the ranking (rank < 1024), ordered by rank, written as key = rank << 20 | latent and value into out_key /
+ * out_val at the row's list position (same row_start / cap layout as idx / val, so the buffers have the same
+ * size), their number into out_count. tb_sae_ablate_ranked then serves any budget: it reads the leading entries
+ * with rank < budget (at most `budget`) and computes what tb_sae_ablate_decode computes in mode 0, the sum taken
+ * in rank order. S <= 2^20. No code in the reference.
+ */
+int tb_sae_rank_lists(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,
+                      const float* val, const uint16_t* rank, int rank_rows, int64_t n_rows, int S,
+                      int32_t* out_key, float* out_val, int32_t* out_count, void* stream);
+int tb_sae_ablate_ranked(const void* x_bf16, const int64_t* row_start, int cap, const int32_t* sel_count,
+                         const int32_t* sel_key, const float* sel_val, const void* w_dec_bf16, int budget,
+                         int64_t n_rows, int d, const float* w_norm, float eps, void* out_x_bf16,
+                         void* out_h_bf16, void* stream);
+
 /* ---- K2: low-rank direction removal x' = x - (x U) U^T ----------------------------------
  * No code in the reference (Execution Plan:148 r_edited = r - P_U(r); random control :150).
  * ut = U^T, bf16 [r, d], r <= 64, columns of U orthonormal. Outputs as for K1b.

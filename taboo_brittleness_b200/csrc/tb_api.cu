@@ -15,6 +15,7 @@
 #include "tb_gemm.cuh"
 #include "tb_rows.cuh"
 #include "tb_cluster_rows.cuh"
+#include "tb_ranked.cuh"
 
 // Progress counters of the soft lockstep between clusters (tb_gemm.cuh): a few rotating slots of
 // 64 counters, so that launches in flight on different streams do not share one.
@@ -575,6 +576,81 @@ int tb_sae_ablate_decode(const void* x, const int64_t* row_start, int cap, const
   else if (nv <= 4) tb::tb_ablate_decode_kernel<4><<<grid, tb::kAblThreads, 0, s>>>(a);
   else tb::tb_ablate_decode_kernel<8><<<grid, tb::kAblThreads, 0, s>>>(a);
   TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_sae_rank_lists(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx, const float* val,
+                      const uint16_t* rank, int rank_rows, int64_t n_rows, int S, int32_t* out_key, float* out_val,
+                      int32_t* out_count, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!count || !idx || !val || !rank || !out_key || !out_val || !out_count) return fail(TB_ERR_INVALID, "null pointer");
+  if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (rank_rows < 0) return fail(TB_ERR_INVALID, "rank_rows < 0");
+  if (S < 1 || S > (1 << 20)) return fail(TB_ERR_INVALID, "S=%d outside [1, 2^20] (latent ids are packed into 20 bits)", S);
+  if (n_rows == 0) return TB_OK;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 8;
+  const unsigned grid = static_cast<unsigned>(n_rows < max_grid ? n_rows : max_grid);
+  tb::tb_rank_lists_kernel<<<grid, tb::kRankListThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      row_start, cap, count, idx, val, rank, rank_rows, static_cast<int>(n_rows), S, out_key, out_val, out_count);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_sae_ablate_ranked(const void* x, const int64_t* row_start, int cap, const int32_t* sel_count,
+                         const int32_t* sel_key, const float* sel_val, const void* w_dec, int budget, int64_t n_rows,
+                         int d, const float* w_norm, float eps, void* out_x, void* out_h, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!x || !sel_count || !sel_key || !sel_val || !w_dec) return fail(TB_ERR_INVALID, "null pointer");
+  if (budget < 0 || budget > tb::kRankedMax) return fail(TB_ERR_INVALID, "budget %d outside [0, %d]", budget, tb::kRankedMax);
+  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (n_rows == 0) return TB_OK;
+  if (d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  const int nv = (d / 8 + tb::kRowGroupThreads - 1) / tb::kRowGroupThreads;
+  if (nv > 8) return fail(TB_ERR_INVALID, "d=%d too large for the ablate/decode kernel (max 8192)", d);
+  tb::AblateRankedArgs a;
+  a.x = static_cast<const __nv_bfloat16*>(x);
+  a.row_start = row_start;
+  a.cap = cap;
+  a.sel_count = sel_count;
+  a.sel_key = sel_key;
+  a.sel_val = sel_val;
+  a.w_dec = static_cast<const __nv_bfloat16*>(w_dec);
+  a.budget = budget;
+  {
+    // prefixes this long go to the whole-CTA kernel (TB_HEAVY_MIN overrides; larger than any budget = never)
+    const char* hm = getenv("TB_HEAVY_MIN");
+    a.heavy_min = hm ? atoi(hm) : 48;
+    if (a.heavy_min < 1 || d > 8 * 2 * tb::kHeavyThreads) a.heavy_min = tb::kRankedMax + 1;
+  }
+  a.w_norm = w_norm;
+  a.eps = eps;
+  a.out_x = static_cast<__nv_bfloat16*>(out_x);
+  a.out_h = static_cast<__nv_bfloat16*>(out_h);
+  a.n_rows = static_cast<int>(n_rows);
+  a.d = d;
+  const int64_t blocks = (n_rows + tb::kRowGroups - 1) / tb::kRowGroups;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 4;
+  const unsigned grid = static_cast<unsigned>(blocks < max_grid ? blocks : max_grid);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (nv == 1) tb::tb_ablate_ranked_kernel<1><<<grid, tb::kAblThreads, 0, s>>>(a);
+  else if (nv == 2) tb::tb_ablate_ranked_kernel<2><<<grid, tb::kAblThreads, 0, s>>>(a);
+  else if (nv <= 4) tb::tb_ablate_ranked_kernel<4><<<grid, tb::kAblThreads, 0, s>>>(a);
+  else tb::tb_ablate_ranked_kernel<8><<<grid, tb::kAblThreads, 0, s>>>(a);
+  TB_CUDA(cudaGetLastError());
+  if (a.heavy_min <= budget && d <= 8 * 2 * tb::kHeavyThreads) {
+    // the rows the row-group kernel skipped (a prefix of heavy_min entries or more): a whole CTA per row
+    const int64_t hgrid = static_cast<int64_t>(di.sms) * 2;      // one resident wave (two 512-thread CTAs per SM)
+    const unsigned hg = static_cast<unsigned>(n_rows < hgrid ? n_rows : hgrid);
+    if (d <= 8 * tb::kHeavyThreads) tb::tb_ablate_heavy_kernel<1><<<hg, tb::kHeavyThreads, 0, s>>>(a);
+    else tb::tb_ablate_heavy_kernel<2><<<hg, tb::kHeavyThreads, 0, s>>>(a);
+    TB_CUDA(cudaGetLastError());
+  }
   return TB_OK;
 }
 

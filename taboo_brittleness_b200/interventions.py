@@ -86,6 +86,7 @@ class InterventionEngine:
         # budget and can sit on SMs the next persistent lens grid wants -- so it is off by default.
         self.overlap = False
         self._side = None
+        self.use_ranked = True       # nested budgets read prefixes of rank-ordered lists (ops.rank_lists) in K1b
         self.ll_alpha = 0.5          # candidate threshold = ll_alpha * previous condition's k-th best sum
         self.ll_cand_cap = 256       # candidate slots per prompt
 
@@ -180,14 +181,20 @@ class InterventionEngine:
 
     def ablate_and_read(self, x, acts, rank, budget: int, *, rank_rows: int = 0, row_table=None,
                         secret_id=None, mode: str = "error", finalize: bool = True, ll: Optional[LLSpec] = None,
-                        ll_state: Optional[LLState] = None):
-        """With ``ll_state`` (from the previous nested condition) returns (Readout, next LLState)."""
+                        ll_state: Optional[LLState] = None, ranked: Optional[ops.RankedActs] = None):
+        """With ``ll_state`` (from the previous nested condition) returns (Readout, next LLState).
+        ``ranked`` (``ops.rank_lists`` of the same acts and ranking; error-term mode only) lets the budget read
+        just the leading entries of rank-ordered lists instead of looking every active latent up in the table."""
         if self.time_lens:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-        _, h = ops.sae_ablate_decode(x, acts, self.sae, rank, budget, mode=mode, rank_rows=rank_rows,
-                                     row_table=row_table, w_norm=self.lens.w_norm, eps=self.lens.eps,
-                                     want_x=False, want_h=True)
+        if ranked is not None and mode == "error" and row_table is None:
+            _, h = ops.sae_ablate_ranked(x, ranked, self.sae, budget, w_norm=self.lens.w_norm, eps=self.lens.eps,
+                                         want_x=False, want_h=True)
+        else:
+            _, h = ops.sae_ablate_decode(x, acts, self.sae, rank, budget, mode=mode, rank_rows=rank_rows,
+                                         row_table=row_table, w_norm=self.lens.w_norm, eps=self.lens.eps,
+                                         want_x=False, want_h=True)
         if self.time_lens:
             e1.record()      # algorithmic traffic: x in, h out
             self.stats.row_events.append((e0, e1, 4.0 * x.shape[0] * x.shape[1]))
@@ -223,12 +230,24 @@ class InterventionEngine:
         if fusable and self.overlap and len(budgets) >= 3:
             return self._nested_budgets_overlapped(x, acts, rank, rank_rows, budgets, secret_id, mode, ll, state)
         out = {}
+        ranked = None
+        if self.use_ranked and mode == "error" and len(budgets) > 1:
+            # one pass over the active lists for the whole chain: each row's ranked latents in rank order
+            if self.time_lens:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            ranked = ops.rank_lists(acts, rank, rank_rows)
+            if self.time_lens:
+                e1.record()      # part of K1b's cost, no algorithmic bytes of its own
+                self.stats.row_events.append((e0, e1, 0.0))
+            self.stats.launches += 1
         for b in sorted(int(v) for v in budgets):
             if fusable and state is not None:
                 out[b], state = self.ablate_and_read(x, acts, rank, b, rank_rows=rank_rows, secret_id=secret_id,
-                                                     mode=mode, ll=ll, ll_state=state)
+                                                     mode=mode, ll=ll, ll_state=state, ranked=ranked)
             else:
-                r = self.ablate_and_read(x, acts, rank, b, rank_rows=rank_rows, secret_id=secret_id, mode=mode, ll=ll)
+                r = self.ablate_and_read(x, acts, rank, b, rank_rows=rank_rows, secret_id=secret_id, mode=mode, ll=ll,
+                                         ranked=ranked)
                 out[b] = r
                 if fusable:
                     state = LLState(r.lens.lse, r.ll_sum[:, ll.k - 1].contiguous())

@@ -312,6 +312,53 @@ def sae_ablate_decode(x: Optional[torch.Tensor], acts: SparseActs, sae: SaeWeigh
     return out_x, out_h
 
 
+@dataclass
+class RankedActs:
+    """Per row, the active latents that appear in one ranking, ordered by rank (``tb_sae_rank_lists``): what the
+    nested budgets of a sweep share. Same list layout as the ``SparseActs`` it was made from."""
+    count: torch.Tensor                 # i32 [rows]
+    key: torch.Tensor                   # i32 flat: rank << 20 | latent
+    val: torch.Tensor                   # f32 flat
+    cap: int = 0
+    row_start: Optional[torch.Tensor] = None
+
+    @property
+    def n_rows(self) -> int:
+        return self.count.shape[0]
+
+
+def rank_lists(acts: SparseActs, rank: torch.Tensor, rank_rows: int = 0) -> RankedActs:
+    """Order every row's ranked active latents by rank, once per ranking (per prompt: ``rank_rows`` rows share a
+    table; 0: one table for all rows)."""
+    _need(rank, torch.uint16, "rank", 2)
+    dev = acts.count.device
+    key = torch.empty_like(acts.idx)
+    val = torch.empty_like(acts.val)
+    cnt = torch.empty(acts.n_rows, dtype=torch.int32, device=dev)
+    if acts.n_rows:
+        check(_lib.load().tb_sae_rank_lists(_ptr(acts.row_start), acts.cap, _ptr(acts.count), _ptr(acts.idx), _ptr(acts.val),
+                                            _ptr(rank), rank_rows, acts.n_rows, acts.S, _ptr(key), _ptr(val), _ptr(cnt),
+                                            _stream()), "tb_sae_rank_lists")
+    return RankedActs(count=cnt, key=key, val=val, cap=acts.cap, row_start=acts.row_start)
+
+
+def sae_ablate_ranked(x: torch.Tensor, ranked: RankedActs, sae: SaeWeights, budget: int, *,
+                      w_norm: Optional[torch.Tensor] = None, eps: float = GEMMA2_EPS, want_x: bool = True,
+                      want_h: bool = False) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+    """x' = x - sum over the row's active latents with rank < budget of a_i W_dec[i] (the error-term form of
+    ``sae_ablate_decode``), from rank-ordered lists: a budget reads only its prefix."""
+    _need(x, torch.bfloat16, "x", 2)
+    n, d = x.shape
+    out_x = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_x else None
+    out_h = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_h else None
+    if n == 0:
+        return out_x, out_h
+    check(_lib.load().tb_sae_ablate_ranked(_ptr(x), _ptr(ranked.row_start), ranked.cap, _ptr(ranked.count), _ptr(ranked.key),
+                                           _ptr(ranked.val), _ptr(sae.w_dec), int(budget), n, d, _ptr(w_norm), eps,
+                                           _ptr(out_x), _ptr(out_h), _stream()), "tb_sae_ablate_ranked")
+    return out_x, out_h
+
+
 LOWRANK_SMALL = 8     # ranks up to this can use the kernel that keeps U^T in shared memory
 LOWRANK_TC_MIN = 8    # ... and from this rank on the tensor-core path is faster (measured: 1.88 vs 2.22 ms at r = 8)
 
