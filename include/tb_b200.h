@@ -226,6 +226,16 @@ int tb_lowrank_remove_fused(const void* x_bf16, const void* ut_bf16, int r, int6
                             const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
                             float* dbg_c, void* stream);
 
+/* ---- K3 with dense output: the compatibility surface of get_layer_logits ------------------
+ * src/models.py:135-144 returns softmax(lm_head(norm(layer_output))) for every position as a dense array.
+ * tb_lens_dense_partials is tb_lens_partials (no secret id, single shard) that also writes the (soft-capped)
+ * logits to logits_out f32 [n_rows, V]; after tb_lens_merge has produced lse, tb_probs_from_logits turns the
+ * array into probabilities in place: p = exp(logit - lse[row]). One GEMM per layer. cta_pair: 0 or 1. */
+int tb_lens_dense_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V, float softcap,
+                           int n_chunks, int cta_pair, float* pm, float* ps, float* psec, float* ptv, int32_t* pti,
+                           float* logits_out, void* stream);
+int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V, void* stream);
+
 /* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------
  * Same readouts as K3 (tb_lens_partials) and K5, for a condition whose rows' logsumexp is
  * already known approximately -- in a sweep over nested ablation budgets, the previous budget's

@@ -961,6 +961,47 @@ int tb_lens_partials(const void* h, const void* w_u, int64_t n_rows, int d, int 
   return launch_gemm_mode<tb::LensEpi>(cm, h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
 }
 
+int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, float softcap, int n_chunks,
+                           int cta_pair, float* pm, float* ps, float* psec, float* ptv, int32_t* pti, float* logits_out,
+                           void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(h, w_u, n_rows, V, d);
+  if (rc != TB_OK) return rc;
+  if (!pm || !ps || !psec || !ptv || !pti || !logits_out) return fail(TB_ERR_INVALID, "null buffer");
+  if (cta_pair != 0 && cta_pair != 1) return fail(TB_ERR_INVALID, "the dense mode runs as single CTAs (0) or CTA pairs (1)");
+  if (reinterpret_cast<uintptr_t>(logits_out) & 15) return fail(TB_ERR_INVALID, "logits_out must be 16-byte aligned");
+  const int G = cta_pair ? 2 : 1;
+  tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, G);
+  if (g.n_chunks != n_chunks)
+    return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)", n_chunks, g.n_tiles,
+                g.n_chunks);
+  tb::LensDenseEpi::Params ep;
+  ep.lens.secret_id = nullptr;
+  ep.lens.vocab_offset = 0;
+  ep.lens.softcap = softcap;
+  ep.lens.pm = pm; ep.lens.ps = ps; ep.lens.psec = psec; ep.lens.ptv = ptv; ep.lens.pti = pti;
+  ep.out = logits_out;
+  if (G == 2) return launch_gemm<tb::LensDenseEpi, 2>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  return launch_gemm<tb::LensDenseEpi, 1>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!logits || !lse) return fail(TB_ERR_INVALID, "null pointer");
+  if (n_rows < 0 || V < 1) return fail(TB_ERR_INVALID, "bad shape");
+  if (n_rows == 0) return TB_OK;
+  const int64_t total = n_rows * static_cast<int64_t>(V);
+  const int64_t want = (total + 255) / 256, cap = static_cast<int64_t>(di.sms) * 16;
+  tb::tb_probs_from_logits_kernel<<<static_cast<unsigned>(want < cap ? want : cap), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      logits, lse, n_rows, V);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
 int tb_lens_merge(const float* pm, const float* ps, const float* psec, const float* ptv, const int32_t* pti,
                   int n_parts, int64_t n_rows, int finalize, float* om, float* os, float* osec,
                   float* otv, int32_t* oti, float* lse, float* secret_prob, float* top_prob,

@@ -845,6 +845,48 @@ struct ProjApplyEpi {
 };
 
 // =========================================================================================
+// K3 with a dense output, for the compatibility surface (src/models.py:135-144 returns the whole
+// [layers, T, V] probability array): the lens readout of LensEpi plus the (soft-capped) logits written
+// to out [M, N] fp32 in the same sweep. tb_probs_from_logits_kernel then turns them into probabilities
+// in place with the merged logsumexp: one GEMM per layer instead of a dense GEMM plus a readout sweep.
+// =========================================================================================
+struct LensDenseEpi {
+  static constexpr int kEpiWarps = LensEpi::kEpiWarps;
+  static constexpr bool kSweepA = false;
+  static constexpr bool kTileHooks = false;
+  static constexpr int kExtraSmem = 0;
+  struct Params {
+    LensEpi::Params lens;
+    float* out;          // [M, N] fp32: soft-capped logits (natural-log units)
+  };
+  using State = LensEpi::State;
+  __device__ __forceinline__ static void begin_unit(State& st, const Params& p, const GemmArgs& g, int row, int part) {
+    LensEpi::begin_unit(st, p.lens, g, row, part);
+  }
+  __device__ __forceinline__ static void process(State& st, const Params& p, const GemmArgs& g,
+                                                 const uint32_t (&v)[32], int row, int col0) {
+    if (row < g.M) {
+      const CapLog2 cap2(p.lens.softcap);
+      float* o = p.out + static_cast<size_t>(row) * g.N + col0;
+      if (col0 + 32 <= g.N && (g.N & 3) == 0) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          reinterpret_cast<float4*>(o)[q] = make_float4(cap2(__uint_as_float(v[4 * q])) * kLn2, cap2(__uint_as_float(v[4 * q + 1])) * kLn2,
+                                                        cap2(__uint_as_float(v[4 * q + 2])) * kLn2, cap2(__uint_as_float(v[4 * q + 3])) * kLn2);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < g.N) o[j] = cap2(__uint_as_float(v[j])) * kLn2;
+      }
+    }
+    LensEpi::process(st, p.lens, g, v, row, col0);
+  }
+  __device__ __forceinline__ static void end_unit(State& st, const Params& p, const GemmArgs& g, int row, int part) {
+    LensEpi::end_unit(st, p.lens, g, row, part);
+  }
+};
+
+// =========================================================================================
 // Validation epilogue: store the fp32 accumulator. Used only by the tests that pin the
 // TMA / UMMA-descriptor / TMEM plumbing against a plain matmul.
 // =========================================================================================

@@ -1258,4 +1258,13 @@ __global__ void __launch_bounds__(kCandSlots) tb_ll_candidates_finalize_kernel(c
   }
 }
 
+// p[r, v] = exp(logit[r, v] - lse[r]) in place over a dense [n_rows, V] fp32 array (the compatibility surface's
+// all_probs, src/models.py:138). HBM-bound: one read and one write of the array.
+__global__ void tb_probs_from_logits_kernel(float* __restrict__ logits, const float* __restrict__ lse, int64_t n_rows, int V) {
+  const int64_t total = n_rows * static_cast<int64_t>(V);
+  for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x)
+    logits[i] = expf(logits[i] - __ldg(lse + i / V));
+}
+
 }  // namespace tb

@@ -230,20 +230,16 @@ def get_layer_logits(model, prompt: str, apply_chat_template: bool = False,
                      layer_of_interest: Optional[int] = None):
     """Compatibility mode of src/models.py:97-170: dense ``all_probs`` [L, T, V] float32 for every
     layer, plus the optional layer residual. Meant for the short sequences the drivers cache
-    (T < ~70): logits come from the tcgen05 main loop with a dense store, the softmax
-    normaliser from the fused readout. Use ``get_layer_readouts`` when only readouts are needed."""
+    (T < ~70): the lens kernel writes the logits of all layers' rows in the same sweep in which it
+    accumulates their logsumexp (``ops.lens_dense_probs``), an elementwise pass normalises them in place. Use ``get_layer_readouts`` when only readouts are needed."""
     prompt = _prepare_prompt(model, prompt, apply_chat_template)
     ids, resid = model.layer_residuals(prompt)            # [L, T, d] bf16
     lens = model.lens_weights()
     L, T, d = resid.shape
     h = ops.rmsnorm(resid.reshape(L * T, d).contiguous(), lens.w_norm, lens.eps)
-    probs_layers = []
-    for l in range(L):
-        hl = h[l * T:(l + 1) * T].contiguous()
-        logits = ops.gemm_nt(hl, lens.w_u)                                   # [T, V] f32
-        lse = ops.lens_merge(ops.lens_partials(hl, lens.w_u)).lse           # reference: no softcap
-        probs_layers.append(torch.exp(logits - lse[:, None]))
-    probs = torch.stack(probs_layers)                                        # [L, T, V]
+    # one sweep over W_U for all layers' rows: logits written by the lens kernel, normalised in place
+    # (reference: no softcap on this surface)
+    probs = ops.lens_dense_probs(h, lens.w_u)[0].view(L, T, -1)              # [L, T, V]
     all_probs = probs.detach().cpu().to(dtype=torch.float32).numpy()
     max_probs, tokens = probs.max(dim=-1)
     words = [[model.tokenizer.decode(t.cpu()) for t in layer_tokens] for layer_tokens in tokens]

@@ -627,6 +627,33 @@ def lens_merge(p: LensPartials, finalize: bool = True):
     return o
 
 
+def lens_dense_probs(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0, n_chunks: int = 4,
+                     cta_pair: bool = True) -> Tuple[torch.Tensor, "LensReadout"]:
+    """(probs f32 [rows, V], readout) of an already normalised operand: softmax(lm_head(h)) as a dense array
+    (src/models.py:135-138, what ``get_layer_logits`` returns per layer) from ONE sweep -- the lens kernel writes
+    the logits while it accumulates the logsumexp, an elementwise pass normalises them in place. For the short
+    sequences of the compatibility surface: rows * V * 4 bytes are materialised."""
+    _need(h, torch.bfloat16, "h", 2)
+    _need(w_u, torch.bfloat16, "w_u", 2)
+    n, d = h.shape
+    V = w_u.shape[0]
+    n_tiles = -(-V // BLOCK_N)
+    n_chunks = max(1, min(n_chunks, n_tiles))
+    while -(-n_tiles // -(-n_tiles // n_chunks)) != n_chunks:      # no empty chunk
+        n_chunks -= 1
+    p = _alloc_partials(n_chunks, n, h.device)
+    probs = torch.empty(n, V, dtype=torch.float32, device=h.device)
+    lib = _lib.load()
+    if n:
+        check(lib.tb_lens_dense_partials(_ptr(h), _ptr(w_u), n, d, V, float(softcap or 0.0), n_chunks, int(bool(cta_pair)),
+                                         _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _ptr(probs),
+                                         _stream()), "tb_lens_dense_partials")
+    out = lens_merge(p, finalize=True)
+    if n:
+        check(lib.tb_probs_from_logits(_ptr(probs), _ptr(out.lse), n, V, _stream()), "tb_probs_from_logits")
+    return probs, out
+
+
 def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,
                secret_id: Optional[torch.Tensor] = None, n_chunks: Optional[int] = None,
                cta_pair=5, prenormed: bool = False) -> LensReadout:
