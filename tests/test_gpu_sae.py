@@ -234,3 +234,40 @@ def test_ranked_lists_and_prefix_ablation(cuda_lib, problem, encoded):
         # (rows whose active set differs from the oracle's at a near-threshold latent are pinned in the encode test)
         clean = ~((acts.to_dense().cpu() > 0) != (problem["acts"] > 0)).any(1)
         assert rel[clean].max().item() <= RESID_REL_TOL
+
+
+def test_ranked_lists_fixed_stride_random_table_and_empty(cuda_lib, problem, encoded):
+    """The same kernels on fixed-stride lists (no overflowing row), one ranking shared by all rows (the random
+    control: rank_rows = 0), a small d (one 16-byte slice per thread in the whole-CTA kernel), and an empty batch."""
+    from taboo_brittleness_b200 import ops
+    rows = [r for r in range(P * T) if r % T != 0][:150]
+    xs = encoded["x"][rows].contiguous()
+    sp = ops.sae_encode(xs, encoded["w"], cap=256)
+    assert sp.row_start is None
+    ridx = oracle.random_latents(S, seed=11, m=1024)
+    rank = ops.rank_table_from_indices(ridx, S).cuda()
+    ranked = ops.rank_lists(sp, rank, 0)
+    w_norm = synthetic.make_lens(D, 8, seed=1).w_norm.cuda()
+    for budget in (1, 300, 1024):
+        ox, oh = ops.sae_ablate_decode(xs, sp, encoded["w"], rank, budget, rank_rows=0, w_norm=w_norm, want_x=True, want_h=True)
+        nx, nh = ops.sae_ablate_ranked(xs, ranked, encoded["w"], budget, w_norm=w_norm, want_x=True, want_h=True)
+        torch.cuda.synchronize()
+        assert (nx != ox).float().mean().item() < 2e-3 and (nh != oh).float().mean().item() < 4e-3
+        assert ((nx.float() - ox.float()).abs() <= 0.0079 * ox.float().abs() + 1e-3).all()
+    dense = sp.to_dense()
+    want_cnt = (dense[:, ridx.cuda()] > 0).sum(1)
+    assert torch.equal(ranked.count.long(), want_cnt)
+    # every row taken by the whole-CTA kernel (threshold 1) gives the row-group kernel's residual
+    import os
+    os.environ["TB_HEAVY_MIN"] = "1"
+    try:
+        hx, _ = ops.sae_ablate_ranked(xs, ranked, encoded["w"], 1024, w_norm=w_norm, want_x=True, want_h=True)
+    finally:
+        del os.environ["TB_HEAVY_MIN"]
+    lx, _ = ops.sae_ablate_ranked(xs, ranked, encoded["w"], 1024, w_norm=w_norm, want_x=True, want_h=True)
+    torch.cuda.synchronize()
+    assert torch.equal(hx, lx)
+    empty = ops.SparseActs(count=torch.empty(0, dtype=torch.int32, device="cuda"), idx=sp.idx[:1], val=sp.val[:1], S=S, cap=256)
+    r0 = ops.rank_lists(empty, rank, 0)
+    e0, _ = ops.sae_ablate_ranked(xs[:0], r0, encoded["w"], 4)
+    assert r0.count.shape == (0,) and e0.shape == (0, D)
