@@ -227,12 +227,12 @@ def leg_projection_vocab_shard(args, ctx):
                                                     device=str(dev)).to(torch.bfloat16)
     sid = synthetic.make_secret_ids(P, T, V, seed=synthetic.SEED_DATA + 777).to(dev)
     v0, v1 = tbd.vocab_shard(V, rank, world)
-    shard = ops.LensWeights(w_norm=lens.w_norm, w_u=lens.w_u[v0:v1], vocab_offset=v0)
     g = torch.Generator(device=dev).manual_seed(7)
     U = torch.linalg.qr(torch.randn(D, max(RANKS), device=dev, generator=g))[0].to(torch.bfloat16).contiguous()
     r0, r1 = tbd.shard_range(n_rows, rank, world)
     can_row_shard = world > 1 and n_rows % world == 0
-    state = {"timers": None, "k2": None, "hgather": None, "check": None}
+    state = {"timers": None, "k2": None, "hgather": None, "check": None, "v": (v0, v1),
+             "shard": ops.LensWeights(w_norm=lens.w_norm, w_u=lens.w_u[v0:v1], vocab_offset=v0)}
 
     def one_pass(k2_mode):
         for r in RANKS:
@@ -251,8 +251,8 @@ def leg_projection_vocab_shard(args, ctx):
             if state["k2"] is not None:
                 state["k2"].append((a, b))
                 state["hgather"].append((b, c))
-            out = tbd.lens_readout_vocab_sharded(h, shard, softcap=SOFTCAP, secret_id=sid, cta_pair=args.cluster_mode,
-                                                 timers=state["timers"])
+            out = tbd.lens_readout_vocab_sharded(h, state["shard"], softcap=SOFTCAP, secret_id=sid,
+                                                 cta_pair=args.cluster_mode, timers=state["timers"])
         state["check"] = out
 
     def measure(k2_mode):
@@ -271,7 +271,7 @@ def leg_projection_vocab_shard(args, ctx):
                 "phase_share_this_rank": {"k2": k2_ms / ms, "h_all_gather": hg_ms / ms,
                                           "shard_gemm_and_local_merge": part_ms / ms,
                                           "partials_all_gather": gat_ms / ms, "merge_over_ranks": mer_ms / ms},
-                "lens_tflops_per_gpu": conds * 2.0 * D * (v1 - v0) / (part_ms * 1e-3) / 1e12,
+                "lens_tflops_per_gpu": conds * 2.0 * D * (state["v"][1] - state["v"][0]) / (part_ms * 1e-3) / 1e12,
                 "k2_gbs": (r1 - r0 if k2_mode != "replicated" else n_rows) * len(RANKS) * 4.0 * D / (k2_ms * 1e-3) / 1e9}
 
     res = {"config": f"BASELINE configs[3]: {P} prompts x {T} tok (all rows on every GPU), low-rank removal ranks "
@@ -288,6 +288,20 @@ def leg_projection_vocab_shard(args, ctx):
         alt = measure("row-sharded")
         alt["k2"] = "row shard per rank, then all_gather of h (7 KB per row)"
         res["alternative_k2_row_sharded"] = alt
+    if world > 1:
+        # shards sized by each GPU's measured GEMM rate (ids per millisecond in the pass above): under their power caps
+        # the GPUs of a box settle at different clocks, and with equal shards every exchange waits for the slowest
+        mine = torch.tensor([(v1 - v0) / max(rep["phase_ms_this_rank"]["shard_gemm_and_local_merge"], 1e-6)], device=dev)
+        rates = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(rates, mine)
+        shards = tbd.vocab_shards_weighted(V, [float(r.item()) for r in rates])
+        w0, w1 = shards[rank]
+        state["v"] = (w0, w1)
+        state["shard"] = ops.LensWeights(w_norm=lens.w_norm, w_u=lens.w_u[w0:w1], vocab_offset=w0)
+        bal = measure("replicated")
+        bal["k2"] = "replicated on every rank"
+        bal["shard_ids_per_rank"] = [b - a for a, b in shards]
+        res["alternative_speed_weighted_shards"] = bal
     return res
 
 

@@ -97,6 +97,29 @@ def vocab_shard(V: int, rank: int, world_size: int, align: int = TILE_V) -> Tupl
     return min(V, t0 * align), min(V, t1 * align)
 
 
+def vocab_shards_weighted(V: int, weights: Sequence[float], align: int = TILE_V) -> List[Tuple[int, int]]:
+    """Tile-aligned vocabulary shards whose sizes follow ``weights`` (one per rank, e.g. each GPU's measured
+    lens-GEMM rate: the GPUs of one box settle at different clocks under their power caps, and with equal shards
+    every exchange waits for the slowest). Every rank gets at least one tile; the shards cover [0, V) in rank order."""
+    w = [max(float(x), 0.0) for x in weights]
+    if not w or sum(w) <= 0.0:
+        raise ValueError("weights must be positive")
+    tiles = -(-V // align)
+    n = len(w)
+    if tiles < n:
+        raise ValueError(f"{tiles} tiles cannot be split over {n} ranks")
+    total = sum(w)
+    bounds, acc = [0], 0.0
+    for r in range(n):
+        acc += w[r]
+        edge = int(round(tiles * acc / total))
+        edge = max(edge, bounds[-1] + 1)                  # at least one tile each ...
+        edge = min(edge, tiles - (n - 1 - r))             # ... and room for the ranks that follow
+        bounds.append(edge)
+    bounds[-1] = tiles
+    return [(min(V, bounds[r] * align), min(V, bounds[r + 1] * align)) for r in range(n)]
+
+
 # ------------------------------------------------------------------------------------------------
 # exchanges
 # ------------------------------------------------------------------------------------------------

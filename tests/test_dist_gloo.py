@@ -50,6 +50,14 @@ def test_shard_arithmetic():
     assert runs[0] == [(0, 0, 4), (1, 0, 2)] and runs[1] == [(1, 2, 4), (2, 0, 4)]
     covered = sorted((s, p) for rr in runs for s, a, b in rr for p in range(a, b))
     assert covered == [(s, p) for s in range(3) for p in range(4)]
+    # speed-weighted shards: tile-aligned, contiguous, cover the vocabulary, follow the weights
+    eq = tbd.vocab_shards_weighted(256000, [1.0] * 8)
+    assert eq == [tbd.vocab_shard(256000, r, 8) for r in range(8)]
+    sh = tbd.vocab_shards_weighted(256000, [1.0, 1.0, 0.9, 1.0, 1.1, 1.0, 1.0, 1.0])
+    assert sh[0][0] == 0 and sh[-1][1] == 256000 and all(a[1] == b[0] for a, b in zip(sh, sh[1:]))
+    assert all(v0 % 256 == 0 for v0, _ in sh) and sh[2][1] - sh[2][0] < sh[4][1] - sh[4][0]
+    tiny = tbd.vocab_shards_weighted(1000, [1e-9, 1.0, 1e-9])
+    assert [b - a for a, b in tiny] == [256, 512, 232]
 
 
 def _lens_worker(rank, world, softcap):
