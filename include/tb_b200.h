@@ -128,7 +128,10 @@ int tb_lowrank_remove(const void* x_bf16, const void* ut_bf16, int r, int64_t n_
                       const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
                       void* stream);
 
-/* K2 for ranks 9..64 on the tensor cores, one call: C = x U (tcgen05, fp32 accumulate), the
+/* (When d is a multiple of 256, at most 4096, the second tcgen05 pass and the norm pass described here run as ONE
+ * kernel on clusters of d / 256 CTAs -- x added into the accumulator by the tensor core, sums of squares exchanged
+ * through distributed shared memory; TB_K2_THREE_PASS=1 in the environment keeps them separate. Same contract.)
+ * K2 for ranks 9..64 on the tensor cores, one call: C = x U (tcgen05, fp32 accumulate), the
  * coefficients split into bf16 head + remainder, x' = bf16(x - [C_hi | C_lo] [U | U]^T) in the epilogue
  * of a second tcgen05 pass (K = 2 * ceil32(r), N = d), and the fused final RMSNorm from the rows' sums
  * of squares collected there. Same result contract as tb_lowrank_remove (Plan:148; no code in the

@@ -36,7 +36,11 @@ if not a.skip_check:
         dbg = torch.full((n, rp), float("nan"), device="cuda")
         fx, fh = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, dbg_c=dbg)
         _, fh2 = ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True)
+        os.environ["TB_K2_THREE_PASS"] = "1"
         tx, th = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, one_pass=False)
+        os.environ.pop("TB_K2_THREE_PASS")
+        ax, ah = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True, one_pass=False)
+        _, ah2 = ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True, one_pass=False)
         torch.cuda.synchronize()
         c_ref = x.float() @ U.float()
         c_err = (dbg[:, :r] - c_ref).abs().max().item() / c_ref.abs().max().item()
@@ -48,6 +52,10 @@ if not a.skip_check:
                           "three_pass_mismatch_vs_dense_fp32": (tx != ref).float().mean().item(),
                           "h_mismatch_vs_three_pass": (fh != th).float().mean().item(),
                           "h_alone_equals_h_with_x": bool(torch.equal(fh, fh2)),
+                          "apply_cluster_x_mismatch_vs_three_pass": (ax != tx).float().mean().item(),
+                          "apply_cluster_x_mismatch_vs_dense_fp32": (ax != ref).float().mean().item(),
+                          "apply_cluster_h_mismatch_vs_three_pass": (ah != th).float().mean().item(),
+                          "apply_cluster_h_alone_equals_h_with_x": bool(torch.equal(ah, ah2)),
                           "x_max_abs_diff": (fx.float() - tx.float()).abs().max().item(),
                           "h_max_abs_diff": (fh.float() - th.float()).abs().max().item()}), flush=True)
 
@@ -77,7 +85,13 @@ def timed(fn, reps=5):
 bytes_alg = a.rows * D * 4
 for r in (8, 16, 32, 64):
     U = torch.linalg.qr(torch.randn(D, r, device="cuda"))[0].to(torch.bfloat16).contiguous()
-    for name, one in (("one pass (cluster)", True), ("three passes", False)):
+    for name, one, env in (("one pass (cluster, DSMEM split-K)", True, None), ("coefficients + cluster apply/norm (default)", False, None),
+                           ("three passes", False, "1")):
+        if env:
+            os.environ["TB_K2_THREE_PASS"] = env
+        else:
+            os.environ.pop("TB_K2_THREE_PASS", None)
         ms = timed(lambda: ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True, one_pass=one))
+        os.environ.pop("TB_K2_THREE_PASS", None)
         print(json.dumps({"kernel": "K2 " + name, "rank": r, "rows": a.rows, "ms": ms, "GBps": bytes_alg / ms / 1e6,
                           "frac_of_measured_copy": bytes_alg / ms / 1e6 / peaks["hbm_gbs"]}), flush=True)

@@ -23,6 +23,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--build-only", action="store_true")
 ap.add_argument("--rows", type=int, default=262144)
 ap.add_argument("--ranks", default="16,64")
+ap.add_argument("--one-pass", type=int, default=1)
 a = ap.parse_args()
 if a.build_only or not os.path.exists(wait_profile.PROF_LIB):
     print(wait_profile.build())
@@ -44,14 +45,14 @@ for r in [int(v) for v in a.ranks.split(",")]:
     for _ in range(2):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True)
+        ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True, one_pass=bool(a.one_pass))
         e1.record()
         torch.cuda.synchronize()
     assert lib.tb_debug_k2_profile(ctypes.cast(buf, ctypes.c_void_p)) == 0
     t = torch.tensor(list(buf), dtype=torch.float64).view(256, 16)
     used = t[t[:, 10] > 0]
     tiles = used[:, 10].mean().item()
-    out = {"rank": r, "ms": e0.elapsed_time(e1), "ctas_reporting": int(used.shape[0]), "clusters": int(used[0, 11].item()),
+    out = {"kernel": "one pass" if a.one_pass else "coefficients + cluster apply (phases 0-3 unused)", "rank": r, "ms": e0.elapsed_time(e1), "ctas_reporting": int(used.shape[0]), "clusters": int(used[0, 11].item()),
            "blocks_per_cta": tiles, "cycles_per_block": used[:, 9].mean().item() / tiles,
            "phase_cycles_per_block": {n: used[:, i].mean().item() / tiles for i, n in enumerate(NAMES)}}
     print(json.dumps(out), flush=True)

@@ -784,19 +784,78 @@ int tb_lowrank_remove_tc(const void* x, const void* ut, int r, int64_t n_rows, i
   __nv_bfloat16* cb = reinterpret_cast<__nv_bfloat16*>(sc + pl.off_cb);
   __nv_bfloat16* ub = reinterpret_cast<__nv_bfloat16*>(sc + pl.off_ub);
   float* ss = reinterpret_cast<float*>(sc + pl.off_ss);
-  // B operand of step 2
-  {
-    const int64_t n = static_cast<int64_t>(d) * pl.kc;
-    tb::tb_lowrank_ub_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, s>>>(
-        static_cast<const __nv_bfloat16*>(ut), r, pl.rp, d, ub);
-    TB_CUDA(cudaGetLastError());
-  }
   // step 1: C = x U, split into bf16 head + remainder
   {
     tb::GemmArgs g = make_args(n_rows, r, d, 1, 2);
     tb::CoeffSplitEpi::Params ep{cb, pl.rp};
     rc = launch_gemm<tb::CoeffSplitEpi, 2>(x, ut, g, ep, s, di.sms);
     if (rc != TB_OK) return rc;
+  }
+  // steps 2 + 3 in one kernel when the rows split into 256-column slices for a cluster (d = 3584: 14 CTAs): x is
+  // read once more and h written once, the sums of squares cross the cluster through distributed shared memory
+  // (tb_cluster_rows.cuh). TB_K2_THREE_PASS=1 keeps the two separate passes below.
+  {
+    const char* tp = getenv("TB_K2_THREE_PASS");
+    if (!(tp && atoi(tp) != 0) && d % tb::kCrW == 0 && d / tb::kCrW <= tb::kCrMaxCta) {
+      tb::CaArgs a;
+      a.n_rows = static_cast<int>(n_rows);
+      a.d = d;
+      a.rp = pl.rp;
+      a.n_cta = d / tb::kCrW;
+      a.n_tiles = static_cast<int>((n_rows + tb::kCrRows - 1) / tb::kCrRows);
+      a.w_norm = w_norm;
+      a.eps = eps;
+      a.want_x = out_x ? 1 : 0;
+      a.want_h = out_h ? 1 : 0;
+      CUtensorMap tmX, tmC, tmU, tmOX, tmOH;
+      rc = make_tmap(&tmX, x, n_rows, d, tb::kCrRows);
+      if (rc != TB_OK) return rc;
+      rc = make_tmap(&tmC, cb, n_rows, pl.kc, tb::kCrRows);
+      if (rc != TB_OK) return rc;
+      rc = make_tmap(&tmU, ut, r, d, pl.rp);
+      if (rc != TB_OK) return rc;
+      rc = make_tmap(&tmOX, out_x ? out_x : out_h, n_rows, d, tb::kCrRows);
+      if (rc != TB_OK) return rc;
+      rc = make_tmap(&tmOH, out_h ? out_h : out_x, n_rows, d, tb::kCrRows);
+      if (rc != TB_OK) return rc;
+      auto kern = tb::tb_lowrank_apply_cluster_kernel;
+      TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tb::kCaSmemBytes));
+      if (a.n_cta > 8) TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      cudaLaunchConfig_t cfg;
+      memset(&cfg, 0, sizeof(cfg));
+      cfg.blockDim = dim3(tb::kCrThreads, 1, 1);
+      cfg.dynamicSmemBytes = tb::kCaSmemBytes;
+      cfg.stream = s;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = static_cast<unsigned>(a.n_cta);
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      static int cached[64][tb::kCrMaxCta + 1];
+      int dev = 0;
+      TB_CUDA(cudaGetDevice(&dev));
+      if (cached[dev][a.n_cta] == 0) {
+        cfg.gridDim = dim3(static_cast<unsigned>((di.sms / a.n_cta) * a.n_cta), 1, 1);
+        int n = 0;
+        TB_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+        if (n < 1) return fail(TB_ERR_CUDA, "no cluster of %d CTAs fits on this device", a.n_cta);
+        cached[dev][a.n_cta] = n;
+      }
+      int clusters = cached[dev][a.n_cta];
+      if (clusters > a.n_tiles) clusters = a.n_tiles;
+      cfg.gridDim = dim3(static_cast<unsigned>(clusters * a.n_cta), 1, 1);
+      TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmX, tmC, tmU, tmOX, tmOH, a));
+      return TB_OK;
+    }
+  }
+  // B operand of step 2
+  {
+    const int64_t n = static_cast<int64_t>(d) * pl.kc;
+    tb::tb_lowrank_ub_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, s>>>(
+        static_cast<const __nv_bfloat16*>(ut), r, pl.rp, d, ub);
+    TB_CUDA(cudaGetLastError());
   }
   // step 2: x' = bf16(x - C U^T) and the rows' sums of squares
   __nv_bfloat16* xp = static_cast<__nv_bfloat16*>(out_x ? out_x : out_h);

@@ -99,6 +99,12 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
 __device__ __forceinline__ void st_cluster_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared::cluster.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+// shared memory of this CTA -> shared memory of a CTA of the cluster, completion counted in bytes on an mbarrier of
+// the destination CTA (dst and bar are shared::cluster addresses from mapa; 16-byte granularity)
+__device__ __forceinline__ void dsmem_bulk_copy(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes, uint32_t bar_cluster) {
+  asm volatile("cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(bar_cluster) : "memory");
+}
 // MN-major operand tile written by TMA with SWIZZLE_128B from a matrix whose CONTIGUOUS dimension is the
 // operand's M/N dimension: shared-memory rows are k (128 bytes = 64 elements of N each), 8 rows form a
 // 1024-byte swizzle atom (stride byte offset), 64-element groups of N are `group_bytes` apart (leading byte offset).
@@ -469,6 +475,327 @@ tb_lowrank_cluster_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_
   }
 
   // teardown: nobody may leave while a peer can still write into its shared memory; TMEM released at the end
+  tc_fence_before();
+  if (n_cta > 1) cluster_sync_all(); else __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+// =========================================================================================
+// K2, passes 2 + 3 in one kernel (the coefficients come from the tensor-core pass 1, CoeffSplitEpi):
+//   x' = bf16(x - [C_hi | C_lo][U | U]^T),  h = bf16((x' * rstd) * (1 + w))
+// with x read once and h written once. Same cluster layout as above (d / 256 CTAs per 128-row block, the U^T
+// slice resident and read MN-major), but nothing is exchanged except the 128 partial sums of squares, and the
+// element-wise work never touches x in shared memory: the x tile is ADDED INTO THE ACCUMULATOR by the tensor
+// core (x_g * I_64 for each 64-column group, an exact product) after -C U^T (the A operand negated in the
+// instruction descriptor), so TMEM holds x - C U^T in fp32. Epilogue pass 1 reads TMEM, rounds to bf16 and sums
+// the squares; after the cluster-wide exchange, pass 2 reads TMEM again, rounds, scales and writes h into the
+// stage the x tile came from (free since the MMAs completed), and a TMA store writes it out. Two accumulators:
+// the MMAs of the next block run under the epilogue of this one.
+// =========================================================================================
+constexpr int kCaOffX = 0;                                             // [2] x tile, later the h tile of the same block
+constexpr int kCaOffC = kCaOffX + kCrStages * kCrTileBytes;            // coefficients [128 x 2 rp] bf16, K-major (1 or 2 blocks)
+constexpr int kCaOffU = kCaOffC + 2 * kCrGroupBytes;                   // U^T slice [4 groups][rp][128 B]
+constexpr int kCaOffI = kCaOffU + kCrGroups * kCrMaxRp * 128;          // identity [64 x 64] bf16, K-major, 128-byte swizzle
+constexpr int kCaOffSsx = kCaOffI + 64 * 128;                          // [2 (block parity)][16 ranks][128] f32
+constexpr int kCaOffSs = kCaOffSsx + 2 * kCrMaxCta * kCrRows * 4;      // [2 (block parity)][128] f32
+constexpr int kCaOffRstd = kCaOffSs + 4 * kCrRows * 4;
+constexpr int kCaOffW1 = kCaOffRstd + kCrRows * 4;
+constexpr int kCaOffBars = kCaOffW1 + kCrW * 4;
+constexpr int kCaSmemBytes = kCaOffBars + 256 + 1024;
+constexpr uint32_t kIdescANegate = 1u << 13;
+
+struct CaArgs {
+  int n_rows, d;
+  int rp;            // 32 or 64: columns of C_hi (= of C_lo) in cb
+  int n_cta, n_tiles;
+  const float* w_norm;
+  float eps;
+  int want_x, want_h;
+};
+
+__global__ void __launch_bounds__(kCrThreads, 1)
+tb_lowrank_apply_cluster_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmC,
+                                const __grid_constant__ CUtensorMap tmU, const __grid_constant__ CUtensorMap tmOutX,
+                                const __grid_constant__ CUtensorMap tmOutH, const CaArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  __builtin_assume(__isShared(smem));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kCaOffBars);
+  uint64_t* full_x = bars;             // [2]
+  uint64_t* empty_x = bars + 2;        // [2]
+  uint64_t* full_u = bars + 4;
+  uint64_t* full_c = bars + 5;
+  uint64_t* empty_c = bars + 6;
+  uint64_t* tfull = bars + 7;          // [2]
+  uint64_t* tempty = bars + 9;         // [2]
+  uint64_t* store_ready = bars + 11;   // [2]
+  uint64_t* xbar = bars + 13;          // [2] by block parity: this CTA's arrival + the bytes of every CTA's partial sums
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
+
+  const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+  const int lane = static_cast<int>(lane_id());
+  const int n_cta = a.n_cta;
+  const int crank = (n_cta > 1) ? static_cast<int>(cluster_ctarank()) : 0;
+  const int cluster_id = static_cast<int>(blockIdx.x) / n_cta;
+  const int num_clusters = static_cast<int>(gridDim.x) / n_cta;
+  const int col0 = crank * kCrW;
+  const int rp = a.rp;
+  const int kc = 2 * rp / 64;                                 // 64-column blocks of [C_hi | C_lo]: 1 or 2
+  const uint32_t u_group_bytes = static_cast<uint32_t>(rp) * 128u;
+  const uint32_t smem0 = smem_u32(smem);
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmX);
+    tma_prefetch_desc(&tmC);
+    tma_prefetch_desc(&tmU);
+    tma_prefetch_desc(&tmOutH);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(smem_u32(&full_x[i]), 1);
+      mbar_init(smem_u32(&empty_x[i]), 1);
+      mbar_init(smem_u32(&tfull[i]), 1);
+      mbar_init(smem_u32(&tempty[i]), kCrEpiThreads / 32);
+      mbar_init(smem_u32(&store_ready[i]), kCrEpiThreads / 32);
+    }
+    mbar_init(smem_u32(full_u), 1);
+    mbar_init(smem_u32(full_c), 1);
+    mbar_init(smem_u32(empty_c), 1);
+    mbar_init(smem_u32(&xbar[0]), 1);
+    mbar_init(smem_u32(&xbar[1]), 1);
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<1>(smem_u32(tmem_slot), 512);
+  if (warp == 3) {
+    // identity tile: row n holds a one in column n; chunk c of row n sits at chunk position c ^ (n & 7)
+    for (int i = lane; i < 64 * 8; i += 32) {
+      const int n = i >> 3, c = i & 7;
+      uint32_t w[4] = {0u, 0u, 0u, 0u};
+      if ((n >> 3) == c) w[(n & 7) >> 1] = (n & 1) ? 0x3F800000u : 0x00003F80u;     // bf16 1.0 in the high / low half
+      *reinterpret_cast<uint4*>(smem + kCaOffI + n * 128 + ((c ^ (n & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+    fence_proxy_async_smem();
+  }
+  tc_fence_before();
+  if (n_cta > 1) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      mbar_arrive_expect_tx(smem_u32(full_u), static_cast<uint32_t>(kCrGroups) * u_group_bytes);
+      for (int g = 0; g < kCrGroups; ++g)
+        tma_load_2d(smem0 + kCaOffU + g * u_group_bytes, &tmU, smem_u32(full_u), col0 + g * 64, 0);
+      int t = 0;
+      for (int tile = cluster_id; tile < a.n_tiles; tile += num_clusters, ++t) {
+        const int s = t & 1, u = t >> 1;
+        mbar_wait(smem_u32(&empty_x[s]), (u & 1) ^ 1);
+        mbar_arrive_expect_tx(smem_u32(&full_x[s]), kCrTileBytes);
+        for (int g = 0; g < kCrGroups; ++g)
+          tma_load_2d_hint(smem0 + kCaOffX + s * kCrTileBytes + g * kCrGroupBytes, &tmX, smem_u32(&full_x[s]),
+                           col0 + g * 64, tile * kCrRows, kPolicyEvictFirst);
+        mbar_wait(smem_u32(empty_c), (t & 1) ^ 1);
+        mbar_arrive_expect_tx(smem_u32(full_c), static_cast<uint32_t>(kc) * kCrGroupBytes);
+        for (int kb = 0; kb < kc; ++kb)
+          tma_load_2d(smem0 + kCaOffC + kb * kCrGroupBytes, &tmC, smem_u32(full_c), kb * 64, tile * kCrRows);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    constexpr uint32_t idesc_p = umma_idesc_bf16_f32(kCrRows, kCrW) | kIdescBMajorMn | kIdescANegate;   // -C U^T
+    constexpr uint32_t idesc_i = umma_idesc_bf16_f32(kCrRows, 64);                                       // + x I
+    mbar_wait(smem_u32(full_u), 0);
+    int t = 0;
+    for (int tile = cluster_id; tile < a.n_tiles; tile += num_clusters, ++t) {
+      const int s = t & 1, u = t >> 1;
+      mbar_wait(smem_u32(full_c), t & 1);
+      mbar_wait(smem_u32(&full_x[s]), u & 1);
+      mbar_wait(smem_u32(&tempty[s]), (u & 1) ^ 1);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t d_tmem = tmem_base + s * kCrW;
+        for (int kb = 0; kb < kc; ++kb) {
+          const uint64_t da = umma_desc_k_sw128(smem0 + kCaOffC + kb * kCrGroupBytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int urow = (kb * 64 + k * 16) % rp;       // heads and remainders multiply the same rows of U^T
+            const uint64_t db = umma_desc_mn_sw128(smem0 + kCaOffU + urow * 128, u_group_bytes);
+            umma_bf16<1>(d_tmem, da + static_cast<uint64_t>(2 * k), db, idesc_p, (kb | k) != 0 ? 1u : 0u);
+          }
+        }
+        umma_commit(smem_u32(empty_c));
+        const uint64_t di = umma_desc_k_sw128(smem0 + kCaOffI);
+        for (int g = 0; g < kCrGroups; ++g) {
+          const uint64_t da = umma_desc_k_sw128(smem0 + kCaOffX + s * kCrTileBytes + g * kCrGroupBytes);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16<1>(d_tmem + g * 64, da + static_cast<uint64_t>(2 * k), di + static_cast<uint64_t>(2 * k), idesc_i, 1u);
+        }
+        umma_commit(smem_u32(&tfull[s]));
+      }
+      __syncwarp();
+    }
+  } else if (warp == 2) {
+    // ================================ TMA store issuer ================================
+    if (lane == 0) {
+      int t = 0;
+      for (int tile = cluster_id; tile < a.n_tiles; tile += num_clusters, ++t) {
+        const int s = t & 1, u = t >> 1;
+        mbar_wait(smem_u32(&store_ready[s]), u & 1);
+        if (a.want_h) {
+          for (int g = 0; g < kCrGroups; ++g)
+            tma_store_2d(&tmOutH, smem0 + kCaOffX + s * kCrTileBytes + g * kCrGroupBytes, col0 + g * 64, tile * kCrRows);
+          bulk_commit();
+          bulk_wait_read0();
+        }
+        mbar_arrive(smem_u32(&empty_x[s]));
+      }
+      bulk_wait0();
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ================================ epilogue ================================
+    const int e = static_cast<int>(threadIdx.x) - 128;
+    const int quad = warp & 3, half = (warp - 4) >> 2;
+    const int row = quad * 32 + lane;
+    const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
+    float* s_ssx = reinterpret_cast<float*>(smem + kCaOffSsx);
+    float* s_ss = reinterpret_cast<float*>(smem + kCaOffSs);
+    float* s_rstd = reinterpret_cast<float*>(smem + kCaOffRstd);
+    float* s_w1 = reinterpret_cast<float*>(smem + kCaOffW1);
+    s_w1[e] = a.w_norm ? __fadd_rn(1.0f, __ldg(a.w_norm + col0 + e)) : 1.0f;
+    s_ss[e] = 0.0f;                                          // [2 parities][128]
+    epi_bar_sync<kCrEpiThreads>();
+#ifdef TB_WAIT_PROFILE
+    long long k2p[16];
+    for (int i = 0; i < 16; ++i) k2p[i] = 0;
+    const long long k2_start = clock64();
+#endif
+    int t = 0;
+    for (int tile = cluster_id; tile < a.n_tiles; tile += num_clusters, ++t) {
+      const int s = t & 1, u = t >> 1;
+      uint8_t* xs = smem + kCaOffX + s * kCrTileBytes;
+      const uint32_t tacc = tmem_base + lane_base + s * kCrW + half * 128;
+      TB_K2_T(p0);
+      mbar_wait(smem_u32(&tfull[s]), u & 1);
+      tc_fence_after();
+      TB_K2_T(p1);
+      // ---- pass 1: sum of squares of the rounded x' (and x' itself into the stage when it is wanted)
+      float ss = 0.0f;
+      {
+        uint32_t va[32], vb[32];
+        tmem_ld_32x32(tacc, va);
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          uint32_t (&v)[32] = (cc & 1) ? vb : va;
+          tmem_ld_wait();
+          if (cc + 1 < 4) tmem_ld_32x32(tacc + (cc + 1) * 32, (cc & 1) ? va : vb);   // in flight under this slice's arithmetic
+          const int cbase = half * 128 + cc * 32;
+          uint8_t* grp = xs + (cbase >> 6) * kCrGroupBytes + row * 128;
+          const int lc0 = (cbase & 63) >> 3;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(v[q * 8 + j]);
+            const Bf16x8 pk = pack8(o);
+            unpack8(pk, o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ss = fmaf(o[j], o[j], ss);
+            if (a.want_x) *reinterpret_cast<int4*>(grp + (((lc0 + q) ^ (row & 7)) << 4)) = *reinterpret_cast<const int4*>(&pk);
+          }
+        }
+      }
+      // the row's two column halves meet in one zero-initialised slot (two addends: the order cannot change the sum)
+      float* s_half = s_ss + (t & 1) * kCrRows;              // [parity][128]: the source of the copies below
+      atomicAdd(&s_half[row], ss);
+      fence_proxy_async_smem();
+      TB_K2_T(p2);
+      if (a.want_x) {
+        epi_bar_sync<kCrEpiThreads>();
+        if (e == 0) {
+          for (int g = 0; g < kCrGroups; ++g)
+            tma_store_2d(&tmOutX, smem0 + kCaOffX + s * kCrTileBytes + g * kCrGroupBytes, col0 + g * 64, tile * kCrRows);
+          bulk_commit();
+          bulk_wait_read0();
+        }
+      }
+      epi_bar_sync<kCrEpiThreads>();
+      // ---- every CTA gets every CTA's partial sums (128 rows = 512 bytes): one bulk copy per peer into
+      // slot [parity][source rank], counted on the peer's mbarrier of this parity. (Scattered st.shared::cluster
+      // stores cost a packet per lane: 1792 of them plus an arrive / wait round measured 4.6 k cycles per block.)
+      const uint32_t xb = smem_u32(&xbar[t & 1]);
+      if (e == 0) mbar_arrive_expect_tx(xb, static_cast<uint32_t>(n_cta) * kCrRows * 4);
+      if (e < n_cta)
+        dsmem_bulk_copy(mapa_shared(smem0 + kCaOffSsx + (((t & 1) * kCrMaxCta + crank) * kCrRows) * 4, static_cast<uint32_t>(e)),
+                        smem_u32(s_half), kCrRows * 4, mapa_shared(xb, static_cast<uint32_t>(e)));
+      TB_K2_T(p3);
+      mbar_wait_cluster(xb, (t >> 1) & 1);
+      TB_K2_T(p4);
+      if (e < kCrRows) {
+        float sum = 0.0f;
+        for (int p = 0; p < n_cta; ++p) sum += s_ssx[((t & 1) * kCrMaxCta + p) * kCrRows + e];   // rank order: same bits everywhere
+        // every peer has passed its wait of the previous block, so the copies that read the other parity's slot are
+        // done: clear it for the next block
+        s_ss[((t & 1) ^ 1) * kCrRows + e] = 0.0f;
+        s_rstd[e] = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(sum, static_cast<float>(a.d)), a.eps)));
+      }
+      epi_bar_sync<kCrEpiThreads>();
+      // ---- pass 2: h = bf16((x' * rstd) * (1 + w)) from the accumulator into the stage, in the swizzled tile layout
+      if (a.want_h) {
+        const float rs = s_rstd[row];
+        uint32_t va[32], vb[32];
+        tmem_ld_32x32(tacc, va);
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          uint32_t (&v)[32] = (cc & 1) ? vb : va;
+          tmem_ld_wait();
+          if (cc + 1 < 4) tmem_ld_32x32(tacc + (cc + 1) * 32, (cc & 1) ? va : vb);
+          const int cbase = half * 128 + cc * 32;
+          uint8_t* grp = xs + (cbase >> 6) * kCrGroupBytes + row * 128;
+          const int lc0 = (cbase & 63) >> 3;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float o[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = __uint_as_float(v[q * 8 + j]);
+            const Bf16x8 pk = pack8(o);
+            unpack8(pk, o);
+            const float4 w0 = *reinterpret_cast<const float4*>(s_w1 + cbase + q * 8);
+            const float4 w1 = *reinterpret_cast<const float4*>(s_w1 + cbase + q * 8 + 4);
+            const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+            float h[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) h[j] = __fmul_rn(__fmul_rn(o[j], rs), ww[j]);
+            const Bf16x8 ph = pack8(h);
+            *reinterpret_cast<int4*>(grp + (((lc0 + q) ^ (row & 7)) << 4)) = *reinterpret_cast<const int4*>(&ph);
+          }
+        }
+        fence_proxy_async_smem();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(smem_u32(&tempty[s]));
+        mbar_arrive(smem_u32(&store_ready[s]));
+      }
+      TB_K2_T(p5);
+      TB_K2_ADD(4, p0, p1); TB_K2_ADD(5, p1, p2); TB_K2_ADD(6, p2, p3); TB_K2_ADD(7, p3, p4); TB_K2_ADD(8, p4, p5);
+    }
+#ifdef TB_WAIT_PROFILE
+    if (e == 0) {
+      k2p[9] = clock64() - k2_start;
+      k2p[10] = t;
+      k2p[11] = num_clusters;
+      for (int i = 0; i < 12; ++i) g_k2_prof[blockIdx.x & 255][i] = k2p[i];
+    }
+#endif
+  }
+
   tc_fence_before();
   if (n_cta > 1) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {

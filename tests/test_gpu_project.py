@@ -115,3 +115,24 @@ def test_lowrank_rejects_rank_above_64(cuda_lib):
     x = torch.zeros(4, 64, dtype=BF16, device="cuda")
     with pytest.raises(TabooKernelError):
         ops.lowrank_remove(x, torch.zeros(64, 65, dtype=BF16, device="cuda"))
+
+
+@pytest.mark.parametrize("r,n_rows", [(8, 129), (16, 700), (33, 1000), (64, 4096)])
+def test_lowrank_cluster_apply_equals_separate_passes(cuda_lib, r, n_rows, monkeypatch):
+    """Ranks 8..64 at d = 3584: the default (coefficient pass + one cluster kernel for apply and norm, x added into the
+    accumulator by the tensor core) against the same path with the apply and norm passes separate
+    (TB_K2_THREE_PASS=1): x' and h equal except for rare roundings that fall the other way."""
+    from taboo_brittleness_b200 import ops
+    d = 3584
+    xc = synthetic.make_residuals(-(-n_rows // 128), 128, d, seed=9 + r)[:n_rows]
+    x = cuda_bf16(xc)
+    U = cuda_bf16(synthetic.bf16_exact(oracle.random_orthonormal(d, r, seed=r)))
+    w = synthetic.make_lens(d, 8, seed=1).w_norm.cuda()
+    ax, ah = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True)
+    _, ah2 = ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True)
+    monkeypatch.setenv("TB_K2_THREE_PASS", "1")
+    tx, th = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True)
+    torch.cuda.synchronize()
+    assert torch.equal(ah, ah2)
+    assert (ax != tx).float().mean().item() < 1e-3 and (ah != th).float().mean().item() < 1e-3
+    assert ((ax.float() - tx.float()).abs() <= 0.0079 * tx.float().abs() + 1e-3).all()
