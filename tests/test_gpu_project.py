@@ -130,6 +130,8 @@ def test_lowrank_cluster_apply_equals_separate_passes(cuda_lib, r, n_rows, monke
     w = synthetic.make_lens(d, 8, seed=1).w_norm.cuda()
     ax, ah = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True)
     _, ah2 = ops.lowrank_remove(x, U, w_norm=w, want_x=False, want_h=True)
+    ox, none_h = ops.lowrank_remove(x, U)                      # x' alone, no norm weight
+    assert none_h is None and torch.equal(ox, ax)
     monkeypatch.setenv("TB_K2_THREE_PASS", "1")
     tx, th = ops.lowrank_remove(x, U, w_norm=w, want_x=True, want_h=True)
     torch.cuda.synchronize()
