@@ -67,6 +67,17 @@ int tb_sae_encode(const void* x_bf16, const void* w_enc_t_bf16, const float* b_e
                   int32_t* out_count, const uint16_t* rank, int rank_rows, int budget,
                   void* stream);
 
+/* K1 for large batches with the sweep over the latents cut into n_sub chunks (2..8, dividing cap): same result as
+ * tb_sae_encode with fixed-stride lists, but several CTA pairs share a row block, so the resident row blocks fit L2
+ * (with one chunk, 74 blocks of 1.8 MB are re-read from DRAM for every W_enc^T tile: 54x the algorithmic traffic in
+ * the ncu capture). Chunk c of a row first writes its own cap / n_sub slots and sub_count[c * n_rows + row]; a merge
+ * kernel then closes the gaps in place: out_count[row] = the row's total, out_truncated[row] = 1 if a sub-list did
+ * not fit its slots (re-encode such rows alone with tb_sae_encode, as for rows whose whole list overflows).
+ * Operands must be the current GPU's own memory (TMA multicast clusters). Replaces sae.encode, 02:67. */
+int tb_sae_encode_chunked(const void* x_bf16, const void* w_enc_t_bf16, const float* b_enc, const float* theta,
+                          int64_t n_rows, int d, int S, int cap, int n_sub, int32_t* out_idx, float* out_val,
+                          int32_t* sub_count, int32_t* out_count, int32_t* out_truncated, void* stream);
+
 /* ---- a2: targeted latent selection ------------------------------------------------------
  * Replaces torch.mean(acts, dim=0) and torch.topk(avg, k), src/02_run_sae_baseline.py:70-73,
  * on the sparse lists. seg (optional): int64 [n_prompts + 1] row offsets of each prompt's

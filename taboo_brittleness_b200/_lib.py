@@ -41,6 +41,7 @@ SIGNATURES = {
     "tb_device_check": (c_int, []),
     "tb_sae_encode": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, _P, _P, c_int, _P, _P, _P, _P,
                               c_int, c_int, _P]),
+    "tb_sae_encode_chunked": (c_int, [_P, _P, _P, _P, c_int64, c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, _P]),
     "tb_sae_latent_mean": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P]),
     "tb_sae_latent_wsum": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, c_int, _P, _P]),
     "tb_topm_select": (c_int, [_P, c_int64, c_int, c_int, _P, _P, _P, _P]),

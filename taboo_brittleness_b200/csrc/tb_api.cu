@@ -457,6 +457,7 @@ int tb_sae_encode(const void* x, const void* w_enc_t, const float* b_enc, const 
   ep.rank = rank;
   ep.rank_rows = rank_rows;
   ep.budget = budget;
+  ep.sub_lists = 1;
   // one unit per row block: a row's list is written by a single thread, in latent order.
   // CTA pairs (UMMA 256 x 256) once there are enough 256-row blocks to fill them; single CTAs for small inputs
   if (n_rows >= static_cast<int64_t>(tb::kBlockM) * di.sms) {
@@ -475,6 +476,50 @@ int tb_sae_encode(const void* x, const void* w_enc_t, const float* b_enc, const 
   }
   tb::GemmArgs g = make_args(n_rows, S, d, 1, 1);
   return launch_gemm<tb::EncodeEpi, 1>(x, w_enc_t, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_sae_encode_chunked(const void* x, const void* w_enc_t, const float* b_enc, const float* theta, int64_t n_rows,
+                          int d, int S, int cap, int n_sub, int32_t* out_idx, float* out_val, int32_t* sub_count,
+                          int32_t* out_count, int32_t* out_truncated, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  rc = check_gemm_operands(x, w_enc_t, n_rows, S, d);
+  if (rc != TB_OK) return rc;
+  if (!b_enc || !theta || !out_idx || !out_val || !sub_count || !out_count || !out_truncated)
+    return fail(TB_ERR_INVALID, "null pointer");
+  if ((reinterpret_cast<uintptr_t>(b_enc) & 15) || (reinterpret_cast<uintptr_t>(theta) & 15))
+    return fail(TB_ERR_INVALID, "b_enc / theta must be 16-byte aligned");
+  if (n_sub < 2 || n_sub > 8 || cap <= 0 || cap % n_sub) return fail(TB_ERR_INVALID, "n_sub=%d must be 2..8 and divide cap=%d", n_sub, cap);
+  tb::GemmArgs g = make_args(n_rows, S, d, n_sub, 2, 2, 1);
+  if (g.n_chunks != n_sub)
+    return fail(TB_ERR_INVALID, "S=%d: %d tiles do not split into %d non-empty chunks", S, g.n_tiles, n_sub);
+  // operands of another GPU would be read through TMA multicast: refuse (the caller keeps tb_sae_encode)
+  rc = operand_is_local(x, static_cast<size_t>(n_rows) * d * 2, "x");
+  if (rc != TB_OK) return rc;
+  rc = operand_is_local(w_enc_t, static_cast<size_t>(S) * d * 2, "w_enc_t");
+  if (rc != TB_OK) return rc;
+  tb::EncodeEpi::Params ep;
+  ep.b_enc = b_enc;
+  ep.theta = theta;
+  ep.row_start = nullptr;
+  ep.cap = cap;
+  ep.row_cap = nullptr;
+  ep.out_idx = out_idx;
+  ep.out_val = out_val;
+  ep.out_count = sub_count;
+  ep.rank = nullptr;
+  ep.rank_rows = 0;
+  ep.budget = 0;
+  ep.sub_lists = n_sub;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  rc = launch_gemm<tb::EncodeEpi, 2, 2, 1, true>(x, w_enc_t, g, ep, s, di.sms);
+  if (rc != TB_OK) return rc;
+  const int64_t threads = n_rows * 32;
+  tb::tb_merge_sublists_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, s>>>(
+      sub_count, n_sub, cap, static_cast<int>(n_rows), out_idx, out_val, out_count, out_truncated);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
 }
 
 int tb_sae_latent_mean(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,

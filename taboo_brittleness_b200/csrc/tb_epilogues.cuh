@@ -181,6 +181,9 @@ struct EncodeEpi {
     const uint16_t* rank;      // ablation rank table(s) [n_tables, S] or nullptr
     int rank_rows;             // rows sharing one table (0: a single table for all rows)
     int budget;                // latents with rank < budget are zeroed
+    int sub_lists;             // > 1 (fixed-stride lists only): the sweep is cut into that many latent chunks, chunk c
+                               // of a row writes slots [c * cap / sub_lists, (c + 1) * cap / sub_lists) and its count to
+                               // out_count[c * M + row]; tb_merge_sublists_kernel closes the gaps afterwards
   };
   struct State {
     int k;
@@ -190,7 +193,7 @@ struct EncodeEpi {
   };
 
   __device__ __forceinline__ static void begin_unit(State& st, const Params& p, const GemmArgs& g,
-                                                    int row, int /*chunk*/) {
+                                                    int row, int chunk) {
     st.k = 0;
     st.limit = 0;
     st.base = 0;
@@ -200,6 +203,9 @@ struct EncodeEpi {
       if (p.row_start != nullptr) {
         st.base = p.row_start[row];
         st.limit = p.row_cap != nullptr ? p.row_cap[row] : 0x7fffffff;
+      } else if (p.sub_lists > 1) {
+        st.limit = p.cap / p.sub_lists;
+        st.base = static_cast<int64_t>(row) * p.cap + static_cast<int64_t>(chunk) * st.limit;
       } else {
         st.base = static_cast<int64_t>(row) * p.cap;
         st.limit = p.cap;
@@ -250,8 +256,8 @@ struct EncodeEpi {
   }
 
   __device__ __forceinline__ static void end_unit(State& st, const Params& p, const GemmArgs& g,
-                                                  int row, int /*chunk*/) {
-    if (row < g.M) p.out_count[row] = st.k;
+                                                  int row, int chunk) {
+    if (row < g.M) p.out_count[(p.sub_lists > 1 ? static_cast<size_t>(chunk) * g.M : 0) + row] = st.k;
   }
 };
 

@@ -1267,4 +1267,47 @@ __global__ void tb_probs_from_logits_kernel(float* __restrict__ logits, const fl
     logits[i] = expf(logits[i] - __ldg(lse + i / V));
 }
 
+// K1 with latent chunks (EncodeEpi::Params::sub_lists): a row's list arrives as `n_sub` sub-lists, each at the start
+// of its own cap / n_sub slots. One warp per row moves sub-lists 1.. down to follow their predecessor (in place:
+// every round reads 32 entries ahead of anything it writes), writes the total count and flags the row if any
+// sub-list did not fit its slots (such rows are encoded once more on their own, like rows whose whole list overflows).
+__global__ void tb_merge_sublists_kernel(const int32_t* __restrict__ sub_count, int n_sub, int cap, int n_rows,
+                                         int32_t* __restrict__ idx, float* __restrict__ val,
+                                         int32_t* __restrict__ out_count, int32_t* __restrict__ out_truncated) {
+  const int lane = threadIdx.x & 31;
+  const int row = static_cast<int>((blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x) >> 5);
+  if (row >= n_rows) return;
+  const int sub = cap / n_sub;
+  const int64_t base = static_cast<int64_t>(row) * cap;
+  int total = 0, filled = 0, trunc = 0;
+  for (int c = 0; c < n_sub; ++c) {
+    const int cnt = sub_count[static_cast<size_t>(c) * n_rows + row];
+    const int have = min(cnt, sub);
+    trunc |= cnt > sub;
+    if (c > 0 && filled < c * sub) {
+      for (int j = 0; j < have; j += 32) {
+        const int i = j + lane;
+        int32_t id = 0;
+        float v = 0.0f;
+        if (i < have) {
+          id = idx[base + c * sub + i];
+          v = val[base + c * sub + i];
+        }
+        __syncwarp();
+        if (i < have) {
+          idx[base + filled + i] = id;
+          val[base + filled + i] = v;
+        }
+      }
+      __syncwarp();
+    }
+    filled += have;
+    total += cnt;
+  }
+  if (lane == 0) {
+    out_count[row] = total;
+    out_truncated[row] = trunc;
+  }
+}
+
 }  // namespace tb

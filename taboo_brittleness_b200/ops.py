@@ -182,6 +182,21 @@ def sae_encode(x: torch.Tensor, sae: SaeWeights, cap: int = 128, *, rank: Option
     dev = x.device
     idx = torch.empty(max(n * cap, 1), dtype=torch.int32, device=dev)
     val = torch.empty(max(n * cap, 1), dtype=torch.float32, device=dev)
+    n_sub = ENCODE_SUB_LISTS
+    if (rank is None and n_sub > 1 and n >= ENCODE_CHUNKED_MIN_ROWS and cap % n_sub == 0
+            and (-(-sae.S // BLOCK_N)) % n_sub == 0):
+        # large batches: the latent sweep in n_sub chunks, so that the row blocks in flight fit L2
+        _need(x, torch.bfloat16, "x", 2)
+        sub = torch.empty(n_sub * n, dtype=torch.int32, device=dev)
+        count = torch.empty(n, dtype=torch.int32, device=dev)
+        trunc = torch.empty(n, dtype=torch.int32, device=dev)
+        check(_lib.load().tb_sae_encode_chunked(_ptr(x), _ptr(sae.w_enc_t), _ptr(sae.b_enc), _ptr(sae.theta), n, x.shape[1],
+                                                sae.S, cap, n_sub, _ptr(idx), _ptr(val), _ptr(sub), _ptr(count), _ptr(trunc),
+                                                _stream()), "tb_sae_encode_chunked")
+        over = torch.nonzero((trunc != 0) | (count > cap)).flatten()
+        if over.numel() == 0:
+            return SparseActs(count=count, idx=idx, val=val, S=sae.S, cap=cap)
+        return _reencode_overflowing(x, sae, cap, idx, val, count, over)
     count = sae_encode_raw(x, sae, cap=cap, idx=idx, val=val, rank=rank, rank_rows=rank_rows, budget=budget)
     if n == 0 or int(count.max().item()) <= cap:
         return SparseActs(count=count, idx=idx, val=val, S=sae.S, cap=cap)
@@ -195,7 +210,17 @@ def sae_encode(x: torch.Tensor, sae: SaeWeights, cap: int = 128, *, rank: Option
         count2 = sae_encode_raw(x, sae, row_start=row_start, row_cap=count, idx=idx, val=val,
                                 rank=rank, rank_rows=rank_rows, budget=budget)
         return SparseActs(count=count2, idx=idx, val=val, S=sae.S, cap=0, row_start=row_start)
-    over = torch.nonzero(count > cap).flatten()
+    return _reencode_overflowing(x, sae, cap, idx, val, count, torch.nonzero(count > cap).flatten())
+
+
+ENCODE_SUB_LISTS = 2               # latent chunks of the large-batch encode (1 = one sweep per row block)
+ENCODE_CHUNKED_MIN_ROWS = 128 * 148
+
+
+def _reencode_overflowing(x, sae, cap, idx, val, count, over) -> SparseActs:
+    """Rows whose list did not fit are encoded once more, alone, into a region appended to the lists."""
+    n = x.shape[0]
+    dev = x.device
     c_over = count[over].to(torch.int64)
     extra = int(c_over.sum().item())
     idx = torch.cat([idx[:n * cap], torch.empty(extra, dtype=torch.int32, device=dev)])

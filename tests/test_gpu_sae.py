@@ -271,3 +271,48 @@ def test_ranked_lists_fixed_stride_random_table_and_empty(cuda_lib, problem, enc
     r0 = ops.rank_lists(empty, rank, 0)
     e0, _ = ops.sae_ablate_ranked(xs[:0], r0, encoded["w"], 4)
     assert r0.count.shape == (0,) and e0.shape == (0, D)
+
+
+def test_encode_with_latent_chunks_equals_one_sweep(cuda_lib, problem):
+    """Large batches encode with the latent sweep cut in two (tb_sae_encode_chunked: sub-lists per chunk, merged in
+    place): same lists, counts and overflow handling as the one-sweep kernel (20,000 rows: ragged last block,
+    <bos>-scale rows that overflow, rows whose first sub-list alone overflows its half of the slots)."""
+    from taboo_brittleness_b200 import ops
+    w = sae_to_cuda(problem["sae"])
+    x = synthetic.make_residuals(157, 128, D, seed=99, device="cuda")[:20000].to(torch.bfloat16).contiguous()
+    assert x.shape[0] >= ops.ENCODE_CHUNKED_MIN_ROWS
+    chunked = ops.sae_encode(x, w, cap=128)
+    old = ops.ENCODE_SUB_LISTS
+    ops.ENCODE_SUB_LISTS = 1
+    try:
+        plain = ops.sae_encode(x, w, cap=128)
+    finally:
+        ops.ENCODE_SUB_LISTS = old
+    torch.cuda.synchronize()
+    assert torch.equal(chunked.count, plain.count)
+    assert chunked.row_start is not None and plain.row_start is not None
+    # same (latent, value) sequence per row; the two layouts may place overflowing rows differently
+    for lo in range(0, 20000, 4000):
+        rows = torch.arange(lo, lo + 4000, device="cuda")
+        a = _dense_rows_for_test(chunked, rows)
+        b = _dense_rows_for_test(plain, rows)
+        assert torch.equal(a, b)
+    c = chunked.count.cpu()
+    rs = chunked.row_start.cpu()
+    idx = chunked.idx.cpu()
+    for r in (0, 1, 127, 128, 5000, 19999):
+        row = idx[rs[r]:rs[r] + c[r]]
+        assert (row[1:] > row[:-1]).all(), "lists must stay in increasing latent order"
+
+
+def _dense_rows_for_test(acts, rows):
+    cnt = acts.count[rows].long()
+    start = acts.row_start[rows] if acts.row_start is not None else rows.long() * acts.cap
+    if acts.row_start is None:
+        cnt = cnt.clamp(max=acts.cap)
+    dense = torch.zeros(rows.numel(), acts.S, dtype=torch.float32, device=rows.device)
+    r = torch.repeat_interleave(torch.arange(rows.numel(), device=rows.device), cnt)
+    offs = torch.arange(int(cnt.sum().item()), device=rows.device) - torch.repeat_interleave(torch.cumsum(cnt, 0) - cnt, cnt)
+    pos = torch.repeat_interleave(start, cnt) + offs
+    dense[r, acts.idx[pos].long()] = acts.val[pos]
+    return dense
