@@ -431,8 +431,9 @@ def leg_stress(args, ctx):
             "ms_per_pass": ms, "lens_rows_per_pass_per_gpu": L * n_rows,
             "lens_row_conditions_per_s": L * n_rows * world / (ms * 1e-3),
             "whole_job_tflops": tokens * (2.0 * D * S2 + L * FLOP_LENS) / (ms * 1e-3) / 1e12,
-            "encode_roofline": {"kernel": "tb_umma_gemm_kernel<EncodeEpi, 2> at S=131072 (first pass over all rows + "
-                                          "second pass over the rows whose list overflowed, host decision in between)",
+            "encode_roofline": {"kernel": "tb_umma_gemm_kernel<EncodeEpi, 2> at S=131072 through ops.sae_encode (latent sweep in two chunks + "
+                                          "sub-list merge, then a second pass over the rows whose list overflowed, host decision "
+                                          "in between)",
                                 "bound": "tensor", "achieved": enc_tf, "peak": peaks["tflops_burst"], "unit": "TFLOP/s",
                                 "frac": enc_tf / peaks["tflops_burst"], "peak_source": "MEASURED_PEAKS.json bf16 burst "
                                 "(a 0.2 s kernel timed alone)", "flops_per_token": 2.0 * D * S2, "ms": enc_ms,
