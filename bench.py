@@ -461,6 +461,7 @@ def run_legs(args, ctx):
             res[name] = {"error": f"{type(e).__name__}: {e}", "trace": traceback.format_exc()[-1500:]}
             torch.cuda.synchronize()
         res[name]["wall_s"] = time.perf_counter() - t0
+        ctx["eng"].release_scratch()
         import gc
         gc.collect()
         torch.cuda.empty_cache()
@@ -518,6 +519,7 @@ def run_native(args, rank, local_rank, world):
     eng.ll_fused = not args.ll_two_sweeps
     eng.ll_alpha = args.ll_alpha
     eng.overlap = args.overlap
+    eng.ll_dense_first = not args.no_ll_dense_first
 
     # ---- inputs: this rank's prompts (weak scaling: every rank gets args.prompts prompts)
     P, BP = args.prompts, min(args.batch_prompts, args.prompts)
@@ -645,6 +647,7 @@ def run_native(args, rank, local_rank, world):
     workloads = None
     if args.workloads and args.workload == "targeted":
         x_dev = sid_dev = ll_dev = x_host = sid_host = ll_host = out_ll = out_sec = out_top = None   # free the headline's buffers
+        eng.release_scratch()
         import gc
         gc.collect()
         torch.cuda.empty_cache()
@@ -698,7 +701,10 @@ def run_native(args, rank, local_rank, world):
                                "redone_with_second_sweep": eng.stats.ll_fallback_prompts,
                                "mean_candidates_per_prompt": eng.stats.ll_candidates / max(eng.stats.ll_fused_prompts, 1),
                                "candidate_threshold": f"{eng.ll_alpha} x previous budget's k-th best sum",
-                               "first_budget": "two sweeps (K3 + K5); later budgets K3F + K6, exact via certificate"}
+                               "first_budget": ("one sweep: the lens kernel also writes its logits (row sub-batches of "
+                                                f"{eng.ll_dense_rows} rows, f32), an HBM-bound kernel sums exp(logit - lse) per prompt "
+                                                "and column, a radix select ranks the sums; later budgets K3F + K6, exact via certificate")
+                               if eng.ll_dense_first else "two sweeps (K3 + K5); later budgets K3F + K6, exact via certificate"}
         if args.ll_topk and ll_ms > 0:
             line["roofline"]["ll_topk_kernel"] = {"kernel": "tb_umma_gemm_kernel<ColSumEpi> (LL-Top-k sweep)",
                                                   "achieved": ll_flops / (ll_ms * 1e-3) / 1e12, "unit": "TFLOP/s",
@@ -742,6 +748,9 @@ def main():
                     help="skip the per-prompt LL-Top-10 readout (then every condition is exactly one GEMM sweep)")
     ap.add_argument("--ll-alpha", type=float, default=0.5, help="K3F candidate threshold as a fraction of the "
                     "previous budget's k-th best LL sum")
+    ap.add_argument("--no-ll-dense-first", action="store_true",
+                    help="first budget of a chain: a second GEMM sweep (K5) for its LL-Top-k instead of reducing the logits "
+                         "the lens kernel writes in its one sweep")
     ap.add_argument("--overlap", action="store_true",
                     help="run K1b / K6 on a side stream under the lens sweeps (measured: no gain)")
     ap.add_argument("--ll-two-sweeps", action="store_true",

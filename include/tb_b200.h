@@ -96,7 +96,7 @@ int tb_sae_latent_wsum(const int64_t* row_start, int cap, const int32_t* count, 
  * first): out_idx/out_val [n_prompts, m]; rank u16 [n_prompts, S], rank[l] = position of
  * latent l in the list or TB_RANK_NONE. Nested budgets m' <= m are "rank < m'". */
 int tb_topm_select(const float* mean, int64_t n_prompts, int S, int m, int32_t* out_idx,
-                   float* out_val, uint16_t* rank, void* stream);
+                   float* out_val, uint16_t* rank /* nullable: sorted lists only */, void* stream);
 
 /* ---- K1b: latent ablation + sparse decode (+ fused final RMSNorm) -----------------------
  * No code in the reference (Execution Plan:126 "zero m latents, decode back to residual";
@@ -240,14 +240,21 @@ int tb_lowrank_remove_fused(const void* x_bf16, const void* ut_bf16, int r, int6
                             const float* w_norm, float eps, void* out_x_bf16, void* out_h_bf16,
                             float* dbg_c, void* stream);
 
-/* ---- K3 with dense output: the compatibility surface of get_layer_logits ------------------
- * src/models.py:135-144 returns softmax(lm_head(norm(layer_output))) for every position as a dense array.
- * tb_lens_dense_partials is tb_lens_partials (no secret id, single shard) that also writes the (soft-capped)
- * logits to logits_out f32 [n_rows, V]; after tb_lens_merge has produced lse, tb_probs_from_logits turns the
- * array into probabilities in place: p = exp(logit - lse[row]). One GEMM per layer. cta_pair: 0 or 1. */
+/* ---- K3 with dense output ------------------------------------------------------------------
+ * tb_lens_dense_partials is tb_lens_partials (single shard, any cluster mode) that also writes the (soft-capped)
+ * logits to logits_out f32 [n_rows, V]. Two users:
+ *  - the compatibility surface of get_layer_logits (src/models.py:135-144 returns softmax(lm_head(norm(.))) for every
+ *    position as a dense array): after tb_lens_merge has produced lse, tb_probs_from_logits turns the array into
+ *    probabilities in place, p = exp(logit - lse[row]). One GEMM per call;
+ *  - LL-Top-k of a condition that has no predecessor (01:35-71, 147-149): instead of a second sweep of the GEMM,
+ *    tb_logits_ll_colsum reduces the stored logits of a row sub-batch to acc f32 [n_prompts, V] (128 row slots per
+ *    prompt, lse = +inf marks an empty slot, cur_id / prev_id zeroed per position) and tb_topm_select (rank = NULL)
+ *    ranks each prompt's sums. HBM-bound: n_rows * V * 4 bytes written once and read once. */
 int tb_lens_dense_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V, float softcap,
-                           int n_chunks, int cta_pair, float* pm, float* ps, float* psec, float* ptv, int32_t* pti,
-                           float* logits_out, void* stream);
+                           const int32_t* secret_id, int n_chunks, int cta_pair, float* pm, float* ps, float* psec,
+                           float* ptv, int32_t* pti, float* logits_out, void* stream);
+int tb_logits_ll_colsum(const float* logits, const float* lse, const int32_t* cur_id, const int32_t* prev_id,
+                        int64_t n_rows, int V, float* acc, void* stream);
 int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V, void* stream);
 
 /* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------

@@ -1,0 +1,64 @@
+#!/usr/bin/env python
+"""Pieces of the first-condition path (ops.lens_ll_from_logits) on one row sub-batch: plain lens sweep, sweep with the
+logits store, column sums from the stored logits, radix select.   python scripts/dense_ll_probe.py [--rows 65536]"""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from taboo_brittleness_b200 import _lib, ops, synthetic  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--rows", type=int, default=65536)
+a = ap.parse_args()
+D, V = 3584, 256000
+lens = synthetic.make_lens(D, V, seed=42, device="cuda", dtype=torch.bfloat16)
+x = synthetic.make_residuals(a.rows // 128, 128, D, seed=1, device="cuda").to(torch.bfloat16)
+h = ops.rmsnorm(x, lens.w_norm.cuda())
+n = h.shape[0]
+cur = torch.randint(0, V, (n,), dtype=torch.int32, device="cuda")
+logits = torch.empty(n, V, dtype=torch.float32, device="cuda")
+lib = _lib.load()
+
+
+def timed(fn, reps=3):
+    fn()
+    torch.cuda.synchronize()
+    best = None
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        best = ms if best is None else min(best, ms)
+    return best, out
+
+
+flops = 2.0 * n * D * V
+ms, _ = timed(lambda: ops.lens_partials(h, lens.W_U, softcap=30.0))
+print(json.dumps({"piece": "lens sweep (K3)", "rows": n, "ms": ms, "tflops": flops / ms / 1e9}), flush=True)
+for chunks in (None, 2, 4, 8):
+    def dense():
+        c = chunks or ops.pick_chunks(n, V, 148, 5)
+        p = ops._alloc_partials(c, n, h.device)
+        _lib.check(lib.tb_lens_dense_partials(h.data_ptr(), lens.W_U.data_ptr(), n, D, V, 30.0, None, c, 5, p.pm.data_ptr(), p.ps.data_ptr(),
+                                              p.psec.data_ptr(), p.ptv.data_ptr(), p.pti.data_ptr(), logits.data_ptr(),
+                                              torch.cuda.current_stream().cuda_stream), "dense")
+        return p
+    ms, p = timed(dense)
+    print(json.dumps({"piece": "lens sweep + logits store", "chunks": chunks or ops.pick_chunks(n, V, 148, 5), "ms": ms,
+                      "tflops": flops / ms / 1e9, "store_GBps": n * V * 4 / ms / 1e6}), flush=True)
+out = ops.lens_merge(p)
+acc = torch.empty(n // 128, V, dtype=torch.float32, device="cuda")
+ms, _ = timed(lambda: _lib.check(lib.tb_logits_ll_colsum(logits.data_ptr(), out.lse.data_ptr(), cur.data_ptr(), None, n, V, acc.data_ptr(),
+                                                         torch.cuda.current_stream().cuda_stream), "colsum"))
+print(json.dumps({"piece": "column sums from logits", "ms": ms, "read_GBps": n * V * 4 / ms / 1e6}), flush=True)
+ms, _ = timed(lambda: ops.topm_select(acc, 10, want_rank=False))
+print(json.dumps({"piece": "radix select of V sums per prompt", "prompts": n // 128, "ms": ms}), flush=True)
+ms, _ = timed(lambda: ops.ll_topk(h, lens.W_U, out.lse, cur, None, softcap=30.0))
+print(json.dumps({"piece": "second sweep (K5)", "ms": ms, "tflops": flops / ms / 1e9}), flush=True)

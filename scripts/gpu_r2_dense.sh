@@ -1,0 +1,10 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_ll_fused.py tests/test_gpu_ll_topk.py tests/test_gpu_sweeps.py tests/test_gpu_lens.py tests/test_gpu_models.py tests/test_gpu_baselines.py tests/test_gpu_sae.py -q > gpurun_out/r02s_pytest.log 2>&1; tail -8 gpurun_out/r02s_pytest.log
+timeout 900 python bench.py --steps 2 --warmup 3 --no-workloads > gpurun_out/r02s_bench.json 2> gpurun_out/r02s_bench.err; echo "bench rc=$?"; tail -c 500 gpurun_out/r02s_bench.err
+python - <<'PY'
+import json
+j = json.loads([l for l in open("gpurun_out/r02s_bench.json") if l.startswith("{")][-1])
+print("value", j["value"], "e2e", j["e2e"]["value"], "ms", j["ms_per_step"])
+print(j["ll_topk"]); print(j["roofline"].get("ll_topk_kernel")); print(j["roofline"]["achieved"], j["roofline"]["kernel_share_of_step"])
+PY

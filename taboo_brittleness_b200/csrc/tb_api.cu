@@ -562,7 +562,7 @@ int tb_topm_select(const float* mean, int64_t n_prompts, int S, int m, int32_t* 
   DevInfo di;
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
-  if (!mean || !out_idx || !out_val || !rank) return fail(TB_ERR_INVALID, "null pointer");
+  if (!mean || !out_idx || !out_val) return fail(TB_ERR_INVALID, "null pointer");
   if (m < 1 || m > TB_TOPM_MAX) return fail(TB_ERR_INVALID, "m=%d outside [1, %d]", m, TB_TOPM_MAX);
   if (S < 1) return fail(TB_ERR_INVALID, "S=%d", S);
   if (n_prompts == 0) return TB_OK;
@@ -1065,30 +1065,49 @@ int tb_lens_partials(const void* h, const void* w_u, int64_t n_rows, int d, int 
   return launch_gemm_mode<tb::LensEpi>(cm, h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
 }
 
-int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, float softcap, int n_chunks,
-                           int cta_pair, float* pm, float* ps, float* psec, float* ptv, int32_t* pti, float* logits_out,
-                           void* stream) {
+int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, float softcap,
+                           const int32_t* secret_id, int n_chunks, int cta_pair, float* pm, float* ps, float* psec,
+                           float* ptv, int32_t* pti, float* logits_out, void* stream) {
   DevInfo di;
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
   rc = check_gemm_operands(h, w_u, n_rows, V, d);
   if (rc != TB_OK) return rc;
   if (!pm || !ps || !psec || !ptv || !pti || !logits_out) return fail(TB_ERR_INVALID, "null buffer");
-  if (cta_pair != 0 && cta_pair != 1) return fail(TB_ERR_INVALID, "the dense mode runs as single CTAs (0) or CTA pairs (1)");
   if (reinterpret_cast<uintptr_t>(logits_out) & 15) return fail(TB_ERR_INVALID, "logits_out must be 16-byte aligned");
-  const int G = cta_pair ? 2 : 1;
-  tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, G);
+  ClusterMode cm;
+  rc = cluster_mode(cta_pair, &cm);
+  if (rc != TB_OK) return rc;
+  tb::GemmArgs g = make_args(n_rows, V, d, n_chunks, cm.group, cm.R, cm.C);
   if (g.n_chunks != n_chunks)
     return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks (use %d)", n_chunks, g.n_tiles,
                 g.n_chunks);
+  if (n_chunks % cm.C)
+    return fail(TB_ERR_INVALID, "n_chunks=%d must be a multiple of %d in cluster mode %d", n_chunks, cm.C, cta_pair);
   tb::LensDenseEpi::Params ep;
-  ep.lens.secret_id = nullptr;
+  ep.lens.secret_id = secret_id;
   ep.lens.vocab_offset = 0;
   ep.lens.softcap = softcap;
   ep.lens.pm = pm; ep.lens.ps = ps; ep.lens.psec = psec; ep.lens.ptv = ptv; ep.lens.pti = pti;
   ep.out = logits_out;
-  if (G == 2) return launch_gemm<tb::LensDenseEpi, 2>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
-  return launch_gemm<tb::LensDenseEpi, 1>(h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+  return launch_gemm_mode<tb::LensDenseEpi>(cm, h, w_u, g, ep, static_cast<cudaStream_t>(stream), di.sms);
+}
+
+int tb_logits_ll_colsum(const float* logits, const float* lse, const int32_t* cur_id, const int32_t* prev_id,
+                        int64_t n_rows, int V, float* acc, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!logits || !lse || !acc) return fail(TB_ERR_INVALID, "null pointer");
+  if (prev_id && !cur_id) return fail(TB_ERR_INVALID, "prev_id given without cur_id");
+  if (n_rows < 0 || V < 1) return fail(TB_ERR_INVALID, "bad shape");
+  if (n_rows == 0) return TB_OK;
+  const int64_t n_prompts = (n_rows + tb::kLlSlots - 1) / tb::kLlSlots;
+  if (n_prompts > 65535) return fail(TB_ERR_INVALID, "at most 65535 prompts per call (%lld)", static_cast<long long>(n_prompts));
+  dim3 grid(static_cast<unsigned>((V + 1023) / 1024), static_cast<unsigned>(n_prompts), 1);     // 4 columns per thread
+  tb::tb_logits_ll_colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, lse, cur_id, prev_id, n_rows, V, acc);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
 }
 
 int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V, void* stream) {

@@ -876,9 +876,10 @@ struct LensDenseEpi {
       float* o = p.out + static_cast<size_t>(row) * g.N + col0;
       if (col0 + 32 <= g.N && (g.N & 3) == 0) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-          reinterpret_cast<float4*>(o)[q] = make_float4(cap2(__uint_as_float(v[4 * q])) * kLn2, cap2(__uint_as_float(v[4 * q + 1])) * kLn2,
-                                                        cap2(__uint_as_float(v[4 * q + 2])) * kLn2, cap2(__uint_as_float(v[4 * q + 3])) * kLn2);
+        for (int q = 0; q < 8; ++q)      // streaming stores: the array is far larger than L2 and must not evict the operand tiles
+          __stcs(reinterpret_cast<float4*>(o) + q,
+                 make_float4(cap2(__uint_as_float(v[4 * q])) * kLn2, cap2(__uint_as_float(v[4 * q + 1])) * kLn2,
+                             cap2(__uint_as_float(v[4 * q + 2])) * kLn2, cap2(__uint_as_float(v[4 * q + 3])) * kLn2));
       } else {
 #pragma unroll
         for (int j = 0; j < 32; ++j)

@@ -621,15 +621,16 @@ tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __r
   }
 
   // ---- outputs
-  uint16_t* rk = rank + static_cast<size_t>(p) * S;
-  for (int j = tid; j < S; j += kTopmThreads) rk[j] = 0xffffu;
+  uint16_t* rk = rank ? rank + static_cast<size_t>(p) * S : nullptr;     // (nullable: only the sorted list is wanted)
+  if (rk)
+    for (int j = tid; j < S; j += kTopmThreads) rk[j] = 0xffffu;
   __syncthreads();
   if (tid < static_cast<int>(mm)) {
     const unsigned long long e = sel[tid];
     const int32_t id = static_cast<int32_t>(0xffffffffu - static_cast<uint32_t>(e & 0xffffffffull));
     out_idx[static_cast<size_t>(p) * m + tid] = id;
     out_val[static_cast<size_t>(p) * m + tid] = key_float(static_cast<uint32_t>(e >> 32));
-    rk[id] = static_cast<uint16_t>(tid);
+    if (rk) rk[id] = static_cast<uint16_t>(tid);
   } else if (tid < m) {
     out_idx[static_cast<size_t>(p) * m + tid] = -1;
     out_val[static_cast<size_t>(p) * m + tid] = 0.0f;
@@ -1308,6 +1309,67 @@ __global__ void tb_merge_sublists_kernel(const int32_t* __restrict__ sub_count, 
     out_count[row] = total;
     out_truncated[row] = trunc;
   }
+}
+
+// a11 from dense LOGITS, all prompts of a batch in one launch: acc[p, v] = sum over the prompt's 128 row slots of
+// exp(logit[t, v] - lse[t]) with the row's current / previous token id zeroed (01_reproduce_logit_lens.py:35-71).
+// The first condition of a sweep has no previous logsumexp to lean on (K3F) -- instead of a second sweep of the GEMM
+// (K5) the lens kernel writes its soft-capped logits in the one sweep it does (LensDenseEpi, row sub-batches), and
+// this kernel reduces them: HBM-bound, rows * V * 4 bytes read once, coalesced. grid = (ceil(V / 256), prompts).
+constexpr int kLlSlots = 128;
+
+__global__ void __launch_bounds__(256) tb_logits_ll_colsum_kernel(const float* __restrict__ logits, const float* __restrict__ lse,
+                                                                  const int32_t* __restrict__ cur_id,
+                                                                  const int32_t* __restrict__ prev_id, int64_t n_rows, int V,
+                                                                  float* __restrict__ acc) {
+  // a thread owns four consecutive columns (one 16-byte load per row), eight rows in flight: 128 bytes per thread
+  __shared__ float s_lse[kLlSlots];
+  __shared__ int32_t s_cur[kLlSlots], s_prev[kLlSlots];
+  const int p = blockIdx.y;
+  const int64_t row0 = static_cast<int64_t>(p) * kLlSlots;
+  if (threadIdx.x < kLlSlots) {
+    const int64_t r = row0 + threadIdx.x;
+    const bool valid = r < n_rows;
+    s_lse[threadIdx.x] = valid ? lse[r] : CUDART_INF_F;            // +inf (also the caller's mark of an empty slot): weight 0
+    s_cur[threadIdx.x] = (valid && cur_id) ? cur_id[r] : -1;
+    s_prev[threadIdx.x] = (valid && prev_id) ? prev_id[r] : -1;
+  }
+  __syncthreads();
+  const int col = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (col >= V) return;
+  const bool vec = (V & 3) == 0;                                   // rows are 16-byte aligned and col + 4 <= V
+  float a[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+  const float* lp = logits + row0 * V + col;
+  for (int t0 = 0; t0 < kLlSlots; t0 += 8) {
+    float4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      v[u] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      if (s_lse[t0 + u] < CUDART_INF_F) {                          // uniform over the block
+        const float* q = lp + static_cast<int64_t>(t0 + u) * V;
+        if (vec) v[u] = __ldcs(reinterpret_cast<const float4*>(q));     // streamed: read once
+        else {
+          v[u].x = __ldg(q);
+          if (col + 1 < V) v[u].y = __ldg(q + 1);
+          if (col + 2 < V) v[u].z = __ldg(q + 2);
+          if (col + 3 < V) v[u].w = __ldg(q + 3);
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const float l = s_lse[t0 + u];
+      if (l < CUDART_INF_F) {
+        const int c = s_cur[t0 + u], q = s_prev[t0 + u];
+        const float e[4] = {expf(v[u].x - l), expf(v[u].y - l), expf(v[u].z - l), expf(v[u].w - l)};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) a[j] = __fadd_rn(a[j], (col + j == c || col + j == q) ? 0.0f : e[j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+    if (col + j < V) acc[static_cast<size_t>(p) * V + col + j] = a[j];
 }
 
 }  // namespace tb

@@ -86,6 +86,12 @@ class InterventionEngine:
         # budget and can sit on SMs the next persistent lens grid wants -- so it is off by default.
         self.overlap = False
         self._side = None
+        # A condition without a predecessor (the first budget of a chain) gets its exact LL-Top-k from the logits the
+        # lens kernel writes in its one sweep (row sub-batches of ll_dense_rows rows, ops.lens_ll_from_logits) instead
+        # of a second sweep of the GEMM (K5): rows * V * 4 bytes of HBM traffic each way instead of 2 d V FLOP per row.
+        self.ll_dense_first = True
+        self.ll_dense_rows = 65536
+        self._dense_logits = None
         self.use_ranked = True       # nested budgets read prefixes of rank-ordered lists (ops.rank_lists) in K1b
         self.ll_alpha = 0.5          # candidate threshold = ll_alpha * previous condition's k-th best sum
         self.ll_cand_cap = 256       # candidate slots per prompt
@@ -160,9 +166,47 @@ class InterventionEngine:
             val[bad], ids[bad], theta[bad] = bv, bi, bv[:, ll.k - 1]
         return Readout(out, val, ids), LLState(out.lse, theta)
 
+    def release_scratch(self) -> None:
+        """Drop the logits scratch of ``read_dense_ll`` (tens of GB)."""
+        self._dense_logits = None
+
+    def read_dense_ll(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], ll: LLSpec) -> Readout:
+        """Lens readout + exact LL-Top-k of a condition with no predecessor, one GEMM sweep (see ``ll_dense_first``)."""
+        n, V = h.shape[0], self.lens.w_u.shape[0]
+        step = max(ops.LL_SLOTS, min(self.ll_dense_rows, n) // ops.LL_SLOTS * ops.LL_SLOTS)
+        free = torch.cuda.mem_get_info(h.device)[0]
+        have = 0 if self._dense_logits is None else self._dense_logits.numel() * 4
+        while step > 8 * ops.LL_SLOTS and step * V * 4 > have + 0.8 * free:    # do not take more than most of what is free
+            step = step // 2 // ops.LL_SLOTS * ops.LL_SLOTS
+        if self._dense_logits is None or self._dense_logits.shape[0] < step or self._dense_logits.shape[1] != V:
+            self._dense_logits = None
+            self._dense_logits = torch.empty(step, V, dtype=torch.float32, device=h.device)
+        outs, sums, ids = [], [], []
+        for r0 in range(0, n, step):
+            r1 = min(n, r0 + step)
+            sl = lambda t: None if t is None else t[r0:r1]      # noqa: E731
+            if self.time_lens:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            o, sv, si = ops.lens_ll_from_logits(h[r0:r1], self.lens.w_u, sl(ll.cur_id), sl(ll.prev_id), self._dense_logits,
+                                                k=ll.k, softcap=self.softcap, secret_id=sl(secret_id), cta_pair=self.cta_pair)
+            if self.time_lens:
+                e1.record()      # the sweep, its merge and the reduction of the stored logits
+                self.stats.lens_events.append((e0, e1, 2.0 * (r1 - r0) * h.shape[1] * V))
+            outs.append(o)
+            sums.append(sv)
+            ids.append(si)
+            self.stats.launches += 4
+        lens = ops.LensReadout(lse=torch.cat([o.lse for o in outs]), secret_prob=torch.cat([o.secret_prob for o in outs]),
+                               top_prob=torch.cat([o.top_prob for o in outs]), top_id=torch.cat([o.top_id for o in outs]))
+        return Readout(lens, torch.cat(sums), torch.cat(ids))
+
     def read(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], finalize: bool = True,
              ll: Optional[LLSpec] = None):
         """Lens readout of an already normalised operand (+ LL-Top-k when ``ll`` is given)."""
+        if (ll is not None and finalize and self.ll_dense_first and self.lens.vocab_offset == 0 and ll.seg is None
+                and ll.rows_per_prompt == ops.LL_SLOTS and h.shape[0] % ops.LL_SLOTS == 0 and h.shape[0] > 0):
+            return self.read_dense_ll(h, secret_id, ll)
         if self.time_lens:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()

@@ -277,13 +277,13 @@ def latent_wsum(acts: SparseActs, rows_per_prompt: int = 0, seg: Optional[torch.
     return out
 
 
-def topm_select(mean: torch.Tensor, m: int) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """Top-m latents per prompt, sorted descending: (idx i32 [P,m], val f32 [P,m], rank u16 [P,S])."""
+def topm_select(mean: torch.Tensor, m: int, want_rank: bool = True) -> Tuple[torch.Tensor, torch.Tensor, Optional[torch.Tensor]]:
+    """Top-m latents per prompt, sorted descending: (idx i32 [P,m], val f32 [P,m], rank u16 [P,S] or None)."""
     _need(mean, torch.float32, "mean", 2)
     P, S = mean.shape
     idx = torch.empty(P, m, dtype=torch.int32, device=mean.device)
     val = torch.empty(P, m, dtype=torch.float32, device=mean.device)
-    rank = torch.empty(P, S, dtype=torch.uint16, device=mean.device)
+    rank = torch.empty(P, S, dtype=torch.uint16, device=mean.device) if want_rank else None
     check(_lib.load().tb_topm_select(_ptr(mean), P, S, m, _ptr(idx), _ptr(val), _ptr(rank), _stream()),
           "tb_topm_select")
     return idx, val, rank
@@ -670,13 +670,50 @@ def lens_dense_probs(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0
     probs = torch.empty(n, V, dtype=torch.float32, device=h.device)
     lib = _lib.load()
     if n:
-        check(lib.tb_lens_dense_partials(_ptr(h), _ptr(w_u), n, d, V, float(softcap or 0.0), n_chunks, int(bool(cta_pair)),
+        check(lib.tb_lens_dense_partials(_ptr(h), _ptr(w_u), n, d, V, float(softcap or 0.0), None, n_chunks, int(bool(cta_pair)),
                                          _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _ptr(probs),
                                          _stream()), "tb_lens_dense_partials")
     out = lens_merge(p, finalize=True)
     if n:
         check(lib.tb_probs_from_logits(_ptr(probs), _ptr(out.lse), n, V, _stream()), "tb_probs_from_logits")
     return probs, out
+
+
+def lens_ll_from_logits(h: torch.Tensor, w_u: torch.Tensor, cur_id: Optional[torch.Tensor], prev_id: Optional[torch.Tensor],
+                        logits: torch.Tensor, *, k: int = TB_TOPK, softcap: float = 0.0,
+                        secret_id: Optional[torch.Tensor] = None, cta_pair=5):
+    """Lens readout AND exact LL-Top-k of one row sub-batch from ONE sweep of the GEMM, for a condition that has no
+    predecessor to take a softmax reference from: the lens kernel writes its soft-capped logits into ``logits``
+    (f32 [>= rows, V] scratch) while it accumulates the readout; once the logsumexp is merged, an HBM-bound kernel
+    sums exp(logit - lse) over each prompt's 128 row slots with the masked ids zeroed, and the radix select ranks each
+    prompt's V sums. Rows in the 128-slots-per-prompt layout. Returns (LensReadout, sums f32 [P, k], ids i32 [P, k])."""
+    _need(h, torch.bfloat16, "h", 2)
+    _need(w_u, torch.bfloat16, "w_u", 2)
+    _need(logits, torch.float32, "logits", 2)
+    n, d = h.shape
+    V = w_u.shape[0]
+    if n % LL_SLOTS or logits.shape[1] != V or logits.shape[0] < n:
+        raise TabooKernelError(f"rows={n} must be a multiple of {LL_SLOTS}; logits scratch {tuple(logits.shape)} too small",
+                               _lib.TB_ERR_INVALID)
+    for name, t in (("cur_id", cur_id), ("prev_id", prev_id), ("secret_id", secret_id)):
+        if t is not None:
+            _need(t, torch.int32, name, 1)
+    dev = h.device
+    n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(dev).multi_processor_count, cta_pair)
+    p = _alloc_partials(n_chunks, n, dev)
+    lib = _lib.load()
+    P = n // LL_SLOTS
+    if n == 0:
+        return lens_merge(p), torch.empty(0, k, device=dev), torch.empty(0, k, dtype=torch.int32, device=dev)
+    check(lib.tb_lens_dense_partials(_ptr(h), _ptr(w_u), n, d, V, float(softcap or 0.0), _ptr(secret_id), n_chunks,
+                                     _mode(cta_pair), _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti),
+                                     _ptr(logits), _stream()), "tb_lens_dense_partials")
+    out = lens_merge(p, finalize=True)
+    acc = torch.empty(P, V, dtype=torch.float32, device=dev)
+    check(lib.tb_logits_ll_colsum(_ptr(logits), _ptr(out.lse), _ptr(cur_id), _ptr(prev_id), n, V, _ptr(acc), _stream()),
+          "tb_logits_ll_colsum")
+    ids, sums, _ = topm_select(acc, k, want_rank=False)
+    return out, sums, ids
 
 
 def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,

@@ -182,3 +182,51 @@ def test_candidate_sums_on_tensor_cores_match_the_oracle_lists(cuda_lib, P):
     assert (cnt.cpu() <= 128).all()
     assert b[3].bool().any()
     _compare(b[0][b[3].bool()], b[1][b[3].bool()], [r for r, f in zip(ref_lists, b[3].tolist()) if f], 10)
+
+
+@pytest.mark.parametrize("softcap", [None, 30.0])
+def test_first_condition_ll_from_stored_logits_equals_second_sweep(cuda_lib, softcap):
+    """A condition without a predecessor: LL-Top-10 from the logits the lens kernel writes in its one sweep
+    (ops.lens_ll_from_logits: dense store + per-prompt column sums + radix select, in row sub-batches) against the
+    second GEMM sweep (K5) and the oracle's lists; the lens readout must be the plain kernel's."""
+    from taboo_brittleness_b200 import interventions, ops
+    P, d, V = 5, 512, 8192
+    h, w_u, sid, cur, prev, plain, ref_lists = _setup(P, d, V, 7, softcap)
+    scratch = torch.empty(2 * 128, V, dtype=torch.float32, device="cuda")
+    outs = [ops.lens_ll_from_logits(h[r0:r0 + 256], w_u, cur[r0:r0 + 256], prev[r0:r0 + 256], scratch, softcap=softcap or 0.0,
+                                    secret_id=sid[r0:r0 + 256], cta_pair=m) for r0, m in ((0, 5), (256, 1), (512, 4))]
+    v5, i5 = ops.ll_topk(h, w_u, plain.lse, cur, prev, softcap=softcap or 0.0)
+    torch.cuda.synchronize()
+    lse = torch.cat([o[0].lse for o in outs])
+    top = torch.cat([o[0].top_id for o in outs])
+    sums = torch.cat([o[1] for o in outs])
+    ids = torch.cat([o[2] for o in outs])
+    assert torch.allclose(lse, plain.lse, atol=2e-4) and torch.equal(top, plain.top_id)
+    assert torch.allclose(torch.cat([o[0].secret_prob for o in outs]), plain.secret_prob, atol=1e-5)
+    assert torch.allclose(sums, v5, rtol=1e-4, atol=1e-7)
+    same = (ids.sort(1).values == i5.sort(1).values).all(1)
+    for q in torch.nonzero(~same).flatten().tolist():
+        assert abs(float(sums[q, 9] - v5[q, 9])) <= 2e-3 * float(v5[q, 9])
+    _compare(sums, ids, ref_lists, 10)
+    # through the engine: the first budget of a chain takes this path, the second the one-sweep K3F + K6 path
+    x = synthetic.make_residuals(P, 128, d, seed=71)
+    lens = synthetic.make_lens(d, V, seed=71)
+    sae = synthetic.make_sae(d, 1024, seed=71, target_l0=20.0)
+    sidc = synthetic.make_secret_ids(P, 128, V, seed=71)
+
+    def mk(dense):
+        e = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                             softcap=softcap or 0.0)
+        e.ll_dense_first = dense
+        e.ll_dense_rows = 256
+        return e
+    ll = interventions.LLSpec(cur, prev, rows_per_prompt=128, k=10)
+    a = mk(True).targeted_budget_sweep(cuda_bf16(x), 128, sidc.cuda(), [2, 16], ll=ll)
+    b = mk(False).targeted_budget_sweep(cuda_bf16(x), 128, sidc.cuda(), [2, 16], ll=ll)
+    torch.cuda.synchronize()
+    for bud in (2, 16):
+        assert torch.equal(a[bud].top_id, b[bud].top_id) and torch.allclose(a[bud].lens.lse, b[bud].lens.lse, atol=2e-4)
+        eq = (a[bud].ll_id.sort(1).values == b[bud].ll_id.sort(1).values).all(1)
+        for q in torch.nonzero(~eq).flatten().tolist():
+            assert abs(float(a[bud].ll_sum[q, 9] - b[bud].ll_sum[q, 9])) <= 2e-3 * float(b[bud].ll_sum[q, 9])
+        assert torch.allclose(a[bud].ll_sum[:, 0], b[bud].ll_sum[:, 0], rtol=2e-3)
