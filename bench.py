@@ -673,7 +673,9 @@ def run_native(args, rank, local_rank, world):
                 "gpu_launches": launches,
                 "roofline": {"bound": "tensor",
                              "kernel": ("tb_umma_gemm_kernel<LensLLEpi> (lens readout + LL-Top-k candidates, one sweep; "
-                                        "first budget: <LensEpi>)" if args.ll_topk and not args.ll_two_sweeps
+                                        + ("first budget: <LensDenseEpi>, timed together with its merge, column-sum and select "
+                                           "kernels)" if eng.ll_dense_first else "first budget: <LensEpi>)")
+                                        if args.ll_topk and not args.ll_two_sweeps
                                         else "tb_umma_gemm_kernel<LensEpi> (logit-lens readout)"),
                              "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s",
                              "frac": achieved / peaks["tflops"], "traffic": None,

@@ -249,12 +249,20 @@ int tb_lowrank_remove_fused(const void* x_bf16, const void* ut_bf16, int r, int6
  *  - LL-Top-k of a condition that has no predecessor (01:35-71, 147-149): instead of a second sweep of the GEMM,
  *    tb_logits_ll_colsum reduces the stored logits of a row sub-batch to acc f32 [n_prompts, V] (128 row slots per
  *    prompt, lse = +inf marks an empty slot, cur_id / prev_id zeroed per position) and tb_topm_select (rank = NULL)
- *    ranks each prompt's sums. HBM-bound: n_rows * V * 4 bytes written once and read once. */
+ *    ranks each prompt's sums. HBM-bound: n_rows * V * 4 bytes written once and read once.
+ *
+ * layout of the logits array (both calls): TB_LOGITS_ROW_MAJOR = [n_rows, V]; TB_LOGITS_PROMPT_TILES =
+ * [n_rows / 128][V / 32][128 rows][32 columns], values in LOG2 units (logit x log2 e; V % 32 == 0, n_rows % 128 == 0;
+ * an intermediate for tb_logits_ll_colsum, not an output format) -- a prompt's 128 x 32 piece is 16 KB of
+ * consecutive memory, which is what lets tb_logits_ll_colsum stream; only the LL-Top-k user wants it. The lens kernel
+ * writes either layout through the TMA unit (row-major with V % 4 != 0: plain stores). */
+#define TB_LOGITS_ROW_MAJOR 0
+#define TB_LOGITS_PROMPT_TILES 1
 int tb_lens_dense_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V, float softcap,
                            const int32_t* secret_id, int n_chunks, int cta_pair, float* pm, float* ps, float* psec,
-                           float* ptv, int32_t* pti, float* logits_out, void* stream);
+                           float* ptv, int32_t* pti, float* logits_out, int layout, void* stream);
 int tb_logits_ll_colsum(const float* logits, const float* lse, const int32_t* cur_id, const int32_t* prev_id,
-                        int64_t n_rows, int V, float* acc, void* stream);
+                        int64_t n_rows, int V, float* acc, int layout, void* stream);
 int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V, void* stream);
 
 /* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------

@@ -42,22 +42,37 @@ def timed(fn, reps=3):
 flops = 2.0 * n * D * V
 ms, _ = timed(lambda: ops.lens_partials(h, lens.W_U, softcap=30.0))
 print(json.dumps({"piece": "lens sweep (K3)", "rows": n, "ms": ms, "tflops": flops / ms / 1e9}), flush=True)
-for chunks in (None, 2, 4, 8):
-    def dense():
-        c = chunks or ops.pick_chunks(n, V, 148, 5)
-        p = ops._alloc_partials(c, n, h.device)
-        _lib.check(lib.tb_lens_dense_partials(h.data_ptr(), lens.W_U.data_ptr(), n, D, V, 30.0, None, c, 5, p.pm.data_ptr(), p.ps.data_ptr(),
-                                              p.psec.data_ptr(), p.ptv.data_ptr(), p.pti.data_ptr(), logits.data_ptr(),
-                                              torch.cuda.current_stream().cuda_stream), "dense")
-        return p
-    ms, p = timed(dense)
-    print(json.dumps({"piece": "lens sweep + logits store", "chunks": chunks or ops.pick_chunks(n, V, 148, 5), "ms": ms,
-                      "tflops": flops / ms / 1e9, "store_GBps": n * V * 4 / ms / 1e6}), flush=True)
-out = ops.lens_merge(p)
-acc = torch.empty(n // 128, V, dtype=torch.float32, device="cuda")
-ms, _ = timed(lambda: _lib.check(lib.tb_logits_ll_colsum(logits.data_ptr(), out.lse.data_ptr(), cur.data_ptr(), None, n, V, acc.data_ptr(),
-                                                         torch.cuda.current_stream().cuda_stream), "colsum"))
-print(json.dumps({"piece": "column sums from logits", "ms": ms, "read_GBps": n * V * 4 / ms / 1e6}), flush=True)
+def dense(c, layout):
+    p = ops._alloc_partials(c, n, h.device)
+    _lib.check(lib.tb_lens_dense_partials(h.data_ptr(), lens.W_U.data_ptr(), n, D, V, 30.0, None, c, 5, p.pm.data_ptr(), p.ps.data_ptr(),
+                                          p.psec.data_ptr(), p.ptv.data_ptr(), p.pti.data_ptr(), logits.data_ptr(), layout,
+                                          torch.cuda.current_stream().cuda_stream), "dense")
+    return p
+
+
+def colsum(out, acc, layout):
+    _lib.check(lib.tb_logits_ll_colsum(logits.data_ptr(), out.lse.data_ptr(), cur.data_ptr(), None, n, V, acc.data_ptr(), layout,
+                                       torch.cuda.current_stream().cuda_stream), "colsum")
+
+
+c0 = ops.pick_chunks(n, V, 148, 5)
+accs = {}
+for layout, name in ((ops.LOGITS_ROW_MAJOR, "row-major"), (ops.LOGITS_PROMPT_TILES, "prompt tiles")):
+    for chunks in ((c0, 8) if layout == ops.LOGITS_ROW_MAJOR else (c0, 2, 8)):
+        ms, p = timed(lambda: dense(chunks, layout))
+        print(json.dumps({"piece": "lens sweep + logits store", "layout": name, "chunks": chunks, "ms": ms,
+                          "tflops": flops / ms / 1e9, "store_GBps": n * V * 4 / ms / 1e6}), flush=True)
+    p = dense(c0, layout)
+    out = ops.lens_merge(p)
+    acc = torch.empty(n // 128, V, dtype=torch.float32, device="cuda")
+    ms, _ = timed(lambda: colsum(out, acc, layout))
+    print(json.dumps({"piece": "column sums from logits", "layout": name, "ms": ms, "read_GBps": n * V * 4 / ms / 1e6}), flush=True)
+    accs[name] = acc
+a, b = accs["row-major"], accs["prompt tiles"]
+rel = ((a - b).abs() / a.abs().clamp_min(1e-30)).max().item()
+print(json.dumps({"check": "column sums, prompt tiles vs row-major", "max_rel_diff": rel,
+                  "top10_ids_equal": bool((a.topk(10).indices.sort().values == b.topk(10).indices.sort().values).all().item())}), flush=True)
+del a, b, accs
 ms, _ = timed(lambda: ops.topm_select(acc, 10, want_rank=False))
 print(json.dumps({"piece": "radix select of V sums per prompt", "prompts": n // 128, "ms": ms}), flush=True)
 ms, _ = timed(lambda: ops.ll_topk(h, lens.W_U, out.lse, cur, None, softcap=30.0))

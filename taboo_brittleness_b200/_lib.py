@@ -57,8 +57,8 @@ SIGNATURES = {
     "tb_rmsnorm": (c_int, [_P, _P, c_float, c_int64, c_int, _P, _P]),
     "tb_lens_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,
                                  _P, _P, _P, _P, _P, _P]),
-    "tb_lens_dense_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_float, _P, c_int, c_int, _P, _P, _P, _P, _P, _P, _P]),
-    "tb_logits_ll_colsum": (c_int, [_P, _P, _P, _P, c_int64, c_int, _P, _P]),
+    "tb_lens_dense_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_float, _P, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, _P]),
+    "tb_logits_ll_colsum": (c_int, [_P, _P, _P, _P, c_int64, c_int, _P, c_int, _P]),
     "tb_probs_from_logits": (c_int, [_P, _P, c_int64, c_int, _P]),
     "tb_lens_merge": (c_int, [_P, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P,
                               _P, _P, _P]),

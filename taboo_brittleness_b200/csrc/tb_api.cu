@@ -1067,13 +1067,17 @@ int tb_lens_partials(const void* h, const void* w_u, int64_t n_rows, int d, int 
 
 int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d, int V, float softcap,
                            const int32_t* secret_id, int n_chunks, int cta_pair, float* pm, float* ps, float* psec,
-                           float* ptv, int32_t* pti, float* logits_out, void* stream) {
+                           float* ptv, int32_t* pti, float* logits_out, int layout, void* stream) {
   DevInfo di;
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
   rc = check_gemm_operands(h, w_u, n_rows, V, d);
   if (rc != TB_OK) return rc;
   if (!pm || !ps || !psec || !ptv || !pti || !logits_out) return fail(TB_ERR_INVALID, "null buffer");
+  if (layout != TB_LOGITS_ROW_MAJOR && layout != TB_LOGITS_PROMPT_TILES) return fail(TB_ERR_INVALID, "layout=%d", layout);
+  if (layout == TB_LOGITS_PROMPT_TILES && (V % 32 != 0 || n_rows % tb::kLlSlots != 0))
+    return fail(TB_ERR_INVALID, "prompt tiles need V %% 32 == 0 and whole prompts of %d rows (V=%d, n_rows=%lld)", tb::kLlSlots, V,
+                static_cast<long long>(n_rows));
   if (reinterpret_cast<uintptr_t>(logits_out) & 15) return fail(TB_ERR_INVALID, "logits_out must be 16-byte aligned");
   ClusterMode cm;
   rc = cluster_mode(cta_pair, &cm);
@@ -1085,6 +1089,30 @@ int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d
   if (n_chunks % cm.C)
     return fail(TB_ERR_INVALID, "n_chunks=%d must be a multiple of %d in cluster mode %d", n_chunks, cm.C, cta_pair);
   tb::LensDenseEpi::Params ep;
+  memset(&ep.tm_out, 0, sizeof(ep.tm_out));
+  static const bool direct = getenv("TB_DENSE_DIRECT_STORE") != nullptr;   // experiments: plain stores from the row owners
+  ep.tma = layout == TB_LOGITS_PROMPT_TILES ? 2 : (V % 4 == 0 && !direct) ? 1 : 0;   // a tensor map wants a 16-byte row pitch
+  if (ep.tma) {                            // box = one warp's [32 rows x 32 columns] fp32, 128-byte swizzle
+    EncodeTiledFn enc;
+    rc = get_encode_fn(&enc);
+    if (rc != TB_OK) return rc;
+    const cuuint64_t n_ct = static_cast<cuuint64_t>(V / 32);
+    // row-major [n_rows, V]; or (column in tile, row in prompt, column tile, prompt) over [P][V / 32][128][32]
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(V), static_cast<cuuint64_t>(n_rows), 1, 1};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(V) * 4, 0, 0};
+    cuuint32_t box[4] = {32, 32, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (ep.tma == 2) {
+      dims[0] = 32; dims[1] = tb::kLlSlots; dims[2] = n_ct; dims[3] = static_cast<cuuint64_t>(n_rows / tb::kLlSlots);
+      strides[0] = 128; strides[1] = 128ull * tb::kLlSlots; strides[2] = strides[1] * n_ct;
+    }
+    CUresult r = enc(&ep.tm_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, ep.tma == 2 ? 4 : 2, logits_out, dims, strides, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS)
+      return fail(TB_ERR_CUDA, "cuTensorMapEncodeTiled (logits) failed with CUresult %d (rows=%lld V=%d)", static_cast<int>(r),
+                  static_cast<long long>(n_rows), V);
+  }
   ep.lens.secret_id = secret_id;
   ep.lens.vocab_offset = 0;
   ep.lens.softcap = softcap;
@@ -1094,16 +1122,30 @@ int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d
 }
 
 int tb_logits_ll_colsum(const float* logits, const float* lse, const int32_t* cur_id, const int32_t* prev_id,
-                        int64_t n_rows, int V, float* acc, void* stream) {
+                        int64_t n_rows, int V, float* acc, int layout, void* stream) {
   DevInfo di;
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
   if (!logits || !lse || !acc) return fail(TB_ERR_INVALID, "null pointer");
   if (prev_id && !cur_id) return fail(TB_ERR_INVALID, "prev_id given without cur_id");
   if (n_rows < 0 || V < 1) return fail(TB_ERR_INVALID, "bad shape");
+  if (layout != TB_LOGITS_ROW_MAJOR && layout != TB_LOGITS_PROMPT_TILES) return fail(TB_ERR_INVALID, "layout=%d", layout);
   if (n_rows == 0) return TB_OK;
   const int64_t n_prompts = (n_rows + tb::kLlSlots - 1) / tb::kLlSlots;
   if (n_prompts > 65535) return fail(TB_ERR_INVALID, "at most 65535 prompts per call (%lld)", static_cast<long long>(n_prompts));
+  if (layout == TB_LOGITS_PROMPT_TILES) {
+    if (V % 32 != 0 || n_rows % tb::kLlSlots != 0)
+      return fail(TB_ERR_INVALID, "prompt tiles need V %% 32 == 0 and whole prompts of %d rows (V=%d, n_rows=%lld)", tb::kLlSlots, V,
+                  static_cast<long long>(n_rows));
+    if ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(acc)) & 15)
+      return fail(TB_ERR_INVALID, "logits and acc must be 16-byte aligned");
+    const int n_ct = V / 32;
+    dim3 tgrid(static_cast<unsigned>((n_ct + tb::kLlTilesPerBlock - 1) / tb::kLlTilesPerBlock), static_cast<unsigned>(n_prompts), 1);
+    tb::tb_logits_ll_colsum_tiled_kernel<<<tgrid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const float4*>(logits), lse, cur_id, prev_id, n_ct, V, acc);
+    TB_CUDA(cudaGetLastError());
+    return TB_OK;
+  }
   dim3 grid(static_cast<unsigned>((V + 1023) / 1024), static_cast<unsigned>(n_prompts), 1);     // 4 columns per thread
   tb::tb_logits_ll_colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, lse, cur_id, prev_id, n_rows, V, acc);
   TB_CUDA(cudaGetLastError());

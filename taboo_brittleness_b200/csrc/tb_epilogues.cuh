@@ -101,6 +101,11 @@ struct LensEpi {
     float c[32];
 #pragma unroll
     for (int j = 0; j < 32; ++j) c[j] = cap2(__uint_as_float(v[j]));
+    process_capped(st, p, g, c, col0);
+  }
+  // The same with the soft-capped logits (log2 units) already in hand.
+  __device__ __forceinline__ static void process_capped(State& st, const Params& p, const GemmArgs& g,
+                                                        float (&c)[32], int col0) {
     if (col0 + 32 > g.N) {  // ragged last tile: columns past N hold zero-filled garbage
 #pragma unroll
       for (int j = 0; j < 32; ++j)
@@ -529,6 +534,7 @@ struct LensLLEpi {
     float* tr = reinterpret_cast<float*>(assume_shared(c.extra) + kOffTr) + (c.half * 4 + quad) * (32 * kTrStride);
     float* cs = reinterpret_cast<float*>(assume_shared(c.extra) + kOffCs) + parity * (4 * 256);
     const CapLog2 cap2(p.lens.softcap);
+    const uint64_t evict_first = l2_policy_evict_first();   // the tiled array is tens of GB, read back once by another kernel
 #pragma unroll 1
     for (int cc = c.half * 4; cc < c.half * 4 + 4; ++cc) {
       const int col0 = nt * kBlockN + cc * 32;
@@ -859,37 +865,79 @@ struct ProjApplyEpi {
 struct LensDenseEpi {
   static constexpr int kEpiWarps = LensEpi::kEpiWarps;
   static constexpr bool kSweepA = false;
-  static constexpr bool kTileHooks = false;
-  static constexpr int kExtraSmem = 0;
+  static constexpr bool kTileHooks = true;
+  // Logits leave through shared memory: a thread owns an accumulator ROW, and rows are N * 4 bytes apart in
+  // memory, so a direct 16-byte store per lane touches 32 lines per warp instruction (measured: the sweep ran
+  // 22-24 % slower than the plain readout). Each warp instead lays its [32 rows x 32 columns] fp32 piece out in
+  // a 4 KB buffer of its own (128-byte swizzle: conflict-free 16-byte stores) and one lane hands it to the TMA
+  // unit, which writes whole 128-byte row segments and clips rows / columns outside the matrix.
+  static constexpr int kStageBytes = 32 * 128;                       // one warp's piece
+  static constexpr int kExtraSmem = kEpiWarps * kStageBytes + 1024;  // + slack: swizzled boxes start on 1024 bytes
   struct Params {
+    CUtensorMap tm_out;  // out through the TMA unit, box [32 rows x 32 columns] fp32, SWIZZLE_128B (valid when tma != 0):
+                         // tma 1: 2-d map of the row-major array; tma 2: 4-d map (column, row in prompt, column tile, prompt)
     LensEpi::Params lens;
-    float* out;          // [M, N] fp32: soft-capped logits (natural-log units)
+    float* out;          // soft-capped logits, fp32: [M, N] row-major in natural-log units, or with tma == 2 in prompt tiles
+                         // [M / 128][N / 32][128 rows][32 columns] in LOG2 units (x log2 e; what
+                         // tb_logits_ll_colsum_tiled_kernel streams through)
+    int tma;             // 0: N * 4 is not a multiple of 16 bytes -> plain stores (row-major only)
   };
   using State = LensEpi::State;
-  __device__ __forceinline__ static void begin_unit(State& st, const Params& p, const GemmArgs& g, int row, int part) {
-    LensEpi::begin_unit(st, p.lens, g, row, part);
+  __device__ __forceinline__ static void begin_unit_tile(State& st, const Params& p, const GemmArgs& g,
+                                                         const SweepCtx& c, int row) {
+    LensEpi::begin_unit(st, p.lens, g, row, c.chunk * 2 + c.half);
   }
-  __device__ __forceinline__ static void process(State& st, const Params& p, const GemmArgs& g,
-                                                 const uint32_t (&v)[32], int row, int col0) {
-    if (row < g.M) {
-      const CapLog2 cap2(p.lens.softcap);
-      float* o = p.out + static_cast<size_t>(row) * g.N + col0;
-      if (col0 + 32 <= g.N && (g.N & 3) == 0) {
+  __device__ __forceinline__ static void process_tile(State& st, const Params& p, const GemmArgs& g,
+                                                      const SweepCtx& c, int row, int nt, uint32_t taddr, int) {
+    const int lane = c.tid & 31;
+    const uint32_t extra = smem_u32(assume_shared(c.extra));
+    const uint32_t buf = ((extra + 1023u) & ~1023u) + static_cast<uint32_t>((c.half * 4 + (c.tid >> 5)) * kStageBytes);
+    const CapLog2 cap2(p.lens.softcap);
+    const uint64_t evict_first = l2_policy_evict_first();   // the tiled array is tens of GB, read back once by another kernel
+#pragma unroll 1
+    for (int cc = c.half * 4; cc < c.half * 4 + 4; ++cc) {
+      const int col0 = nt * kBlockN + cc * 32;
+      uint32_t v[32];
+      tmem_ld_32x32(taddr + cc * 32, v);
+      tmem_ld_wait();
+      float cv[32];                      // capped once: the softcap is two MUFU ops a column, and MUFU bounds this epilogue
 #pragma unroll
-        for (int q = 0; q < 8; ++q)      // streaming stores: the array is far larger than L2 and must not evict the operand tiles
-          __stcs(reinterpret_cast<float4*>(o) + q,
-                 make_float4(cap2(__uint_as_float(v[4 * q])) * kLn2, cap2(__uint_as_float(v[4 * q + 1])) * kLn2,
-                             cap2(__uint_as_float(v[4 * q + 2])) * kLn2, cap2(__uint_as_float(v[4 * q + 3])) * kLn2));
-      } else {
+      for (int j = 0; j < 32; ++j) cv[j] = cap2(__uint_as_float(v[j]));
+      if (p.tma) {
+        if (lane == 0) bulk_wait_read0();   // the TMA unit has read the previous piece out of the buffer
+        __syncwarp();
+        if (p.tma == 2) {                     // prompt tiles keep the kernel's log2 units (their one reader wants them)
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * 128 + ((q ^ (lane & 7)) << 4)),
+                         "f"(cv[4 * q]), "f"(cv[4 * q + 1]), "f"(cv[4 * q + 2]), "f"(cv[4 * q + 3]) : "memory");
+        } else {
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * 128 + ((q ^ (lane & 7)) << 4)),
+                         "f"(cv[4 * q] * kLn2), "f"(cv[4 * q + 1] * kLn2), "f"(cv[4 * q + 2] * kLn2), "f"(cv[4 * q + 3] * kLn2)
+                         : "memory");
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0 && col0 < g.N && row < g.M) {      // (lane 0 holds the warp's first row)
+          if (p.tma == 2) tma_store_4d_hint(&p.tm_out, buf, 0, row & 127, col0 >> 5, row >> 7, evict_first);
+          else tma_store_2d(&p.tm_out, buf, col0, row);
+          bulk_commit();
+        }
+      } else if (row < g.M) {
+        float* o = p.out + static_cast<size_t>(row) * g.N + col0;
 #pragma unroll
         for (int j = 0; j < 32; ++j)
-          if (col0 + j < g.N) o[j] = cap2(__uint_as_float(v[j])) * kLn2;
+          if (col0 + j < g.N) o[j] = cv[j] * kLn2;
       }
+      LensEpi::process_capped(st, p.lens, g, cv, col0);
     }
-    LensEpi::process(st, p.lens, g, v, row, col0);
   }
-  __device__ __forceinline__ static void end_unit(State& st, const Params& p, const GemmArgs& g, int row, int part) {
-    LensEpi::end_unit(st, p.lens, g, row, part);
+  __device__ __forceinline__ static void end_unit_tile(State& st, const Params& p, const GemmArgs& g,
+                                                       const SweepCtx& c, int row) {
+    if (p.tma && (c.tid & 31) == 0) bulk_wait0();     // this unit's logits are written
+    LensEpi::end_unit(st, p.lens, g, row, c.chunk * 2 + c.half);
   }
 };
 

@@ -133,7 +133,8 @@ static __device__ long long g_wait_prof[256][8];
 template <class Epi, int kCtaGroup, int kR = 1, int kC = 1, bool kHetero = false>
 __global__ void __launch_bounds__(gemm_threads<Epi>(), 1)
 tb_umma_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmS1, const GemmArgs g, const typename Epi::Params ep) {
+                    const __grid_constant__ CUtensorMap tmS1, const GemmArgs g,
+                    const __grid_constant__ typename Epi::Params ep) {   // (an epilogue may keep a tensor map of its own in there)
   static_assert(!kHetero || (kCtaGroup == 2 && kR == 2 && kC == 1), "preferred/fallback clusters: 2x1 pairs only");
   using Cfg = GemmCfg<kCtaGroup, EpiStages<Epi>::value>;
   constexpr int kStages = Cfg::kStages;

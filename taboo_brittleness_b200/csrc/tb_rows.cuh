@@ -1372,4 +1372,91 @@ __global__ void __launch_bounds__(256) tb_logits_ll_colsum_kernel(const float* _
     if (col + j < V) acc[static_cast<size_t>(p) * V + col + j] = a[j];
 }
 
+// The same from logits stored in PROMPT TILES [prompt][V / 32][128 rows][32 columns], in log2 units (LensDenseEpi with tma == 2): a
+// prompt's 128 x 32 piece of the array is 16 KB of consecutive memory, so a block streams 8 of them (256 columns,
+// 128 KB) front to back -- whole DRAM pages, few TLB entries -- where the row-major array gives 512 bytes per row, 1 MB
+// apart. Thread t takes the 16-byte piece t + 256 i of a tile (row t / 8 + 32 i, columns 4 (t % 8) ...), sums its four
+// rows, the 32 threads of a column piece are combined by shuffles (4 lanes) and through shared memory (8 warps), in a
+// fixed order. grid = (ceil(V / 256), prompts). V % 32 == 0, whole prompts.
+constexpr int kLlTilesPerBlock = 8;
+__device__ __forceinline__ float ex2_approx_rows(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__global__ void __launch_bounds__(256) tb_logits_ll_colsum_tiled_kernel(const float4* __restrict__ lt, const float* __restrict__ lse,
+                                                                        const int32_t* __restrict__ cur_id,
+                                                                        const int32_t* __restrict__ prev_id, int n_tiles, int V,
+                                                                        float* __restrict__ acc) {
+  __shared__ float s_lse[kLlSlots];
+  __shared__ int32_t s_cur[kLlSlots], s_prev[kLlSlots];
+  __shared__ float4 s_red[kLlTilesPerBlock][8][8];                 // [tile][warp][column piece]
+  const int p = blockIdx.y, t = threadIdx.x;
+  const int tile0 = blockIdx.x * kLlTilesPerBlock;
+  if (t < kLlSlots) {
+    const int64_t r = static_cast<int64_t>(p) * kLlSlots + t;
+    s_lse[t] = lse[r];                                             // +inf (the caller's mark of an empty slot): weight 0
+    s_cur[t] = cur_id ? cur_id[r] : -1;
+    s_prev[t] = prev_id ? prev_id[r] : -1;
+  }
+  __syncthreads();
+  const int c4 = t & 7, r0 = t >> 3, warp = t >> 5, lane = t & 31;
+  float l[4];                                                      // the row's logsumexp in log2 units, like the logits
+  int32_t cu[4], pv[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    l[i] = s_lse[r0 + 32 * i] * 1.4426950408889634f;
+    cu[i] = s_cur[r0 + 32 * i];
+    pv[i] = s_prev[r0 + 32 * i];
+  }
+  const float4* base = lt + (static_cast<size_t>(p) * n_tiles + tile0) * 1024 + t;
+#pragma unroll 1
+  for (int tj = 0; tj < kLlTilesPerBlock; tj += 2) {                // two tiles = eight 16-byte loads in flight per thread
+    float4 v[2][4];
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        v[u][i] = (tile0 + tj + u < n_tiles) ? __ldcs(base + (tj + u) * 1024 + 256 * i) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int col = (tile0 + tj + u) * 32 + c4 * 4;
+      float a[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float e[4] = {ex2_approx_rows(v[u][i].x - l[i]), ex2_approx_rows(v[u][i].y - l[i]), ex2_approx_rows(v[u][i].z - l[i]),
+                      ex2_approx_rows(v[u][i].w - l[i])};
+        const uint32_t dc = static_cast<uint32_t>(cu[i] - col), dp = static_cast<uint32_t>(pv[i] - col);
+        if (dc < 4u || dp < 4u) {                                 // a masked id among my four columns: rare
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (dc == static_cast<uint32_t>(j) || dp == static_cast<uint32_t>(j)) e[j] = 0.0f;
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) a[j] = __fadd_rn(a[j], e[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        a[j] = __fadd_rn(a[j], __shfl_xor_sync(0xffffffffu, a[j], 8));
+        a[j] = __fadd_rn(a[j], __shfl_xor_sync(0xffffffffu, a[j], 16));
+      }
+      if (lane < 8) s_red[tj + u][warp][lane] = make_float4(a[0], a[1], a[2], a[3]);
+    }
+  }
+  __syncthreads();
+  if (t < kLlTilesPerBlock * 8) {
+    const int tile = t >> 3, c = t & 7;
+    if (tile0 + tile < n_tiles) {
+      float4 r = s_red[tile][0][c];
+#pragma unroll
+      for (int w = 1; w < 8; ++w) {
+        const float4 o = s_red[tile][w][c];
+        r.x = __fadd_rn(r.x, o.x); r.y = __fadd_rn(r.y, o.y); r.z = __fadd_rn(r.z, o.z); r.w = __fadd_rn(r.w, o.w);
+      }
+      *reinterpret_cast<float4*>(acc + static_cast<size_t>(p) * V + (tile0 + tile) * 32 + c * 4) = r;
+    }
+  }
+}
+
 }  // namespace tb

@@ -672,7 +672,7 @@ def lens_dense_probs(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0
     if n:
         check(lib.tb_lens_dense_partials(_ptr(h), _ptr(w_u), n, d, V, float(softcap or 0.0), None, n_chunks, int(bool(cta_pair)),
                                          _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _ptr(probs),
-                                         _stream()), "tb_lens_dense_partials")
+                                         LOGITS_ROW_MAJOR, _stream()), "tb_lens_dense_partials")
     out = lens_merge(p, finalize=True)
     if n:
         check(lib.tb_probs_from_logits(_ptr(probs), _ptr(out.lse), n, V, _stream()), "tb_probs_from_logits")
@@ -681,7 +681,7 @@ def lens_dense_probs(h: torch.Tensor, w_u: torch.Tensor, *, softcap: float = 0.0
 
 def lens_ll_from_logits(h: torch.Tensor, w_u: torch.Tensor, cur_id: Optional[torch.Tensor], prev_id: Optional[torch.Tensor],
                         logits: torch.Tensor, *, k: int = TB_TOPK, softcap: float = 0.0,
-                        secret_id: Optional[torch.Tensor] = None, cta_pair=5):
+                        secret_id: Optional[torch.Tensor] = None, cta_pair=5, row_major: bool = False):
     """Lens readout AND exact LL-Top-k of one row sub-batch from ONE sweep of the GEMM, for a condition that has no
     predecessor to take a softmax reference from: the lens kernel writes its soft-capped logits into ``logits``
     (f32 [>= rows, V] scratch) while it accumulates the readout; once the logsumexp is merged, an HBM-bound kernel
@@ -705,13 +705,16 @@ def lens_ll_from_logits(h: torch.Tensor, w_u: torch.Tensor, cur_id: Optional[tor
     P = n // LL_SLOTS
     if n == 0:
         return lens_merge(p), torch.empty(0, k, device=dev), torch.empty(0, k, dtype=torch.int32, device=dev)
+    # the scratch is only ever read by the column-sum kernel: prompt tiles (16 KB of consecutive memory per prompt and
+    # 32 columns) let that kernel stream; the row-major form is kept for vocabularies that are no multiple of 32
+    layout = LOGITS_PROMPT_TILES if (V % 32 == 0 and not row_major) else LOGITS_ROW_MAJOR
     check(lib.tb_lens_dense_partials(_ptr(h), _ptr(w_u), n, d, V, float(softcap or 0.0), _ptr(secret_id), n_chunks,
                                      _mode(cta_pair), _ptr(p.pm), _ptr(p.ps), _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti),
-                                     _ptr(logits), _stream()), "tb_lens_dense_partials")
+                                     _ptr(logits), layout, _stream()), "tb_lens_dense_partials")
     out = lens_merge(p, finalize=True)
     acc = torch.empty(P, V, dtype=torch.float32, device=dev)
-    check(lib.tb_logits_ll_colsum(_ptr(logits), _ptr(out.lse), _ptr(cur_id), _ptr(prev_id), n, V, _ptr(acc), _stream()),
-          "tb_logits_ll_colsum")
+    check(lib.tb_logits_ll_colsum(_ptr(logits), _ptr(out.lse), _ptr(cur_id), _ptr(prev_id), n, V, _ptr(acc), layout,
+                                  _stream()), "tb_logits_ll_colsum")
     ids, sums, _ = topm_select(acc, k, want_rank=False)
     return out, sums, ids
 
@@ -733,6 +736,7 @@ def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,
 # K5 LL-Top-k
 # ------------------------------------------------------------------------------------------
 LL_SLOTS = 128             # row slots per prompt in the K5 kernel
+LOGITS_ROW_MAJOR, LOGITS_PROMPT_TILES = 0, 1     # tb_b200.h: layout of a stored-logits array
 LL_MAX_CHUNK_IDS = 65536   # vocabulary ids one chunk may span (mask bitmap)
 
 

@@ -206,21 +206,22 @@ def test_multicast_modes_check_the_whole_operand_extent(cuda_lib):
     assert "current GPU" in err or "no mapping" in err or "separate mappings" in err, err
 
 
+@pytest.mark.parametrize("V", [1000, 1001])      # 16-byte row pitch (logits leave through the TMA unit) / not (plain stores)
 @pytest.mark.parametrize("softcap", [None, 30.0])
 @pytest.mark.parametrize("pair", [False, True])
-def test_dense_probabilities_from_one_sweep(cuda_lib, softcap, pair):
+def test_dense_probabilities_from_one_sweep(cuda_lib, softcap, pair, V):
     """ops.lens_dense_probs: the dense [rows, V] softmax the compatibility surface returns (src/models.py:135-138)
     from one sweep (logits written by the lens kernel + in-place normalisation), ragged rows and vocabulary; its
     readout equals the plain lens readout."""
     from taboo_brittleness_b200 import ops
-    x, lens, sid = _problem(1, 200, 264, 1000, seed=9)
+    x, lens, sid = _problem(1, 200, 264, V, seed=9)
     h = ops.rmsnorm(cuda_bf16(x), lens.w_norm.cuda())
     wu = cuda_bf16(lens.W_U)
     probs, out = ops.lens_dense_probs(h, wu, softcap=softcap or 0.0, n_chunks=2, cta_pair=pair)
     plain = ops.lens_merge(ops.lens_partials(h, wu, softcap=softcap or 0.0, n_chunks=2, cta_pair=pair))
     torch.cuda.synchronize()
     ref = oracle.lens_probs(x, lens.w_norm, lens.W_U, softcap, residual_dtype=BF16)
-    assert probs.shape == (200, 1000)
+    assert probs.shape == (200, V)
     assert (probs.cpu() - ref).abs().max().item() <= SECRET_ABS_TOL
     assert (probs.sum(1) - 1.0).abs().max().item() <= 1e-4
     assert torch.equal(out.top_id, plain.top_id) and torch.equal(out.lse, plain.lse)

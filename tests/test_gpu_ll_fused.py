@@ -230,3 +230,46 @@ def test_first_condition_ll_from_stored_logits_equals_second_sweep(cuda_lib, sof
         for q in torch.nonzero(~eq).flatten().tolist():
             assert abs(float(a[bud].ll_sum[q, 9] - b[bud].ll_sum[q, 9])) <= 2e-3 * float(b[bud].ll_sum[q, 9])
         assert torch.allclose(a[bud].ll_sum[:, 0], b[bud].ll_sum[:, 0], rtol=2e-3)
+
+
+@pytest.mark.parametrize("mode", [1, 5])
+def test_stored_logits_prompt_tiles_are_the_row_major_logits(cuda_lib, mode):
+    """The two layouts tb_lens_dense_partials writes (tb_b200.h: TB_LOGITS_ROW_MAJOR, TB_LOGITS_PROMPT_TILES) hold the same
+    logits (prompt tiles in log2 units), the column sums of either agree to rounding, and ops.lens_ll_from_logits returns the same lists from both."""
+    from taboo_brittleness_b200 import _lib, ops
+    P, d, V = 3, 264, 4096 + 96              # 17 column tiles of 256: the last one ragged, V % 32 == 0
+    h, w_u, sid, cur, prev, plain, _ = _setup(P, d, V, 11, 30.0)
+    n = P * 128
+    lib = _lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    bufs, accs = {}, {}
+    for layout in (ops.LOGITS_ROW_MAJOR, ops.LOGITS_PROMPT_TILES):
+        c = ops.pick_chunks(n, V, 148, mode)
+        p = ops._alloc_partials(c, n, h.device)
+        buf = torch.full((n, V), float("nan"), dtype=torch.float32, device="cuda")
+        _lib.check(lib.tb_lens_dense_partials(h.data_ptr(), w_u.data_ptr(), n, d, V, 30.0, sid.data_ptr(), c, mode, p.pm.data_ptr(),
+                                              p.ps.data_ptr(), p.psec.data_ptr(), p.ptv.data_ptr(), p.pti.data_ptr(), buf.data_ptr(),
+                                              layout, st), "dense")
+        out = ops.lens_merge(p)
+        acc = torch.empty(P, V, dtype=torch.float32, device="cuda")
+        _lib.check(lib.tb_logits_ll_colsum(buf.data_ptr(), out.lse.data_ptr(), cur.data_ptr(), prev.data_ptr(), n, V, acc.data_ptr(),
+                                           layout, st), "colsum")
+        bufs[layout], accs[layout] = buf, acc
+        assert torch.equal(out.top_id, plain.top_id)
+    torch.cuda.synchronize()
+    tiles = bufs[ops.LOGITS_PROMPT_TILES].view(P, V // 32, 128, 32).permute(0, 2, 1, 3).reshape(n, V)
+    assert not torch.isnan(tiles).any()
+    ln2 = torch.tensor(0.6931471805599453, dtype=torch.float32, device="cuda")      # tiles are in log2 units
+    assert torch.equal(tiles * ln2, bufs[ops.LOGITS_ROW_MAJOR])
+    assert torch.allclose(accs[ops.LOGITS_PROMPT_TILES], accs[ops.LOGITS_ROW_MAJOR], rtol=1e-5, atol=1e-12)
+    scratch = torch.empty(n, V, dtype=torch.float32, device="cuda")
+    a = ops.lens_ll_from_logits(h, w_u, cur, prev, scratch, softcap=30.0, secret_id=sid, cta_pair=mode)
+    b = ops.lens_ll_from_logits(h, w_u, cur, prev, scratch, softcap=30.0, secret_id=sid, cta_pair=mode, row_major=True)
+    torch.cuda.synchronize()
+    assert torch.allclose(a[1], b[1], rtol=1e-5)
+    same = (a[2].sort(1).values == b[2].sort(1).values).all(1)
+    for q in torch.nonzero(~same).flatten().tolist():       # a tie at the k-th place to within rounding
+        assert abs(float(a[1][q, 9] - b[1][q, 9])) <= 1e-5 * float(b[1][q, 9])
+    with pytest.raises(ops.TabooKernelError):               # prompt tiles want whole prompts and V % 32 == 0
+        _lib.check(lib.tb_logits_ll_colsum(scratch.data_ptr(), a[0].lse.data_ptr(), None, None, n - 1, V, accs[0].data_ptr(),
+                                           ops.LOGITS_PROMPT_TILES, st), "colsum")
