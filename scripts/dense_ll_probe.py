@@ -68,6 +68,12 @@ for layout, name in ((ops.LOGITS_ROW_MAJOR, "row-major"), (ops.LOGITS_PROMPT_TIL
     ms, _ = timed(lambda: colsum(out, acc, layout))
     print(json.dumps({"piece": "column sums from logits", "layout": name, "ms": ms, "read_GBps": n * V * 4 / ms / 1e6}), flush=True)
     accs[name] = acc
+for skip, what in ((16, "staged in shared memory, TMA store not issued"), (32, "no staging, no store"),
+                   (64, "stores issued without waiting for the staging buffer (garbage out)")):
+    os.environ["TB_DEBUG_SKIP"] = str(skip)        # experiments only: where the store's cost sits
+    ms, _ = timed(lambda: dense(c0, ops.LOGITS_PROMPT_TILES))
+    print(json.dumps({"piece": "lens sweep + logits store", "layout": "prompt tiles", "experiment": what, "chunks": c0, "ms": ms}), flush=True)
+os.environ.pop("TB_DEBUG_SKIP")
 a, b = accs["row-major"], accs["prompt tiles"]
 rel = ((a - b).abs() / a.abs().clamp_min(1e-30)).max().item()
 print(json.dumps({"check": "column sums, prompt tiles vs row-major", "max_rel_diff": rel,

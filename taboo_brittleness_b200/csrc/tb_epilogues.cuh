@@ -903,8 +903,8 @@ struct LensDenseEpi {
       float cv[32];                      // capped once: the softcap is two MUFU ops a column, and MUFU bounds this epilogue
 #pragma unroll
       for (int j = 0; j < 32; ++j) cv[j] = cap2(__uint_as_float(v[j]));
-      if (p.tma) {
-        if (lane == 0) bulk_wait_read0();   // the TMA unit has read the previous piece out of the buffer
+      if (p.tma && !(g.debug_skip & 32)) {   // (debug_skip, experiments only: 32 = no staging and no store, 16 = staging, no store, 64 = no wait for the buffer)
+        if (lane == 0 && !(g.debug_skip & 64)) bulk_wait_read0();   // the TMA unit has read the previous piece out of the buffer
         __syncwarp();
         if (p.tma == 2) {                     // prompt tiles keep the kernel's log2 units (their one reader wants them)
 #pragma unroll
@@ -920,12 +920,12 @@ struct LensDenseEpi {
         }
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0 && col0 < g.N && row < g.M) {      // (lane 0 holds the warp's first row)
+        if (lane == 0 && col0 < g.N && row < g.M && !(g.debug_skip & 16)) {      // (lane 0 holds the warp's first row)
           if (p.tma == 2) tma_store_4d_hint(&p.tm_out, buf, 0, row & 127, col0 >> 5, row >> 7, evict_first);
           else tma_store_2d(&p.tm_out, buf, col0, row);
           bulk_commit();
         }
-      } else if (row < g.M) {
+      } else if (!p.tma && row < g.M) {
         float* o = p.out + static_cast<size_t>(row) * g.N + col0;
 #pragma unroll
         for (int j = 0; j < 32; ++j)
