@@ -74,6 +74,11 @@ for skip, what in ((16, "staged in shared memory, TMA store not issued"), (32, "
     ms, _ = timed(lambda: dense(c0, ops.LOGITS_PROMPT_TILES))
     print(json.dumps({"piece": "lens sweep + logits store", "layout": "prompt tiles", "experiment": what, "chunks": c0, "ms": ms}), flush=True)
 os.environ.pop("TB_DEBUG_SKIP")
+for pol in ("nl", "ln", "ll", "fl"):                # experiments only: L2 eviction policy of the (stationary, swept) operand loads
+    os.environ["TB_L2_POLICY"] = pol
+    ms, _ = timed(lambda: dense(c0, ops.LOGITS_PROMPT_TILES))
+    print(json.dumps({"piece": "lens sweep + logits store", "layout": "prompt tiles", "experiment": "TB_L2_POLICY=" + pol, "chunks": c0, "ms": ms}), flush=True)
+os.environ.pop("TB_L2_POLICY")
 a, b = accs["row-major"], accs["prompt tiles"]
 rel = ((a - b).abs() / a.abs().clamp_min(1e-30)).max().item()
 print(json.dumps({"check": "column sums, prompt tiles vs row-major", "max_rel_diff": rel,
