@@ -443,10 +443,86 @@ def leg_stress(args, ctx):
             "readout_checksum": {"mean_secret_prob": float(out["sec_mean"].item())}}
 
 
+def leg_rank_update(args, ctx):
+    """configs[1]'s nested budgets as RANK UPDATES of stored base logits
+    (InterventionEngine.targeted_budget_sweep_rank_update), beside the dense sweep of the same rows WITHOUT LL-Top-k
+    (the update path has lens readouts only). Not the reference's arithmetic -- the drift of every readout against
+    the dense sweep is part of the result. Every rank takes its own prompts (weak scaling)."""
+    import torch
+    from taboo_brittleness_b200 import synthetic
+    dev, rank, world, dist, eng = ctx["dev"], ctx["rank"], ctx["world"], ctx["dist"], ctx["eng"]
+    P = args.ru_prompts
+    n_rows = P * T
+    x = torch.empty(n_rows, D, dtype=torch.bfloat16, device=dev)
+    for p0 in range(0, P, 512):
+        p1 = min(P, p0 + 512)
+        x[p0 * T:p1 * T] = synthetic.make_residuals(p1 - p0, T, D, seed=synthetic.SEED_DATA + 777 + 1000 * rank + p0,
+                                                    device=str(dev)).to(torch.bfloat16)
+    sid = synthetic.make_secret_ids(P, T, V, seed=synthetic.SEED_DATA + 777 + rank).to(dev)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    Dm = eng.update_matrix()
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t0
+    out = {}
+    eng.targeted_budget_sweep_rank_update(x[:8 * T], sid[:8 * T], BUDGETS, split=args.ru_split)      # warm-up (and scratch)
+    eng.targeted_budget_sweep_rank_update(x, sid, BUDGETS[:1], split=args.ru_split)
+    eng.targeted_budget_sweep(x[:8 * T], T, sid[:8 * T], BUDGETS)
+    stats0 = eng.stats
+    from taboo_brittleness_b200 import interventions
+    eng.stats = interventions.SweepStats()
+    eng.time_lens = True
+    ms_ru = _leg_time(lambda: out.__setitem__("ru", eng.targeted_budget_sweep_rank_update(x, sid, BUDGETS, split=args.ru_split)),
+                      1, dev, world, dist)
+    eng.time_lens = False
+    base_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.lens_events)
+    base_flops = sum(f for _, _, f in eng.stats.lens_events)
+    upd_ms = sum(a.elapsed_time(b) for a, b, _ in eng.stats.ll_events)
+    upd_flops = sum(f for _, _, f in eng.stats.ll_events)
+    n_sub = max(1, len(eng.stats.lens_events))
+    per_budget = [sum(eng.stats.ll_events[i * len(BUDGETS) + j][0].elapsed_time(eng.stats.ll_events[i * len(BUDGETS) + j][1])
+                      for i in range(n_sub)) for j in range(len(BUDGETS))]
+    eng.stats = stats0
+    ms_dense = _leg_time(lambda: out.__setitem__("dense", eng.targeted_budget_sweep(x, T, sid, BUDGETS)), 1, dev, world, dist)
+    drift = {}
+    for b in BUDGETS:
+        r, dn = out["ru"][b], out["dense"][b]
+        drift[str(b)] = {"max_abs_dlse": float((r.lse - dn.lse).abs().max().item()),
+                         "max_abs_dsecret_prob": float((r.secret_prob - dn.secret_prob).abs().max().item()),
+                         "max_rel_dsecret_prob_where_p_gt_1e-3": float((((r.secret_prob - dn.secret_prob).abs() /
+                                                                        dn.secret_prob.clamp_min(1e-30)) *
+                                                                       (dn.secret_prob > 1e-3)).max().item()),
+                         "max_abs_dtop1_prob": float((r.top_prob[:, 0] - dn.top_prob[:, 0]).abs().max().item()),
+                         "top1_id_equal": float((r.top_id[:, 0] == dn.top_id[:, 0]).float().mean().item()),
+                         "top10_set_equal": float((r.top_id.sort(1).values == dn.top_id.sort(1).values).all(1).float().mean().item())}
+    conds = n_rows * len(BUDGETS) * world
+    return {"config": f"SURVEY 8 (f4): configs[1] budgets {list(BUDGETS)} as rank updates of stored base logits, {P} prompts x {T} "
+                      f"tok per GPU, lens readouts without LL-Top-k; beside it the dense sweep of the same rows (also without "
+                      f"LL-Top-k). D = (W_dec (1+w)) W_U^T ({Dm.numel() * 2 / 1e9:.1f} GB bf16) is computed once per weight set "
+                      f"outside the timed region ({setup_s:.2f} s, cuBLAS)",
+            "scaling": "weak", "n_gpus": world, "passes": 1, "unit": UNIT,
+            "value": conds / (ms_ru * 1e-3), "ms_per_pass": ms_ru,
+            "dense_sweep_same_rows": {"value": conds / (ms_dense * 1e-3), "ms_per_pass": ms_dense},
+            "speedup_over_dense": ms_dense / ms_ru,
+            "activation_remainders": bool(args.ru_split),
+            "not_the_reference_arithmetic": "the normalised residual is not rounded to bf16 per budget and D is a rounded "
+                                            "product: readouts drift (table below, against the dense sweep); reported beside "
+                                            "the dense line, never as tensor-pipe utilisation",
+            "phase_ms_this_rank": {"base_sweeps_with_store": base_ms, "updates_all_budgets": upd_ms,
+                                   "updates_per_budget": dict(zip([str(b) for b in BUDGETS], [round(v, 2) for v in per_budget])),
+                                   "rest (encode, target, rank lists, dense activations, K1b rstd x 11, merges)":
+                                       ms_ru - base_ms - upd_ms},
+            "flops_done": {"base_sweep_tflops": base_flops / max(base_ms, 1e-9) / 1e9,
+                           "update_tflops": upd_flops / max(upd_ms, 1e-9) / 1e9,
+                           "flops_per_row_all_budgets": (base_flops + upd_flops) / max(n_rows, 1),
+                           "dense_flops_per_row_all_budgets": len(BUDGETS) * FLOP_LENS},
+            "drift_vs_dense_this_rank": drift}
+
+
 def run_legs(args, ctx):
     import torch
     legs = {"projection_vocab_shard": leg_projection_vocab_shard, "random_control": leg_random_control,
-            "stress": leg_stress}
+            "stress": leg_stress, "rank_update": leg_rank_update}
     want = [w for w in args.workloads.split(",") if w]
     res = {}
     for name in want:
@@ -738,8 +814,10 @@ def main():
     ap.add_argument("--workload", default="targeted", choices=["targeted", "random-control", "projection-vocab-shard"],
                     help="targeted = BASELINE configs[1] (the headline); the others are configs[2] and configs[3]")
     ap.add_argument("--seeds", type=int, default=2, help="random-control: seeds per step (configs[2] has 32)")
-    ap.add_argument("--workloads", default="projection_vocab_shard,random_control,stress",
-                    help="comma-separated legs run after the headline region (BASELINE configs[3], [2], [4])")
+    ap.add_argument("--workloads", default="projection_vocab_shard,random_control,stress,rank_update",
+                    help="comma-separated legs run after the headline region (BASELINE configs[3], [2], [4]; SURVEY 8 f4)")
+    ap.add_argument("--ru-prompts", type=int, default=1024, help="rank_update leg: prompts per GPU")
+    ap.add_argument("--ru-split", action="store_true", help="rank_update leg: bf16 remainders of the activations as extra depth")
     ap.add_argument("--no-workloads", dest="workloads", action="store_const", const="")
     ap.add_argument("--leg-passes", type=int, default=2, help="timed passes of the projection_vocab_shard leg")
     ap.add_argument("--proj-prompts", type=int, default=2048, help="projection_vocab_shard leg: prompts (all on every rank)")

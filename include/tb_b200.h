@@ -121,7 +121,8 @@ int tb_sae_ablate_decode(const void* x_bf16, const int64_t* row_start, int cap,
  * out_val at the row's list position (same row_start / cap layout as idx / val, so the buffers have the same
  * size), their number into out_count. tb_sae_ablate_ranked then serves any budget: it reads the leading entries
  * with rank < budget (at most `budget`) and computes what tb_sae_ablate_decode computes in mode 0, the sum taken
- * in rank order. S <= 2^20. No code in the reference.
+ * in rank order. S <= 2^20. out_rstd (nullable, f32 [n_rows]): the final RMSNorm's 1 / sqrt(mean(x'^2) + eps) of the
+ * rounded x' -- all the rank-update lens (tb_lens_rank_update_partials) needs of a budget. No code in the reference.
  */
 int tb_sae_rank_lists(const int64_t* row_start, int cap, const int32_t* count, const int32_t* idx,
                       const float* val, const uint16_t* rank, int rank_rows, int64_t n_rows, int S,
@@ -129,7 +130,7 @@ int tb_sae_rank_lists(const int64_t* row_start, int cap, const int32_t* count, c
 int tb_sae_ablate_ranked(const void* x_bf16, const int64_t* row_start, int cap, const int32_t* sel_count,
                          const int32_t* sel_key, const float* sel_val, const void* w_dec_bf16, int budget,
                          int64_t n_rows, int d, const float* w_norm, float eps, void* out_x_bf16,
-                         void* out_h_bf16, void* stream);
+                         void* out_h_bf16, float* out_rstd, void* stream);
 
 /* ---- K2: low-rank direction removal x' = x - (x U) U^T ----------------------------------
  * No code in the reference (Execution Plan:148 r_edited = r - P_U(r); random control :150).
@@ -258,12 +259,35 @@ int tb_lowrank_remove_fused(const void* x_bf16, const void* ut_bf16, int r, int6
  * writes either layout through the TMA unit (row-major with V % 4 != 0: plain stores). */
 #define TB_LOGITS_ROW_MAJOR 0
 #define TB_LOGITS_PROMPT_TILES 1
+#define TB_LOGITS_PROMPT_TILES_RAW 2 /* prompt tiles holding the RAW products h W_U^T (no soft cap, natural units), no
+                                        readout written (pm .. pti may be NULL): the base logits of the rank-update lens */
 int tb_lens_dense_partials(const void* h_bf16, const void* w_u_bf16, int64_t n_rows, int d, int V, float softcap,
                            const int32_t* secret_id, int n_chunks, int cta_pair, float* pm, float* ps, float* psec,
                            float* ptv, int32_t* pti, float* logits_out, int layout, void* stream);
 int tb_logits_ll_colsum(const float* logits, const float* lse, const int32_t* cur_id, const int32_t* prev_id,
                         int64_t n_rows, int V, float* acc, int layout, void* stream);
 int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V, void* stream);
+
+/* ---- nested budgets as rank updates of stored base logits (budgets of Execution Plan:126) -----------
+ * For the error-term ablation the lens logits of budget m are rstd_m[t] * (L0[t, v] - sum_{rank(j) < m} a_j[t] D[j, v]) with
+ * L0 = (x (.) (1 + w)) W_U^T and D = (W_dec (.) (1 + w)) W_U^T [S, V] (bf16, computed once per weight set by the caller).
+ * Per row sub-batch of whole prompts:
+ *   tb_scale_cols(x, w_norm) -> xw = bf16(x (.) (1 + w));  tb_lens_dense_partials(xw, W_U, ..., l0, TB_LOGITS_PROMPT_TILES_RAW);
+ *   tb_rank_acts_dense: the rank-ordered lists of tb_sae_rank_lists as a dense matrix acts bf16 [n_rows, a_cols]:
+ *     column r = the activation of the prompt's rank-r latent (a_cols a multiple of 64, >= 1024; lo_off != 0: the bf16
+ *     remainders a - bf16(a) in column lo_off + r, which halves the rounding of the activations for twice the depth);
+ *   per budget: tb_sae_ablate_ranked(..., out_rstd) and tb_lens_rank_update_partials: same partial layout as
+ *     tb_lens_partials with 2 partials per (chunk, row) -> tb_lens_merge. rank_ids i32 [n_rows / 128, rank_stride]: the
+ *     latent id of each rank of each prompt (tb_topm_select's ids).
+ * Not the arithmetic of the reference path (no bf16 rounding of the normalised residual per budget, D is a rounded
+ * product): drift against the dense kernels is reported in DESIGN.md; no code in the reference. */
+int tb_scale_cols(const void* x_bf16, const float* w_norm, int64_t n_rows, int d, void* out_bf16, void* stream);
+int tb_rank_acts_dense(const int64_t* row_start, int cap, const int32_t* sel_count, const int32_t* sel_key,
+                       const float* sel_val, int64_t n_rows, int a_cols, int lo_off, void* out_bf16, void* stream);
+int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
+                                 const void* d_bf16, const float* l0_tiles, const float* rstd, int64_t n_rows, int V,
+                                 int budget, float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps,
+                                 float* psec, float* ptv, int32_t* pti, void* stream);
 
 /* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------
  * Same readouts as K3 (tb_lens_partials) and K5, for a condition whose rows' logsumexp is

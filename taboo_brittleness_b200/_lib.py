@@ -48,7 +48,7 @@ SIGNATURES = {
     "tb_sae_ablate_decode": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int,
                                      c_int64, c_int, c_int, _P, c_float, _P, _P, _P]),
     "tb_sae_rank_lists": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P]),
-    "tb_sae_ablate_ranked": (c_int, [_P, _P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
+    "tb_sae_ablate_ranked": (c_int, [_P, _P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P, _P]),
     "tb_lowrank_remove": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
     "tb_lowrank_tc_scratch_bytes": (c_int64, [c_int64, c_int, c_int]),
     "tb_lowrank_remove_tc": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, c_int64, _P, _P, _P]),
@@ -58,6 +58,10 @@ SIGNATURES = {
     "tb_lens_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_int, c_float, _P, c_int, c_int,
                                  _P, _P, _P, _P, _P, _P]),
     "tb_lens_dense_partials": (c_int, [_P, _P, c_int64, c_int, c_int, c_float, _P, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, _P]),
+    "tb_scale_cols": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
+    "tb_rank_acts_dense": (c_int, [_P, c_int, _P, _P, _P, c_int64, c_int, c_int, _P, _P]),
+    "tb_lens_rank_update_partials": (c_int, [_P, c_int, c_int, _P, c_int, _P, _P, _P, c_int64, c_int, c_int, c_float, _P, c_int,
+                                             _P, _P, _P, _P, _P, _P]),
     "tb_logits_ll_colsum": (c_int, [_P, _P, _P, _P, c_int64, c_int, _P, c_int, _P]),
     "tb_probs_from_logits": (c_int, [_P, _P, c_int64, c_int, _P]),
     "tb_lens_merge": (c_int, [_P, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P,

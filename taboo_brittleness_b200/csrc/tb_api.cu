@@ -16,6 +16,7 @@
 #include "tb_rows.cuh"
 #include "tb_cluster_rows.cuh"
 #include "tb_ranked.cuh"
+#include "tb_rankupdate.cuh"
 
 // Progress counters of the soft lockstep between clusters (tb_gemm.cuh): a few rotating slots of
 // 64 counters, so that launches in flight on different streams do not share one.
@@ -105,6 +106,26 @@ int make_tmap(CUtensorMap* map, const void* base, int64_t rows, int K, int box_r
   if (r != CUDA_SUCCESS)
     return fail(TB_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld K=%d box_rows=%d)",
                 static_cast<int>(r), static_cast<long long>(rows), K, box_rows);
+  return TB_OK;
+}
+
+// fp32 logits in prompt tiles [n_rows / 128][V / 32][128 rows][32 ids] as a 4-d map (id in tile, row in prompt, tile,
+// prompt), box = one warp's [32 rows x 32 ids], 128-byte swizzle
+int make_tile_map(CUtensorMap* map, const float* base, int64_t n_rows, int V) {
+  EncodeTiledFn enc;
+  int rc = get_encode_fn(&enc);
+  if (rc != TB_OK) return rc;
+  const cuuint64_t n_ct = static_cast<cuuint64_t>(V / 32);
+  cuuint64_t dims[4] = {32, 128, n_ct, static_cast<cuuint64_t>(n_rows / 128)};
+  cuuint64_t strides[3] = {128, 128ull * 128, 128ull * 128 * n_ct};
+  cuuint32_t box[4] = {32, 32, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return fail(TB_ERR_CUDA, "cuTensorMapEncodeTiled (prompt tiles) failed with CUresult %d (rows=%lld V=%d)", static_cast<int>(r),
+                static_cast<long long>(n_rows), V);
   return TB_OK;
 }
 
@@ -645,13 +666,14 @@ int tb_sae_rank_lists(const int64_t* row_start, int cap, const int32_t* count, c
 
 int tb_sae_ablate_ranked(const void* x, const int64_t* row_start, int cap, const int32_t* sel_count,
                          const int32_t* sel_key, const float* sel_val, const void* w_dec, int budget, int64_t n_rows,
-                         int d, const float* w_norm, float eps, void* out_x, void* out_h, void* stream) {
+                         int d, const float* w_norm, float eps, void* out_x, void* out_h, float* out_rstd,
+                         void* stream) {
   DevInfo di;
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
   if (!x || !sel_count || !sel_key || !sel_val || !w_dec) return fail(TB_ERR_INVALID, "null pointer");
   if (budget < 0 || budget > tb::kRankedMax) return fail(TB_ERR_INVALID, "budget %d outside [0, %d]", budget, tb::kRankedMax);
-  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (!out_x && !out_h && !out_rstd) return fail(TB_ERR_INVALID, "no output requested");
   if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
   if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
   if (n_rows == 0) return TB_OK;
@@ -677,6 +699,7 @@ int tb_sae_ablate_ranked(const void* x, const int64_t* row_start, int cap, const
   a.eps = eps;
   a.out_x = static_cast<__nv_bfloat16*>(out_x);
   a.out_h = static_cast<__nv_bfloat16*>(out_h);
+  a.out_rstd = out_rstd;
   a.n_rows = static_cast<int>(n_rows);
   a.d = d;
   const int64_t blocks = (n_rows + tb::kRowGroups - 1) / tb::kRowGroups;
@@ -1073,9 +1096,10 @@ int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d
   if (rc != TB_OK) return rc;
   rc = check_gemm_operands(h, w_u, n_rows, V, d);
   if (rc != TB_OK) return rc;
-  if (!pm || !ps || !psec || !ptv || !pti || !logits_out) return fail(TB_ERR_INVALID, "null buffer");
-  if (layout != TB_LOGITS_ROW_MAJOR && layout != TB_LOGITS_PROMPT_TILES) return fail(TB_ERR_INVALID, "layout=%d", layout);
-  if (layout == TB_LOGITS_PROMPT_TILES && (V % 32 != 0 || n_rows % tb::kLlSlots != 0))
+  const bool raw = layout == TB_LOGITS_PROMPT_TILES_RAW;
+  if (!logits_out || (!raw && (!pm || !ps || !psec || !ptv || !pti))) return fail(TB_ERR_INVALID, "null buffer");
+  if (layout != TB_LOGITS_ROW_MAJOR && layout != TB_LOGITS_PROMPT_TILES && !raw) return fail(TB_ERR_INVALID, "layout=%d", layout);
+  if (layout != TB_LOGITS_ROW_MAJOR && (V % 32 != 0 || n_rows % tb::kLlSlots != 0))
     return fail(TB_ERR_INVALID, "prompt tiles need V %% 32 == 0 and whole prompts of %d rows (V=%d, n_rows=%lld)", tb::kLlSlots, V,
                 static_cast<long long>(n_rows));
   if (reinterpret_cast<uintptr_t>(logits_out) & 15) return fail(TB_ERR_INVALID, "logits_out must be 16-byte aligned");
@@ -1091,7 +1115,7 @@ int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d
   tb::LensDenseEpi::Params ep;
   memset(&ep.tm_out, 0, sizeof(ep.tm_out));
   static const bool direct = getenv("TB_DENSE_DIRECT_STORE") != nullptr;   // experiments: plain stores from the row owners
-  ep.tma = layout == TB_LOGITS_PROMPT_TILES ? 2 : (V % 4 == 0 && !direct) ? 1 : 0;   // a tensor map wants a 16-byte row pitch
+  ep.tma = raw ? 3 : layout == TB_LOGITS_PROMPT_TILES ? 2 : (V % 4 == 0 && !direct) ? 1 : 0;   // a tensor map wants a 16-byte row pitch
   if (ep.tma) {                            // box = one warp's [32 rows x 32 columns] fp32, 128-byte swizzle
     EncodeTiledFn enc;
     rc = get_encode_fn(&enc);
@@ -1102,11 +1126,11 @@ int tb_lens_dense_partials(const void* h, const void* w_u, int64_t n_rows, int d
     cuuint64_t strides[3] = {static_cast<cuuint64_t>(V) * 4, 0, 0};
     cuuint32_t box[4] = {32, 32, 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
-    if (ep.tma == 2) {
+    if (ep.tma >= 2) {
       dims[0] = 32; dims[1] = tb::kLlSlots; dims[2] = n_ct; dims[3] = static_cast<cuuint64_t>(n_rows / tb::kLlSlots);
       strides[0] = 128; strides[1] = 128ull * tb::kLlSlots; strides[2] = strides[1] * n_ct;
     }
-    CUresult r = enc(&ep.tm_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, ep.tma == 2 ? 4 : 2, logits_out, dims, strides, box, estr,
+    CUresult r = enc(&ep.tm_out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, ep.tma >= 2 ? 4 : 2, logits_out, dims, strides, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS)
@@ -1148,6 +1172,104 @@ int tb_logits_ll_colsum(const float* logits, const float* lse, const int32_t* cu
   }
   dim3 grid(static_cast<unsigned>((V + 1023) / 1024), static_cast<unsigned>(n_prompts), 1);     // 4 columns per thread
   tb::tb_logits_ll_colsum_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(logits, lse, cur_id, prev_id, n_rows, V, acc);
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_scale_cols(const void* x, const float* w, int64_t n_rows, int d, void* out, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!x || !w || !out) return fail(TB_ERR_INVALID, "null pointer");
+  if (n_rows < 0 || d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "bad shape (d must be a multiple of 8)");
+  if (n_rows == 0) return TB_OK;
+  const int64_t n_vec = n_rows * (d / 8);
+  const int64_t want = (n_vec + 255) / 256, cap = static_cast<int64_t>(di.sms) * 16;
+  tb::tb_scale_cols_kernel<<<static_cast<unsigned>(want < cap ? want : cap), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const __nv_bfloat16*>(x), w, n_vec, d / 8, static_cast<__nv_bfloat16*>(out));
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_rank_acts_dense(const int64_t* row_start, int cap, const int32_t* sel_count, const int32_t* sel_key,
+                       const float* sel_val, int64_t n_rows, int a_cols, int lo_off, void* out_bf16, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!sel_count || !sel_key || !sel_val || !out_bf16) return fail(TB_ERR_INVALID, "null pointer");
+  if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (a_cols % 64 != 0 || a_cols < tb::kRankedMax || (lo_off != 0 && (lo_off < tb::kRankedMax || lo_off + tb::kRankedMax > a_cols)))
+    return fail(TB_ERR_INVALID, "a_cols=%d lo_off=%d: need a multiple of 64 >= %d, remainders inside", a_cols, lo_off, tb::kRankedMax);
+  if (n_rows < 0) return fail(TB_ERR_INVALID, "bad shape");
+  if (n_rows == 0) return TB_OK;
+  tb::tb_rank_acts_dense_kernel<<<static_cast<unsigned>((n_rows + 7) / 8), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      row_start, cap, sel_count, sel_key, sel_val, n_rows, a_cols, lo_off, static_cast<__nv_bfloat16*>(out_bf16));
+  TB_CUDA(cudaGetLastError());
+  return TB_OK;
+}
+
+int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
+                                 const void* d_bf16, const float* l0_tiles, const float* rstd, int64_t n_rows, int V, int budget,
+                                 float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps, float* psec,
+                                 float* ptv, int32_t* pti, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!acts_bf16 || !rank_ids || !d_bf16 || !l0_tiles || !rstd || !pm || !ps || !psec || !ptv || !pti)
+    return fail(TB_ERR_INVALID, "null pointer");
+  if (n_rows <= 0 || n_rows % tb::kLlSlots != 0 || V % 32 != 0 || V <= 0)
+    return fail(TB_ERR_INVALID, "whole prompts of %d rows and V %% 32 == 0 (n_rows=%lld, V=%d)", tb::kLlSlots,
+                static_cast<long long>(n_rows), V);
+  if (budget < 1 || budget > tb::kRankedMax || rank_stride < budget) return fail(TB_ERR_INVALID, "budget %d / rank_stride %d", budget, rank_stride);
+  if (a_cols % 64 != 0 || a_cols < tb::kRankedMax || (lo_off != 0 && lo_off + tb::kRankedMax > a_cols))
+    return fail(TB_ERR_INVALID, "a_cols=%d lo_off=%d", a_cols, lo_off);
+  if ((reinterpret_cast<uintptr_t>(acts_bf16) | reinterpret_cast<uintptr_t>(d_bf16) | reinterpret_cast<uintptr_t>(l0_tiles)) & 15)
+    return fail(TB_ERR_INVALID, "operands must be 16-byte aligned");
+  tb::RankUpdateArgs a;
+  a.n_prompts = static_cast<int>(n_rows / tb::kLlSlots);
+  a.V = V;
+  a.n_tiles = (V + 255) / 256;
+  if (n_chunks < 1 || n_chunks > a.n_tiles) return fail(TB_ERR_INVALID, "n_chunks=%d", n_chunks);
+  a.tiles_per_chunk = (a.n_tiles + n_chunks - 1) / n_chunks;
+  if ((a.n_tiles + a.tiles_per_chunk - 1) / a.tiles_per_chunk != n_chunks)
+    return fail(TB_ERR_INVALID, "n_chunks=%d does not divide %d tiles into non-empty chunks", n_chunks, a.n_tiles);
+  a.n_chunks = n_chunks;
+  a.m = budget;
+  a.n_slabs = (budget + tb::kRuSlabK - 1) / tb::kRuSlabK;
+  a.parts = lo_off > 0 ? 2 : 1;
+  a.a_lo_off = lo_off;
+  a.rank_ids = rank_ids;
+  a.rank_stride = rank_stride;
+  a.D = static_cast<const __nv_bfloat16*>(d_bf16);
+  a.rstd = rstd;
+  {
+    const char* dbg = getenv("TB_RU_DEBUG");
+    a.debug = dbg ? atoi(dbg) : 0;
+  }
+  tb::LensEpi::Params lens;
+  lens.secret_id = secret_id;
+  lens.vocab_offset = 0;
+  lens.softcap = softcap;
+  lens.pm = pm; lens.ps = ps; lens.psec = psec; lens.ptv = ptv; lens.pti = pti;
+  CUtensorMap tmA, tmL0;
+  rc = make_tmap(&tmA, acts_bf16, n_rows, a_cols, 128);
+  if (rc != TB_OK) return rc;
+  rc = make_tile_map(&tmL0, l0_tiles, n_rows, V);
+  if (rc != TB_OK) return rc;
+  const int units = a.n_prompts * a.n_chunks;
+  const unsigned grid = static_cast<unsigned>(units < di.sms ? units : di.sms);
+  static const char* force = getenv("TB_RU_CONFIG");      // experiments: "3" = three stages + two L0 buffers for every budget
+  if (a.n_slabs * a.parts <= 2 && !(force && force[0] == '3')) {
+    auto k = tb::tb_rank_update_lens_kernel<2, 4>;
+    constexpr int smem = tb::RuCfg<2, 4>::kSmemBytes;
+    TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    k<<<grid, tb::kRuThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
+  } else {
+    auto k = tb::tb_rank_update_lens_kernel<3, 2>;
+    constexpr int smem = tb::RuCfg<3, 2>::kSmemBytes;
+    TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    k<<<grid, tb::kRuThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
+  }
   TB_CUDA(cudaGetLastError());
   return TB_OK;
 }

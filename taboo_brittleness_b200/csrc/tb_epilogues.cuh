@@ -875,7 +875,9 @@ struct LensDenseEpi {
   static constexpr int kExtraSmem = kEpiWarps * kStageBytes + 1024;  // + slack: swizzled boxes start on 1024 bytes
   struct Params {
     CUtensorMap tm_out;  // out through the TMA unit, box [32 rows x 32 columns] fp32, SWIZZLE_128B (valid when tma != 0):
-                         // tma 1: 2-d map of the row-major array; tma 2: 4-d map (column, row in prompt, column tile, prompt)
+                         // tma 1: 2-d map of the row-major array; tma 2: 4-d map (column, row in prompt, column tile, prompt);
+                         // tma 3: the same 4-d map, but the RAW accumulator is stored and no readout is produced (the base
+                         // logits of tb_rank_update_lens_kernel)
     LensEpi::Params lens;
     float* out;          // soft-capped logits, fp32: [M, N] row-major in natural-log units, or with tma == 2 in prompt tiles
                          // [M / 128][N / 32][128 rows][32 columns] in LOG2 units (x log2 e; what
@@ -900,6 +902,21 @@ struct LensDenseEpi {
       uint32_t v[32];
       tmem_ld_32x32(taddr + cc * 32, v);
       tmem_ld_wait();
+      if (p.tma == 3) {                  // base logits of the rank-update lens: the accumulator as it is, no readout
+        if (lane == 0) bulk_wait_read0();
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(buf + lane * 128 + ((q ^ (lane & 7)) << 4)),
+                       "r"(v[4 * q]), "r"(v[4 * q + 1]), "r"(v[4 * q + 2]), "r"(v[4 * q + 3]) : "memory");
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0 && col0 < g.N && row < g.M) {
+          tma_store_4d_hint(&p.tm_out, buf, 0, row & 127, col0 >> 5, row >> 7, evict_first);
+          bulk_commit();
+        }
+        continue;
+      }
       float cv[32];                      // capped once: the softcap is two MUFU ops a column, and MUFU bounds this epilogue
 #pragma unroll
       for (int j = 0; j < 32; ++j) cv[j] = cap2(__uint_as_float(v[j]));
@@ -937,7 +954,7 @@ struct LensDenseEpi {
   __device__ __forceinline__ static void end_unit_tile(State& st, const Params& p, const GemmArgs& g,
                                                        const SweepCtx& c, int row) {
     if (p.tma && (c.tid & 31) == 0) bulk_wait0();     // this unit's logits are written
-    LensEpi::end_unit(st, p.lens, g, row, c.chunk * 2 + c.half);
+    if (p.tma != 3) LensEpi::end_unit(st, p.lens, g, row, c.chunk * 2 + c.half);
   }
 };
 

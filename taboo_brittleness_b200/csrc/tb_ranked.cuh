@@ -92,6 +92,7 @@ struct AblateRankedArgs {
   float eps;
   __nv_bfloat16* out_x;        // nullable
   __nv_bfloat16* out_h;        // nullable
+  float* out_rstd;             // nullable, [n_rows]: the RMSNorm's 1 / sqrt(mean(x'^2) + eps) of the rounded x' (rank-update lens)
   int n_rows, d;
 };
 
@@ -169,13 +170,14 @@ __global__ void __launch_bounds__(kAblThreads, (NV <= 4 ? 2 : 1)) tb_ablate_rank
         for (int e = 0; e < 8; ++e) ss = fmaf(acc[q][e], acc[q][e], ss);
       }
     }
-    if (a.out_h) {
+    if (a.out_h || a.out_rstd) {
       ss = group_sum(ss, s_red[group], group, gwarp, lane);
       const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, static_cast<float>(a.d)), a.eps)));
+      if (a.out_rstd && gt == 0) a.out_rstd[row] = rstd;
 #pragma unroll
       for (int q = 0; q < NV; ++q) {
         const int vec = gt + q * kRowGroupThreads;
-        if (vec < nvec) {
+        if (a.out_h && vec < nvec) {
           const float4 w0 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec);
           const float4 w1 = __ldg(reinterpret_cast<const float4*>(a.w_norm) + 2 * vec + 1);
           const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
@@ -285,7 +287,9 @@ __global__ void __launch_bounds__(kHeavyThreads) tb_ablate_heavy_kernel(const Ab
           unpack8(p, xb[q]);
         }
       }
-      if (a.out_h) rmsnorm_store<NV>(xb, a.w_norm, a.d, a.eps, a.out_h + static_cast<size_t>(row) * a.d, s_red);
+      if (a.out_h || a.out_rstd)
+        rmsnorm_store<NV>(xb, a.w_norm, a.d, a.eps, a.out_h ? a.out_h + static_cast<size_t>(row) * a.d : nullptr, s_red,
+                          a.out_rstd ? a.out_rstd + row : nullptr);
     }
   }
   (void)lane; (void)warp;

@@ -61,7 +61,7 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 template <int NV>
 __device__ __forceinline__ void rmsnorm_store(const float (&xb)[NV][8], const float* __restrict__ w,
                                               int d, float eps, __nv_bfloat16* __restrict__ out_h,
-                                              float* red) {
+                                              float* red, float* out_rstd = nullptr) {
   const int nvec = d >> 3;
   float ss = 0.0f;
 #pragma unroll
@@ -74,6 +74,8 @@ __device__ __forceinline__ void rmsnorm_store(const float (&xb)[NV][8], const fl
   }
   ss = block_sum(ss, red);
   const float rstd = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(ss, static_cast<float>(d)), eps)));
+  if (out_rstd && threadIdx.x == 0) *out_rstd = rstd;
+  if (out_h == nullptr) return;
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
     const int vec = threadIdx.x + i * blockDim.x;

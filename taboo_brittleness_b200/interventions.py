@@ -92,6 +92,7 @@ class InterventionEngine:
         self.ll_dense_first = True
         self.ll_dense_rows = 65536
         self._dense_logits = None
+        self._update_matrix = None
         self.use_ranked = True       # nested budgets read prefixes of rank-ordered lists (ops.rank_lists) in K1b
         self.ll_alpha = 0.5          # candidate threshold = ll_alpha * previous condition's k-th best sum
         self.ll_cand_cap = 256       # candidate slots per prompt
@@ -167,8 +168,9 @@ class InterventionEngine:
         return Readout(out, val, ids), LLState(out.lse, theta)
 
     def release_scratch(self) -> None:
-        """Drop the logits scratch of ``read_dense_ll`` (tens of GB)."""
+        """Drop the logits scratch of ``read_dense_ll`` (tens of GB) and the rank-update matrix."""
         self._dense_logits = None
+        self._update_matrix = None
 
     def read_dense_ll(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], ll: LLSpec) -> Readout:
         """Lens readout + exact LL-Top-k of a condition with no predecessor, one GEMM sweep (see ``ll_dense_first``)."""
@@ -404,6 +406,72 @@ class InterventionEngine:
         acts = self.encode(x)
         _, _, rank = self.targeted_rank(acts, rows_per_prompt, m=min(max(budgets), TB_TOPM_MAX))
         return self._nested_budgets(x, acts, rank, rows_per_prompt, budgets, secret_id, mode, ll)[0]
+
+    def update_matrix(self) -> torch.Tensor:
+        """D = (W_dec (.) (1 + w)) W_U^T, bf16 [S, V], computed on first use and kept (8.4 GB for Gemma-2 / 16k)."""
+        if self._update_matrix is None:
+            self._update_matrix = ops.lens_update_matrix(self.sae, self.lens)
+        return self._update_matrix
+
+    def targeted_budget_sweep_rank_update(self, x: torch.Tensor, secret_id: Optional[torch.Tensor],
+                                          budgets: Sequence[int] = DEFAULT_BUDGETS, *, split: bool = False,
+                                          sub_rows: int = 65536) -> Dict[int, ops.LensReadout]:
+        """configs[1] with the nested budgets as RANK UPDATES of stored base logits: per row sub-batch one
+        sweep of L0 = (x (.) (1 + w)) W_U^T, then per budget rstd_m * (L0 - A_m D[ids]) with a product of depth m instead
+        of d. Error-term ablation, 128 rows per prompt, single shard, lens readouts only (no LL-Top-k). NOT the
+        arithmetic of the reference path -- the normalised residual is not rounded to bf16 per budget and D is a
+        rounded product -- so this is a workload of its own, reported beside the dense sweep."""
+        T = ops.LL_SLOTS
+        n, V = x.shape[0], self.lens.w_u.shape[0]
+        if n % T or self.lens.vocab_offset != 0 or V % 32:
+            raise ops.TabooKernelError("rank-update sweep: whole prompts of 128 rows, unsharded vocabulary, V % 32 == 0",
+                                       ops._lib.TB_ERR_INVALID)
+        bs = sorted(int(v) for v in budgets)
+        D = self.update_matrix()
+        acts = self.encode(x)
+        ids, _, rank = self.targeted_rank(acts, T, m=min(max(bs), TB_TOPM_MAX))
+        ranked = ops.rank_lists(acts, rank, T)
+        A = ops.rank_acts_dense(ranked, n, split)
+        rstd = torch.empty(len(bs), n, dtype=torch.float32, device=x.device)
+        for i, b in enumerate(bs):      # K1b without an output row: only the RMSNorm factor of the rounded x'
+            ops.sae_ablate_ranked(x, ranked, self.sae, b, w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False,
+                                  want_h=False, out_rstd=rstd[i])
+        self.stats.launches += 3 + len(bs)
+        step = max(T, min(sub_rows, n) // T * T)
+        free = torch.cuda.mem_get_info(x.device)[0]
+        have = 0 if self._dense_logits is None else self._dense_logits.numel() * 4
+        while step > 8 * T and step * V * 4 > have + 0.8 * free:
+            step = step // 2 // T * T
+        if self._dense_logits is None or self._dense_logits.numel() < step * V:
+            self._dense_logits = None
+            self._dense_logits = torch.empty(step, V, dtype=torch.float32, device=x.device)
+        l0 = self._dense_logits
+        outs = {b: [] for b in bs}
+        for r0 in range(0, n, step):
+            r1 = min(n, r0 + step)
+            xw = ops.scale_cols(x[r0:r1], self.lens.w_norm)
+            if self.time_lens:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            ops.lens_base_logits(xw, self.lens.w_u, l0, cta_pair=self.cta_pair)
+            if self.time_lens:
+                e1.record()
+                self.stats.lens_events.append((e0, e1, 2.0 * (r1 - r0) * x.shape[1] * V))
+            for i, b in enumerate(bs):
+                if self.time_lens:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                o = ops.lens_rank_update(A[r0:r1], ids[r0 // T:r1 // T], D, l0, rstd[i, r0:r1], b, softcap=self.softcap,
+                                         secret_id=None if secret_id is None else secret_id[r0:r1])
+                if self.time_lens:
+                    e1.record()      # FLOPs actually done: depth = the budget rounded up to 64 (x 2 with remainders)
+                    depth = -(-b // 64) * 64 * (2 if split else 1)
+                    self.stats.ll_events.append((e0, e1, 2.0 * (r1 - r0) * depth * V))
+                outs[b].append(o)
+            self.stats.launches += 2 + 2 * len(bs)
+        cat = lambda xs, f: torch.cat([getattr(o, f) for o in xs])      # noqa: E731
+        return {b: ops.LensReadout(lse=cat(v, "lse"), secret_prob=cat(v, "secret_prob"), top_prob=cat(v, "top_prob"),
+                                   top_id=cat(v, "top_id")) for b, v in outs.items()}
 
     def random_budget_sweep(self, x: torch.Tensor, secret_id, budgets: Sequence[int] = DEFAULT_BUDGETS,
                             seeds: Iterable[int] = range(32), mode: str = "error",

@@ -369,18 +369,24 @@ def rank_lists(acts: SparseActs, rank: torch.Tensor, rank_rows: int = 0) -> Rank
 
 def sae_ablate_ranked(x: torch.Tensor, ranked: RankedActs, sae: SaeWeights, budget: int, *,
                       w_norm: Optional[torch.Tensor] = None, eps: float = GEMMA2_EPS, want_x: bool = True,
-                      want_h: bool = False) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
+                      want_h: bool = False, out_rstd: Optional[torch.Tensor] = None
+                      ) -> Tuple[Optional[torch.Tensor], Optional[torch.Tensor]]:
     """x' = x - sum over the row's active latents with rank < budget of a_i W_dec[i] (the error-term form of
-    ``sae_ablate_decode``), from rank-ordered lists: a budget reads only its prefix."""
+    ``sae_ablate_decode``), from rank-ordered lists: a budget reads only its prefix. ``out_rstd`` (f32 [rows]) receives
+    the final RMSNorm's 1 / sqrt(mean(x'^2) + eps) of the rounded x'."""
     _need(x, torch.bfloat16, "x", 2)
     n, d = x.shape
     out_x = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_x else None
     out_h = torch.empty(n, d, dtype=torch.bfloat16, device=x.device) if want_h else None
+    if out_rstd is not None:
+        _need(out_rstd, torch.float32, "out_rstd", 1)
+        if out_rstd.shape[0] != n:
+            raise TabooKernelError("out_rstd must hold one value per row", _lib.TB_ERR_INVALID)
     if n == 0:
         return out_x, out_h
     check(_lib.load().tb_sae_ablate_ranked(_ptr(x), _ptr(ranked.row_start), ranked.cap, _ptr(ranked.count), _ptr(ranked.key),
                                            _ptr(ranked.val), _ptr(sae.w_dec), int(budget), n, d, _ptr(w_norm), eps,
-                                           _ptr(out_x), _ptr(out_h), _stream()), "tb_sae_ablate_ranked")
+                                           _ptr(out_x), _ptr(out_h), _ptr(out_rstd), _stream()), "tb_sae_ablate_ranked")
     return out_x, out_h
 
 
@@ -717,6 +723,84 @@ def lens_ll_from_logits(h: torch.Tensor, w_u: torch.Tensor, cur_id: Optional[tor
                                   _stream()), "tb_logits_ll_colsum")
     ids, sums, _ = topm_select(acc, k, want_rank=False)
     return out, sums, ids
+
+
+# ------------------------------------------------------------------------------------------
+# nested budgets as rank updates of stored base logits (tb_b200.h, "rank updates")
+# ------------------------------------------------------------------------------------------
+LOGITS_PROMPT_TILES_RAW = 2
+RANKED_MAX = TB_TOPM_MAX
+
+
+def scale_cols(x: torch.Tensor, w_norm: torch.Tensor) -> torch.Tensor:
+    """bf16(x * (1 + w)): the operand of the base sweep L0 = (x (.) (1 + w)) W_U^T."""
+    _need(x, torch.bfloat16, "x", 2)
+    _need(w_norm, torch.float32, "w_norm", 1)
+    out = torch.empty_like(x)
+    if x.shape[0]:
+        check(_lib.load().tb_scale_cols(_ptr(x), _ptr(w_norm), x.shape[0], x.shape[1], _ptr(out), _stream()), "tb_scale_cols")
+    return out
+
+
+def lens_update_matrix(sae: SaeWeights, lens: LensWeights) -> torch.Tensor:
+    """D = (W_dec (.) (1 + w)) W_U^T, bf16 [S, V]: once per weight set (a plain library GEMM, not part of any timed step)."""
+    wd = (sae.w_dec.float() * (1.0 + lens.w_norm.float())[None]).to(torch.bfloat16)
+    return torch.matmul(wd, lens.w_u.t()).contiguous()
+
+
+def rank_acts_dense(ranked: RankedActs, n_rows: int, split: bool = False) -> torch.Tensor:
+    """The rank-ordered lists as a dense bf16 matrix [rows, 1024 (+ 1024 remainders)]: column r = the activation of the
+    prompt's rank-r latent."""
+    cols = RANKED_MAX * (2 if split else 1)
+    out = torch.empty(n_rows, cols, dtype=torch.bfloat16, device=ranked.count.device)
+    if n_rows:
+        check(_lib.load().tb_rank_acts_dense(_ptr(ranked.row_start), ranked.cap, _ptr(ranked.count), _ptr(ranked.key),
+                                             _ptr(ranked.val), n_rows, cols, RANKED_MAX if split else 0, _ptr(out), _stream()),
+              "tb_rank_acts_dense")
+    return out
+
+
+def lens_base_logits(xw: torch.Tensor, w_u: torch.Tensor, l0: torch.Tensor, cta_pair=5) -> None:
+    """L0 = xw W_U^T (raw products, f32) into ``l0`` (>= rows * V floats) in prompt tiles, one sweep, no readout."""
+    _need(xw, torch.bfloat16, "xw", 2)
+    _need(w_u, torch.bfloat16, "w_u", 2)
+    n, d = xw.shape
+    V = w_u.shape[0]
+    if l0.dtype != torch.float32 or l0.numel() < n * V or not l0.is_cuda:
+        raise TabooKernelError("l0 scratch too small", _lib.TB_ERR_INVALID)
+    n_chunks = pick_chunks(n, V, torch.cuda.get_device_properties(xw.device).multi_processor_count, cta_pair)
+    check(_lib.load().tb_lens_dense_partials(_ptr(xw), _ptr(w_u), n, d, V, 0.0, None, n_chunks, _mode(cta_pair), None, None, None,
+                                             None, None, _ptr(l0), LOGITS_PROMPT_TILES_RAW, _stream()), "tb_lens_dense_partials")
+
+
+def lens_rank_update(acts_dense: torch.Tensor, rank_ids: torch.Tensor, D: torch.Tensor, l0: torch.Tensor, rstd: torch.Tensor,
+                     budget: int, *, softcap: float = 0.0, secret_id: Optional[torch.Tensor] = None,
+                     n_chunks: Optional[int] = None) -> "LensReadout":
+    """Lens readout of one budget from the base logits: rstd * (L0 - acts[:, :budget] D[rank_ids[:budget]]) per prompt."""
+    _need(acts_dense, torch.bfloat16, "acts_dense", 2)
+    _need(rank_ids, torch.int32, "rank_ids", 2)
+    _need(D, torch.bfloat16, "D", 2)
+    _need(rstd, torch.float32, "rstd", 1)
+    n, cols = acts_dense.shape
+    V = D.shape[1]
+    if secret_id is not None:
+        _need(secret_id, torch.int32, "secret_id", 1)
+    if rank_ids.shape[0] * LL_SLOTS != n or rstd.shape[0] != n or l0.numel() < n * V:
+        raise TabooKernelError("rank_ids / rstd / l0 do not match the rows", _lib.TB_ERR_INVALID)
+    n_tiles = -(-V // BLOCK_N)
+    sms = torch.cuda.get_device_properties(acts_dense.device).multi_processor_count
+    if n_chunks is None:       # a dozen (prompt, chunk) units per SM: little tail waste, chunks still hundreds of tiles long
+        n_chunks = max(1, min(max(1, n_tiles // 8), -(-12 * sms // max(1, n // LL_SLOTS))))
+    n_chunks = max(1, min(n_chunks, n_tiles))
+    while -(-n_tiles // -(-n_tiles // n_chunks)) != n_chunks:
+        n_chunks -= 1
+    p = _alloc_partials(n_chunks, n, acts_dense.device)
+    check(_lib.load().tb_lens_rank_update_partials(_ptr(acts_dense), cols, RANKED_MAX if cols > RANKED_MAX else 0, _ptr(rank_ids),
+                                                   rank_ids.shape[1], _ptr(D), _ptr(l0), _ptr(rstd), n, V, int(budget),
+                                                   float(softcap or 0.0), _ptr(secret_id), n_chunks, _ptr(p.pm), _ptr(p.ps),
+                                                   _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _stream()),
+          "tb_lens_rank_update_partials")
+    return lens_merge(p, finalize=True)
 
 
 def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,

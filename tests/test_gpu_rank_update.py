@@ -1,0 +1,132 @@
+"""Nested budgets as rank updates of stored base logits (InterventionEngine.targeted_budget_sweep_rank_update)
+against the oracle's whole path and against the dense sweep of the same engine. The arithmetic differs from the
+reference path by design (no bf16 rounding of the normalised residual per budget, D is a rounded product): the
+tolerances here are the measured drift of that change (a logit moves by ~1e-2, at worst 4e-2; a probability by as much of itself), wider
+than north_star's 1e-3 on large probabilities -- which is why the dense sweep stays the product path."""
+import pytest
+import torch
+
+from _common import BF16, cuda_bf16, oracle, sae_to_cuda, synthetic, topk_sets_match
+
+pytestmark = pytest.mark.gpu
+
+P, T, D, S, V = 5, 128, 512, 2048, 4096 + 96      # 17 column tiles of 256, the last one ragged; V % 32 == 0
+BUDGETS = [1, 8, 100, 256, 1024]                   # one slab, a budget that is no multiple of 64, several slabs
+
+
+@pytest.fixture(scope="module")
+def setup(cuda_lib):
+    from taboo_brittleness_b200 import interventions, ops
+    x = synthetic.make_residuals(P, T, D, seed=41)
+    sae = synthetic.make_sae(D, S, seed=41, target_l0=60.0)
+    lens = synthetic.make_lens(D, V, seed=41)
+    sid = synthetic.make_secret_ids(P, T, V, seed=41)
+    synthetic.plant_secret_direction(lens, x, sid)
+    eng = interventions.InterventionEngine(sae_to_cuda(sae), ops.LensWeights(lens.w_norm.cuda(), cuda_bf16(lens.W_U)),
+                                           softcap=30.0)
+    return dict(x=x, sae=sae, lens=lens, sid=sid, eng=eng)
+
+
+def test_pieces_rstd_dense_acts_and_base_logits(setup):
+    """The three inputs of the update kernel: K1b's out_rstd is the RMSNorm factor of its own x', the dense activation
+    matrix holds the rank-ordered lists, the raw base logits in prompt tiles are the plain product."""
+    from taboo_brittleness_b200 import ops
+    eng, x = setup["eng"], cuda_bf16(setup["x"])
+    acts = eng.encode(x)
+    ids, _, rank = eng.targeted_rank(acts, T, m=1024)
+    ranked = ops.rank_lists(acts, rank, T)
+    rstd = torch.empty(P * T, dtype=torch.float32, device="cuda")
+    x1, _ = ops.sae_ablate_ranked(x, ranked, eng.sae, 100, w_norm=eng.lens.w_norm, want_x=True, want_h=False, out_rstd=rstd)
+    ref = torch.rsqrt(x1.float().pow(2).mean(1) + 1e-6)
+    assert torch.allclose(rstd, ref, rtol=2e-6)
+    only = torch.empty_like(rstd)
+    ops.sae_ablate_ranked(x, ranked, eng.sae, 100, w_norm=eng.lens.w_norm, want_x=False, want_h=False, out_rstd=only)
+    assert torch.equal(only, rstd)
+    A = ops.rank_acts_dense(ranked, P * T, split=True)
+    torch.cuda.synchronize()
+    assert A.shape == (P * T, 2048)
+    cnt, key, val = ranked.count.cpu(), ranked.key.cpu(), ranked.val.cpu()
+    dense = torch.zeros(P * T, 1024)
+    for r in range(P * T):
+        base = r * ranked.cap if ranked.row_start is None else int(ranked.row_start[r])
+        k = key[base:base + int(cnt[r])]
+        dense[r, (k >> 20).long()] = val[base:base + int(cnt[r])]
+    hi = dense.to(torch.bfloat16)
+    assert torch.equal(A[:, :1024].cpu(), hi)
+    assert torch.equal(A[:, 1024:].cpu(), (dense - hi.float()).to(torch.bfloat16))
+    xw = ops.scale_cols(x, eng.lens.w_norm)
+    assert torch.equal(xw, (x.float() * (1.0 + eng.lens.w_norm)[None]).to(torch.bfloat16))
+    l0 = torch.full((P * T * V,), float("nan"), dtype=torch.float32, device="cuda")
+    ops.lens_base_logits(xw, eng.lens.w_u, l0)
+    torch.cuda.synchronize()
+    got = l0.view(P, V // 32, 128, 32).permute(0, 2, 1, 3).reshape(P * T, V)
+    want = xw.float() @ eng.lens.w_u.float().t()
+    assert not torch.isnan(got).any()
+    assert (got - want).abs().max().item() <= 2e-3 * want.abs().max().item()
+
+
+@pytest.mark.parametrize("split", [False, True])
+def test_update_kernel_is_exact_for_its_own_arithmetic(setup, split):
+    """tb_lens_rank_update_partials against plain fp32 torch on the SAME rounded operands (xw, A, D, rstd): this pins the
+    gather, the MN-major operand layout, the zero-fill beyond the budget and the L0 pieces; the drift test below then
+    measures only what the change of arithmetic costs."""
+    from taboo_brittleness_b200 import ops
+    eng, sid = setup["eng"], setup["sid"].cuda()
+    x = cuda_bf16(setup["x"])
+    n = P * T
+    acts = eng.encode(x)
+    ids, _, rank = eng.targeted_rank(acts, T, m=1024)
+    ranked = ops.rank_lists(acts, rank, T)
+    A = ops.rank_acts_dense(ranked, n, split)
+    Dm = eng.update_matrix()
+    xw = ops.scale_cols(x, eng.lens.w_norm)
+    l0 = torch.empty(n * V, dtype=torch.float32, device="cuda")
+    ops.lens_base_logits(xw, eng.lens.w_u, l0)
+    L0 = xw.float() @ eng.lens.w_u.float().t()
+    for b in (1, 100, 1024):
+        rstd = torch.empty(n, dtype=torch.float32, device="cuda")
+        ops.sae_ablate_ranked(x, ranked, eng.sae, b, w_norm=eng.lens.w_norm, want_x=False, want_h=False, out_rstd=rstd)
+        out = ops.lens_rank_update(A, ids, Dm, l0, rstd, b, softcap=30.0, secret_id=sid)
+        torch.cuda.synchronize()
+        a_eff = A[:, :b].float() + (A[:, 1024:1024 + b].float() if split else 0.0)
+        U = torch.cat([a_eff[p * T:(p + 1) * T] @ Dm[ids[p, :b].long()].float() for p in range(P)])
+        logits = 30.0 * torch.tanh(rstd[:, None] * (L0 - U) / 30.0)
+        lse = torch.logsumexp(logits, 1)
+        assert (out.lse - lse).abs().max().item() <= 2e-4
+        sec = torch.exp(logits.gather(1, sid.long()[:, None])[:, 0] - lse)
+        assert ((out.secret_prob - sec).abs() <= 1e-6 + 1e-3 * sec).all()
+        assert (out.top_id[:, 0] == logits.argmax(1)).float().mean().item() >= 0.995
+
+
+@pytest.mark.parametrize("split", [False, True])
+def test_rank_update_sweep_against_oracle_and_dense_sweep(setup, split):
+    eng, x, sae, lens, sid = (setup[k] for k in ("eng", "x", "sae", "lens", "sid"))
+    xd = cuda_bf16(x)
+    res = eng.targeted_budget_sweep_rank_update(xd, sid.cuda(), BUDGETS, split=split, sub_rows=3 * T)   # two sub-batches
+    dense = eng.targeted_budget_sweep(xd, T, sid.cuda(), BUDGETS)
+    torch.cuda.synchronize()
+    acts = oracle.jumprelu_encode(x, sae.W_enc, sae.b_enc, sae.threshold)
+    a_dev = eng.encode(xd)
+    ids, _, _ = eng.targeted_rank(a_dev, T, m=1024)
+    ids = ids.cpu().long()
+    for b in BUDGETS:
+        x1 = torch.cat([oracle.ablate_decode(x[p * T:(p + 1) * T], acts[p * T:(p + 1) * T], ids[p, :b], sae.W_dec, sae.b_dec,
+                                             "error", residual_dtype=BF16) for p in range(P)])
+        probs = oracle.lens_probs(x1, lens.w_norm, lens.W_U, 30.0, residual_dtype=BF16)
+        r, dn = res[b], dense[b]
+        # the update path keeps the normalised residual in fp32 where the reference (and the oracle) round it to bf16 per
+        # budget: a logit moves by ~1e-2, a probability by ~1 % of itself -- DESIGN.md section 3 has the drift table
+        ref_sec = oracle.secret_prob(probs, sid)
+        err = (r.secret_prob.cpu() - ref_sec).abs()
+        assert (err <= 2e-4 + 0.15 * ref_sec).all(), float(err.max())
+        assert (r.lse - dn.lse).abs().max().item() <= 0.15       # (a <bos>-scale row with a planted, near-certain token)
+        assert ((r.secret_prob - dn.secret_prob).abs() <= 2e-4 + 0.15 * dn.secret_prob).all()
+        assert (r.top_id[:, 0] == dn.top_id[:, 0]).float().mean().item() >= 0.97
+        top10 = probs.topk(10, 1).indices
+        inter = (r.top_id.cpu()[:, :, None] == top10[:, None, :]).any(2).float().sum(1)       # ids shared with the oracle's top-10
+        assert inter.mean().item() >= 9.5 and inter.min().item() >= 8
+    if split:      # remainders of the activations included: closer to the single-rounding result, never further from the dense one
+        plain = eng.targeted_budget_sweep_rank_update(xd, sid.cuda(), BUDGETS, split=False, sub_rows=P * T)
+        torch.cuda.synchronize()
+        for b in BUDGETS:
+            assert (res[b].lse - plain[b].lse).abs().max().item() <= 2e-2
