@@ -277,13 +277,14 @@ int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V,
  *     column r = the activation of the prompt's rank-r latent (a_cols a multiple of 64, >= 1024; lo_off != 0: the bf16
  *     remainders a - bf16(a) in column lo_off + r, which halves the rounding of the activations for twice the depth);
  *   per budget: tb_sae_ablate_ranked(..., out_rstd) and tb_lens_rank_update_partials: same partial layout as
- *     tb_lens_partials with 2 partials per (chunk, row) -> tb_lens_merge. rank_ids i32 [n_rows / 128, rank_stride]: the
+ *     tb_lens_partials with tb_lens_rank_update_parts(budget, lo_off) partials per (chunk, row) -> tb_lens_merge. rank_ids i32 [n_rows / 128, rank_stride]: the
  *     latent id of each rank of each prompt (tb_topm_select's ids).
  * Not the arithmetic of the reference path (no bf16 rounding of the normalised residual per budget, D is a rounded
  * product): drift against the dense kernels is reported in DESIGN.md; no code in the reference. */
 int tb_scale_cols(const void* x_bf16, const float* w_norm, int64_t n_rows, int d, void* out_bf16, void* stream);
 int tb_rank_acts_dense(const int64_t* row_start, int cap, const int32_t* sel_count, const int32_t* sel_key,
                        const float* sel_val, int64_t n_rows, int a_cols, int lo_off, void* out_bf16, void* stream);
+int tb_lens_rank_update_parts(int budget, int lo_off);   /* partials per (chunk, row) the next call writes: 2 or 4 */
 int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
                                  const void* d_bf16, const float* l0_tiles, const float* rstd, int64_t n_rows, int V,
                                  int budget, float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps,

@@ -11,3 +11,4 @@ print(json.dumps({k: v for k, v in w.items() if k not in ("drift_vs_dense_this_r
 for b, d in w.get("drift_vs_dense_this_rank", {}).items():
     print(b, {k: round(v, 5) for k, v in d.items()})
 PY
+for cfg in 8 16; do echo "TB_RU_CONFIG=$cfg"; TB_RU_CONFIG=$cfg timeout 600 python scripts/rank_update_probe.py --prompts 512 2>&1 | sed -n 2p | cut -c1-700; done

@@ -1208,6 +1208,18 @@ int tb_rank_acts_dense(const int64_t* row_start, int cap, const int32_t* sel_cou
   return TB_OK;
 }
 
+// 16 epilogue warps (4 partials per chunk and row) for budgets of up to eight slabs per tile, 8 (2 partials) beyond;
+// TB_RU_CONFIG=8 / 16 forces one of them (experiments)
+static int ru_variant(int budget, int lo_off) {
+  const char* force = getenv("TB_RU_CONFIG");
+  if (force && atoi(force) == 8) return 8;
+  if (force && atoi(force) == 16) return 16;
+  const int slabs = (budget + tb::kRuSlabK - 1) / tb::kRuSlabK * (lo_off > 0 ? 2 : 1);
+  return slabs <= 8 ? 16 : 8;      // measured at 65,536 rows: 256: 27 vs 43 ms, 512: 47 vs 48, 1024: 84 vs 65
+}
+
+int tb_lens_rank_update_parts(int budget, int lo_off) { return ru_variant(budget, lo_off) / 4; }
+
 int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
                                  const void* d_bf16, const float* l0_tiles, const float* rstd, int64_t n_rows, int V, int budget,
                                  float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps, float* psec,
@@ -1258,17 +1270,17 @@ int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, 
   if (rc != TB_OK) return rc;
   const int units = a.n_prompts * a.n_chunks;
   const unsigned grid = static_cast<unsigned>(units < di.sms ? units : di.sms);
-  static const char* force = getenv("TB_RU_CONFIG");      // experiments: "3" = three stages + two L0 buffers for every budget
-  if (a.n_slabs * a.parts <= 2 && !(force && force[0] == '3')) {
-    auto k = tb::tb_rank_update_lens_kernel<2, 4>;
-    constexpr int smem = tb::RuCfg<2, 4>::kSmemBytes;
-    TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    k<<<grid, tb::kRuThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
+  const int variant = ru_variant(budget, lo_off);
+  if (variant == 16) {
+    auto k = tb::tb_rank_update_lens_kernel<2, 2, 16>;
+    using Cfg = tb::RuCfg<2, 2, 16>;
+    TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    k<<<grid, Cfg::kThreads, Cfg::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
   } else {
-    auto k = tb::tb_rank_update_lens_kernel<3, 2>;
-    constexpr int smem = tb::RuCfg<3, 2>::kSmemBytes;
-    TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    k<<<grid, tb::kRuThreads, smem, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
+    auto k = tb::tb_rank_update_lens_kernel<3, 2, 8>;
+    using Cfg = tb::RuCfg<3, 2, 8>;
+    TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
+    k<<<grid, Cfg::kThreads, Cfg::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
   }
   TB_CUDA(cudaGetLastError());
   return TB_OK;

@@ -106,14 +106,19 @@ struct LensEpi {
   // The same with the soft-capped logits (log2 units) already in hand.
   __device__ __forceinline__ static void process_capped(State& st, const Params& p, const GemmArgs& g,
                                                         float (&c)[32], int col0) {
-    if (col0 + 32 > g.N) {  // ragged last tile: columns past N hold zero-filled garbage
+    process_capped_w<32>(st, p, g, c, col0);
+  }
+  template <int W>
+  __device__ __forceinline__ static void process_capped_w(State& st, const Params& p, const GemmArgs& g,
+                                                          float (&c)[W], int col0) {
+    if (col0 + W > g.N) {  // ragged last tile: columns past N hold zero-filled garbage
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
+      for (int j = 0; j < W; ++j)
         if (col0 + j >= g.N) c[j] = -CUDART_INF_F;
     }
     float cmax = c[0];
 #pragma unroll
-    for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, c[j]);
+    for (int j = 1; j < W; ++j) cmax = fmaxf(cmax, c[j]);
 
     // online logsumexp (base 2), rescaled at most once per 32 columns
     if (cmax > st.m) {
@@ -123,7 +128,7 @@ struct LensEpi {
     if (st.m > -CUDART_INF_F) {
       float acc0 = 0.0f, acc1 = 0.0f;
 #pragma unroll
-      for (int j = 0; j < 32; j += 2) {
+      for (int j = 0; j < W; j += 2) {
         acc0 += ex2_approx(c[j] - st.m);
         acc1 += ex2_approx(c[j + 1] - st.m);
       }
@@ -133,15 +138,15 @@ struct LensEpi {
     // running top-10 (strict '>' keeps the lowest column among equal values)
     if (cmax > st.tv[kTopK - 1]) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
+      for (int j = 0; j < W; ++j)
         if (c[j] > st.tv[kTopK - 1]) insert(st, c[j], p.vocab_offset + col0 + j);
     }
 
     // secret-token logit
     const uint32_t rel = static_cast<uint32_t>(st.sid - col0);
-    if (rel < 32u) {
+    if (rel < static_cast<uint32_t>(W)) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j)
+      for (int j = 0; j < W; ++j)
         if (rel == static_cast<uint32_t>(j)) st.sec = c[j];
     }
   }
@@ -534,7 +539,6 @@ struct LensLLEpi {
     float* tr = reinterpret_cast<float*>(assume_shared(c.extra) + kOffTr) + (c.half * 4 + quad) * (32 * kTrStride);
     float* cs = reinterpret_cast<float*>(assume_shared(c.extra) + kOffCs) + parity * (4 * 256);
     const CapLog2 cap2(p.lens.softcap);
-    const uint64_t evict_first = l2_policy_evict_first();   // the tiled array is tens of GB, read back once by another kernel
 #pragma unroll 1
     for (int cc = c.half * 4; cc < c.half * 4 + 4; ++cc) {
       const int col0 = nt * kBlockN + cc * 32;

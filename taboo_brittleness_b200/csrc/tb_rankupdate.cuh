@@ -15,7 +15,8 @@
 //     16-byte cp.async straight into the 128-byte-swizzled layout the UMMA descriptor expects (one warp instruction
 //     = one latent's 512 bytes); rows at or beyond the budget are zero-filled, so one A matrix serves all budgets;
 //   accumulator U in TMEM (two tiles in flight); the epilogue warps fetch their [32 rows x 32 ids] piece of L0 with a
-//     TMA load of their own (4 KB, double-buffered), form rstd * (L0 - U) and hand it to the lens readout epilogue.
+//     TMA load of their own (4 KB, double-buffered), form rstd * (L0 - U) and hand it to the lens readout epilogue
+//     (LensEpi's state and arithmetic; 2 or 4 partials per (chunk, row): tb_lens_rank_update_parts).
 // All CTAs work on the same vocabulary chunk at the same time (unit = chunk * prompts + prompt), so a tile's slab of
 // D (8 MB for 16384 latents) is served from L2.
 //
@@ -33,21 +34,29 @@ constexpr int kRuBGroupBytes = kRuSlabK * 128;           // 8 KB: 64 k-rows x 64
 constexpr int kRuBBytes = 4 * kRuBGroupBytes;            // 32 KB: four column groups = 256 ids
 constexpr int kRuStageBytes = kRuABytes + kRuBBytes;
 constexpr int kRuL0Bytes = 32 * 128;                     // one epilogue warp's [32 rows x 32 ids] fp32 piece
-// Two things must be in flight per SM: gathered rows of D (from L2) and pieces of L0 (from HBM, ~2 us away; one 4 KB
-// piece per epilogue warp in flight caps the L0 stream at ~2.4 TB/s for the whole GPU -- measured: 38 ms per budget and
-// sub-batch whatever the depth). Shared memory holds kStages operand stages and kNB L0 buffers per epilogue warp:
-// <2, 4> for budgets of up to two slabs per tile (three L0 pieces in flight per warp), <3, 2> beyond (the gather is
-// what needs the depth there).
-template <int kStages, int kNB>
+// What bounds the kernel (profiles/r02ru_update_kernel_what_bounds_it.log, 65,536 rows, budgets <= 128): not the L0
+// stream (deeper prefetch changes nothing), not the gather, but the readout arithmetic of eight epilogue warps -- two
+// per scheduler, each a chain of TMEM load -> soft cap -> max / exp-sum / top-10 with little to overlap: 23 of 37 ms.
+// Hence kEW = 16 epilogue warps: four per TMEM lane quadrant, each owning 64 of a tile's 256 ids (two L0 pieces, worked
+// through in 16-id steps to stay inside 96 registers): 37.5 -> 20 ms per budget. That leaves room for two operand
+// stages; budget 1024 (16 slabs per tile, 768 KB of A and D rows from L2 per tile: bound by the gather) keeps eight
+// epilogue warps, three stages and four gather warps (65 vs 84 ms).
+template <int kStages, int kNB, int kEW>
 struct RuCfg {
+  static constexpr int kGatherWarps = kEW == 16 ? 2 : 4;
+  static constexpr int kGatherWarp0 = kEW == 16 ? 2 : 4;
+  static constexpr int kEpiWarp0 = kEW == 16 ? 4 : 8;     // a multiple of 4: warp % 4 is the TMEM lane quadrant
+  static constexpr int kAllocWarp = kEW == 16 ? 0 : 2;
+  static constexpr int kThreads = 32 * (kEpiWarp0 + kEW);
+  static constexpr int kColGroups = kEW / 4;              // column groups of a tile, one partial each
+  static constexpr int kColsPerWarp = 256 / kColGroups;   // 128 or 64 ids of every tile
+  static constexpr int kPiecesPerTile = kColsPerWarp / 32;
   static constexpr int kOffL0 = kStages * kRuStageBytes;
-  static constexpr int kOffBars = kOffL0 + 8 * kNB * kRuL0Bytes;
+  static constexpr int kOffBars = kOffL0 + kEW * kNB * kRuL0Bytes;
   static constexpr int kSmemBytes = kOffBars + 512 + 1024;    // + barriers + alignment slack
   static_assert(kSmemBytes <= 232448, "shared memory");
-  static_assert(2 * kStages + 4 + 8 * kNB + 1 <= 64, "barrier block");
+  static_assert(2 * kStages + 4 + kEW * kNB + 1 <= 64, "barrier block");
 };
-constexpr int kRuThreads = 16 * 32;                      // warp 0 A loads, 1 MMA, 2 TMEM, 3 idle, 4-7 gather, 8-15 epilogue
-constexpr int kRuGatherWarps = 4;
 
 struct RankUpdateArgs {
   int n_prompts;               // rows = 128 * n_prompts
@@ -112,22 +121,23 @@ __global__ void __launch_bounds__(256) tb_scale_cols_kernel(const __nv_bfloat16*
   }
 }
 
-template <int kRuStages, int kNB>
-__global__ void __launch_bounds__(kRuThreads, 1)
+template <int kRuStages, int kNB, int kEW>
+__global__ void __launch_bounds__((RuCfg<kRuStages, kNB, kEW>::kThreads), 1)
 tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmL0,
                            const RankUpdateArgs a, const LensEpi::Params lens) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const uint32_t smem0 = smem_u32(smem);
-  using Cfg = RuCfg<kRuStages, kNB>;
+  using Cfg = RuCfg<kRuStages, kNB, kEW>;
   constexpr int kRuOffL0 = Cfg::kOffL0;
+  constexpr int kRuGatherWarps = Cfg::kGatherWarps;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Cfg::kOffBars);
   uint64_t* full_bar = bars;                       // [stages] A bytes (TMA) + one arrive per gather warp
   uint64_t* empty_bar = bars + kRuStages;          // [stages] MMA commit
   uint64_t* tfull_bar = bars + 2 * kRuStages;      // [2]
   uint64_t* tempty_bar = bars + 2 * kRuStages + 2; // [2] one arrive per epilogue warp
-  uint64_t* l0_bar = bars + 2 * kRuStages + 4;     // [8 warps][kNB]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kRuStages + 4 + 8 * kNB);
+  uint64_t* l0_bar = bars + 2 * kRuStages + 4;     // [kEW warps][kNB]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kRuStages + 4 + kEW * kNB);
 
   const int warp = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
   const int lane = static_cast<int>(threadIdx.x & 31);
@@ -143,12 +153,13 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tfull_bar[i]), 1);
-      mbar_init(smem_u32(&tempty_bar[i]), 8);
+      mbar_init(smem_u32(&tempty_bar[i]), kEW);
     }
-    for (int i = 0; i < 8 * kNB; ++i) mbar_init(smem_u32(&l0_bar[i]), 1);
+    for (int i = 0; i < kEW * kNB; ++i) mbar_init(smem_u32(&l0_bar[i]), 1);
     fence_mbar_init();
   }
-  if (warp == 2) tmem_alloc<1>(smem_u32(tmem_slot), 512);
+  __syncwarp();
+  if (warp == Cfg::kAllocWarp) tmem_alloc<1>(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -211,9 +222,10 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         }
       }
     }
-  } else if (warp >= 4 && warp < 4 + kRuGatherWarps) {
+  } else if (warp >= Cfg::kGatherWarp0 && warp < Cfg::kGatherWarp0 + kRuGatherWarps) {
     // ================================ B gather (cp.async) ================================
-    const int pw = warp - 4;
+    const int pw = warp - Cfg::kGatherWarp0;
+    constexpr int kRowsPerWarp = kRuSlabK / kRuGatherWarps;   // 16 or 32 k-rows of every slab
     uint32_t it = 0;
     int prev_stage = -1;
     for (int unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
@@ -226,16 +238,16 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         for (int s = 0; s < slabs_per_tile; ++s, ++it) {
           const uint32_t stage = it % kRuStages, ph = (it / kRuStages) & 1u;
           const int sl = s % a.n_slabs;
-          // ids of my 16 rows of the slab (rows pw, pw + 4, ...): lane jj fetches row jj's
+          // ids of my rows of the slab (rows pw, pw + kRuGatherWarps, ...): lane jj fetches row jj's
           int my_id = 0;
           {
-            const int r = sl * kRuSlabK + (lane & 15) * kRuGatherWarps + pw;
-            if (lane < 16 && r < a.m) my_id = __ldg(ids + r);
+            const int r = sl * kRuSlabK + (lane % kRowsPerWarp) * kRuGatherWarps + pw;
+            if (lane < kRowsPerWarp && r < a.m) my_id = __ldg(ids + r);
           }
           mbar_wait(smem_u32(&empty_bar[stage]), ph ^ 1u);
           const uint32_t sb = smem0 + stage * kRuStageBytes + kRuABytes + (lane >> 3) * kRuBGroupBytes;
 #pragma unroll 4
-          for (int jj = 0; jj < kRuSlabK / kRuGatherWarps; ++jj) {
+          for (int jj = 0; jj < kRowsPerWarp; ++jj) {
             const int j = jj * kRuGatherWarps + pw;           // k-row of the slab
             const int id = __shfl_sync(0xffffffffu, my_id, jj);
             const bool ok = (sl * kRuSlabK + j < a.m) && col_ok && !(a.debug & 2);
@@ -259,9 +271,11 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&full_bar[prev_stage]));
     }
-  } else if (warp >= 8) {
+  } else if (warp >= Cfg::kEpiWarp0) {
     // ================================ epilogue ================================
-    const int ew = warp - 8, quad = warp & 3, half = ew >> 2;
+    const int ew = warp - Cfg::kEpiWarp0, quad = warp & 3, cg = ew >> 2;   // cg: which column group of every tile
+    constexpr int kPPT = Cfg::kPiecesPerTile;
+    const int col_base = cg * Cfg::kColsPerWarp;
     const int row_in_blk = quad * 32 + lane;
     const uint32_t lane_base = static_cast<uint32_t>(quad * 32) << 16;
     const uint32_t l0_buf = smem0 + kRuOffL0 + ew * kNB * kRuL0Bytes;
@@ -277,12 +291,12 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
       decode(unit, prompt, chunk, t0, t1);
       const int row = prompt * 128 + row_in_blk;
       const float rs = __ldg(a.rstd + row);
-      LensEpi::begin_unit(st, lens, g, row, chunk * 2 + half);
-      const int n_pieces = (t1 - t0) * 4;
-      // piece q of the unit: tile t0 + q / 4, columns half * 128 + (q % 4) * 32 of it
+      LensEpi::begin_unit(st, lens, g, row, chunk * Cfg::kColGroups + cg);
+      const int n_pieces = (t1 - t0) * kPPT;
+      // piece q of the unit: tile t0 + q / kPPT, columns col_base + (q % kPPT) * 32 of it
       auto request = [&](int q, uint32_t slot) {
         if (lane == 0 && !(a.debug & 1)) {
-          const int c32 = ((t0 + (q >> 2)) * 256 + half * 128 + (q & 3) * 32) >> 5;
+          const int c32 = ((t0 + q / kPPT) * 256 + col_base + (q % kPPT) * 32) >> 5;
           mbar_arrive_expect_tx(l0_b0 + slot * 8, kRuL0Bytes);
           tma_load_4d(l0_buf + slot * kRuL0Bytes, &tmL0, l0_b0 + slot * 8, 0, quad * 32, c32, prompt);
         }
@@ -295,45 +309,74 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         mbar_wait(smem_u32(&tfull_bar[acc]), (acc_it >> 1) & 1u);
         tc_fence_after();
 #pragma unroll 1
-        for (int cq = 0; cq < 4; ++cq, ++pc) {
-          const int q = (nt - t0) * 4 + cq;
+        for (int cq = 0; cq < kPPT; ++cq, ++pc) {
+          const int q = (nt - t0) * kPPT + cq;
           const uint32_t slot = pc % kNB;
           __syncwarp();                                       // everybody is done with the buffer of the piece before this one
           if (q + kNB - 1 < n_pieces) request(q + kNB - 1, (pc + kNB - 1) % kNB);
-          const int col0 = nt * 256 + half * 128 + cq * 32;
-          uint32_t v[32];
-          tmem_ld_32x32(tmem_base + lane_base + acc * 256 + half * 128 + cq * 32, v);
-          if (!(a.debug & 1)) mbar_wait(l0_b0 + slot * 8, (pc / kNB) & 1u);
-          tmem_ld_wait();
-          float c[32];
+          const int col0 = nt * 256 + col_base + cq * 32;
+          const uint32_t taddr = tmem_base + lane_base + acc * 256 + col_base + cq * 32;
+          const uint32_t l0_row = l0_buf + slot * kRuL0Bytes + lane * 128;
+          if constexpr (kEW == 16) {
+#pragma unroll 1
+            for (int hf = 0; hf < 2; ++hf) {                  // 16 ids at a time: 96 registers per thread
+              uint32_t v[16];
+              tmem_ld_32x16(taddr + hf * 16, v);
+              if (hf == 0 && !(a.debug & 1)) mbar_wait(l0_b0 + slot * 8, (pc / kNB) & 1u);
+              tmem_ld_wait();
+              float c[16];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            float4 l0;
-            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                         : "=f"(l0.x), "=f"(l0.y), "=f"(l0.z), "=f"(l0.w)
-                         : "r"(l0_buf + slot * kRuL0Bytes + lane * 128 + ((k ^ (lane & 7)) << 4)));
-            c[4 * k] = cap2(rs * (l0.x - __uint_as_float(v[4 * k])));
-            c[4 * k + 1] = cap2(rs * (l0.y - __uint_as_float(v[4 * k + 1])));
-            c[4 * k + 2] = cap2(rs * (l0.z - __uint_as_float(v[4 * k + 2])));
-            c[4 * k + 3] = cap2(rs * (l0.w - __uint_as_float(v[4 * k + 3])));
-          }
-          if (!(a.debug & 4)) LensEpi::process_capped(st, lens, g, c, col0);
-          else {
+              for (int k = 0; k < 4; ++k) {
+                float4 l0;
+                asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                             : "=f"(l0.x), "=f"(l0.y), "=f"(l0.z), "=f"(l0.w)
+                             : "r"(l0_row + (((hf * 4 + k) ^ (lane & 7)) << 4)));
+                c[4 * k] = cap2(rs * (l0.x - __uint_as_float(v[4 * k])));
+                c[4 * k + 1] = cap2(rs * (l0.y - __uint_as_float(v[4 * k + 1])));
+                c[4 * k + 2] = cap2(rs * (l0.z - __uint_as_float(v[4 * k + 2])));
+                c[4 * k + 3] = cap2(rs * (l0.w - __uint_as_float(v[4 * k + 3])));
+              }
+              if (!(a.debug & 4)) LensEpi::process_capped_w<16>(st, lens, g, c, col0 + hf * 16);
+              else {
 #pragma unroll
-            for (int k = 0; k < 32; ++k) st.s += c[k];
+                for (int k = 0; k < 16; ++k) st.s += c[k];
+              }
+            }
+          } else {
+            uint32_t v[32];
+            tmem_ld_32x32(taddr, v);
+            if (!(a.debug & 1)) mbar_wait(l0_b0 + slot * 8, (pc / kNB) & 1u);
+            tmem_ld_wait();
+            float c[32];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              float4 l0;
+              asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                           : "=f"(l0.x), "=f"(l0.y), "=f"(l0.z), "=f"(l0.w)
+                           : "r"(l0_row + ((k ^ (lane & 7)) << 4)));
+              c[4 * k] = cap2(rs * (l0.x - __uint_as_float(v[4 * k])));
+              c[4 * k + 1] = cap2(rs * (l0.y - __uint_as_float(v[4 * k + 1])));
+              c[4 * k + 2] = cap2(rs * (l0.z - __uint_as_float(v[4 * k + 2])));
+              c[4 * k + 3] = cap2(rs * (l0.w - __uint_as_float(v[4 * k + 3])));
+            }
+            if (!(a.debug & 4)) LensEpi::process_capped(st, lens, g, c, col0);
+            else {
+#pragma unroll
+              for (int k = 0; k < 32; ++k) st.s += c[k];
+            }
           }
         }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
       }
-      LensEpi::end_unit(st, lens, g, row, chunk * 2 + half);
+      LensEpi::end_unit(st, lens, g, row, chunk * Cfg::kColGroups + cg);
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == Cfg::kAllocWarp) {
     tc_fence_after();
     tmem_dealloc<1>(tmem_base, 512);
   }

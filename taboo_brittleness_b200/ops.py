@@ -794,8 +794,14 @@ def lens_rank_update(acts_dense: torch.Tensor, rank_ids: torch.Tensor, D: torch.
     n_chunks = max(1, min(n_chunks, n_tiles))
     while -(-n_tiles // -(-n_tiles // n_chunks)) != n_chunks:
         n_chunks -= 1
-    p = _alloc_partials(n_chunks, n, acts_dense.device)
-    check(_lib.load().tb_lens_rank_update_partials(_ptr(acts_dense), cols, RANKED_MAX if cols > RANKED_MAX else 0, _ptr(rank_ids),
+    lo_off = RANKED_MAX if cols > RANKED_MAX else 0
+    parts = n_chunks * _lib.load().tb_lens_rank_update_parts(int(budget), lo_off)
+    dev = acts_dense.device
+    p = LensPartials(pm=torch.empty(parts, n, dtype=torch.float32, device=dev), ps=torch.empty(parts, n, dtype=torch.float32, device=dev),
+                     psec=torch.empty(parts, n, dtype=torch.float32, device=dev),
+                     ptv=torch.empty(parts, n, TB_TOPK, dtype=torch.float32, device=dev),
+                     pti=torch.empty(parts, n, TB_TOPK, dtype=torch.int32, device=dev))
+    check(_lib.load().tb_lens_rank_update_partials(_ptr(acts_dense), cols, lo_off, _ptr(rank_ids),
                                                    rank_ids.shape[1], _ptr(D), _ptr(l0), _ptr(rstd), n, V, int(budget),
                                                    float(softcap or 0.0), _ptr(secret_id), n_chunks, _ptr(p.pm), _ptr(p.ps),
                                                    _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _stream()),
