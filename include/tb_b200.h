@@ -270,7 +270,8 @@ int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V,
 
 /* ---- nested budgets as rank updates of stored base logits (budgets of Execution Plan:126) -----------
  * For the error-term ablation the lens logits of budget m are rstd_m[t] * (L0[t, v] - sum_{rank(j) < m} a_j[t] D[j, v]) with
- * L0 = (x (.) (1 + w)) W_U^T and D = (W_dec (.) (1 + w)) W_U^T [S, V] (bf16, computed once per weight set by the caller).
+ * L0 = (x (.) (1 + w)) W_U^T and D = (W_dec (.) (1 + w)) W_U^T [S, V] (bf16, computed once per weight set by the caller and
+ * handed over TILE-MAJOR: d_tiles [ceil(V / 256)][S][256], ids past V zero).
  * Per row sub-batch of whole prompts:
  *   tb_scale_cols(x, w_norm) -> xw = bf16(x (.) (1 + w));  tb_lens_dense_partials(xw, W_U, ..., l0, TB_LOGITS_PROMPT_TILES_RAW);
  *   tb_rank_acts_dense: the rank-ordered lists of tb_sae_rank_lists as a dense matrix acts bf16 [n_rows, a_cols]:
@@ -286,7 +287,7 @@ int tb_rank_acts_dense(const int64_t* row_start, int cap, const int32_t* sel_cou
                        const float* sel_val, int64_t n_rows, int a_cols, int lo_off, void* out_bf16, void* stream);
 int tb_lens_rank_update_parts(int budget, int lo_off);   /* partials per (chunk, row) the next call writes: 2 or 4 */
 int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
-                                 const void* d_bf16, const float* l0_tiles, const float* rstd, int64_t n_rows, int V,
+                                 const void* d_tiles_bf16, int S, const float* l0_tiles, const float* rstd, int64_t n_rows, int V,
                                  int budget, float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps,
                                  float* psec, float* ptv, int32_t* pti, void* stream);
 

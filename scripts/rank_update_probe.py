@@ -67,3 +67,29 @@ for b in BUDGETS:
                       "max_abs_dsecret_prob": (r.secret_prob - d.secret_prob).abs().max().item(),
                       "max_abs_dtop_prob": (r.top_prob[:, 0] - d.top_prob[:, 0]).abs().max().item(),
                       "top1_id_equal": (r.top_id[:, 0] == d.top_id[:, 0]).float().mean().item(), "top10_set_equal": same10}), flush=True)
+
+# Which of the two is closer to the same path WITHOUT any rounding of intermediates (x', h in fp32)? 256 rows, fp32 torch.
+n_s = 2 * T
+acts = eng.encode(x[:n_s])
+ids, _, rank = eng.targeted_rank(acts, T, m=1024)
+ranked = ops.rank_lists(acts, rank, T)
+cnt, key, val = ranked.count.cpu(), ranked.key.cpu(), ranked.val.cpu()
+a_full = torch.zeros(n_s, 1024)
+for r in range(n_s):
+    base = r * ranked.cap if ranked.row_start is None else int(ranked.row_start[r])
+    k = key[base:base + int(cnt[r])]
+    a_full[r, (k >> 20).long()] = val[base:base + int(cnt[r])]
+a_full = a_full.cuda()
+w1 = 1.0 + eng.lens.w_norm.float()
+for b in (1, 64, 1024):
+    x1 = torch.cat([x[p * T:(p + 1) * T].float() - a_full[p * T:(p + 1) * T, :b] @ eng.sae.w_dec[ids[p, :b].long()].float()
+                    for p in range(2)])
+    h = x1 * torch.rsqrt(x1.pow(2).mean(1, keepdim=True) + 1e-6) * w1[None]
+    lg = 30.0 * torch.tanh(h @ eng.lens.w_u.float().t() / 30.0)
+    lse = torch.logsumexp(lg, 1)
+    p1 = torch.exp(lg.max(1).values - lse)
+    print(json.dumps({"budget": b, "rows": n_s, "against": "fp32 path without rounding of x' and h",
+                      "dense_max_abs_dlse": (dn[b].lse[:n_s] - lse).abs().max().item(),
+                      "rank_update_max_abs_dlse": (ru[b].lse[:n_s] - lse).abs().max().item(),
+                      "dense_max_abs_dtop1_prob": (dn[b].top_prob[:n_s, 0] - p1).abs().max().item(),
+                      "rank_update_max_abs_dtop1_prob": (ru[b].top_prob[:n_s, 0] - p1).abs().max().item()}), flush=True)

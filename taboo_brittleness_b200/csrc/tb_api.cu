@@ -1221,7 +1221,7 @@ static int ru_variant(int budget, int lo_off) {
 int tb_lens_rank_update_parts(int budget, int lo_off) { return ru_variant(budget, lo_off) / 4; }
 
 int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
-                                 const void* d_bf16, const float* l0_tiles, const float* rstd, int64_t n_rows, int V, int budget,
+                                 const void* d_bf16, int S, const float* l0_tiles, const float* rstd, int64_t n_rows, int V, int budget,
                                  float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps, float* psec,
                                  float* ptv, int32_t* pti, void* stream) {
   DevInfo di;
@@ -1253,6 +1253,8 @@ int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, 
   a.rank_ids = rank_ids;
   a.rank_stride = rank_stride;
   a.D = static_cast<const __nv_bfloat16*>(d_bf16);
+  a.S = S;
+  if (S <= 0) return fail(TB_ERR_INVALID, "S=%d", S);
   a.rstd = rstd;
   {
     const char* dbg = getenv("TB_RU_DEBUG");

@@ -2,7 +2,7 @@
 //
 // For the error-term ablation x' = x - sum_{j in S_m} a_j W_dec[j] the lens logits of budget m are
 //   l_m[t, v] = rstd_m[t] * ( L0[t, v] - sum_{j in S_m} a_j[t] D[j, v] ),
-//   L0 = (x (.) (1 + w)) W_U^T,   D = (W_dec (.) (1 + w)) W_U^T   [S, V] (computed once per weight set),
+//   L0 = (x (.) (1 + w)) W_U^T,   D = (W_dec (.) (1 + w)) W_U^T   [S, V] (computed once per weight set, kept tile-major),
 // with rstd_m the RMSNorm factor of the rounded x' (K1b writes it, tb_sae_ablate_ranked out_rstd). L0 is what
 // costs 2 d V FLOP per row; it is swept ONCE per row sub-batch (LensDenseEpi, raw mode, prompt tiles) and every
 // budget then needs a product of depth m <= 1024 instead of d = 3584, plus the same readout epilogue.
@@ -18,7 +18,7 @@
 //     TMA load of their own (4 KB, double-buffered), form rstd * (L0 - U) and hand it to the lens readout epilogue
 //     (LensEpi's state and arithmetic; 2 or 4 partials per (chunk, row): tb_lens_rank_update_parts).
 // All CTAs work on the same vocabulary chunk at the same time (unit = chunk * prompts + prompt), so a tile's slab of
-// D (8 MB for 16384 latents) is served from L2.
+// D (8 MB for 16384 latents, contiguous in the tile-major layout) can be served from L2.
 //
 // This changes the arithmetic of the reference path (the normalised residual no longer passes through bf16 per
 // budget; D is a rounded product): it is a separate workload with its drift reported, never the dense line.
@@ -67,7 +67,9 @@ struct RankUpdateArgs {
   int a_lo_off;
   const int32_t* rank_ids;     // [n_prompts, rank_stride]: latent id per rank
   int rank_stride;
-  const __nv_bfloat16* D;      // [S, V]
+  const __nv_bfloat16* D;      // [n_tiles][S][256]: tile-major, so that the rows one tile step gathers lie within S * 512 bytes
+                               // (a handful of pages) instead of one 2 MB page per four rows of the [S, V] matrix
+  int S;
   const float* rstd;           // [rows]
   int debug;                   // experiments only (TB_RU_DEBUG; results are garbage): 1 = no L0 loads, 2 = no gather traffic,
                                // 4 = no readout arithmetic
@@ -233,8 +235,7 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
       decode(unit, prompt, chunk, t0, t1);
       const int32_t* ids = a.rank_ids + static_cast<size_t>(prompt) * a.rank_stride;
       for (int nt = t0; nt < t1; ++nt) {
-        const int col = nt * 256 + lane * 8;                 // this lane's 8 ids of the tile
-        const bool col_ok = col + 8 <= a.V;
+        const __nv_bfloat16* d_tile = a.D + static_cast<size_t>(nt) * a.S * 256 + lane * 8;   // this lane's 8 ids of the tile
         for (int s = 0; s < slabs_per_tile; ++s, ++it) {
           const uint32_t stage = it % kRuStages, ph = (it / kRuStages) & 1u;
           const int sl = s % a.n_slabs;
@@ -250,8 +251,8 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
           for (int jj = 0; jj < kRowsPerWarp; ++jj) {
             const int j = jj * kRuGatherWarps + pw;           // k-row of the slab
             const int id = __shfl_sync(0xffffffffu, my_id, jj);
-            const bool ok = (sl * kRuSlabK + j < a.m) && col_ok && !(a.debug & 2);
-            const __nv_bfloat16* src = a.D + (ok ? static_cast<size_t>(id) * a.V + col : 0);
+            const bool ok = (sl * kRuSlabK + j < a.m) && !(a.debug & 2);      // (ids past V are zero padding in D)
+            const __nv_bfloat16* src = d_tile + (ok ? static_cast<size_t>(id) * 256 : 0);
             cp_async16(sb + j * 128 + (((lane & 7) ^ (j & 7)) << 4), src, ok ? 16u : 0u);
           }
           cp_async_commit();

@@ -408,7 +408,7 @@ class InterventionEngine:
         return self._nested_budgets(x, acts, rank, rows_per_prompt, budgets, secret_id, mode, ll)[0]
 
     def update_matrix(self) -> torch.Tensor:
-        """D = (W_dec (.) (1 + w)) W_U^T, bf16 [S, V], computed on first use and kept (8.4 GB for Gemma-2 / 16k)."""
+        """D = (W_dec (.) (1 + w)) W_U^T, bf16, tile-major, computed on first use and kept (8.4 GB for Gemma-2 / 16k)."""
         if self._update_matrix is None:
             self._update_matrix = ops.lens_update_matrix(self.sae, self.lens)
         return self._update_matrix
@@ -461,7 +461,7 @@ class InterventionEngine:
                 if self.time_lens:
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     e0.record()
-                o = ops.lens_rank_update(A[r0:r1], ids[r0 // T:r1 // T], D, l0, rstd[i, r0:r1], b, softcap=self.softcap,
+                o = ops.lens_rank_update(A[r0:r1], ids[r0 // T:r1 // T], D, l0, rstd[i, r0:r1], b, V=V, softcap=self.softcap,
                                          secret_id=None if secret_id is None else secret_id[r0:r1])
                 if self.time_lens:
                     e1.record()      # FLOPs actually done: depth = the budget rounded up to 64 (x 2 with remainders)

@@ -743,9 +743,25 @@ def scale_cols(x: torch.Tensor, w_norm: torch.Tensor) -> torch.Tensor:
 
 
 def lens_update_matrix(sae: SaeWeights, lens: LensWeights) -> torch.Tensor:
-    """D = (W_dec (.) (1 + w)) W_U^T, bf16 [S, V]: once per weight set (a plain library GEMM, not part of any timed step)."""
+    """D = (W_dec (.) (1 + w)) W_U^T in bf16, TILE-MAJOR [ceil(V / 256), S, 256] (ids past V zero): once per weight set (a
+    plain library GEMM, not part of any timed step). ``update_matrix_rows`` gives rows of the [S, V] form back."""
     wd = (sae.w_dec.float() * (1.0 + lens.w_norm.float())[None]).to(torch.bfloat16)
-    return torch.matmul(wd, lens.w_u.t()).contiguous()
+    S, V = wd.shape[0], lens.w_u.shape[0]
+    n_tiles = -(-V // BLOCK_N)
+    out = torch.zeros(n_tiles, S, BLOCK_N, dtype=torch.bfloat16, device=wd.device)
+    for t0 in range(0, n_tiles, 64):           # 64 tiles at a time: no second copy of the whole matrix
+        t1 = min(n_tiles, t0 + 64)
+        v0, v1 = t0 * BLOCK_N, min(V, t1 * BLOCK_N)
+        blk = torch.matmul(wd, lens.w_u[v0:v1].t())                      # [S, v1 - v0]
+        if (v1 - v0) % BLOCK_N:
+            blk = torch.nn.functional.pad(blk, (0, BLOCK_N - (v1 - v0) % BLOCK_N))
+        out[t0:t1] = blk.view(S, t1 - t0, BLOCK_N).permute(1, 0, 2)
+    return out
+
+
+def update_matrix_rows(D_tiles: torch.Tensor, ids: torch.Tensor, V: int) -> torch.Tensor:
+    """Rows ``ids`` of D in the plain [len(ids), V] form (tests, probes)."""
+    return D_tiles[:, ids.long()].permute(1, 0, 2).reshape(ids.numel(), -1)[:, :V]
 
 
 def rank_acts_dense(ranked: RankedActs, n_rows: int, split: bool = False) -> torch.Tensor:
@@ -774,15 +790,17 @@ def lens_base_logits(xw: torch.Tensor, w_u: torch.Tensor, l0: torch.Tensor, cta_
 
 
 def lens_rank_update(acts_dense: torch.Tensor, rank_ids: torch.Tensor, D: torch.Tensor, l0: torch.Tensor, rstd: torch.Tensor,
-                     budget: int, *, softcap: float = 0.0, secret_id: Optional[torch.Tensor] = None,
+                     budget: int, *, V: Optional[int] = None, softcap: float = 0.0, secret_id: Optional[torch.Tensor] = None,
                      n_chunks: Optional[int] = None) -> "LensReadout":
     """Lens readout of one budget from the base logits: rstd * (L0 - acts[:, :budget] D[rank_ids[:budget]]) per prompt."""
     _need(acts_dense, torch.bfloat16, "acts_dense", 2)
     _need(rank_ids, torch.int32, "rank_ids", 2)
-    _need(D, torch.bfloat16, "D", 2)
+    _need(D, torch.bfloat16, "D", 3)
     _need(rstd, torch.float32, "rstd", 1)
     n, cols = acts_dense.shape
-    V = D.shape[1]
+    V = int(V if V is not None else D.shape[0] * D.shape[2])
+    if D.shape[2] != BLOCK_N or D.shape[0] != -(-V // BLOCK_N):
+        raise TabooKernelError("D must be tile-major [ceil(V / 256), S, 256] (ops.lens_update_matrix)", _lib.TB_ERR_INVALID)
     if secret_id is not None:
         _need(secret_id, torch.int32, "secret_id", 1)
     if rank_ids.shape[0] * LL_SLOTS != n or rstd.shape[0] != n or l0.numel() < n * V:
@@ -802,7 +820,7 @@ def lens_rank_update(acts_dense: torch.Tensor, rank_ids: torch.Tensor, D: torch.
                      ptv=torch.empty(parts, n, TB_TOPK, dtype=torch.float32, device=dev),
                      pti=torch.empty(parts, n, TB_TOPK, dtype=torch.int32, device=dev))
     check(_lib.load().tb_lens_rank_update_partials(_ptr(acts_dense), cols, lo_off, _ptr(rank_ids),
-                                                   rank_ids.shape[1], _ptr(D), _ptr(l0), _ptr(rstd), n, V, int(budget),
+                                                   rank_ids.shape[1], _ptr(D), D.shape[1], _ptr(l0), _ptr(rstd), n, V, int(budget),
                                                    float(softcap or 0.0), _ptr(secret_id), n_chunks, _ptr(p.pm), _ptr(p.ps),
                                                    _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _stream()),
           "tb_lens_rank_update_partials")

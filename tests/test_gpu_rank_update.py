@@ -86,10 +86,10 @@ def test_update_kernel_is_exact_for_its_own_arithmetic(setup, split):
     for b in (1, 100, 1024):
         rstd = torch.empty(n, dtype=torch.float32, device="cuda")
         ops.sae_ablate_ranked(x, ranked, eng.sae, b, w_norm=eng.lens.w_norm, want_x=False, want_h=False, out_rstd=rstd)
-        out = ops.lens_rank_update(A, ids, Dm, l0, rstd, b, softcap=30.0, secret_id=sid)
+        out = ops.lens_rank_update(A, ids, Dm, l0, rstd, b, V=V, softcap=30.0, secret_id=sid)
         torch.cuda.synchronize()
         a_eff = A[:, :b].float() + (A[:, 1024:1024 + b].float() if split else 0.0)
-        U = torch.cat([a_eff[p * T:(p + 1) * T] @ Dm[ids[p, :b].long()].float() for p in range(P)])
+        U = torch.cat([a_eff[p * T:(p + 1) * T] @ ops.update_matrix_rows(Dm, ids[p, :b], V).float() for p in range(P)])
         logits = 30.0 * torch.tanh(rstd[:, None] * (L0 - U) / 30.0)
         lse = torch.logsumexp(logits, 1)
         assert (out.lse - lse).abs().max().item() <= 2e-4
