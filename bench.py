@@ -484,6 +484,33 @@ def leg_rank_update(args, ctx):
                       for i in range(n_sub)) for j in range(len(BUDGETS))]
     eng.stats = stats0
     ms_dense = _leg_time(lambda: out.__setitem__("dense", eng.targeted_budget_sweep(x, T, sid, BUDGETS)), 1, dev, world, dist)
+    # the same two sweeps WITH the per-prompt LL-Top-10 (the headline's readouts): the update path stores every budget's
+    # logits and reduces them with the column-sum kernel, the dense path is the headline's (stored logits / K3F + K6)
+    with_ll = None
+    if args.ll_topk:
+        g = torch.Generator().manual_seed(synthetic.SEED_DATA + 778 + rank)
+        ids2 = torch.randint(0, V, (2, n_rows), generator=g, dtype=torch.int32)
+        ids2[1, ::T] = -1
+        ids2 = ids2.to(dev)
+        ll = interventions.LLSpec(ids2[0], ids2[1], rows_per_prompt=T)
+        eng.release_scratch()
+        torch.cuda.empty_cache()
+        eng.update_matrix()
+        eng.targeted_budget_sweep_rank_update(x, sid, BUDGETS[:1], split=args.ru_split, ll=ll)      # scratch
+        ms_ru_ll = _leg_time(lambda: out.__setitem__("ru_ll", eng.targeted_budget_sweep_rank_update(x, sid, BUDGETS, split=args.ru_split,
+                                                                                                     ll=ll)), 1, dev, world, dist)
+        eng._dense_logits2 = None
+        torch.cuda.empty_cache()
+        ms_dense_ll = _leg_time(lambda: out.__setitem__("dense_ll", eng.targeted_budget_sweep(x, T, sid, BUDGETS, ll=ll)), 1, dev,
+                                world, dist)
+        common = [float((out["ru_ll"][b].ll_id[:, :, None] == out["dense_ll"][b].ll_id[:, None, :]).any(2).float().sum(1).mean().item())
+                  for b in BUDGETS]
+        with_ll = {"value": n_rows * len(BUDGETS) * world / (ms_ru_ll * 1e-3), "ms_per_pass": ms_ru_ll,
+                   "dense_sweep_same_rows": {"value": n_rows * len(BUDGETS) * world / (ms_dense_ll * 1e-3), "ms_per_pass": ms_dense_ll},
+                   "speedup_over_dense": ms_dense_ll / ms_ru_ll,
+                   "ll_top10_ids_shared_with_dense_mean_per_budget": dict(zip([str(b) for b in BUDGETS], [round(c, 3) for c in common])),
+                   "how": "every budget's soft-capped logits stored in prompt tiles (a second 67 GB scratch per 65,536 rows) and "
+                          "reduced by tb_logits_ll_colsum + tb_topm_select: exact for this path's logits, no candidate lists"}
     drift = {}
     for b in BUDGETS:
         r, dn = out["ru"][b], out["dense"][b]
@@ -498,12 +525,13 @@ def leg_rank_update(args, ctx):
     conds = n_rows * len(BUDGETS) * world
     return {"config": f"SURVEY 8 (f4): configs[1] budgets {list(BUDGETS)} as rank updates of stored base logits, {P} prompts x {T} "
                       f"tok per GPU, lens readouts without LL-Top-k; beside it the dense sweep of the same rows (also without "
-                      f"LL-Top-k). D = (W_dec (1+w)) W_U^T ({Dm.numel() * 2 / 1e9:.1f} GB bf16) is computed once per weight set "
+                      f"LL-Top-k); with_ll_top10: both with the per-prompt LL-Top-10. D = (W_dec (1+w)) W_U^T ({Dm.numel() * 2 / 1e9:.1f} GB bf16) is computed once per weight set "
                       f"outside the timed region ({setup_s:.2f} s, cuBLAS)",
             "scaling": "weak", "n_gpus": world, "passes": 1, "unit": UNIT,
             "value": conds / (ms_ru * 1e-3), "ms_per_pass": ms_ru,
             "dense_sweep_same_rows": {"value": conds / (ms_dense * 1e-3), "ms_per_pass": ms_dense},
             "speedup_over_dense": ms_dense / ms_ru,
+            "with_ll_top10": with_ll,
             "activation_remainders": bool(args.ru_split),
             "not_the_reference_arithmetic": "the normalised residual is not rounded to bf16 per budget and D is a rounded "
                                             "product: readouts drift (table below, against the dense sweep); reported beside "

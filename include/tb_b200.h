@@ -279,7 +279,8 @@ int tb_probs_from_logits(float* logits, const float* lse, int64_t n_rows, int V,
  *     remainders a - bf16(a) in column lo_off + r, which halves the rounding of the activations for twice the depth);
  *   per budget: tb_sae_ablate_ranked(..., out_rstd) and tb_lens_rank_update_partials: same partial layout as
  *     tb_lens_partials with tb_lens_rank_update_parts(budget, lo_off) partials per (chunk, row) -> tb_lens_merge. rank_ids i32 [n_rows / 128, rank_stride]: the
- *     latent id of each rank of each prompt (tb_topm_select's ids).
+ *     latent id of each rank of each prompt (tb_topm_select's ids). logits_out_tiles (nullable, its own n_rows * V floats):
+ *     the budget's soft-capped logits in the TB_LOGITS_PROMPT_TILES form, for LL-Top-k by tb_logits_ll_colsum.
  * Not the arithmetic of the reference path (no bf16 rounding of the normalised residual per budget, D is a rounded
  * product): drift against the dense kernels is reported in DESIGN.md; no code in the reference. */
 int tb_scale_cols(const void* x_bf16, const float* w_norm, int64_t n_rows, int d, void* out_bf16, void* stream);
@@ -289,7 +290,7 @@ int tb_lens_rank_update_parts(int budget, int lo_off);   /* partials per (chunk,
 int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
                                  const void* d_tiles_bf16, int S, const float* l0_tiles, const float* rstd, int64_t n_rows, int V,
                                  int budget, float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps,
-                                 float* psec, float* ptv, int32_t* pti, void* stream);
+                                 float* psec, float* ptv, int32_t* pti, float* logits_out_tiles, void* stream);
 
 /* ---- K3F + K6: lens readout and LL-Top-k in one sweep -------------------------------------
  * Same readouts as K3 (tb_lens_partials) and K5, for a condition whose rows' logsumexp is

@@ -62,7 +62,7 @@ SIGNATURES = {
     "tb_rank_acts_dense": (c_int, [_P, c_int, _P, _P, _P, c_int64, c_int, c_int, _P, _P]),
     "tb_lens_rank_update_parts": (c_int, [c_int, c_int]),
     "tb_lens_rank_update_partials": (c_int, [_P, c_int, c_int, _P, c_int, _P, c_int, _P, _P, c_int64, c_int, c_int, c_float, _P, c_int,
-                                             _P, _P, _P, _P, _P, _P]),
+                                             _P, _P, _P, _P, _P, _P, _P]),
     "tb_logits_ll_colsum": (c_int, [_P, _P, _P, _P, c_int64, c_int, _P, c_int, _P]),
     "tb_probs_from_logits": (c_int, [_P, _P, c_int64, c_int, _P]),
     "tb_lens_merge": (c_int, [_P, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P,

@@ -1223,7 +1223,7 @@ int tb_lens_rank_update_parts(int budget, int lo_off) { return ru_variant(budget
 int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, const int32_t* rank_ids, int rank_stride,
                                  const void* d_bf16, int S, const float* l0_tiles, const float* rstd, int64_t n_rows, int V, int budget,
                                  float softcap, const int32_t* secret_id, int n_chunks, float* pm, float* ps, float* psec,
-                                 float* ptv, int32_t* pti, void* stream) {
+                                 float* ptv, int32_t* pti, float* logits_out_tiles, void* stream) {
   DevInfo di;
   int rc = device_info(&di);
   if (rc != TB_OK) return rc;
@@ -1270,6 +1270,13 @@ int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, 
   if (rc != TB_OK) return rc;
   rc = make_tile_map(&tmL0, l0_tiles, n_rows, V);
   if (rc != TB_OK) return rc;
+  CUtensorMap tmOut = tmL0;
+  a.store = logits_out_tiles ? 1 : 0;
+  if (logits_out_tiles) {
+    if (reinterpret_cast<uintptr_t>(logits_out_tiles) & 15) return fail(TB_ERR_INVALID, "logits_out_tiles must be 16-byte aligned");
+    rc = make_tile_map(&tmOut, logits_out_tiles, n_rows, V);
+    if (rc != TB_OK) return rc;
+  }
   const int units = a.n_prompts * a.n_chunks;
   const unsigned grid = static_cast<unsigned>(units < di.sms ? units : di.sms);
   const int variant = ru_variant(budget, lo_off);
@@ -1277,12 +1284,12 @@ int tb_lens_rank_update_partials(const void* acts_bf16, int a_cols, int lo_off, 
     auto k = tb::tb_rank_update_lens_kernel<2, 2, 16>;
     using Cfg = tb::RuCfg<2, 2, 16>;
     TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    k<<<grid, Cfg::kThreads, Cfg::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
+    k<<<grid, Cfg::kThreads, Cfg::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, tmOut, a, lens);
   } else {
     auto k = tb::tb_rank_update_lens_kernel<3, 2, 8>;
     using Cfg = tb::RuCfg<3, 2, 8>;
     TB_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes));
-    k<<<grid, Cfg::kThreads, Cfg::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, a, lens);
+    k<<<grid, Cfg::kThreads, Cfg::kSmemBytes, static_cast<cudaStream_t>(stream)>>>(tmA, tmL0, tmOut, a, lens);
   }
   TB_CUDA(cudaGetLastError());
   return TB_OK;

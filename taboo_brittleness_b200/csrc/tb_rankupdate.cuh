@@ -71,6 +71,7 @@ struct RankUpdateArgs {
                                // (a handful of pages) instead of one 2 MB page per four rows of the [S, V] matrix
   int S;
   const float* rstd;           // [rows]
+  int store;                   // 1: also write the soft-capped logits (log2 units, prompt tiles: tmOut) for tb_logits_ll_colsum
   int debug;                   // experiments only (TB_RU_DEBUG; results are garbage): 1 = no L0 loads, 2 = no gather traffic,
                                // 4 = no readout arithmetic
 };
@@ -126,7 +127,7 @@ __global__ void __launch_bounds__(256) tb_scale_cols_kernel(const __nv_bfloat16*
 template <int kRuStages, int kNB, int kEW>
 __global__ void __launch_bounds__((RuCfg<kRuStages, kNB, kEW>::kThreads), 1)
 tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmL0,
-                           const RankUpdateArgs a, const LensEpi::Params lens) {
+                           const __grid_constant__ CUtensorMap tmOut, const RankUpdateArgs a, const LensEpi::Params lens) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   const uint32_t smem0 = smem_u32(smem);
@@ -149,6 +150,7 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmL0);
+    if (a.store) tma_prefetch_desc(&tmOut);
     for (int i = 0; i < kRuStages; ++i) {
       mbar_init(smem_u32(&full_bar[i]), 1 + kRuGatherWarps);
       mbar_init(smem_u32(&empty_bar[i]), 1);
@@ -285,6 +287,7 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
     g.M = a.n_prompts * 128;
     g.N = a.V;
     const CapLog2 cap2(lens.softcap);
+    const uint64_t evict_first = l2_policy_evict_first();
     LensEpi::State st;
     uint32_t acc_it = 0, pc = 0;                              // tiles / L0 pieces consumed so far
     for (int unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
@@ -297,6 +300,7 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
       // piece q of the unit: tile t0 + q / kPPT, columns col_base + (q % kPPT) * 32 of it
       auto request = [&](int q, uint32_t slot) {
         if (lane == 0 && !(a.debug & 1)) {
+          if (a.store) bulk_wait_read0();                     // the logits stored from this buffer have been read out of it
           const int c32 = ((t0 + q / kPPT) * 256 + col_base + (q % kPPT) * 32) >> 5;
           mbar_arrive_expect_tx(l0_b0 + slot * 8, kRuL0Bytes);
           tma_load_4d(l0_buf + slot * kRuL0Bytes, &tmL0, l0_b0 + slot * 8, 0, quad * 32, c32, prompt);
@@ -337,6 +341,12 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
                 c[4 * k + 2] = cap2(rs * (l0.z - __uint_as_float(v[4 * k + 2])));
                 c[4 * k + 3] = cap2(rs * (l0.w - __uint_as_float(v[4 * k + 3])));
               }
+              if (a.store) {                                 // the capped logits replace the base logits in the buffer
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(l0_row + (((hf * 4 + k) ^ (lane & 7)) << 4)),
+                               "f"(c[4 * k]), "f"(c[4 * k + 1]), "f"(c[4 * k + 2]), "f"(c[4 * k + 3]) : "memory");
+              }
               if (!(a.debug & 4)) LensEpi::process_capped_w<16>(st, lens, g, c, col0 + hf * 16);
               else {
 #pragma unroll
@@ -360,10 +370,24 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
               c[4 * k + 2] = cap2(rs * (l0.z - __uint_as_float(v[4 * k + 2])));
               c[4 * k + 3] = cap2(rs * (l0.w - __uint_as_float(v[4 * k + 3])));
             }
+            if (a.store) {
+#pragma unroll
+              for (int k = 0; k < 8; ++k)
+                asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(l0_row + ((k ^ (lane & 7)) << 4)),
+                             "f"(c[4 * k]), "f"(c[4 * k + 1]), "f"(c[4 * k + 2]), "f"(c[4 * k + 3]) : "memory");
+            }
             if (!(a.debug & 4)) LensEpi::process_capped(st, lens, g, c, col0);
             else {
 #pragma unroll
               for (int k = 0; k < 32; ++k) st.s += c[k];
+            }
+          }
+          if (a.store) {
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0 && col0 < a.V) {
+              tma_store_4d_hint(&tmOut, l0_buf + slot * kRuL0Bytes, 0, quad * 32, col0 >> 5, prompt, evict_first);
+              bulk_commit();
             }
           }
         }
@@ -371,6 +395,7 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
       }
+      if (a.store && lane == 0) bulk_wait0();                 // this unit's logits are written
       LensEpi::end_unit(st, lens, g, row, chunk * Cfg::kColGroups + cg);
     }
   }

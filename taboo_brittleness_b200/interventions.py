@@ -92,6 +92,7 @@ class InterventionEngine:
         self.ll_dense_first = True
         self.ll_dense_rows = 65536
         self._dense_logits = None
+        self._dense_logits2 = None
         self._update_matrix = None
         self.use_ranked = True       # nested budgets read prefixes of rank-ordered lists (ops.rank_lists) in K1b
         self.ll_alpha = 0.5          # candidate threshold = ll_alpha * previous condition's k-th best sum
@@ -170,6 +171,7 @@ class InterventionEngine:
     def release_scratch(self) -> None:
         """Drop the logits scratch of ``read_dense_ll`` (tens of GB) and the rank-update matrix."""
         self._dense_logits = None
+        self._dense_logits2 = None
         self._update_matrix = None
 
     def read_dense_ll(self, h: torch.Tensor, secret_id: Optional[torch.Tensor], ll: LLSpec) -> Readout:
@@ -415,12 +417,15 @@ class InterventionEngine:
 
     def targeted_budget_sweep_rank_update(self, x: torch.Tensor, secret_id: Optional[torch.Tensor],
                                           budgets: Sequence[int] = DEFAULT_BUDGETS, *, split: bool = False,
-                                          sub_rows: int = 65536) -> Dict[int, ops.LensReadout]:
+                                          sub_rows: int = 65536, ll: Optional[LLSpec] = None):
         """configs[1] with the nested budgets as RANK UPDATES of stored base logits: per row sub-batch one
         sweep of L0 = (x (.) (1 + w)) W_U^T, then per budget rstd_m * (L0 - A_m D[ids]) with a product of depth m instead
-        of d. Error-term ablation, 128 rows per prompt, single shard, lens readouts only (no LL-Top-k). NOT the
-        arithmetic of the reference path -- the normalised residual is not rounded to bf16 per budget and D is a
-        rounded product -- so this is a workload of its own, reported beside the dense sweep."""
+        of d. Error-term ablation, 128 rows per prompt, single shard. With ``ll`` every budget's soft-capped logits are
+        also stored (a second scratch of the same size) and reduced to the LL-Top-k by the HBM-bound column-sum kernel of
+        the first-condition path: exact for this path's logits, no candidate lists. Returns LensReadout per budget, or
+        Readout (lens, ll_sum, ll_id) with ``ll``. NOT the arithmetic of the reference path -- the normalised residual is
+        not rounded to bf16 per budget and D is a rounded product -- so this is a workload of its own, reported beside the
+        dense sweep."""
         T = ops.LL_SLOTS
         n, V = x.shape[0], self.lens.w_u.shape[0]
         if n % T or self.lens.vocab_offset != 0 or V % 32:
@@ -437,16 +442,24 @@ class InterventionEngine:
             ops.sae_ablate_ranked(x, ranked, self.sae, b, w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False,
                                   want_h=False, out_rstd=rstd[i])
         self.stats.launches += 3 + len(bs)
+        if ll is not None and (ll.seg is not None or ll.rows_per_prompt != T):
+            raise ops.TabooKernelError("rank-update sweep: LL-Top-k needs 128 row slots per prompt", ops._lib.TB_ERR_INVALID)
+        n_scratch = 2 if ll is not None else 1
         step = max(T, min(sub_rows, n) // T * T)
         free = torch.cuda.mem_get_info(x.device)[0]
-        have = 0 if self._dense_logits is None else self._dense_logits.numel() * 4
-        while step > 8 * T and step * V * 4 > have + 0.8 * free:
+        have = sum(0 if t is None else t.numel() * 4 for t in (self._dense_logits, self._dense_logits2)[:n_scratch])
+        while step > 8 * T and n_scratch * step * V * 4 > have + 0.8 * free:
             step = step // 2 // T * T
         if self._dense_logits is None or self._dense_logits.numel() < step * V:
             self._dense_logits = None
             self._dense_logits = torch.empty(step, V, dtype=torch.float32, device=x.device)
+        if ll is not None and (self._dense_logits2 is None or self._dense_logits2.numel() < step * V):
+            self._dense_logits2 = None
+            self._dense_logits2 = torch.empty(step * V, dtype=torch.float32, device=x.device)
         l0 = self._dense_logits
+        stored = self._dense_logits2 if ll is not None else None
         outs = {b: [] for b in bs}
+        lls = {b: [] for b in bs}
         for r0 in range(0, n, step):
             r1 = min(n, r0 + step)
             xw = ops.scale_cols(x[r0:r1], self.lens.w_norm)
@@ -462,7 +475,10 @@ class InterventionEngine:
                     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     e0.record()
                 o = ops.lens_rank_update(A[r0:r1], ids[r0 // T:r1 // T], D, l0, rstd[i, r0:r1], b, V=V, softcap=self.softcap,
-                                         secret_id=None if secret_id is None else secret_id[r0:r1])
+                                         secret_id=None if secret_id is None else secret_id[r0:r1], logits_out=stored)
+                if ll is not None:
+                    lls[b].append(ops.ll_topk_from_tiles(stored, o.lse, None if ll.cur_id is None else ll.cur_id[r0:r1],
+                                                         None if ll.prev_id is None else ll.prev_id[r0:r1], V, ll.k))
                 if self.time_lens:
                     e1.record()      # FLOPs actually done: depth = the budget rounded up to 64 (x 2 with remainders)
                     depth = -(-b // 64) * 64 * (2 if split else 1)
@@ -470,8 +486,11 @@ class InterventionEngine:
                 outs[b].append(o)
             self.stats.launches += 2 + 2 * len(bs)
         cat = lambda xs, f: torch.cat([getattr(o, f) for o in xs])      # noqa: E731
-        return {b: ops.LensReadout(lse=cat(v, "lse"), secret_prob=cat(v, "secret_prob"), top_prob=cat(v, "top_prob"),
-                                   top_id=cat(v, "top_id")) for b, v in outs.items()}
+        lens_out = {b: ops.LensReadout(lse=cat(v, "lse"), secret_prob=cat(v, "secret_prob"), top_prob=cat(v, "top_prob"),
+                                       top_id=cat(v, "top_id")) for b, v in outs.items()}
+        if ll is None:
+            return lens_out
+        return {b: Readout(lens_out[b], torch.cat([s_ for s_, _ in lls[b]]), torch.cat([i_ for _, i_ in lls[b]])) for b in bs}
 
     def random_budget_sweep(self, x: torch.Tensor, secret_id, budgets: Sequence[int] = DEFAULT_BUDGETS,
                             seeds: Iterable[int] = range(32), mode: str = "error",

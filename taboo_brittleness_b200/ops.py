@@ -791,7 +791,7 @@ def lens_base_logits(xw: torch.Tensor, w_u: torch.Tensor, l0: torch.Tensor, cta_
 
 def lens_rank_update(acts_dense: torch.Tensor, rank_ids: torch.Tensor, D: torch.Tensor, l0: torch.Tensor, rstd: torch.Tensor,
                      budget: int, *, V: Optional[int] = None, softcap: float = 0.0, secret_id: Optional[torch.Tensor] = None,
-                     n_chunks: Optional[int] = None) -> "LensReadout":
+                     n_chunks: Optional[int] = None, logits_out: Optional[torch.Tensor] = None) -> "LensReadout":
     """Lens readout of one budget from the base logits: rstd * (L0 - acts[:, :budget] D[rank_ids[:budget]]) per prompt."""
     _need(acts_dense, torch.bfloat16, "acts_dense", 2)
     _need(rank_ids, torch.int32, "rank_ids", 2)
@@ -805,6 +805,9 @@ def lens_rank_update(acts_dense: torch.Tensor, rank_ids: torch.Tensor, D: torch.
         _need(secret_id, torch.int32, "secret_id", 1)
     if rank_ids.shape[0] * LL_SLOTS != n or rstd.shape[0] != n or l0.numel() < n * V:
         raise TabooKernelError("rank_ids / rstd / l0 do not match the rows", _lib.TB_ERR_INVALID)
+    if logits_out is not None and (logits_out.dtype != torch.float32 or logits_out.numel() < n * V or not logits_out.is_cuda
+                                   or logits_out.data_ptr() == l0.data_ptr()):
+        raise TabooKernelError("logits_out: its own f32 scratch of rows * V", _lib.TB_ERR_INVALID)
     n_tiles = -(-V // BLOCK_N)
     sms = torch.cuda.get_device_properties(acts_dense.device).multi_processor_count
     if n_chunks is None:       # a dozen (prompt, chunk) units per SM: little tail waste, chunks still hundreds of tiles long
@@ -822,9 +825,20 @@ def lens_rank_update(acts_dense: torch.Tensor, rank_ids: torch.Tensor, D: torch.
     check(_lib.load().tb_lens_rank_update_partials(_ptr(acts_dense), cols, lo_off, _ptr(rank_ids),
                                                    rank_ids.shape[1], _ptr(D), D.shape[1], _ptr(l0), _ptr(rstd), n, V, int(budget),
                                                    float(softcap or 0.0), _ptr(secret_id), n_chunks, _ptr(p.pm), _ptr(p.ps),
-                                                   _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _stream()),
+                                                   _ptr(p.psec), _ptr(p.ptv), _ptr(p.pti), _ptr(logits_out), _stream()),
           "tb_lens_rank_update_partials")
     return lens_merge(p, finalize=True)
+
+
+def ll_topk_from_tiles(logits_tiles: torch.Tensor, lse: torch.Tensor, cur_id: Optional[torch.Tensor],
+                       prev_id: Optional[torch.Tensor], V: int, k: int = TB_TOPK) -> Tuple[torch.Tensor, torch.Tensor]:
+    """LL-Top-k (sums f32 [P, k], ids i32 [P, k]) from soft-capped logits stored in prompt tiles (log2 units)."""
+    n = lse.shape[0]
+    acc = torch.empty(n // LL_SLOTS, V, dtype=torch.float32, device=lse.device)
+    check(_lib.load().tb_logits_ll_colsum(_ptr(logits_tiles), _ptr(lse), _ptr(cur_id), _ptr(prev_id), n, V, _ptr(acc),
+                                          LOGITS_PROMPT_TILES, _stream()), "tb_logits_ll_colsum")
+    ids, sums, _ = topm_select(acc, k, want_rank=False)
+    return sums, ids
 
 
 def logit_lens(x: torch.Tensor, lens: LensWeights, *, softcap: float = 0.0,

@@ -130,3 +130,80 @@ def test_rank_update_sweep_against_oracle_and_dense_sweep(setup, split):
         torch.cuda.synchronize()
         for b in BUDGETS:
             assert (res[b].lse - plain[b].lse).abs().max().item() <= 2e-2
+
+
+def test_ll_topk_of_the_update_path(setup):
+    """With ``ll`` the sweep stores every budget's soft-capped logits and reduces them with the column-sum kernel of the
+    first-condition path: the lists must be those of fp32 torch on the same logits (exact for this path's arithmetic) and
+    close to the dense sweep's."""
+    from taboo_brittleness_b200 import interventions, ops
+    eng, sid = setup["eng"], setup["sid"].cuda()
+    x = cuda_bf16(setup["x"])
+    n = P * T
+    g = torch.Generator().manual_seed(5)
+    cur = torch.randint(0, V, (n,), generator=g, dtype=torch.int32).cuda()
+    prev = torch.randint(0, V, (n,), generator=g, dtype=torch.int32)
+    prev[::T] = -1
+    prev = prev.cuda()
+    ll = interventions.LLSpec(cur, prev, rows_per_prompt=T, k=10)
+    budgets = [1, 100, 1024]
+    res = eng.targeted_budget_sweep_rank_update(x, sid, budgets, sub_rows=3 * T, ll=ll)
+    plain = eng.targeted_budget_sweep_rank_update(x, sid, budgets, sub_rows=3 * T)
+    dense = eng.targeted_budget_sweep(x, T, sid, budgets, ll=ll)
+    torch.cuda.synchronize()
+    # the same logits rebuilt in torch for one budget
+    acts = eng.encode(x)
+    ids, _, rank = eng.targeted_rank(acts, T, m=1024)
+    ranked = ops.rank_lists(acts, rank, T)
+    A = ops.rank_acts_dense(ranked, n)
+    Dm = eng.update_matrix()
+    xw = ops.scale_cols(x, eng.lens.w_norm)
+    L0 = xw.float() @ eng.lens.w_u.float().t()
+    for b in budgets:
+        assert torch.equal(res[b].lens.lse, plain[b].lse) and torch.equal(res[b].lens.top_id, plain[b].top_id)
+        rstd = torch.empty(n, dtype=torch.float32, device="cuda")
+        ops.sae_ablate_ranked(x, ranked, eng.sae, b, w_norm=eng.lens.w_norm, want_x=False, want_h=False, out_rstd=rstd)
+        U = torch.cat([A[p * T:(p + 1) * T, :b].float() @ ops.update_matrix_rows(Dm, ids[p, :b], V).float() for p in range(P)])
+        logits = 30.0 * torch.tanh(rstd[:, None] * (L0 - U) / 30.0)
+        pr = torch.softmax(logits, 1)
+        rows = torch.arange(n, device="cuda")
+        pr[rows, cur.long()] = 0.0
+        keep = prev >= 0
+        pr[rows[keep], prev[keep].long()] = 0.0
+        acc = pr.view(P, T, V).sum(1)
+        want_v, want_i = acc.topk(10, 1)
+        assert torch.allclose(res[b].ll_sum, want_v, rtol=2e-3, atol=1e-7)
+        same = (res[b].ll_id.long().sort(1).values == want_i.sort(1).values).all(1)
+        for q in torch.nonzero(~same).flatten().tolist():       # a tie at the k-th place to within rounding
+            assert abs(float(res[b].ll_sum[q, 9] - want_v[q, 9])) <= 2e-3 * float(want_v[q, 9])
+        # against the dense sweep (the reference arithmetic): the same lists up to this path's drift
+        common = (res[b].ll_id[:, :, None] == dense[b].ll_id[:, None, :]).any(2).float().sum(1)
+        assert common.mean().item() >= 9.0
+        assert torch.allclose(res[b].ll_sum[:, 0], dense[b].ll_sum[:, 0], rtol=0.15)
+
+
+def test_argument_checks(setup):
+    """The new entry points refuse what they cannot handle (no CPU path, no silent fallback)."""
+    from taboo_brittleness_b200 import _lib, ops
+    eng = setup["eng"]
+    x = cuda_bf16(setup["x"])
+    n = P * T
+    Dm = eng.update_matrix()
+    A = torch.zeros(n, 1024, dtype=torch.bfloat16, device="cuda")
+    ids = torch.zeros(P, 1024, dtype=torch.int32, device="cuda")
+    rstd = torch.ones(n, dtype=torch.float32, device="cuda")
+    l0 = torch.zeros(n * V, dtype=torch.float32, device="cuda")
+    with pytest.raises(ops.TabooKernelError):      # budget beyond the ranking
+        ops.lens_rank_update(A, ids[:, :64].contiguous(), Dm, l0, rstd, 100, V=V)
+    with pytest.raises(ops.TabooKernelError):      # D in the plain [S, V] form
+        ops.lens_rank_update(A, ids, torch.zeros(S, V, dtype=torch.bfloat16, device="cuda"), l0, rstd, 8, V=V)
+    with pytest.raises(ops.TabooKernelError):      # not whole prompts
+        ops.lens_rank_update(A[:-1], ids, Dm, l0, rstd[:-1], 8, V=V)
+    with pytest.raises(ops.TabooKernelError):      # base logits too small
+        ops.lens_base_logits(x, eng.lens.w_u, l0[:100])
+    lib = _lib.load()
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.tb_rank_acts_dense(None, 64, A.data_ptr(), A.data_ptr(), A.data_ptr(), n, 1000, 0, A.data_ptr(), st) != 0   # a_cols
+    assert lib.tb_lens_dense_partials(x.data_ptr(), eng.lens.w_u.data_ptr(), n - 1, D, V, 0.0, None, 1, 1, None, None, None, None,
+                                      None, l0.data_ptr(), ops.LOGITS_PROMPT_TILES_RAW, st) != 0                        # whole prompts
+    assert lib.tb_lens_rank_update_parts(64, 0) == 4 and lib.tb_lens_rank_update_parts(1024, 0) == 2
