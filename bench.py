@@ -624,6 +624,7 @@ def run_native(args, rank, local_rank, world):
     eng.ll_alpha = args.ll_alpha
     eng.overlap = args.overlap
     eng.ll_dense_first = not args.no_ll_dense_first
+    eng.multi_budget = not args.no_multi_budget
 
     # ---- inputs: this rank's prompts (weak scaling: every rank gets args.prompts prompts)
     P, BP = args.prompts, min(args.batch_prompts, args.prompts)
@@ -794,7 +795,8 @@ def run_native(args, rank, local_rank, world):
             gbs = row_bytes / (row_ms * 1e-3) / 1e9
             line["roofline"]["hbm_path"] = {
                 "kernel": ("tb_lowrank_remove / tb_lowrank_remove_tc (K2, ranks %s)" % list(RANKS)) if proj
-                else "tb_sae_rank_lists once + tb_sae_ablate_ranked per budget (K1b, budgets %s)" % list(BUDGETS),
+                else ("tb_sae_rank_lists once + tb_sae_ablate_ranked_multi: all budgets in one pass over the rows (K1b, budgets %s)"
+                      if eng.multi_budget else "tb_sae_rank_lists once + tb_sae_ablate_ranked per budget (K1b, budgets %s)") % list(BUDGETS),
                 "bound": "hbm", "achieved": gbs, "peak": peaks.get("hbm_gbs"), "unit": "GB/s",
                 "frac": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
                 "algorithmic_bytes_per_row": 4 * D, "share_of_step": row_ms / (ms_step * args.steps)}
@@ -859,6 +861,8 @@ def main():
     ap.add_argument("--no-ll-dense-first", action="store_true",
                     help="first budget of a chain: a second GEMM sweep (K5) for its LL-Top-k instead of reducing the logits "
                          "the lens kernel writes in its one sweep")
+    ap.add_argument("--no-multi-budget", action="store_true",
+                    help="K1b: one launch per budget instead of all budgets of a chain in one pass over the rows")
     ap.add_argument("--overlap", action="store_true",
                     help="run K1b / K6 on a side stream under the lens sweeps (measured: no gain)")
     ap.add_argument("--ll-two-sweeps", action="store_true",

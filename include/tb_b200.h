@@ -131,6 +131,16 @@ int tb_sae_ablate_ranked(const void* x_bf16, const int64_t* row_start, int cap, 
                          const int32_t* sel_key, const float* sel_val, const void* w_dec_bf16, int budget,
                          int64_t n_rows, int d, const float* w_norm, float eps, void* out_x_bf16,
                          void* out_h_bf16, float* out_rstd, void* stream);
+/* All budgets of a chain in one pass over the rows: x is read once and every W_dec row a row needs is gathered once;
+ * after each budget's entries the row is rounded, normalised and written to that budget's output (the same bits as
+ * one tb_sae_ablate_ranked call per budget). budgets_host: n_budgets (<= 16) strictly ascending values, a HOST array
+ * read during the call. Output k at out_x / out_h + k * out_stride elements (out_stride >= n_rows * d), out_rstd +
+ * k * n_rows. */
+int tb_sae_ablate_ranked_multi(const void* x_bf16, const int64_t* row_start, int cap, const int32_t* sel_count,
+                               const int32_t* sel_key, const float* sel_val, const void* w_dec_bf16,
+                               const int32_t* budgets_host, int n_budgets, int64_t n_rows, int d, const float* w_norm,
+                               float eps, void* out_x_bf16, void* out_h_bf16, float* out_rstd, int64_t out_stride,
+                               void* stream);
 
 /* ---- K2: low-rank direction removal x' = x - (x U) U^T ----------------------------------
  * No code in the reference (Execution Plan:148 r_edited = r - P_U(r); random control :150).

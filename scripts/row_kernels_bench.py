@@ -69,3 +69,14 @@ for b in (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024):
                       "frac_of_measured_copy_ranked_prefix": ba / ms2 / 1e6 / peaks["hbm_gbs"]}), flush=True)
 print(json.dumps({"kernel": "K1b, 11-budget sweep", "GBps_table_lookup": 11 * ba / tot_old / 1e6, "GBps_ranked_prefix": 11 * ba / tot_new / 1e6,
                   "frac_ranked_prefix": 11 * ba / tot_new / 1e6 / peaks["hbm_gbs"]}), flush=True)
+BS = [1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024]
+ms = timed(lambda: ops.sae_ablate_ranked_multi(x[:n_enc], ranked, sae, BS, w_norm=w_norm))
+print(json.dumps({"kernel": "K1b, all 11 budgets in one pass (tb_sae_ablate_ranked_multi)", "rows": n_enc, "ms": ms,
+                  "ms_one_launch_per_budget": tot_new, "GBps_algorithmic": 11 * ba / ms / 1e6,
+                  "frac_of_measured_copy": 11 * ba / ms / 1e6 / peaks["hbm_gbs"],
+                  "bytes_moved_GB": (n_enc * D * 2 * 12) / 1e9}), flush=True)
+for sub in ([1, 2, 4, 8], [128, 256, 512, 1024], [1024]):
+    ms = timed(lambda: ops.sae_ablate_ranked_multi(x[:n_enc], ranked, sae, sub, w_norm=w_norm))
+    print(json.dumps({"kernel": "K1b multi", "budgets": sub, "ms": ms}), flush=True)
+ms = timed(lambda: ops.sae_ablate_ranked_multi(x[:n_enc], ranked, sae, BS, w_norm=w_norm, want_h=False, want_rstd=True))
+print(json.dumps({"kernel": "K1b multi, rstd only (no row output)", "ms": ms}), flush=True)

@@ -48,6 +48,8 @@ SIGNATURES = {
     "tb_sae_ablate_decode": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int,
                                      c_int64, c_int, c_int, _P, c_float, _P, _P, _P]),
     "tb_sae_rank_lists": (c_int, [_P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, _P, _P, _P]),
+    "tb_sae_ablate_ranked_multi": (c_int, [_P, _P, c_int, _P, _P, _P, _P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P, c_int64,
+                                           _P]),
     "tb_sae_ablate_ranked": (c_int, [_P, _P, c_int, _P, _P, _P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P, _P]),
     "tb_lowrank_remove": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
     "tb_lowrank_tc_scratch_bytes": (c_int64, [c_int64, c_int, c_int]),

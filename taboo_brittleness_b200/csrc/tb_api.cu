@@ -722,6 +722,72 @@ int tb_sae_ablate_ranked(const void* x, const int64_t* row_start, int cap, const
   return TB_OK;
 }
 
+int tb_sae_ablate_ranked_multi(const void* x, const int64_t* row_start, int cap, const int32_t* sel_count,
+                               const int32_t* sel_key, const float* sel_val, const void* w_dec, const int32_t* budgets_host,
+                               int n_budgets, int64_t n_rows, int d, const float* w_norm, float eps, void* out_x, void* out_h,
+                               float* out_rstd, int64_t out_stride, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!x || !sel_count || !sel_key || !sel_val || !w_dec || !budgets_host) return fail(TB_ERR_INVALID, "null pointer");
+  if (n_budgets < 1 || n_budgets > tb::kMaxBudgets) return fail(TB_ERR_INVALID, "n_budgets=%d outside [1, %d]", n_budgets, tb::kMaxBudgets);
+  for (int k = 0; k < n_budgets; ++k)
+    if (budgets_host[k] < 0 || budgets_host[k] > tb::kRankedMax || (k > 0 && budgets_host[k] <= budgets_host[k - 1]))
+      return fail(TB_ERR_INVALID, "budgets must be strictly ascending within [0, %d]", tb::kRankedMax);
+  if (!out_x && !out_h && !out_rstd) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  if (!row_start && cap <= 0) return fail(TB_ERR_INVALID, "fixed-stride lists need cap > 0");
+  if (n_rows == 0) return TB_OK;
+  if (d <= 0 || d % 8 != 0) return fail(TB_ERR_INVALID, "d=%d must be a positive multiple of 8", d);
+  if ((out_x || out_h) && n_budgets > 1 && out_stride < n_rows * static_cast<int64_t>(d))
+    return fail(TB_ERR_INVALID, "out_stride=%lld smaller than one output (%lld elements)", static_cast<long long>(out_stride),
+                static_cast<long long>(n_rows * static_cast<int64_t>(d)));
+  const int nv = (d / 8 + tb::kRowGroupThreads - 1) / tb::kRowGroupThreads;
+  if (nv > 8) return fail(TB_ERR_INVALID, "d=%d too large for the ablate/decode kernel (max 8192)", d);
+  tb::AblateRankedMultiArgs m;
+  tb::AblateRankedArgs& a = m.base;
+  a.x = static_cast<const __nv_bfloat16*>(x);
+  a.row_start = row_start;
+  a.cap = cap;
+  a.sel_count = sel_count;
+  a.sel_key = sel_key;
+  a.sel_val = sel_val;
+  a.w_dec = static_cast<const __nv_bfloat16*>(w_dec);
+  a.budget = budgets_host[n_budgets - 1];
+  {
+    const char* hm = getenv("TB_HEAVY_MIN");
+    a.heavy_min = hm ? atoi(hm) : 48;
+    if (a.heavy_min < 1 || d > 8 * 2 * tb::kHeavyThreads) a.heavy_min = tb::kRankedMax + 1;
+  }
+  a.w_norm = w_norm;
+  a.eps = eps;
+  a.out_x = static_cast<__nv_bfloat16*>(out_x);
+  a.out_h = static_cast<__nv_bfloat16*>(out_h);
+  a.out_rstd = out_rstd;
+  a.n_rows = static_cast<int>(n_rows);
+  a.d = d;
+  m.n_budgets = n_budgets;
+  for (int k = 0; k < tb::kMaxBudgets; ++k) m.budgets[k] = k < n_budgets ? budgets_host[k] : 0;
+  m.out_stride = out_stride;
+  const int64_t blocks = (n_rows + tb::kRowGroups - 1) / tb::kRowGroups;
+  const int64_t max_grid = static_cast<int64_t>(di.sms) * 4;
+  const unsigned grid = static_cast<unsigned>(blocks < max_grid ? blocks : max_grid);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (nv == 1) tb::tb_ablate_ranked_multi_kernel<1><<<grid, tb::kAblThreads, 0, st>>>(m);
+  else if (nv == 2) tb::tb_ablate_ranked_multi_kernel<2><<<grid, tb::kAblThreads, 0, st>>>(m);
+  else if (nv <= 4) tb::tb_ablate_ranked_multi_kernel<4><<<grid, tb::kAblThreads, 0, st>>>(m);
+  else tb::tb_ablate_ranked_multi_kernel<8><<<grid, tb::kAblThreads, 0, st>>>(m);
+  TB_CUDA(cudaGetLastError());
+  if (a.heavy_min <= a.budget && d <= 8 * 2 * tb::kHeavyThreads) {
+    const int64_t hgrid = static_cast<int64_t>(di.sms) * 2;
+    const unsigned hg = static_cast<unsigned>(n_rows < hgrid ? n_rows : hgrid);
+    if (d <= 8 * tb::kHeavyThreads) tb::tb_ablate_heavy_multi_kernel<1><<<hg, tb::kHeavyThreads, 0, st>>>(m);
+    else tb::tb_ablate_heavy_multi_kernel<2><<<hg, tb::kHeavyThreads, 0, st>>>(m);
+    TB_CUDA(cudaGetLastError());
+  }
+  return TB_OK;
+}
+
 int tb_lowrank_remove(const void* x, const void* ut, int r, int64_t n_rows, int d, const float* w_norm,
                       float eps, void* out_x, void* out_h, void* stream) {
   DevInfo di;

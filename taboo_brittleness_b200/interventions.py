@@ -71,6 +71,11 @@ class Readout:
         return getattr(self.lens, name)
 
 
+def _free_bytes(dev) -> int:
+    """Bytes a new tensor can still get: what the driver reports free plus what torch's caching allocator holds unused."""
+    return int(torch.cuda.mem_get_info(dev)[0] + torch.cuda.memory_reserved(dev) - torch.cuda.memory_allocated(dev))
+
+
 class InterventionEngine:
     """Holds one SAE + one lens (norm weight and unembedding shard) and runs sweeps over them."""
 
@@ -95,6 +100,7 @@ class InterventionEngine:
         self._dense_logits2 = None
         self._update_matrix = None
         self.use_ranked = True       # nested budgets read prefixes of rank-ordered lists (ops.rank_lists) in K1b
+        self.multi_budget = True     # ... and all budgets of a chain are produced in one pass over the rows when they fit
         self.ll_alpha = 0.5          # candidate threshold = ll_alpha * previous condition's k-th best sum
         self.ll_cand_cap = 256       # candidate slots per prompt
 
@@ -178,7 +184,7 @@ class InterventionEngine:
         """Lens readout + exact LL-Top-k of a condition with no predecessor, one GEMM sweep (see ``ll_dense_first``)."""
         n, V = h.shape[0], self.lens.w_u.shape[0]
         step = max(ops.LL_SLOTS, min(self.ll_dense_rows, n) // ops.LL_SLOTS * ops.LL_SLOTS)
-        free = torch.cuda.mem_get_info(h.device)[0]
+        free = _free_bytes(h.device)
         have = 0 if self._dense_logits is None else self._dense_logits.numel() * 4
         while step > 8 * ops.LL_SLOTS and step * V * 4 > have + 0.8 * free:    # do not take more than most of what is free
             step = step // 2 // ops.LL_SLOTS * ops.LL_SLOTS
@@ -289,16 +295,37 @@ class InterventionEngine:
                 e1.record()      # part of K1b's cost, no algorithmic bytes of its own
                 self.stats.row_events.append((e0, e1, 0.0))
             self.stats.launches += 1
-        for b in sorted(int(v) for v in budgets):
-            if fusable and state is not None:
+        bs = sorted(set(int(v) for v in budgets))
+        h_all = None
+        if ranked is not None and self.multi_budget and 1 < len(bs) <= 16:
+            # all budgets' lens operands in ONE pass over the rows (x read once, every W_dec row gathered once): needs
+            # len(bs) operands of rows * d bf16 at once
+            need = len(bs) * x.shape[0] * x.shape[1] * 2
+            if need <= 0.45 * _free_bytes(x.device):
+                if self.time_lens:
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                _, h_all, _ = ops.sae_ablate_ranked_multi(x, ranked, self.sae, bs, w_norm=self.lens.w_norm, eps=self.lens.eps)
+                if self.time_lens:
+                    e1.record()      # algorithmic traffic: x in, h out, per budget
+                    self.stats.row_events.append((e0, e1, 4.0 * x.shape[0] * x.shape[1] * len(bs)))
+                self.stats.launches += 1
+        for i, b in enumerate(bs):
+            if h_all is not None:
+                if fusable and state is not None:
+                    out[b], state = self.read_fused(h_all[i], secret_id, ll, state)
+                    continue
+                r = self.read(h_all[i], secret_id, True, ll)
+            elif fusable and state is not None:
                 out[b], state = self.ablate_and_read(x, acts, rank, b, rank_rows=rank_rows, secret_id=secret_id,
                                                      mode=mode, ll=ll, ll_state=state, ranked=ranked)
+                continue
             else:
                 r = self.ablate_and_read(x, acts, rank, b, rank_rows=rank_rows, secret_id=secret_id, mode=mode, ll=ll,
                                          ranked=ranked)
-                out[b] = r
-                if fusable:
-                    state = LLState(r.lens.lse, r.ll_sum[:, ll.k - 1].contiguous())
+            out[b] = r
+            if fusable:
+                state = LLState(r.lens.lse, r.ll_sum[:, ll.k - 1].contiguous())
         return out, state
 
     def _nested_budgets_overlapped(self, x, acts, rank, rank_rows: int, budgets: Sequence[int], secret_id, mode: str,
@@ -437,16 +464,20 @@ class InterventionEngine:
         ids, _, rank = self.targeted_rank(acts, T, m=min(max(bs), TB_TOPM_MAX))
         ranked = ops.rank_lists(acts, rank, T)
         A = ops.rank_acts_dense(ranked, n, split)
-        rstd = torch.empty(len(bs), n, dtype=torch.float32, device=x.device)
-        for i, b in enumerate(bs):      # K1b without an output row: only the RMSNorm factor of the rounded x'
-            ops.sae_ablate_ranked(x, ranked, self.sae, b, w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False,
-                                  want_h=False, out_rstd=rstd[i])
-        self.stats.launches += 3 + len(bs)
+        if len(bs) <= 16:               # K1b without an output row: only the RMSNorm factors of the rounded x', one pass
+            _, _, rstd = ops.sae_ablate_ranked_multi(x, ranked, self.sae, bs, w_norm=self.lens.w_norm, eps=self.lens.eps,
+                                                     want_h=False, want_rstd=True)
+        else:
+            rstd = torch.empty(len(bs), n, dtype=torch.float32, device=x.device)
+            for i, b in enumerate(bs):
+                ops.sae_ablate_ranked(x, ranked, self.sae, b, w_norm=self.lens.w_norm, eps=self.lens.eps, want_x=False,
+                                      want_h=False, out_rstd=rstd[i])
+        self.stats.launches += 4
         if ll is not None and (ll.seg is not None or ll.rows_per_prompt != T):
             raise ops.TabooKernelError("rank-update sweep: LL-Top-k needs 128 row slots per prompt", ops._lib.TB_ERR_INVALID)
         n_scratch = 2 if ll is not None else 1
         step = max(T, min(sub_rows, n) // T * T)
-        free = torch.cuda.mem_get_info(x.device)[0]
+        free = _free_bytes(x.device)
         have = sum(0 if t is None else t.numel() * 4 for t in (self._dense_logits, self._dense_logits2)[:n_scratch])
         while step > 8 * T and n_scratch * step * V * 4 > have + 0.8 * free:
             step = step // 2 // T * T

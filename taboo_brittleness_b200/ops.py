@@ -7,7 +7,7 @@ a missing library or a failed call raises ``TabooKernelError``.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Optional, Tuple
+from typing import Optional, Sequence, Tuple
 
 import torch
 
@@ -388,6 +388,32 @@ def sae_ablate_ranked(x: torch.Tensor, ranked: RankedActs, sae: SaeWeights, budg
                                            _ptr(ranked.val), _ptr(sae.w_dec), int(budget), n, d, _ptr(w_norm), eps,
                                            _ptr(out_x), _ptr(out_h), _ptr(out_rstd), _stream()), "tb_sae_ablate_ranked")
     return out_x, out_h
+
+
+def sae_ablate_ranked_multi(x: torch.Tensor, ranked: RankedActs, sae: SaeWeights, budgets: Sequence[int], *,
+                            w_norm: Optional[torch.Tensor] = None, eps: float = GEMMA2_EPS, want_x: bool = False,
+                            want_h: bool = True, want_rstd: bool = False):
+    """All nested budgets in one pass over the rows (``tb_sae_ablate_ranked_multi``): returns (x' bf16 [B, rows, d] or None,
+    h bf16 [B, rows, d] or None, rstd f32 [B, rows] or None) for the ascending ``budgets``; the same bits as one
+    ``sae_ablate_ranked`` call per budget."""
+    _need(x, torch.bfloat16, "x", 2)
+    n, d = x.shape
+    bs = [int(b) for b in budgets]
+    if bs != sorted(set(bs)) or not bs:
+        raise TabooKernelError("budgets must be strictly ascending", _lib.TB_ERR_INVALID)
+    B = len(bs)
+    out_x = torch.empty(B, n, d, dtype=torch.bfloat16, device=x.device) if want_x else None
+    out_h = torch.empty(B, n, d, dtype=torch.bfloat16, device=x.device) if want_h else None
+    rstd = torch.empty(B, n, dtype=torch.float32, device=x.device) if want_rstd else None
+    if n == 0:
+        return out_x, out_h, rstd
+    import ctypes
+    arr = (ctypes.c_int32 * B)(*bs)
+    check(_lib.load().tb_sae_ablate_ranked_multi(_ptr(x), _ptr(ranked.row_start), ranked.cap, _ptr(ranked.count), _ptr(ranked.key),
+                                                 _ptr(ranked.val), _ptr(sae.w_dec), ctypes.cast(arr, ctypes.c_void_p), B, n, d,
+                                                 _ptr(w_norm), eps, _ptr(out_x), _ptr(out_h), _ptr(rstd), n * d, _stream()),
+          "tb_sae_ablate_ranked_multi")
+    return out_x, out_h, rstd
 
 
 LOWRANK_SMALL = 8     # ranks up to this can use the kernel that keeps U^T in shared memory

@@ -273,6 +273,49 @@ def test_ranked_lists_fixed_stride_random_table_and_empty(cuda_lib, problem, enc
     assert r0.count.shape == (0,) and e0.shape == (0, D)
 
 
+def test_all_budgets_in_one_pass_equal_one_launch_per_budget(cuda_lib, problem, encoded):
+    """tb_sae_ablate_ranked_multi: the residual, the lens operand and the RMSNorm factor of every budget of a chain from one
+    pass over the rows -- bit for bit what one tb_sae_ablate_ranked launch per budget gives (CSR lists with <bos>-scale rows
+    for the whole-CTA kernel, fixed-stride lists with one shared ranking, every row forced through either kernel)."""
+    import os
+    from taboo_brittleness_b200 import ops
+    acts, w, xs = encoded["acts"], encoded["w"], encoded["x"]
+    mean = ops.latent_mean(acts, rows_per_prompt=T)
+    _, _, rank = ops.topm_select(mean, 1024)
+    ranked = ops.rank_lists(acts, rank, T)
+    w_norm = synthetic.make_lens(D, 8, seed=1).w_norm.cuda()
+    budgets = [1, 2, 4, 8, 16, 32, 64, 100, 256, 512, 1024]
+
+    def check(x_rows, rk, same_kernel=True):
+        mx, mh, mr = ops.sae_ablate_ranked_multi(x_rows, rk, w, budgets, w_norm=w_norm, want_x=True, want_h=True, want_rstd=True)
+        for i, b in enumerate(budgets):
+            rstd = torch.empty(x_rows.shape[0], dtype=torch.float32, device="cuda")
+            ox, oh = ops.sae_ablate_ranked(x_rows, rk, w, b, w_norm=w_norm, want_x=True, want_h=True, out_rstd=rstd)
+            torch.cuda.synchronize()
+            assert torch.equal(mx[i], ox), b
+            if same_kernel:
+                assert torch.equal(mh[i], oh) and torch.equal(mr[i], rstd), b
+            else:   # a long list sends a row to the whole-CTA kernel for ALL budgets here, per budget only from 48 entries
+                    # on: the two kernels add the squares in a different order (512 vs 128 threads): last bit of rstd
+                assert torch.allclose(mr[i], rstd, rtol=1e-6) and (mh[i] != oh).float().mean().item() < 1e-4, b
+
+    check(xs, ranked, same_kernel=False)
+    for hm in ("1", "100000"):          # every row through the whole-CTA kernel / through the row-group kernel
+        os.environ["TB_HEAVY_MIN"] = hm
+        try:
+            check(xs, ranked)
+        finally:
+            del os.environ["TB_HEAVY_MIN"]
+    rows = [r for r in range(P * T) if r % T != 0][:150]
+    sp = ops.sae_encode(xs[rows].contiguous(), w, cap=256)
+    rk2 = ops.rank_lists(sp, ops.rank_table_from_indices(oracle.random_latents(S, seed=11, m=1024), S).cuda(), 0)
+    check(xs[rows].contiguous(), rk2, same_kernel=False)
+    only_h = ops.sae_ablate_ranked_multi(xs, ranked, w, [4, 64], w_norm=w_norm)
+    assert only_h[0] is None and only_h[2] is None and only_h[1].shape == (2, xs.shape[0], D)
+    with pytest.raises(ops.TabooKernelError):
+        ops.sae_ablate_ranked_multi(xs, ranked, w, [8, 4], w_norm=w_norm)
+
+
 def test_encode_with_latent_chunks_equals_one_sweep(cuda_lib, problem):
     """Large batches encode with the latent sweep cut in two (tb_sae_encode_chunked: sub-lists per chunk, merged in
     place): same lists, counts and overflow handling as the one-sweep kernel (20,000 rows: ragged last block,
