@@ -530,7 +530,15 @@ tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __r
   // ---- pass 1: top 11 bits
   for (int i = tid; i < 2048; i += kTopmThreads) hist[i] = 0;
   __syncthreads();
-  for (int j = tid; j < S; j += kTopmThreads) atomicAdd(&hist[float_key(v[j]) >> 21], 1u);
+  for (int base = 0; base < S; base += kTopmThreads) {
+    // lanes of a warp that hit the same bin add once (column sums of probabilities crowd into a handful of bins: one
+    // shared-memory atomic per element serialised the whole pass at V = 256000)
+    const int j = base + tid;
+    const bool in = j < S;
+    const uint32_t bin = in ? (float_key(v[j]) >> 21) : 0xffffffffu;
+    const uint32_t peers = __match_any_sync(0xffffffffu, bin);
+    if (in && (tid & 31) == __ffs(peers) - 1) atomicAdd(&hist[bin], static_cast<uint32_t>(__popc(peers)));
+  }
   __syncthreads();
   pick_bin(hist, 2048, mm, &s_bin, &s_above);
   __syncthreads();
@@ -578,6 +586,7 @@ tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __r
       gt = k > kth;
       eq = k == kth;
     }
+    if (!__syncthreads_or(gt || eq)) continue;      // nothing at or above the threshold in these 1024 values (the usual case for large S)
     const uint32_t bal_eq = __ballot_sync(0xffffffffu, eq);
     const uint32_t bal_gt = __ballot_sync(0xffffffffu, gt);
     if (lane == 0) { s_warp_eq[warp] = __popc(bal_eq); s_warp_gt[warp] = __popc(bal_gt); }
