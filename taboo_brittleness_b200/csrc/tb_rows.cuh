@@ -530,14 +530,21 @@ tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __r
   // ---- pass 1: top 11 bits
   for (int i = tid; i < 2048; i += kTopmThreads) hist[i] = 0;
   __syncthreads();
-  for (int base = 0; base < S; base += kTopmThreads) {
-    // lanes of a warp that hit the same bin add once (column sums of probabilities crowd into a handful of bins: one
-    // shared-memory atomic per element serialised the whole pass at V = 256000)
-    const int j = base + tid;
-    const bool in = j < S;
-    const uint32_t bin = in ? (float_key(v[j]) >> 21) : 0xffffffffu;
-    const uint32_t peers = __match_any_sync(0xffffffffu, bin);
-    if (in && (tid & 31) == __ffs(peers) - 1) atomicAdd(&hist[bin], static_cast<uint32_t>(__popc(peers)));
+  for (int base = 0; base < S; base += 4 * kTopmThreads) {
+    // four loads in flight per thread (one block reads a whole row of up to V values: latency-bound otherwise); lanes of a
+    // warp that hit the same bin add once (column sums of probabilities crowd into a handful of bins: one shared-memory
+    // atomic per element serialised the whole pass at V = 256000)
+    uint32_t bin[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = base + u * kTopmThreads + tid;
+      bin[u] = j < S ? (float_key(v[j]) >> 21) : 0xffffffffu;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t peers = __match_any_sync(0xffffffffu, bin[u]);
+      if (bin[u] != 0xffffffffu && (tid & 31) == __ffs(peers) - 1) atomicAdd(&hist[bin[u]], static_cast<uint32_t>(__popc(peers)));
+    }
   }
   __syncthreads();
   pick_bin(hist, 2048, mm, &s_bin, &s_above);
@@ -548,9 +555,16 @@ tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __r
   // ---- pass 2: middle 11 bits inside bin b1
   for (int i = tid; i < 2048; i += kTopmThreads) hist[i] = 0;
   __syncthreads();
-  for (int j = tid; j < S; j += kTopmThreads) {
-    const uint32_t k = float_key(v[j]);
-    if ((k >> 21) == b1) atomicAdd(&hist[(k >> 10) & 0x7ffu], 1u);
+  for (int base = 0; base < S; base += 4 * kTopmThreads) {
+    uint32_t k[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = base + u * kTopmThreads + tid;
+      k[u] = j < S ? float_key(v[j]) : 0u;       // (key 0 = -NaN pattern, never a value's key inside a chosen bin with need > 0)
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (base + u * kTopmThreads + tid < S && (k[u] >> 21) == b1) atomicAdd(&hist[(k[u] >> 10) & 0x7ffu], 1u);
   }
   __syncthreads();
   pick_bin(hist, 2048, need, &s_bin, &s_above);
@@ -562,9 +576,16 @@ tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __r
   for (int i = tid; i < 1024; i += kTopmThreads) hist[i] = 0;
   __syncthreads();
   const uint32_t hi22 = (b1 << 11) | b2;
-  for (int j = tid; j < S; j += kTopmThreads) {
-    const uint32_t k = float_key(v[j]);
-    if ((k >> 10) == hi22) atomicAdd(&hist[k & 0x3ffu], 1u);
+  for (int base = 0; base < S; base += 4 * kTopmThreads) {
+    uint32_t k[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int j = base + u * kTopmThreads + tid;
+      k[u] = j < S ? float_key(v[j]) : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (base + u * kTopmThreads + tid < S && (k[u] >> 10) == hi22) atomicAdd(&hist[k[u] & 0x3ffu], 1u);
   }
   __syncthreads();
   pick_bin(hist, 1024, need, &s_bin, &s_above);
@@ -577,12 +598,26 @@ tb_topm_select_kernel(const float* __restrict__ mean, int S, int m, int32_t* __r
   for (int i = tid; i < kTopmMax; i += kTopmThreads) sel[i] = 0ull;
   __syncthreads();
   const int warp = tid >> 5, lane = tid & 31;
+  uint32_t kpre[4] = {0u, 0u, 0u, 0u};
+  bool live = true;                               // does the current group of four rounds hold anything at or above the threshold?
   for (int base = 0; base < S; base += kTopmThreads) {
+    const int u4 = (base / kTopmThreads) & 3;
+    if (u4 == 0) {                                // four rounds' values at once, one barrier to rule all four out
+      bool any = false;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int jj = base + u * kTopmThreads + tid;
+        kpre[u] = jj < S ? float_key(v[jj]) : 0u;
+        any = any || (jj < S && kpre[u] >= kth);
+      }
+      live = __syncthreads_or(any) != 0;
+    }
+    if (!live) continue;
     const int j = base + tid;
     uint32_t k = 0;
     bool gt = false, eq = false;
     if (j < S) {
-      k = float_key(v[j]);
+      k = u4 == 0 ? kpre[0] : u4 == 1 ? kpre[1] : u4 == 2 ? kpre[2] : kpre[3];
       gt = k > kth;
       eq = k == kth;
     }
