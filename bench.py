@@ -234,13 +234,28 @@ def leg_projection_vocab_shard(args, ctx):
     state = {"timers": None, "k2": None, "hgather": None, "check": None, "v": (v0, v1),
              "shard": ops.LensWeights(w_norm=lens.w_norm, w_u=lens.w_u[v0:v1], vocab_offset=v0)}
 
+    tc_ranks = [r for r in RANKS if r >= ops.LOWRANK_MULTI_MIN]
+
     def one_pass(k2_mode):
+        h_multi = {}
+        if k2_mode == "replicated" and len(tc_ranks) >= 2 and D % 256 == 0:
+            # the tensor-core ranks share one coefficient pass (tb_lowrank_remove_tc_multi: x U of the largest rank once)
+            a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
+            a.record()
+            _, hm = ops.lowrank_remove_multi(x, U, tc_ranks, w_norm=lens.w_norm, eps=lens.eps)
+            b.record()
+            if state["k2"] is not None:
+                state["k2"].append((a, b))
+            h_multi = {r: hm[i] for i, r in enumerate(tc_ranks)}
         for r in RANKS:
             Ur = U[:, :r].contiguous()
             a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
             c = torch.cuda.Event(enable_timing=True)
             a.record()
-            if k2_mode == "replicated":
+            if r in h_multi:
+                h = h_multi[r]
+                b.record()
+            elif k2_mode == "replicated":
                 _, h = ops.lowrank_remove(x, Ur, w_norm=lens.w_norm, eps=lens.eps, want_x=False, want_h=True)
                 b.record()
             else:

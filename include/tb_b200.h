@@ -163,6 +163,16 @@ int64_t tb_lowrank_tc_scratch_bytes(int64_t n_rows, int d, int r);
 int tb_lowrank_remove_tc(const void* x_bf16, const void* ut_bf16, int r, int64_t n_rows, int d,
                          const float* w_norm, float eps, void* scratch, int64_t scratch_bytes,
                          void* out_x_bf16, void* out_h_bf16, void* stream);
+/* Nested ranks (the first r columns of one U, for several r: Plan:148-150 sweeps r = 1 .. 64) in one call: the
+ * coefficients x U of the largest rank are computed ONCE (one pass over x instead of one per rank) and every rank's
+ * removal + norm pass uses its leading r of them -- the same products in the same order, so the same bits as one
+ * tb_lowrank_remove_tc call per rank. ranks_host: n_ranks (<= 16) strictly ascending values, a HOST array; ut holds the
+ * largest rank's rows; output k at out + k * out_stride elements; scratch as for the largest rank. d % 256 == 0,
+ * d <= 4096. */
+int tb_lowrank_remove_tc_multi(const void* x_bf16, const void* ut_bf16, const int32_t* ranks_host, int n_ranks,
+                               int64_t n_rows, int d, const float* w_norm, float eps, void* scratch,
+                               int64_t scratch_bytes, void* out_x_bf16, void* out_h_bf16, int64_t out_stride,
+                               void* stream);
 
 /* ---- a6: final RMSNorm -------------------------------------------------------------------
  * Replaces model.model.norm(...), src/models.py:135 (Gemma2RMSNorm.forward on a bf16

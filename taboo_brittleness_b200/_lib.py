@@ -54,6 +54,7 @@ SIGNATURES = {
     "tb_lowrank_remove": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P]),
     "tb_lowrank_tc_scratch_bytes": (c_int64, [c_int64, c_int, c_int]),
     "tb_lowrank_remove_tc": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, c_int64, _P, _P, _P]),
+    "tb_lowrank_remove_tc_multi": (c_int, [_P, _P, _P, c_int, c_int64, c_int, _P, c_float, _P, c_int64, _P, _P, c_int64, _P]),
     "tb_lowrank_fused_supported": (c_int, [c_int, c_int]),
     "tb_lowrank_remove_fused": (c_int, [_P, _P, c_int, c_int64, c_int, _P, c_float, _P, _P, _P, _P]),
     "tb_rmsnorm": (c_int, [_P, _P, c_float, c_int64, c_int, _P, _P]),

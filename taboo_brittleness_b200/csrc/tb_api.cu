@@ -888,6 +888,65 @@ ProjTcPlan proj_tc_plan(int64_t n_rows, int d, int r, int sms) {
 }
 }  // namespace
 
+// steps 2 + 3 of K2 on the tensor cores in one cluster kernel (tb_cluster_rows.cuh): rank r (padded to rp) removed with
+// the coefficients in cb, whose layout is [C_hi(c_rp) | C_lo(c_rp)], c_rp >= rp
+static bool apply_cluster_supported(int d) { return d % tb::kCrW == 0 && d / tb::kCrW <= tb::kCrMaxCta; }
+static int launch_apply_cluster(const void* x, const __nv_bfloat16* cb, int c_rp, const void* ut, int r, int rp, int64_t n_rows,
+                                int d, const float* w_norm, float eps, void* out_x, void* out_h, cudaStream_t s, int sms) {
+  tb::CaArgs a;
+  a.n_rows = static_cast<int>(n_rows);
+  a.d = d;
+  a.rp = rp;
+  a.c_rp = c_rp;
+  a.n_cta = d / tb::kCrW;
+  a.n_tiles = static_cast<int>((n_rows + tb::kCrRows - 1) / tb::kCrRows);
+  a.w_norm = w_norm;
+  a.eps = eps;
+  a.want_x = out_x ? 1 : 0;
+  a.want_h = out_h ? 1 : 0;
+  CUtensorMap tmX, tmC, tmU, tmOX, tmOH;
+  int rc = make_tmap(&tmX, x, n_rows, d, tb::kCrRows);
+  if (rc != TB_OK) return rc;
+  rc = make_tmap(&tmC, cb, n_rows, 2 * c_rp, tb::kCrRows);
+  if (rc != TB_OK) return rc;
+  rc = make_tmap(&tmU, ut, r, d, rp);            // rows r .. rp - 1 of the box: zero-filled
+  if (rc != TB_OK) return rc;
+  rc = make_tmap(&tmOX, out_x ? out_x : out_h, n_rows, d, tb::kCrRows);
+  if (rc != TB_OK) return rc;
+  rc = make_tmap(&tmOH, out_h ? out_h : out_x, n_rows, d, tb::kCrRows);
+  if (rc != TB_OK) return rc;
+  auto kern = tb::tb_lowrank_apply_cluster_kernel;
+  TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tb::kCaSmemBytes));
+  if (a.n_cta > 8) TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.blockDim = dim3(tb::kCrThreads, 1, 1);
+  cfg.dynamicSmemBytes = tb::kCaSmemBytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = static_cast<unsigned>(a.n_cta);
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  static int cached[64][tb::kCrMaxCta + 1];
+  int dev = 0;
+  TB_CUDA(cudaGetDevice(&dev));
+  if (cached[dev][a.n_cta] == 0) {
+    cfg.gridDim = dim3(static_cast<unsigned>((sms / a.n_cta) * a.n_cta), 1, 1);
+    int n = 0;
+    TB_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    if (n < 1) return fail(TB_ERR_CUDA, "no cluster of %d CTAs fits on this device", a.n_cta);
+    cached[dev][a.n_cta] = n;
+  }
+  int clusters = cached[dev][a.n_cta];
+  if (clusters > a.n_tiles) clusters = a.n_tiles;
+  cfg.gridDim = dim3(static_cast<unsigned>(clusters * a.n_cta), 1, 1);
+  TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmX, tmC, tmU, tmOX, tmOH, a));
+  return TB_OK;
+}
+
 int64_t tb_lowrank_tc_scratch_bytes(int64_t n_rows, int d, int r) {
   DevInfo di;
   if (device_info(&di) != TB_OK || n_rows < 0 || d <= 0 || r < 1) return -1;
@@ -930,59 +989,8 @@ int tb_lowrank_remove_tc(const void* x, const void* ut, int r, int64_t n_rows, i
   // (tb_cluster_rows.cuh). TB_K2_THREE_PASS=1 keeps the two separate passes below.
   {
     const char* tp = getenv("TB_K2_THREE_PASS");
-    if (!(tp && atoi(tp) != 0) && d % tb::kCrW == 0 && d / tb::kCrW <= tb::kCrMaxCta) {
-      tb::CaArgs a;
-      a.n_rows = static_cast<int>(n_rows);
-      a.d = d;
-      a.rp = pl.rp;
-      a.n_cta = d / tb::kCrW;
-      a.n_tiles = static_cast<int>((n_rows + tb::kCrRows - 1) / tb::kCrRows);
-      a.w_norm = w_norm;
-      a.eps = eps;
-      a.want_x = out_x ? 1 : 0;
-      a.want_h = out_h ? 1 : 0;
-      CUtensorMap tmX, tmC, tmU, tmOX, tmOH;
-      rc = make_tmap(&tmX, x, n_rows, d, tb::kCrRows);
-      if (rc != TB_OK) return rc;
-      rc = make_tmap(&tmC, cb, n_rows, pl.kc, tb::kCrRows);
-      if (rc != TB_OK) return rc;
-      rc = make_tmap(&tmU, ut, r, d, pl.rp);
-      if (rc != TB_OK) return rc;
-      rc = make_tmap(&tmOX, out_x ? out_x : out_h, n_rows, d, tb::kCrRows);
-      if (rc != TB_OK) return rc;
-      rc = make_tmap(&tmOH, out_h ? out_h : out_x, n_rows, d, tb::kCrRows);
-      if (rc != TB_OK) return rc;
-      auto kern = tb::tb_lowrank_apply_cluster_kernel;
-      TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tb::kCaSmemBytes));
-      if (a.n_cta > 8) TB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-      cudaLaunchConfig_t cfg;
-      memset(&cfg, 0, sizeof(cfg));
-      cfg.blockDim = dim3(tb::kCrThreads, 1, 1);
-      cfg.dynamicSmemBytes = tb::kCaSmemBytes;
-      cfg.stream = s;
-      cudaLaunchAttribute attr[1];
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = static_cast<unsigned>(a.n_cta);
-      attr[0].val.clusterDim.y = 1;
-      attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr;
-      cfg.numAttrs = 1;
-      static int cached[64][tb::kCrMaxCta + 1];
-      int dev = 0;
-      TB_CUDA(cudaGetDevice(&dev));
-      if (cached[dev][a.n_cta] == 0) {
-        cfg.gridDim = dim3(static_cast<unsigned>((di.sms / a.n_cta) * a.n_cta), 1, 1);
-        int n = 0;
-        TB_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
-        if (n < 1) return fail(TB_ERR_CUDA, "no cluster of %d CTAs fits on this device", a.n_cta);
-        cached[dev][a.n_cta] = n;
-      }
-      int clusters = cached[dev][a.n_cta];
-      if (clusters > a.n_tiles) clusters = a.n_tiles;
-      cfg.gridDim = dim3(static_cast<unsigned>(clusters * a.n_cta), 1, 1);
-      TB_CUDA(cudaLaunchKernelEx(&cfg, kern, tmX, tmC, tmU, tmOX, tmOH, a));
-      return TB_OK;
-    }
+    if (!(tp && atoi(tp) != 0) && apply_cluster_supported(d))
+      return launch_apply_cluster(x, cb, pl.rp, ut, r, pl.rp, n_rows, d, w_norm, eps, out_x, out_h, s, di.sms);
   }
   // B operand of step 2
   {
@@ -1022,6 +1030,47 @@ int make_tmap_box(CUtensorMap* map, const void* base, int64_t rows, int cols, in
   return make_tmap(map, base, rows, cols, box_rows);
 }
 }  // namespace
+
+int tb_lowrank_remove_tc_multi(const void* x, const void* ut, const int32_t* ranks_host, int n_ranks, int64_t n_rows, int d,
+                               const float* w_norm, float eps, void* scratch, int64_t scratch_bytes, void* out_x, void* out_h,
+                               int64_t out_stride, void* stream) {
+  DevInfo di;
+  int rc = device_info(&di);
+  if (rc != TB_OK) return rc;
+  if (!ranks_host || n_ranks < 1 || n_ranks > 16) return fail(TB_ERR_INVALID, "1 .. 16 ranks");
+  for (int k = 0; k < n_ranks; ++k)
+    if (ranks_host[k] < 1 || ranks_host[k] > tb::kProjMaxRank || (k > 0 && ranks_host[k] <= ranks_host[k - 1]))
+      return fail(TB_ERR_INVALID, "ranks must be strictly ascending within [1, %d]", tb::kProjMaxRank);
+  const int r_max = ranks_host[n_ranks - 1];
+  rc = check_gemm_operands(x, ut, n_rows, r_max, d);
+  if (rc != TB_OK) return rc;
+  if (!out_x && !out_h) return fail(TB_ERR_INVALID, "no output requested");
+  if (out_h && !w_norm) return fail(TB_ERR_INVALID, "out_h needs w_norm");
+  if (!apply_cluster_supported(d)) return fail(TB_ERR_INVALID, "d=%d: needs d %% 256 == 0 and d <= %d", d, tb::kCrW * tb::kCrMaxCta);
+  if (n_ranks > 1 && out_stride < n_rows * static_cast<int64_t>(d)) return fail(TB_ERR_INVALID, "out_stride smaller than one output");
+  if (n_rows == 0) return TB_OK;
+  const ProjTcPlan pl = proj_tc_plan(n_rows, d, r_max, di.sms);
+  if (!scratch || scratch_bytes < static_cast<int64_t>(pl.bytes))
+    return fail(TB_ERR_INVALID, "scratch of %lld bytes needed (tb_lowrank_tc_scratch_bytes of the largest rank), got %lld",
+                static_cast<long long>(pl.bytes), static_cast<long long>(scratch_bytes));
+  if (reinterpret_cast<uintptr_t>(scratch) % 256) return fail(TB_ERR_INVALID, "scratch must be 256-byte aligned");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  __nv_bfloat16* cb = reinterpret_cast<__nv_bfloat16*>(static_cast<uint8_t*>(scratch) + pl.off_cb);
+  {   // the coefficients of all r_max directions, once: rank r uses the first r of them
+    tb::GemmArgs g = make_args(n_rows, r_max, d, 1, 2);
+    tb::CoeffSplitEpi::Params ep{cb, pl.rp};
+    rc = launch_gemm<tb::CoeffSplitEpi, 2>(x, ut, g, ep, s, di.sms);
+    if (rc != TB_OK) return rc;
+  }
+  for (int k = 0; k < n_ranks; ++k) {
+    const int r = ranks_host[k], rp = (r + 31) / 32 * 32;
+    __nv_bfloat16* ox = out_x ? static_cast<__nv_bfloat16*>(out_x) + k * out_stride : nullptr;
+    __nv_bfloat16* oh = out_h ? static_cast<__nv_bfloat16*>(out_h) + k * out_stride : nullptr;
+    rc = launch_apply_cluster(x, cb, pl.rp, ut, r, rp, n_rows, d, w_norm, eps, ox, oh, s, di.sms);
+    if (rc != TB_OK) return rc;
+  }
+  return TB_OK;
+}
 
 int tb_lowrank_fused_supported(int d, int r) {
   DevInfo di;

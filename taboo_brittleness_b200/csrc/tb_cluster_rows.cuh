@@ -501,7 +501,9 @@ constexpr uint32_t kIdescANegate = 1u << 13;
 
 struct CaArgs {
   int n_rows, d;
-  int rp;            // 32 or 64: columns of C_hi (= of C_lo) in cb
+  int rp;            // 32 or 64: coefficients used (columns of C_hi and of C_lo that enter the product)
+  int c_rp;          // 32 or 64 >= rp: columns of C_hi (= of C_lo) in cb's layout [C_hi(c_rp) | C_lo(c_rp)] -- larger than rp
+                     // when one coefficient pass for the largest rank serves a whole sweep of nested ranks
   int n_cta, n_tiles;
   const float* w_norm;
   float eps;
@@ -535,7 +537,7 @@ tb_lowrank_apply_cluster_kernel(const __grid_constant__ CUtensorMap tmX, const _
   const int num_clusters = static_cast<int>(gridDim.x) / n_cta;
   const int col0 = crank * kCrW;
   const int rp = a.rp;
-  const int kc = 2 * rp / 64;                                 // 64-column blocks of [C_hi | C_lo]: 1 or 2
+  const int kc = 2 * a.c_rp / 64;                             // 64-column blocks of [C_hi | C_lo] in cb: 1 or 2
   const uint32_t u_group_bytes = static_cast<uint32_t>(rp) * 128u;
   const uint32_t smem0 = smem_u32(smem);
 
@@ -610,13 +612,14 @@ tb_lowrank_apply_cluster_kernel(const __grid_constant__ CUtensorMap tmX, const _
       tc_fence_after();
       if (elect_one()) {
         const uint32_t d_tmem = tmem_base + s * kCrW;
-        for (int kb = 0; kb < kc; ++kb) {
-          const uint64_t da = umma_desc_k_sw128(smem0 + kCaOffC + kb * kCrGroupBytes);
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const int urow = (kb * 64 + k * 16) % rp;       // heads and remainders multiply the same rows of U^T
-            const uint64_t db = umma_desc_mn_sw128(smem0 + kCaOffU + urow * 128, u_group_bytes);
-            umma_bf16<1>(d_tmem, da + static_cast<uint64_t>(2 * k), db, idesc_p, (kb | k) != 0 ? 1u : 0u);
+        // heads, then remainders, 16 coefficients per step; both multiply the same rows of U^T. Column of cb =
+        // part * c_rp + 16 k: the same sequence of products whatever c_rp is (same bits)
+        for (int part = 0; part < 2; ++part) {
+          for (int k = 0; k < rp / 16; ++k) {
+            const int ccol = part * a.c_rp + k * 16;
+            const uint64_t da = umma_desc_k_sw128(smem0 + kCaOffC + (ccol >> 6) * kCrGroupBytes);
+            const uint64_t db = umma_desc_mn_sw128(smem0 + kCaOffU + k * 16 * 128, u_group_bytes);
+            umma_bf16<1>(d_tmem, da + static_cast<uint64_t>(2 * ((ccol & 63) >> 4)), db, idesc_p, (part | k) != 0 ? 1u : 0u);
           }
         }
         umma_commit(smem_u32(empty_c));

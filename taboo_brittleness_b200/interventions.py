@@ -552,12 +552,33 @@ class InterventionEngine:
         exact lse as reference (like nested ablation budgets; results are exact either way)."""
         fusable = (ll is not None and self.ll_fused and ll.seg is None and ll.rows_per_prompt == ops.LL_SLOTS)
         out, state = {}, None
-        for r in sorted(int(v) for v in ranks):
-            Ur = U[:, :r].contiguous()
-            if fusable and state is not None:
-                out[r], state = self.project_and_read(x, Ur, secret_id=secret_id, ll=ll, ll_state=state)
+        rs = sorted(set(int(v) for v in ranks))
+        # the tensor-core ranks share ONE coefficient pass (the coefficients of the largest rank: rank r uses its first r)
+        tc = [r for r in rs if r >= ops.LOWRANK_MULTI_MIN]
+        h_multi = {}
+        d = x.shape[1]
+        if (self.multi_budget and len(tc) >= 2 and d % 256 == 0 and d <= 4096
+                and len(tc) * x.shape[0] * d * 2 <= 0.45 * _free_bytes(x.device)):
+            if self.time_lens:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            _, hm = ops.lowrank_remove_multi(x, U, tc, w_norm=self.lens.w_norm, eps=self.lens.eps)
+            if self.time_lens:
+                e1.record()
+                self.stats.row_events.append((e0, e1, 4.0 * x.shape[0] * d * len(tc)))
+            self.stats.launches += 1
+            h_multi = {r: hm[i] for i, r in enumerate(tc)}
+        for r in rs:
+            if r in h_multi:
+                if fusable and state is not None:
+                    out[r], state = self.read_fused(h_multi[r], secret_id, ll, state)
+                    continue
+                out[r] = self.read(h_multi[r], secret_id, True, ll)
+            elif fusable and state is not None:
+                out[r], state = self.project_and_read(x, U[:, :r].contiguous(), secret_id=secret_id, ll=ll, ll_state=state)
+                continue
             else:
-                out[r] = self.project_and_read(x, Ur, secret_id=secret_id, ll=ll)
-                if fusable:
-                    state = LLState(out[r].lens.lse, out[r].ll_sum[:, ll.k - 1].contiguous())
+                out[r] = self.project_and_read(x, U[:, :r].contiguous(), secret_id=secret_id, ll=ll)
+            if fusable:
+                state = LLState(out[r].lens.lse, out[r].ll_sum[:, ll.k - 1].contiguous())
         return out

@@ -138,3 +138,32 @@ def test_lowrank_cluster_apply_equals_separate_passes(cuda_lib, r, n_rows, monke
     assert torch.equal(ah, ah2)
     assert (ax != tx).float().mean().item() < 1e-3 and (ah != th).float().mean().item() < 1e-3
     assert ((ax.float() - tx.float()).abs() <= 0.0079 * tx.float().abs() + 1e-3).all()
+
+
+@pytest.mark.parametrize("d", [512, 3584])
+def test_nested_ranks_share_one_coefficient_pass(cuda_lib, d):
+    """tb_lowrank_remove_tc_multi: the coefficients of the largest rank computed once, every nested rank's removal + norm
+    pass on its leading ones -- bit for bit what one tb_lowrank_remove_tc call per rank gives (ranks that are no multiple
+    of 16 or 32 included: the rows of U^T past the rank are zero-filled by the tensor map)."""
+    from taboo_brittleness_b200 import ops
+    n = 700
+    x = cuda_bf16(synthetic.make_residuals(1, n, d, seed=17))
+    U = cuda_bf16(synthetic.bf16_exact(oracle.random_orthonormal(d, 64, seed=5)))
+    w = synthetic.make_lens(d, 8, seed=2).w_norm.cuda()
+    ranks = [8, 12, 16, 24, 32, 40, 64]
+    mx, mh = ops.lowrank_remove_multi(x, U, ranks, w_norm=w, want_x=True, want_h=True)
+    for i, r in enumerate(ranks):
+        ox, oh = ops.lowrank_remove(x, U[:, :r].contiguous(), w_norm=w, want_x=True, want_h=True)
+        torch.cuda.synchronize()
+        assert torch.equal(mx[i], ox) and torch.equal(mh[i], oh), r
+    # ranks below 8 are taken by a CUDA-core kernel when called alone: same residual to rounding, oracle tolerance either way
+    lx, _ = ops.lowrank_remove_multi(x, U, [4, 8], w_norm=w, want_x=True, want_h=False)
+    sx, _ = ops.lowrank_remove(x, U[:, :4].contiguous(), want_x=True)
+    ref = oracle.lowrank_remove(x.float().cpu(), U[:, :4].float().cpu(), residual_dtype=BF16)
+    torch.cuda.synchronize()
+    assert ((lx[0].float().cpu() - ref).norm(dim=1) / ref.norm(dim=1)).max().item() <= 2e-2
+    assert (lx[0] != sx).float().mean().item() < 2e-3 and torch.equal(lx[1], mx[0])
+    one = ops.lowrank_remove_multi(x, U, [32], w_norm=w)
+    assert one[0] is None and torch.equal(one[1][0], mh[ranks.index(32)])
+    with pytest.raises(ops.TabooKernelError):
+        ops.lowrank_remove_multi(x, U, [16, 8], w_norm=w)
