@@ -37,6 +37,12 @@ struct CapLog2 {
     const float r = rcp_approx(1.0f + ex2_approx(x * k1));
     return fmaf(r, m2k2, k2);
   }
+  // the same for an argument that already carries the factor k1 (a caller with a per-row scale folds the two)
+  __device__ __forceinline__ float from_scaled(float xk1) const {
+    if (!on) return xk1;
+    const float r = rcp_approx(1.0f + ex2_approx(xk1));
+    return fmaf(r, m2k2, k2);
+  }
 };
 
 // =========================================================================================

@@ -294,7 +294,7 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
       int prompt, chunk, t0, t1;
       decode(unit, prompt, chunk, t0, t1);
       const int row = prompt * 128 + row_in_blk;
-      const float rs = __ldg(a.rstd + row);
+      const float rk1 = __ldg(a.rstd + row) * cap2.k1;      // the row's RMSNorm factor and the soft cap's input scale in one
       LensEpi::begin_unit(st, lens, g, row, chunk * Cfg::kColGroups + cg);
       const int n_pieces = (t1 - t0) * kPPT;
       // piece q of the unit: tile t0 + q / kPPT, columns col_base + (q % kPPT) * 32 of it
@@ -336,10 +336,10 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
                 asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                              : "=f"(l0.x), "=f"(l0.y), "=f"(l0.z), "=f"(l0.w)
                              : "r"(l0_row + (((hf * 4 + k) ^ (lane & 7)) << 4)));
-                c[4 * k] = cap2(rs * (l0.x - __uint_as_float(v[4 * k])));
-                c[4 * k + 1] = cap2(rs * (l0.y - __uint_as_float(v[4 * k + 1])));
-                c[4 * k + 2] = cap2(rs * (l0.z - __uint_as_float(v[4 * k + 2])));
-                c[4 * k + 3] = cap2(rs * (l0.w - __uint_as_float(v[4 * k + 3])));
+                c[4 * k] = cap2.from_scaled(rk1 * (l0.x - __uint_as_float(v[4 * k])));
+                c[4 * k + 1] = cap2.from_scaled(rk1 * (l0.y - __uint_as_float(v[4 * k + 1])));
+                c[4 * k + 2] = cap2.from_scaled(rk1 * (l0.z - __uint_as_float(v[4 * k + 2])));
+                c[4 * k + 3] = cap2.from_scaled(rk1 * (l0.w - __uint_as_float(v[4 * k + 3])));
               }
               if (a.store) {                                 // the capped logits replace the base logits in the buffer
 #pragma unroll
@@ -365,10 +365,10 @@ tb_rank_update_lens_kernel(const __grid_constant__ CUtensorMap tmA, const __grid
               asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                            : "=f"(l0.x), "=f"(l0.y), "=f"(l0.z), "=f"(l0.w)
                            : "r"(l0_row + ((k ^ (lane & 7)) << 4)));
-              c[4 * k] = cap2(rs * (l0.x - __uint_as_float(v[4 * k])));
-              c[4 * k + 1] = cap2(rs * (l0.y - __uint_as_float(v[4 * k + 1])));
-              c[4 * k + 2] = cap2(rs * (l0.z - __uint_as_float(v[4 * k + 2])));
-              c[4 * k + 3] = cap2(rs * (l0.w - __uint_as_float(v[4 * k + 3])));
+              c[4 * k] = cap2.from_scaled(rk1 * (l0.x - __uint_as_float(v[4 * k])));
+              c[4 * k + 1] = cap2.from_scaled(rk1 * (l0.y - __uint_as_float(v[4 * k + 1])));
+              c[4 * k + 2] = cap2.from_scaled(rk1 * (l0.z - __uint_as_float(v[4 * k + 2])));
+              c[4 * k + 3] = cap2.from_scaled(rk1 * (l0.w - __uint_as_float(v[4 * k + 3])));
             }
             if (a.store) {
 #pragma unroll
