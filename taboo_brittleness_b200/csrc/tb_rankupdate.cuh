@@ -11,12 +11,14 @@
 // ranked latents in slabs of 64.
 //   A [rows, 1024 (+1024)] bf16, K-major: a_j[t] in column rank(j) (tb_rank_acts_dense_kernel; optionally the bf16
 //     remainders in columns 1024 + rank), loaded by TMA;
-//   B = the rows D[id_j, tile] of the prompt's own latents: an MN-major operand GATHERED by four producer warps with
+//   B = the rows D[id_j, tile] of the prompt's own latents: an MN-major operand GATHERED by two or four producer warps with
 //     16-byte cp.async straight into the 128-byte-swizzled layout the UMMA descriptor expects (one warp instruction
 //     = one latent's 512 bytes); rows at or beyond the budget are zero-filled, so one A matrix serves all budgets;
 //   accumulator U in TMEM (two tiles in flight); the epilogue warps fetch their [32 rows x 32 ids] piece of L0 with a
 //     TMA load of their own (4 KB, double-buffered), form rstd * (L0 - U) and hand it to the lens readout epilogue
-//     (LensEpi's state and arithmetic; 2 or 4 partials per (chunk, row): tb_lens_rank_update_parts).
+//     (LensEpi's state and arithmetic; 2 or 4 partials per (chunk, row): tb_lens_rank_update_parts). With `store` the
+//     soft-capped logits (log2 units) go back into the buffer the L0 piece came in and one lane TMA-stores it to a second
+//     prompt-tile array, from which tb_logits_ll_colsum gets the budget's LL-Top-k.
 // All CTAs work on the same vocabulary chunk at the same time (unit = chunk * prompts + prompt), so a tile's slab of
 // D (8 MB for 16384 latents, contiguous in the tile-major layout) can be served from L2.
 //
@@ -40,7 +42,7 @@ constexpr int kRuL0Bytes = 32 * 128;                     // one epilogue warp's 
 // Hence kEW = 16 epilogue warps: four per TMEM lane quadrant, each owning 64 of a tile's 256 ids (two L0 pieces, worked
 // through in 16-id steps to stay inside 96 registers): 37.5 -> 20 ms per budget. That leaves room for two operand
 // stages; budget 1024 (16 slabs per tile, 768 KB of A and D rows from L2 per tile: bound by the gather) keeps eight
-// epilogue warps, three stages and four gather warps (65 vs 84 ms).
+// epilogue warps, three stages and four gather warps (65 vs 84 ms; 60 with the tile-major D).
 template <int kStages, int kNB, int kEW>
 struct RuCfg {
   static constexpr int kGatherWarps = kEW == 16 ? 2 : 4;
